@@ -1,0 +1,666 @@
+/*
+ * oracle/mtd_oracle.c -- CPU restatement of the reference hot path.  TEST INFRASTRUCTURE ONLY (see mtd_oracle.h).
+ * Sequential, single-threaded, written to mirror the reference's control flow one-to-one so that a reader can
+ * check each block against the cited reference lines.  Build: see oracle/Makefile (gcc -O2 -shared -fPIC).
+ */
+#include "mtd_oracle.h"
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+/* ------------------------------------------------------------------ enums (epidemiologyclasses.py, cellsclasses.py) */
+enum { S_UNDEF = 0, S_SUS = 1, S_EXP = 2, S_INF = 3, S_REC = 4, S_DEC = 5 };
+enum { IT_UNDEF = 0, IT_PREASYMP = 1, IT_PRESYMP = 2, IT_ASYMP = 3, IT_SYMP = 4 };
+enum { SV_UNDEF = 0, SV_MILD = 1, SV_SEVERE = 2, SV_CRITICAL = 3 };
+enum { T_EXP_INF = 0, T_INF_SYMP = 1, T_SYMP_SEV = 2, T_SEV_CRI = 3, T_CRI_DEATH = 4, T_ASYMP_REC = 5,
+       T_MILD_REC = 6, T_SEV_REC = 7, T_CRI_REC = 8, T_REC_SUS = 9 };
+enum { CT_HOUSEHOLD = 0, CT_WORKPLACE = 1, CT_ACCOM = 2, CT_HOSPITAL = 3, CT_ENTERTAINMENT = 4, CT_SCHOOL = 5,
+       CT_CLASSROOM = 6, CT_INSTITUTION = 7, CT_TRANSPORT = 8, CT_RELIGION = 9, CT_AIRPORT = 10 };
+enum { SCT_RESIDENCE = 0, SCT_WORKPLACE = 1, SCT_SCHOOL = 2, SCT_COMMUNITY = 3 };
+enum { Q_SYMPTOMATIC = 0, Q_POSITIVE = 1, Q_POSITIVE_CONTACT = 2, Q_SECONDARY_CONTACT = 3 };
+
+/* ------------------------------------------------------------------ Philox4x32-10 (Salmon et al. 2011) */
+void mtdo_philox4x32(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4])
+{
+    uint32_t c0 = ctr[0], c1 = ctr[1], c2 = ctr[2], c3 = ctr[3], k0 = key[0], k1 = key[1];
+    for (int r = 0; r < 10; r++) {
+        uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+        uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0, n1 = (uint32_t)p1;
+        uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1, n3 = (uint32_t)p0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+double mtdo_u53(uint32_t a, uint32_t b)
+{
+    return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) / 9007199254740992.0;
+}
+
+static void philox_site(const mtdo_dayctx *D, uint32_t site, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t out[4])
+{
+    uint32_t ctr[4] = { (uint32_t)D->day, c1, c2, c3 }, key[2] = { D->seed, site };
+    mtdo_philox4x32(ctr, key, out);
+}
+
+/* ------------------------------------------------------------------ numpy float64 add.reduce (pairwise, blocks of 128) */
+double mtdo_np_pairwise_sum(const double *a, int64_t n)
+{
+    if (n < 8) {
+        double r = -0.0;
+        for (int64_t i = 0; i < n; i++) r += a[i];
+        return r;
+    } else if (n <= 128) {
+        double r[8];
+        int64_t i;
+        for (int j = 0; j < 8; j++) r[j] = a[j];
+        for (i = 8; i < n - (n % 8); i += 8)
+            for (int j = 0; j < 8; j++) r[j] += a[i + j];
+        double res = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+        for (; i < n; i++) res += a[i];
+        return res;
+    } else {
+        int64_t n2 = n / 2;
+        n2 -= n2 % 8;
+        return mtdo_np_pairwise_sum(a, n2) + mtdo_np_pairwise_sum(a + n2, n - n2);
+    }
+}
+
+/* Python round() on a float: round-half-even, correctly rounded -> rint() in the default rounding mode */
+static int64_t py_round(double x) { return (int64_t)rint(x); }
+
+/* ------------------------------------------------------------------ small tables */
+int mtdo_activity_of_celltype(int ct, int indid)   /* contactnetwork.py:317-347 */
+{
+    if (indid == 9 && ct != CT_ACCOM) return 5;
+    switch (ct) {
+    case CT_HOUSEHOLD: return 1;
+    case CT_WORKPLACE: return 3;
+    case CT_ACCOM: return 1;
+    case CT_HOSPITAL: return 5;
+    case CT_ENTERTAINMENT: return 5;
+    case CT_SCHOOL: return 2;
+    case CT_INSTITUTION: return 1;
+    case CT_TRANSPORT: return 4;
+    case CT_RELIGION: return 5;
+    case CT_AIRPORT: return 5;
+    default: return 0;   /* Classroom falls here (quirk B5) */
+    }
+}
+
+int mtdo_simcelltype(int ct)   /* util.py:239-268 */
+{
+    switch (ct) {
+    case CT_HOUSEHOLD: case CT_ACCOM: case CT_INSTITUTION: return SCT_RESIDENCE;
+    case CT_WORKPLACE: return SCT_WORKPLACE;
+    case CT_SCHOOL: case CT_CLASSROOM: return SCT_SCHOOL;
+    default: return SCT_COMMUNITY;
+    }
+}
+
+void mtdo_transition(int seir, int it, int sv, int trans, int *ns, int *nt, int *nv)   /* seirstateutil.py:105-136 */
+{
+    switch (trans) {
+    case T_EXP_INF:  *ns = S_INF; *nt = (it == IT_PREASYMP) ? IT_ASYMP : it; *nv = SV_MILD; return;
+    case T_INF_SYMP: *ns = IT_SYMP /* quirk B1: InfectionType.Symptomatic (4) lands in the SEIR slot */;
+                     *nt = (it == IT_PRESYMP) ? IT_SYMP : it; *nv = sv; return;
+    case T_SYMP_SEV: *ns = seir; *nt = it; *nv = SV_SEVERE; return;
+    case T_SEV_CRI:  *ns = seir; *nt = it; *nv = SV_CRITICAL; return;
+    case T_CRI_DEATH: *ns = S_DEC; *nt = it; *nv = sv; return;
+    case T_ASYMP_REC: case T_MILD_REC: case T_SEV_REC: case T_CRI_REC:
+                     *ns = S_REC; *nt = IT_UNDEF; *nv = SV_UNDEF; return;
+    case T_REC_SUS:  *ns = S_SUS; *nt = it; *nv = sv; return;
+    default:         *ns = S_UNDEF; *nt = IT_UNDEF; *nv = SV_UNDEF; return;
+    }
+}
+
+void mtdo_vacc_multipliers(const mtdo_params *P, int32_t last, int32_t day, double *imm, double *asym)   /* util.py:117-150 */
+{
+    *imm = 1.0; *asym = 1.0;
+    if (last == MTDO_NONE) return;
+    int32_t d = day - last;
+    if (d == 0) { *imm = 1.0 - P->vacc_immunity; *asym = 1.0 - P->vacc_asymptomatic; return; }
+    double x = (double)d / P->vacc_decay_interval;
+    if (x < 1) x = 1;
+    *imm = 1.0 - pow(P->vacc_immunity, x);
+    *asym = 1.0 - pow(P->vacc_asymptomatic, x);
+}
+
+/* ------------------------------------------------------------------ replay-tape lookups (binary search on sorted keys) */
+static int64_t tape_find_sel(const mtdo_tape *T, int32_t cell, int32_t agent)
+{
+    uint64_t key = ((uint64_t)(uint32_t)cell << 32) | (uint32_t)agent;
+    int64_t lo = 0, hi = T->n_sel;
+    while (lo < hi) { int64_t mid = (lo + hi) >> 1; if (T->sel_key[mid] < key) lo = mid + 1; else hi = mid; }
+    return (lo < T->n_sel && T->sel_key[lo] == key) ? lo : -1;
+}
+
+static int64_t tape_find_pair(const mtdo_tape *T, int32_t cell, int32_t a1, int32_t a2)
+{
+    uint64_t k1 = ((uint64_t)(uint32_t)cell << 32) | (uint32_t)a1;
+    uint32_t k2 = (uint32_t)a2;
+    int64_t lo = 0, hi = T->n_pair;
+    while (lo < hi) {
+        int64_t mid = (lo + hi) >> 1;
+        if (T->pair_k1[mid] < k1 || (T->pair_k1[mid] == k1 && T->pair_k2[mid] < k2)) lo = mid + 1; else hi = mid;
+    }
+    return (lo < T->n_pair && T->pair_k1[lo] == k1 && T->pair_k2[lo] == k2) ? lo : -1;
+}
+
+static int64_t tape_find_expo(const mtdo_tape *T, int32_t agent)
+{
+    int64_t lo = 0, hi = T->n_expo;
+    while (lo < hi) { int64_t mid = (lo + hi) >> 1; if (T->expo_agent[mid] < agent) lo = mid + 1; else hi = mid; }
+    return (lo < T->n_expo && T->expo_agent[lo] == agent) ? lo : -1;
+}
+
+/* ------------------------------------------------------------------ grouping of the emission stream by cell
+ * vars_util.cells_agents_timesteps is a dict {cellid: [(agent, start, end), ...]} filled in emission order
+ * (itinerary.py:1446-1452): cell order = order of first appearance, list order = emission order. */
+typedef struct {
+    int64_t n_slots;
+    int32_t max_cell;
+    int32_t *slot_of_cell;   /* [max_cell+1], -1 = inactive */
+    int32_t *cell_of_slot;   /* [n_slots] */
+    int64_t *off;            /* [n_slots+1] */
+    int64_t *idx;            /* [M] emission indices grouped by slot, stable */
+} cellgroups;
+
+static void group_by_cell(int64_t M, const int32_t *iv_cell, cellgroups *G)
+{
+    int32_t mx = -1;
+    for (int64_t i = 0; i < M; i++) if (iv_cell[i] > mx) mx = iv_cell[i];
+    G->max_cell = mx;
+    G->slot_of_cell = (int32_t *)malloc(sizeof(int32_t) * (size_t)(mx + 2));
+    for (int32_t c = 0; c <= mx; c++) G->slot_of_cell[c] = -1;
+    int64_t ns = 0;
+    for (int64_t i = 0; i < M; i++) if (G->slot_of_cell[iv_cell[i]] < 0) G->slot_of_cell[iv_cell[i]] = (int32_t)ns++;
+    G->n_slots = ns;
+    G->cell_of_slot = (int32_t *)malloc(sizeof(int32_t) * (size_t)(ns + 1));
+    G->off = (int64_t *)calloc((size_t)(ns + 2), sizeof(int64_t));
+    G->idx = (int64_t *)malloc(sizeof(int64_t) * (size_t)(M + 1));
+    for (int64_t i = 0; i < M; i++) { int32_t s = G->slot_of_cell[iv_cell[i]]; G->cell_of_slot[s] = iv_cell[i]; G->off[s + 1]++; }
+    for (int64_t s = 0; s < ns; s++) G->off[s + 1] += G->off[s];
+    int64_t *cur = (int64_t *)malloc(sizeof(int64_t) * (size_t)(ns + 1));
+    memcpy(cur, G->off, sizeof(int64_t) * (size_t)ns);
+    for (int64_t i = 0; i < M; i++) G->idx[cur[G->slot_of_cell[iv_cell[i]]]++] = i;
+    free(cur);
+}
+
+static void free_groups(cellgroups *G) { free(G->slot_of_cell); free(G->cell_of_slot); free(G->off); free(G->idx); }
+
+/* ------------------------------------------------------------------ generate_contact_network (contactnetwork.py:134-315) */
+typedef struct { int32_t a, b; int32_t ov_head, ov_tail; } potpair;    /* key (a,b) in local agent indices */
+typedef struct { uint8_t s, e; int32_t next; } ovent;
+
+typedef struct {
+    /* per-cell scratch, grown on demand */
+    int64_t cap_m, cap_n, cap_nn, cap_pairs, cap_ov, cap_adj;
+    int32_t *la;        /* [m] local agent index of interval */
+    int32_t *ids;       /* [n] agents_ids (first appearance order) */
+    int64_t *ts;        /* [n] agents_total_timesteps */
+    int32_t *pc;        /* [n] agents_potentialcontacts_count */
+    uint8_t *has_pc;    /* [n] entry exists in agents_potentialcontacts_count */
+    double *degf;       /* [n] float degrees */
+    int64_t *deg;       /* [n] integer degrees */
+    uint8_t *dead;      /* [n] all pairs of this agent were deleted (delete_all_pairs_by_id) */
+    int32_t *order;     /* [n] greedy order */
+    int32_t *pidx;      /* [n*n] pair index for key (a,b), -1 none */
+    potpair *pairs; int64_t n_pairs;
+    ovent *ov; int64_t n_ov;
+    int32_t *adj_head, *adj_tail;   /* [n] per-agent list of pair indices, insertion order */
+    int32_t *adj_next_a, *adj_next_b; /* [pairs] next pair in a's / b's list */
+    int32_t *cand;      /* [n] candidate partners */
+    int32_t *local_of_agent; int64_t n_agents;
+} cellws;
+
+static void ws_reserve(cellws *W, int64_t m, int64_t n)
+{
+    if (m > W->cap_m) { W->cap_m = m * 2; W->la = (int32_t *)realloc(W->la, sizeof(int32_t) * (size_t)W->cap_m); }
+    if (n > W->cap_n) {
+        W->cap_n = n * 2;
+        size_t c = (size_t)W->cap_n;
+        W->ids = (int32_t *)realloc(W->ids, 4 * c); W->ts = (int64_t *)realloc(W->ts, 8 * c);
+        W->pc = (int32_t *)realloc(W->pc, 4 * c); W->has_pc = (uint8_t *)realloc(W->has_pc, c);
+        W->degf = (double *)realloc(W->degf, 8 * c); W->deg = (int64_t *)realloc(W->deg, 8 * c);
+        W->dead = (uint8_t *)realloc(W->dead, c); W->order = (int32_t *)realloc(W->order, 4 * c);
+        W->adj_head = (int32_t *)realloc(W->adj_head, 4 * c); W->adj_tail = (int32_t *)realloc(W->adj_tail, 4 * c);
+        W->cand = (int32_t *)realloc(W->cand, 4 * c);
+    }
+    if (n * n > W->cap_nn) { W->cap_nn = n * n * 2; W->pidx = (int32_t *)realloc(W->pidx, 4 * (size_t)W->cap_nn); }
+}
+
+static int32_t ws_new_pair(cellws *W, int32_t a, int32_t b)
+{
+    if (W->n_pairs >= W->cap_pairs) {
+        W->cap_pairs = W->cap_pairs ? W->cap_pairs * 2 : 1024;
+        W->pairs = (potpair *)realloc(W->pairs, sizeof(potpair) * (size_t)W->cap_pairs);
+        W->adj_next_a = (int32_t *)realloc(W->adj_next_a, 4 * (size_t)W->cap_pairs);
+        W->adj_next_b = (int32_t *)realloc(W->adj_next_b, 4 * (size_t)W->cap_pairs);
+    }
+    int32_t p = (int32_t)W->n_pairs++;
+    W->pairs[p].a = a; W->pairs[p].b = b; W->pairs[p].ov_head = W->pairs[p].ov_tail = -1;
+    W->adj_next_a[p] = W->adj_next_b[p] = -1;
+    /* append p to a's and b's per-agent lists (dict insertion order restricted to keys containing the agent) */
+    int32_t ends[2] = { a, b };
+    for (int k = 0; k < 2; k++) {
+        int32_t x = ends[k];
+        if (W->adj_head[x] < 0) W->adj_head[x] = p;
+        else {
+            int32_t t = W->adj_tail[x];
+            if (W->pairs[t].a == x) W->adj_next_a[t] = p; else W->adj_next_b[t] = p;
+        }
+        W->adj_tail[x] = p;
+    }
+    return p;
+}
+
+static void ws_add_overlap(cellws *W, int32_t p, int lo, int hi)
+{
+    if (W->n_ov >= W->cap_ov) {
+        W->cap_ov = W->cap_ov ? W->cap_ov * 2 : 4096;
+        W->ov = (ovent *)realloc(W->ov, sizeof(ovent) * (size_t)W->cap_ov);
+    }
+    int32_t o = (int32_t)W->n_ov++;
+    W->ov[o].s = (uint8_t)lo; W->ov[o].e = (uint8_t)hi; W->ov[o].next = -1;
+    if (W->pairs[p].ov_head < 0) W->pairs[p].ov_head = o; else W->ov[W->pairs[p].ov_tail].next = o;
+    W->pairs[p].ov_tail = o;
+}
+
+static int cmp_desc_deg_id(const void *x, const void *y, void *arg)
+{
+    cellws *W = (cellws *)arg;
+    int32_t i = *(const int32_t *)x, j = *(const int32_t *)y;
+    if (W->deg[i] != W->deg[j]) return W->deg[i] > W->deg[j] ? -1 : 1;     /* sorted(zip(deg, id), reverse=True) */
+    return W->ids[i] > W->ids[j] ? -1 : (W->ids[i] < W->ids[j] ? 1 : 0);
+}
+
+/* One cell.  iv = emission indices of the cell's intervals in list order.  Appends rows; returns number appended,
+ * or -1 on output overflow. */
+static int64_t run_cell(const mtdo_params *P, const mtdo_dayctx *D, cellws *W, int32_t cellid, int64_t m,
+                        const int64_t *iv, const int32_t *iv_agent, const uint8_t *iv_start, const uint8_t *iv_end,
+                        int ctype, int indid, const mtdo_agents *A, int64_t cap_left, int32_t *rows, int32_t *row_dur,
+                        int32_t *row_cell, mtdo_stats *S)
+{
+    /* agents_ids in order of first appearance (contactnetwork.py:161-163) */
+    int64_t n = 0;
+    ws_reserve(W, m, m);
+    for (int64_t i = 0; i < m; i++) {
+        int32_t ag = iv_agent[iv[i]];
+        if (W->local_of_agent[ag] < 0) { W->local_of_agent[ag] = (int32_t)n; W->ids[n] = ag; n++; }
+        W->la[i] = W->local_of_agent[ag];
+    }
+    for (int64_t a = 0; a < n; a++) {
+        W->ts[a] = 0; W->pc[a] = 0; W->has_pc[a] = 0; W->degf[a] = 0.0; W->deg[a] = 0; W->dead[a] = 0;
+        W->adj_head[a] = W->adj_tail[a] = -1;
+    }
+    for (int64_t q = 0; q < n * n; q++) W->pidx[q] = -1;
+    W->n_pairs = 0; W->n_ov = 0;
+
+    int act = mtdo_activity_of_celltype(ctype, ctype == CT_WORKPLACE ? indid : -1);   /* :150-156 */
+    int64_t ts_sum = 0, same_agent_sq = 0;
+
+    /* ---- pair enumeration (:160-196) ---- */
+    for (int64_t i = 0; i < m; i++) {
+        int32_t a = W->la[i];
+        int si = iv_start[iv[i]], ei = iv_end[iv[i]];
+        int len = ei - si + 1;            /* len(range(start, end+1)) */
+        if (len < 0) len = 0;
+        ts_sum += len; W->ts[a] += len;
+        for (int64_t j = 0; j < m; j++) {
+            int32_t b = W->la[j];
+            if (b == a) continue;
+            if (W->pidx[(int64_t)b * n + a] >= 0) continue;            /* pair_already_computed: (ag_id, agentid) in dict */
+            int sj = iv_start[iv[j]], ej = iv_end[iv[j]];
+            int lo = si > sj ? si : sj, hi = ei < ej ? ei : ej;        /* get_overlapping_range (:426-432) */
+            W->has_pc[a] = 1; W->has_pc[b] = 1;
+            if (lo <= hi) {
+                int32_t p = W->pidx[(int64_t)a * n + b];
+                if (p < 0) {                                            /* pair_exists is false in both orientations */
+                    W->pc[a]++; W->pc[b]++;
+                    p = ws_new_pair(W, a, b);
+                    W->pidx[(int64_t)a * n + b] = p;
+                }
+                ws_add_overlap(W, p, lo, hi);
+            }
+        }
+    }
+    {   /* metric: unordered interval pairs of different agents */
+        int64_t *cnt = (int64_t *)calloc((size_t)n, sizeof(int64_t));
+        for (int64_t i = 0; i < m; i++) cnt[W->la[i]]++;
+        for (int64_t a = 0; a < n; a++) same_agent_sq += cnt[a] * cnt[a];
+        free(cnt);
+        S->pairs_evaluated += (m * m - same_agent_sq) / 2;
+        S->n_potential += W->n_pairs;
+    }
+    for (int64_t a = 0; a < n; a++) W->local_of_agent[W->ids[a]] = -1;   /* reset the global map */
+
+    int64_t n_rows = 0;
+    if (W->n_pairs == 0) return 0;                                      /* :198 */
+
+    /* ---- degrees (:210-269) ---- */
+    int64_t k = P->k_by_act[act];
+    int64_t max_degree = k * n;                                          /* round(k * n) */
+    double avg_ts = (double)ts_sum / (double)n;
+    int64_t pc_sum = 0, pc_cnt = 0;
+    for (int64_t a = 0; a < n; a++) if (W->has_pc[a]) { pc_sum += W->pc[a]; pc_cnt++; }
+    double avg_pc = (double)pc_sum / (double)pc_cnt;                     /* np.mean */
+    double one_minus_mhd = 1 - D->mhd;
+    for (int64_t a = 0; a < n; a++) {
+        if (W->pc[a] > 0) {
+            int ab = A->age_bracket[W->ids[a]];
+            if (ab < 0) ab += 16;                                        /* numpy negative index */
+            double cmv = P->cm[ab][act];
+            double tsm = 1.0, pcm = 1.0;
+            if ((double)W->ts[a] != avg_ts && avg_ts > 1) tsm = log((double)W->ts[a]) / log(avg_ts);   /* math.log(x, base) */
+            if ((double)W->pc[a] != avg_pc && avg_pc > 1) pcm = log((double)W->pc[a]) / log(avg_pc);
+            double soc = A->soc_rate[W->ids[a]];
+            W->degf[a] = cmv * tsm * pcm * soc * one_minus_mhd;
+        }
+    }
+    int64_t deg_sum = py_round(mtdo_np_pairwise_sum(W->degf, n));
+    for (int64_t a = 0; a < n; a++) {
+        int64_t d;
+        if (deg_sum > max_degree) d = py_round((W->degf[a] / (double)deg_sum) * (double)max_degree);
+        else d = py_round(W->degf[a]);
+        if (d > W->pc[a]) d = W->pc[a];
+        W->deg[a] = d;
+    }
+
+    /* ---- greedy sampling (:283-301) ---- */
+    for (int64_t a = 0; a < n; a++) W->order[a] = (int32_t)a;
+    qsort_r(W->order, (size_t)n, sizeof(int32_t), cmp_desc_deg_id, W);
+    for (int64_t oi = 0; oi < n; oi++) {
+        int32_t x = W->order[oi];
+        int64_t degree = W->deg[x];
+        if (degree <= 0) continue;
+        /* util.get_all_contacts_ids_by_id: keys in insertion order containing x whose partner has degree > 0 */
+        int64_t nc = 0;
+        for (int32_t p = W->adj_head[x]; p >= 0; p = (W->pairs[p].a == x) ? W->adj_next_a[p] : W->adj_next_b[p]) {
+            int32_t y = (W->pairs[p].a == x) ? W->pairs[p].b : W->pairs[p].a;
+            if (W->dead[x] || W->dead[y]) continue;                     /* key was deleted */
+            if (W->deg[y] > 0) W->cand[nc++] = y;
+        }
+        if (nc == 0) continue;                                          /* returns None (:294) */
+        if (degree > nc) degree = nc;
+        /* np.random.shuffle + np.random.choice(size=degree, replace=False): replay or Philox */
+        int32_t picks_local[1];
+        (void)picks_local;
+        const int32_t *tp = NULL; int64_t ntp = 0;
+        if (D->mode == MTDO_MODE_REPLAY) {
+            int64_t r = tape_find_sel(D->tape, cellid, W->ids[x]);
+            if (r < 0) { S->tape_miss++; continue; }
+            tp = D->tape->sel_picks + D->tape->sel_off[r];
+            ntp = D->tape->sel_off[r + 1] - D->tape->sel_off[r];
+            if (ntp != degree) { S->tape_miss++; if (ntp > degree) ntp = degree; }
+        } else {
+            for (int64_t t = 0; t < degree; t++) {                       /* partial Fisher-Yates on the ordered list */
+                uint32_t w[4];
+                philox_site(D, MTDO_SITE_SELECT, (uint32_t)cellid, (uint32_t)W->ids[x], (uint32_t)(t >> 2), w);
+                int64_t r = t + (int64_t)(((uint64_t)w[t & 3] * (uint64_t)(nc - t)) >> 32);
+                int32_t tmp = W->cand[t]; W->cand[t] = W->cand[r]; W->cand[r] = tmp;
+            }
+            ntp = degree;
+        }
+        /* create_contacts (:386-424) */
+        for (int64_t t = 0; t < ntp; t++) {
+            int32_t y;
+            if (tp) { int32_t pi = tp[t]; if (pi < 0 || pi >= nc) { S->tape_miss++; continue; } y = W->cand[pi]; }
+            else y = W->cand[t];
+            int32_t p = W->pidx[(int64_t)x * n + y];
+            if (p < 0) p = W->pidx[(int64_t)y * n + x];
+            if (n_rows >= cap_left) return -1;
+            int32_t *r = rows + 5 * n_rows;
+            int dur = 0;
+            for (int32_t o = W->pairs[p].ov_head; o >= 0; o = W->ov[o].next) dur += W->ov[o].e - W->ov[o].s + 1;
+            r[0] = mtdo_simcelltype(ctype);
+            r[1] = W->ids[W->pairs[p].a]; r[2] = W->ids[W->pairs[p].b];
+            r[3] = W->ov[W->pairs[p].ov_head].s;                        /* first element's start (:101, quirk B7) */
+            r[4] = W->ov[W->pairs[p].ov_tail].e;                        /* last element's end */
+            row_dur[n_rows] = dur; row_cell[n_rows] = cellid;
+            n_rows++;
+            W->deg[y] -= 1;
+            if (W->deg[y] == 0) W->dead[y] = 1;                          /* delete_all_pairs_by_id(contact) */
+        }
+        W->deg[x] = degree - ntp;                                        /* main_agent_degree -= len(direct_contacts_ids) */
+        if (W->deg[x] == 0) W->dead[x] = 1;
+    }
+    return n_rows;
+}
+
+int64_t mtdo_contact_network(const mtdo_params *P, const mtdo_dayctx *D, int64_t M, const int32_t *iv_cell,
+                             const int32_t *iv_agent, const uint8_t *iv_start, const uint8_t *iv_end,
+                             const int8_t *cell_type, const int16_t *cell_indid, const mtdo_agents *A,
+                             int64_t cap, int32_t *rows, int32_t *row_dur, int32_t *row_cell, mtdo_stats *S)
+{
+    cellgroups G;
+    group_by_cell(M, iv_cell, &G);
+    cellws W;
+    memset(&W, 0, sizeof(W));
+    W.n_agents = A->n_agents;
+    W.local_of_agent = (int32_t *)malloc(sizeof(int32_t) * (size_t)(A->n_agents + 1));
+    for (int64_t i = 0; i < A->n_agents; i++) W.local_of_agent[i] = -1;
+    int64_t total = 0;
+    S->n_cells += G.n_slots;
+    for (int64_t s = 0; s < G.n_slots; s++) {
+        int32_t cellid = G.cell_of_slot[s];
+        int64_t m = G.off[s + 1] - G.off[s];
+        int64_t r = run_cell(P, D, &W, cellid, m, G.idx + G.off[s], iv_agent, iv_start, iv_end, cell_type[cellid],
+                             cell_indid ? cell_indid[cellid] : -1, A, cap - total, rows + 5 * total, row_dur + total,
+                             row_cell + total, S);
+        if (r < 0) { total = -1; break; }
+        total += r;
+    }
+    free(W.la); free(W.ids); free(W.ts); free(W.pc); free(W.has_pc); free(W.degf); free(W.deg); free(W.dead);
+    free(W.order); free(W.pidx); free(W.pairs); free(W.ov); free(W.adj_head); free(W.adj_tail); free(W.adj_next_a);
+    free(W.adj_next_b); free(W.cand); free(W.local_of_agent);
+    free_groups(&G);
+    return total;
+}
+
+/* ------------------------------------------------------------------ draws of one exposure (replay row or Philox) */
+typedef struct { const mtdo_dayctx *D; int32_t agent; const double *row; mtdo_stats *S; } expodraws;
+
+static double ed_uniform(expodraws *E, int slot)
+{
+    if (E->D->mode == MTDO_MODE_REPLAY) {
+        if (!E->row || isnan(E->row[slot])) { E->S->tape_miss++; return 1.0; }
+        return E->row[slot];
+    }
+    uint32_t w[4];
+    philox_site(E->D, MTDO_SITE_EXPO, (uint32_t)E->agent, (uint32_t)slot, 0, w);
+    return mtdo_u53(w[0], w[1]);
+}
+
+/* util.sample_log_normal(mean, std, 1, isInt=True): np.random.lognormal then Python round (util.py:88-115) */
+static int32_t ed_lognormal_days(expodraws *E, int slot, double mu, double sigma)
+{
+    if (E->D->mode == MTDO_MODE_REPLAY) {
+        if (!E->row || isnan(E->row[slot])) { E->S->tape_miss++; return 0; }
+        return (int32_t)E->row[slot];
+    }
+    uint32_t w[4];
+    philox_site(E->D, MTDO_SITE_EXPO, (uint32_t)E->agent, (uint32_t)slot, 0, w);
+    double u1 = mtdo_u53(w[0], w[1]), u2 = mtdo_u53(w[2], w[3]);
+    double z = sqrt(-2.0 * log(1.0 - u1)) * cos(6.283185307179586 * u2);      /* Box-Muller */
+    return (int32_t)py_round(exp(mu + sigma * z));
+}
+
+static int32_t ed_timestep_option(expodraws *E, int slot)   /* np.random.choice(np.arange(42, 121)) (epidemiology.py:84) */
+{
+    if (E->D->mode == MTDO_MODE_REPLAY) {
+        if (!E->row || isnan(E->row[slot])) { E->S->tape_miss++; return 42; }
+        return (int32_t)E->row[slot];
+    }
+    uint32_t w[4];
+    philox_site(E->D, MTDO_SITE_EXPO, (uint32_t)E->agent, (uint32_t)slot, 0, w);
+    return 42 + (int32_t)(((uint64_t)w[0] * 79u) >> 32);
+}
+
+static void sched_append(mtdo_agents *A, int32_t ag, int32_t day, int trans, int ts, mtdo_stats *S)
+{
+    uint8_t c = A->sched_cnt[ag];
+    if (c >= MTDO_MAXSCHED) { S->sched_overflow++; return; }
+    A->sched[(int64_t)ag * MTDO_MAXSCHED + c] = (int32_t)(((uint32_t)day << 16) | ((uint32_t)trans << 8) | (uint32_t)ts);
+    A->sched_cnt[ag] = c + 1;
+}
+
+/* simulate_seir_state_transition + schedule_* as reached from simulate_direct_contacts (epidemiology.py:233-660) */
+static void expose_agent(const mtdo_params *P, const mtdo_dayctx *D, mtdo_agents *A, int32_t ag, int n_ts,
+                         const uint8_t *ts_list, double asym_mult, mtdo_stats *S)
+{
+    expodraws E = { D, ag, NULL, S };
+    if (D->mode == MTDO_MODE_REPLAY) {
+        int64_t r = tape_find_expo(D->tape, ag);
+        if (r >= 0) E.row = D->tape->expo_row + r * MTDO_EXPO_W; else S->tape_miss++;
+    }
+    int32_t current_day = D->day, incr = D->day;
+    int b = A->epi_age_bracket[ag];
+    /* sampled_exposed_timestep = np.random.choice(overlapping_timesteps) (:246) */
+    int ts;
+    if (D->mode == MTDO_MODE_REPLAY) ts = (E.row && !isnan(E.row[0])) ? (int)E.row[0] : 0;
+    else {
+        uint32_t w[4];
+        philox_site(D, MTDO_SITE_EXPO, (uint32_t)ag, 0, 0, w);
+        ts = ts_list[(int64_t)(((uint64_t)w[0] * (uint64_t)n_ts) >> 32)];
+    }
+    int symptomatic_day = -1, recovered = 0, start_hosp = MTDO_NONE, end_hosp = MTDO_NONE;
+    int inf_type;
+#define STEP(T) do { incr += ed_lognormal_days(&E, 1 + (T), P->ln_mu[T], P->ln_sigma[T]); \
+                     if (incr >= current_day) sched_append(A, ag, incr, (T), ts, S); } while (0)
+    STEP(T_EXP_INF);                                                                   /* :248-256 */
+    double u = ed_uniform(&E, 11);                                                    /* :268 */
+    if (u < P->probs_by_age[1][b] * asym_mult) {
+        inf_type = IT_PRESYMP;
+        STEP(T_INF_SYMP); symptomatic_day = incr;                                      /* :275-281 */
+        if (ed_uniform(&E, 12) < P->probs_by_age[2][b]) {                              /* :293-297 */
+            STEP(T_SYMP_SEV); start_hosp = incr;
+            if (ed_uniform(&E, 13) < P->probs_by_age[3][b]) {                          /* :317-321 */
+                STEP(T_SEV_CRI);
+                if (ed_uniform(&E, 14) < P->probs_by_age[4][b]) { STEP(T_CRI_DEATH); end_hosp = incr; }   /* :339-347 */
+                else { STEP(T_CRI_REC); end_hosp = incr; recovered = 1; }
+            } else { STEP(T_SEV_REC); end_hosp = incr; recovered = 1; }
+        } else { STEP(T_MILD_REC); recovered = 1; }
+    } else {
+        inf_type = IT_PREASYMP;
+        STEP(T_ASYMP_REC); recovered = 1;                                              /* :428-447 */
+    }
+    if (recovered) STEP(T_REC_SUS);                                                    /* :449-455 */
+#undef STEP
+    if (start_hosp != MTDO_NONE) {                                                     /* schedule_hospitalisation (:647-660) */
+        int32_t *h = A->hosp + (int64_t)ag * 3;
+        if (h[0] != MTDO_NONE) { h[1] = ts; h[2] = end_hosp; }                         /* keeps the earlier start day */
+        else { h[0] = start_hosp; h[1] = ts; h[2] = end_hosp; }
+    }
+    if (symptomatic_day > -1) {
+        int tts = ed_timestep_option(&E, 15);                                          /* :480 */
+        if (D->testing_enabled) {                                                      /* schedule_test (:502-565), Symptomatic */
+            int32_t *td = A->test_day + (int64_t)ag * 2, *tr = A->test_result_day + (int64_t)ag * 2;
+            if (td[0] == MTDO_NONE) {
+                if (ed_uniform(&E, 16) < P->testing_after_symptoms_probability) {
+                    int32_t testing_day = symptomatic_day + ed_lognormal_days(&E, 17, P->test_mu, P->test_sigma);
+                    td[0] = testing_day; td[1] = tts;
+                    tr[0] = testing_day + ed_lognormal_days(&E, 18, P->result_mu, P->result_sigma); tr[1] = tts;
+                }
+            }
+        }
+        (void)ed_timestep_option(&E, 19);                                              /* :496 */
+        if (D->quarantine_enabled) {
+            /* schedule_quarantine(Symptomatic) consumes one uniform (:575); whatever it stores in
+             * agent["quarantine_days"] is overwritten by simulate_direct_contacts with the value read before the
+             * call (epidemiology.py:206,216) -> no state change. */
+            (void)ed_uniform(&E, 20);
+        }
+    }
+    A->seir[ag] = S_EXP; A->inf_type[ag] = (int8_t)inf_type; A->inf_sev[ag] = SV_UNDEF;   /* :219-225 */
+}
+
+int64_t mtdo_transmission(const mtdo_params *P, const mtdo_dayctx *D, int64_t M, const int32_t *iv_cell,
+                          const int32_t *iv_agent, const uint8_t *iv_start, const uint8_t *iv_end,
+                          const int8_t *cell_type, int64_t n_rows, const int32_t *rows, const int32_t *row_dur,
+                          const int32_t *row_cell, mtdo_agents *A, int64_t cap_e, int32_t *exposed, double *p_out,
+                          mtdo_stats *S)
+{
+    cellgroups G;
+    group_by_cell(M, iv_cell, &G);
+    int64_t n_exp = 0;
+    uint8_t *tsbuf = (uint8_t *)malloc(144 * 64);
+    int64_t tscap = 144 * 64;
+    for (int64_t r = 0; r < n_rows; r++) {
+        if (p_out) p_out[r] = NAN;
+        int32_t a1 = rows[5 * r + 1], a2 = rows[5 * r + 2], cellid = row_cell[r];
+        int s1 = A->seir[a1], s2 = A->seir[a2];
+        if (!((s1 == S_INF && s2 == S_SUS) || (s1 == S_SUS && s2 == S_INF))) continue;      /* :106-107 */
+        int dur = row_dur[r];
+        if (dur <= 0) continue;
+        int32_t ex = (s1 == S_SUS) ? a1 : a2;
+        double susc = P->probs_by_age[0][A->epi_age_bracket[ex]];
+        int sct = mtdo_simcelltype(cell_type[cellid]);
+        double base;                                                                     /* :998-1014 */
+        if (sct == SCT_RESIDENCE) base = P->p_household;
+        else if (sct == SCT_WORKPLACE) base = (cellid == A->res_cellid[ex]) ? P->p_workplace : P->p_community;  /* quirk B4 */
+        else if (sct == SCT_SCHOOL) base = P->p_school;
+        else base = P->p_community;
+        double lg = log((double)dur);
+        double mult = (lg > 1.0) ? lg : 1.0;                                             /* max(1, math.log(duration)) */
+        double imm, asym;
+        mtdo_vacc_multipliers(P, A->last_dose_day[ex], D->day, &imm, &asym);
+        double p = base * (mult * susc * (1 - D->mhd) * imm);                            /* :196 */
+        if (p_out) p_out[r] = p;
+        double u;
+        if (D->mode == MTDO_MODE_REPLAY) {
+            int64_t t = tape_find_pair(D->tape, cellid, a1, a2);
+            if (t < 0) { S->tape_miss++; continue; }
+            u = D->tape->pair_u[t];
+        } else {
+            uint32_t w[4];
+            philox_site(D, MTDO_SITE_PAIR, (uint32_t)cellid, (uint32_t)a1, (uint32_t)a2, w);
+            u = mtdo_u53(w[0], w[1]);
+        }
+        if (!(u < p)) continue;
+        /* overlapping timesteps, flattened in overlap-list order: a1's intervals (outer) x a2's (inner) */
+        int64_t nts = 0;
+        int32_t slot = G.slot_of_cell[cellid];
+        for (int64_t i = G.off[slot]; i < G.off[slot + 1]; i++) {
+            if (iv_agent[G.idx[i]] != a1) continue;
+            for (int64_t j = G.off[slot]; j < G.off[slot + 1]; j++) {
+                if (iv_agent[G.idx[j]] != a2) continue;
+                int lo = iv_start[G.idx[i]] > iv_start[G.idx[j]] ? iv_start[G.idx[i]] : iv_start[G.idx[j]];
+                int hi = iv_end[G.idx[i]] < iv_end[G.idx[j]] ? iv_end[G.idx[i]] : iv_end[G.idx[j]];
+                for (int t = lo; t <= hi; t++) {
+                    if (nts >= tscap) { tscap *= 2; tsbuf = (uint8_t *)realloc(tsbuf, (size_t)tscap); }
+                    tsbuf[nts++] = (uint8_t)t;
+                }
+            }
+        }
+        if (n_exp >= cap_e) { n_exp = -1; break; }
+        exposed[n_exp++] = ex;
+        expose_agent(P, D, A, ex, (int)nts, tsbuf, asym, S);
+    }
+    free(tsbuf);
+    free_groups(&G);
+    return n_exp;
+}
+
+/* ------------------------------------------------------------------ seirstateutil.update_agent_state (seirstateutil.py:38-72) */
+int64_t mtdo_advance(int32_t day, mtdo_agents *A, const uint8_t *mask)
+{
+    int64_t fired = 0;
+    for (int64_t ag = 0; ag < A->n_agents; ag++) {
+        if (mask && !mask[ag]) continue;
+        int c = A->sched_cnt[ag];
+        int32_t *sc = A->sched + ag * MTDO_MAXSCHED;
+        int today = -1;
+        for (int i = 0; i < c; i++) if ((sc[i] >> 16) == day) { today = i; break; }   /* first entry dated today (quirk B3) */
+        if (today < 0) continue;
+        int trans = (sc[today] >> 8) & 0xff;
+        int ns, nt, nv;
+        mtdo_transition(A->seir[ag], A->inf_type[ag], A->inf_sev[ag], trans, &ns, &nt, &nv);
+        A->seir[ag] = (int8_t)ns; A->inf_type[ag] = (int8_t)nt; A->inf_sev[ag] = (int8_t)nv;
+        for (int i = today; i + 1 < c; i++) sc[i] = sc[i + 1];                          /* del list[today_index] */
+        A->sched_cnt[ag] = (uint8_t)(c - 1);
+        fired++;
+    }
+    return fired;
+}

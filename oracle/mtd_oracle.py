@@ -1,0 +1,216 @@
+"""ctypes front-end of the CPU oracle (oracle/libmtd_oracle.so).  TEST INFRASTRUCTURE ONLY.
+
+Used by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs as the checker.
+The product package (mtdcovabm_b200/) never imports this module.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+MAXSCHED = 12
+NONE = -32768
+EXPO_W = 21
+MODE_REPLAY, MODE_PHILOX = 0, 1
+
+
+def build(force=False):
+    so = os.path.join(HERE, "libmtd_oracle.so")
+    src = [os.path.join(HERE, f) for f in ("mtd_oracle.c", "mtd_oracle.h", "Makefile")]
+    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in src):
+        subprocess.check_call(["make", "-C", HERE, "-s", "-B", "libmtd_oracle.so"])
+    return so
+
+
+class Tape(C.Structure):
+    _fields_ = [("n_sel", C.c_int64), ("sel_key", C.c_void_p), ("sel_off", C.c_void_p), ("sel_picks", C.c_void_p),
+                ("n_pair", C.c_int64), ("pair_k1", C.c_void_p), ("pair_k2", C.c_void_p), ("pair_u", C.c_void_p),
+                ("n_expo", C.c_int64), ("expo_agent", C.c_void_p), ("expo_row", C.c_void_p)]
+
+
+class DayCtx(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("seed", C.c_uint32), ("day", C.c_int32), ("mhd", C.c_double),
+                ("testing_enabled", C.c_int32), ("quarantine_enabled", C.c_int32), ("tape", C.POINTER(Tape))]
+
+
+class Agents(C.Structure):
+    _fields_ = [("n_agents", C.c_int64),
+                ("age_bracket", C.c_void_p), ("epi_age_bracket", C.c_void_p), ("soc_rate", C.c_void_p),
+                ("res_cellid", C.c_void_p),
+                ("seir", C.c_void_p), ("inf_type", C.c_void_p), ("inf_sev", C.c_void_p), ("last_dose_day", C.c_void_p),
+                ("sched", C.c_void_p), ("sched_cnt", C.c_void_p), ("test_day", C.c_void_p),
+                ("test_result_day", C.c_void_p), ("quarantine", C.c_void_p), ("hosp", C.c_void_p)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("pairs_evaluated", C.c_int64), ("n_cells", C.c_int64), ("n_potential", C.c_int64),
+                ("tape_miss", C.c_int64), ("sched_overflow", C.c_int64)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(build())
+        _lib.mtdo_contact_network.restype = C.c_int64
+        _lib.mtdo_transmission.restype = C.c_int64
+        _lib.mtdo_advance.restype = C.c_int64
+        _lib.mtdo_np_pairwise_sum.restype = C.c_double
+        _lib.mtdo_u53.restype = C.c_double
+    return _lib
+
+
+def _p(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+class AgentState:
+    """Dense per-agent arrays (index = agent id); the same layout the C-ABI of the product uses."""
+
+    STATIC = (("age_bracket", np.int8), ("epi_age_bracket", np.int8), ("soc_rate", np.float64), ("res_cellid", np.int32))
+    DYN = (("seir", np.int8, ()), ("inf_type", np.int8, ()), ("inf_sev", np.int8, ()), ("last_dose_day", np.int32, ()),
+           ("sched", np.int32, (MAXSCHED,)), ("sched_cnt", np.uint8, ()), ("test_day", np.int32, (2,)),
+           ("test_result_day", np.int32, (2,)), ("quarantine", np.int32, (3,)), ("hosp", np.int32, (3,)))
+
+    def __init__(self, n):
+        self.n = int(n)
+        self.age_bracket = np.zeros(n, np.int8)
+        self.epi_age_bracket = np.zeros(n, np.int8)
+        self.soc_rate = np.ones(n, np.float64)
+        self.res_cellid = np.full(n, -1, np.int32)
+        self.seir = np.zeros(n, np.int8)
+        self.inf_type = np.zeros(n, np.int8)
+        self.inf_sev = np.zeros(n, np.int8)
+        self.last_dose_day = np.full(n, NONE, np.int32)
+        self.sched = np.zeros((n, MAXSCHED), np.int32)
+        self.sched_cnt = np.zeros(n, np.uint8)
+        self.test_day = np.full((n, 2), NONE, np.int32)
+        self.test_result_day = np.full((n, 2), NONE, np.int32)
+        self.quarantine = np.full((n, 3), NONE, np.int32)
+        self.hosp = np.full((n, 3), NONE, np.int32)
+
+    def copy(self):
+        o = AgentState.__new__(AgentState)
+        o.n = self.n
+        for name, *_ in self.STATIC + self.DYN:
+            setattr(o, name, getattr(self, name).copy())
+        return o
+
+    def struct(self):
+        s = Agents()
+        s.n_agents = self.n
+        for name, *_ in self.STATIC + self.DYN:
+            a = getattr(self, name)
+            assert a.flags["C_CONTIGUOUS"]
+            setattr(s, name, a.ctypes.data)
+        return s
+
+    def dyn_equal(self, other):
+        return {name: bool(np.array_equal(getattr(self, name), getattr(other, name))) for name, *_ in self.DYN}
+
+
+def pack_sched(day, trans, ts):
+    return np.int32(np.uint32((int(day) & 0xFFFF) << 16 | (int(trans) & 0xFF) << 8 | (int(ts) & 0xFF)))
+
+
+def unpack_sched(v):
+    v = int(np.int32(v))
+    return v >> 16, (v >> 8) & 0xFF, v & 0xFF
+
+
+class TapeArrays:
+    """Sorted key/value arrays of one day's replay tape."""
+
+    def __init__(self, sel_cell, sel_agent, sel_off, sel_picks, pair_key, pair_u, expo_agent, expo_row):
+        sk = (sel_cell.astype(np.uint64) << np.uint64(32)) | sel_agent.astype(np.uint32).astype(np.uint64)
+        order = np.argsort(sk, kind="stable")
+        self.sel_key = np.ascontiguousarray(sk[order])
+        lens = np.diff(sel_off)[order]
+        self.sel_off = np.zeros(len(sk) + 1, np.int32)
+        self.sel_off[1:] = np.cumsum(lens)
+        self.sel_picks = np.concatenate([sel_picks[sel_off[i]:sel_off[i + 1]] for i in order]).astype(np.int32) \
+            if len(order) else np.zeros(0, np.int32)
+        k1 = (pair_key[:, 0].astype(np.uint64) << np.uint64(32)) | pair_key[:, 1].astype(np.uint32).astype(np.uint64)
+        k2 = pair_key[:, 2].astype(np.uint32)
+        po = np.lexsort((k2, k1))
+        self.pair_k1 = np.ascontiguousarray(k1[po])
+        self.pair_k2 = np.ascontiguousarray(k2[po])
+        self.pair_u = np.ascontiguousarray(pair_u[po].astype(np.float64))
+        eo = np.argsort(expo_agent, kind="stable")
+        self.expo_agent = np.ascontiguousarray(expo_agent[eo].astype(np.int32))
+        self.expo_row = np.ascontiguousarray(expo_row[eo].astype(np.float64)).reshape(-1, EXPO_W)
+
+    def struct(self):
+        t = Tape()
+        t.n_sel = len(self.sel_key); t.sel_key = self.sel_key.ctypes.data
+        t.sel_off = self.sel_off.ctypes.data; t.sel_picks = self.sel_picks.ctypes.data
+        t.n_pair = len(self.pair_k1); t.pair_k1 = self.pair_k1.ctypes.data
+        t.pair_k2 = self.pair_k2.ctypes.data; t.pair_u = self.pair_u.ctypes.data
+        t.n_expo = len(self.expo_agent); t.expo_agent = self.expo_agent.ctypes.data
+        t.expo_row = self.expo_row.ctypes.data
+        return t
+
+
+def make_ctx(mode, day, mhd, testing_enabled, quarantine_enabled, seed=0, tape: TapeArrays | None = None):
+    ctx = DayCtx()
+    ctx.mode = mode; ctx.seed = seed; ctx.day = day; ctx.mhd = mhd
+    ctx.testing_enabled = int(testing_enabled); ctx.quarantine_enabled = int(quarantine_enabled)
+    keep = None
+    if tape is not None:
+        keep = tape.struct()
+        ctx.tape = C.pointer(keep)
+    ctx._keep = (keep, tape)
+    return ctx
+
+
+def contact_network(params, ctx, iv_cell, iv_agent, iv_start, iv_end, cell_type, cell_indid, agents: AgentState,
+                    cap=None):
+    """-> (rows[D,5] int32, row_dur[D], row_cell[D], Stats)"""
+    M = len(iv_cell)
+    cap = int(cap if cap is not None else max(1024, 12 * M))
+    rows = np.zeros((cap, 5), np.int32); dur = np.zeros(cap, np.int32); rc = np.zeros(cap, np.int32)
+    st = Stats()
+    a = agents.struct()
+    iv_cell = np.ascontiguousarray(iv_cell, np.int32); iv_agent = np.ascontiguousarray(iv_agent, np.int32)
+    iv_start = np.ascontiguousarray(iv_start, np.uint8); iv_end = np.ascontiguousarray(iv_end, np.uint8)
+    cell_type = np.ascontiguousarray(cell_type, np.int8); cell_indid = np.ascontiguousarray(cell_indid, np.int16)
+    n = lib().mtdo_contact_network(C.byref(params), C.byref(ctx), C.c_int64(M), _p(iv_cell), _p(iv_agent), _p(iv_start),
+                                   _p(iv_end), _p(cell_type), _p(cell_indid), C.byref(a), C.c_int64(cap), _p(rows),
+                                   _p(dur), _p(rc), C.byref(st))
+    if n < 0:
+        raise RuntimeError("oracle: contact row capacity exceeded")
+    return rows[:n].copy(), dur[:n].copy(), rc[:n].copy(), st
+
+
+def transmission(params, ctx, iv_cell, iv_agent, iv_start, iv_end, cell_type, rows, row_dur, row_cell,
+                 agents: AgentState, want_p=False):
+    """Mutates `agents`.  -> (exposed ids in order, p per row or None, Stats)"""
+    M = len(iv_cell); n_rows = len(rows)
+    exposed = np.zeros(max(16, n_rows), np.int32)
+    p = np.zeros(max(1, n_rows), np.float64) if want_p else None
+    st = Stats()
+    a = agents.struct()
+    iv_cell = np.ascontiguousarray(iv_cell, np.int32); iv_agent = np.ascontiguousarray(iv_agent, np.int32)
+    iv_start = np.ascontiguousarray(iv_start, np.uint8); iv_end = np.ascontiguousarray(iv_end, np.uint8)
+    cell_type = np.ascontiguousarray(cell_type, np.int8)
+    rows = np.ascontiguousarray(rows, np.int32); row_dur = np.ascontiguousarray(row_dur, np.int32)
+    row_cell = np.ascontiguousarray(row_cell, np.int32)
+    n = lib().mtdo_transmission(C.byref(params), C.byref(ctx), C.c_int64(M), _p(iv_cell), _p(iv_agent), _p(iv_start),
+                                _p(iv_end), _p(cell_type), C.c_int64(n_rows), _p(rows), _p(row_dur), _p(row_cell),
+                                C.byref(a), C.c_int64(len(exposed)), _p(exposed), _p(p), C.byref(st))
+    if n < 0:
+        raise RuntimeError("oracle: exposed capacity exceeded")
+    return exposed[:n].copy(), (p[:n_rows] if want_p else None), st
+
+
+def advance(day, agents: AgentState, mask=None):
+    a = agents.struct()
+    if mask is not None:
+        mask = np.ascontiguousarray(mask, np.uint8)
+    return lib().mtdo_advance(C.c_int32(day), C.byref(a), _p(mask))
