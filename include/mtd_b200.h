@@ -1,0 +1,148 @@
+/*
+ * include/mtd_b200.h -- C ABI of libmtd_b200.so: the B200 (sm_100a) implementation of mtdcovabm's per-day
+ * contact-network + transmission + SEIR-advance path.  Plain C: pointers and sizes only, no torch / C++ types.
+ *
+ * Every entry point replaces a reference interface (paths relative to /root/reference/simulator):
+ *   mtd_simulate_contact_network   ContactNetwork.simulate_contact_network        contactnetwork.py:65-124
+ *                                  (+ generate_contact_network                    contactnetwork.py:134-315)
+ *   mtd_simulate_direct_contacts   Epidemiology.simulate_direct_contacts          epidemiology.py:88-231
+ *                                  (+ simulate_seir_state_transition, schedule_*  epidemiology.py:233-660)
+ *   mtd_advance_seir               seirstateutil.update_agent_state               seirstateutil.py:38-72
+ *   mtd_set_static                 Static.get(id, "age_bracket_index" | "epi_age_bracket_index" | "soc_rate" |
+ *                                  "res_cellid")                                  static.py:351-363
+ *   mtd_set_state / mtd_get_state  vars_util.agents_seir_state / agents_infection_type / agents_infection_severity /
+ *                                  agents_vaccination_doses (vars.py:52-56) and agents_epi[id][...] (agentsutil.py:56-62)
+ *   mtd_set_params                 Epidemiology.__init__ / ContactNetwork.__init__ parameter extraction
+ *                                  epidemiology.py:29-70, contactnetwork.py:41-42
+ *   mtd_get_contacts               vars_util.directcontacts_by_simcelltype_by_day rows   contactnetwork.py:98-105
+ *   mtd_apply_deltas               the "updated agents" exchange of the reference's stateful-actor strategy
+ *                                  actor_dist.py:491-518 (multi-GPU: one allgather per day in between)
+ *
+ * Conventions: every function returns 0 on success, non-zero MTD_E_* otherwise; mtd_last_error(h) gives the text.
+ * No C++ exception crosses this boundary.  One handle = one device + one stream; calls on a handle are not
+ * re-entrant.  `mem` arguments say where the caller's buffers live: MTD_MEM_HOST (the library copies through its
+ * stream) or MTD_MEM_DEVICE (used in place / copied device-to-device).
+ */
+#ifndef MTD_B200_H
+#define MTD_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MTD_MAXSCHED 12          /* live + stale schedule entries per agent */
+#define MTD_NONE (-32768)        /* "None" for day-valued record fields */
+#define MTD_EXPO_W 21            /* doubles per replay-tape exposure record (tests/golden/ref_harness.py) */
+#define MTD_DELTA_WORDS 20       /* int32 words per exposure delta record */
+#define MTD_MAX_CELL_INTERVALS 1024  /* largest cell (intervals) the on-chip path handles */
+
+enum { MTD_OK = 0, MTD_E_ARG = 1, MTD_E_CUDA = 2, MTD_E_CAPACITY = 3, MTD_E_CELL_TOO_LARGE = 4, MTD_E_STATE = 5 };
+enum { MTD_MEM_HOST = 0, MTD_MEM_DEVICE = 1 };
+enum { MTD_MODE_REPLAY = 0, MTD_MODE_PHILOX = 1 };
+
+typedef struct mtd_handle_s *mtd_handle;
+
+typedef struct {
+    int32_t device;              /* CUDA device ordinal */
+    int64_t n_agents;            /* N: agent ids are dense in [0, N) */
+    int64_t n_cells;             /* cell ids are dense in [0, n_cells) */
+    int64_t max_intervals;       /* capacity M of one day's interval stream */
+    int64_t max_rows;            /* capacity of the dense contact-row buffer of one day (0 = derive from M) */
+    int64_t max_exposures;       /* capacity of the per-day exposure delta buffer (0 = derive) */
+    void *stream;                /* cudaStream_t to run on; NULL = library-owned stream */
+} mtd_config;
+
+/* Same field order as oracle/mtd_oracle.h:mtdo_params (kept separate on purpose: the oracle is not product code). */
+typedef struct {
+    double cm[16][6];
+    int32_t k_by_act[6];
+    double p_household, p_workplace, p_school, p_community;
+    double probs_by_age[5][11];
+    double ln_mu[10], ln_sigma[10];
+    double test_mu, test_sigma, result_mu, result_sigma;
+    double testing_after_symptoms_probability;
+    double quarantine_after_symptoms_probability;
+    double ignore_quarantine_rules_probability;
+    int32_t quarantine_positive_duration, quarantine_positive_contact_duration, quarantine_secondary_contact_duration;
+    int32_t contact_tracing_days_back, contact_tracing_positive_delay_days, contact_tracing_secondary_delay_days;
+    double tracing_success_prob[4];
+    double vacc_immunity, vacc_asymptomatic, vacc_decay_interval;
+} mtd_params;
+
+typedef struct {
+    int32_t mode;                /* MTD_MODE_* */
+    uint32_t seed;               /* Philox key word 0 */
+    int32_t day;
+    double mhd;                  /* dyn_params.masks_hygiene_distancing_multiplier (dynamicparams.py:67-73) */
+    int32_t testing_enabled, quarantine_enabled;
+} mtd_day;
+
+/* replay tape of one day (host pointers; sorted by key) */
+typedef struct {
+    int64_t n_sel;  const uint64_t *sel_key;  const int32_t *sel_off;  const int32_t *sel_picks;
+    int64_t n_pair; const uint64_t *pair_k1;  const uint32_t *pair_k2; const double *pair_u;
+    int64_t n_expo; const int32_t *expo_agent; const double *expo_row;
+} mtd_tape;
+
+typedef struct {
+    int64_t n_slots;             /* active cells of the day */
+    int64_t n_rows;              /* direct contacts (dense rows) */
+    int64_t n_exposed;           /* exposures applied */
+    int64_t pairs_evaluated;     /* sum over cells of #{i<j: different agents}: the headline metric's unit */
+    int64_t n_potential;         /* overlapping agent pairs */
+    int64_t n_si_rows;           /* rows with exactly one Susceptible and one Infectious endpoint */
+    int64_t sched_overflow;      /* schedule entries dropped (MTD_MAXSCHED reached) */
+    int64_t tape_miss;           /* replay lookups without a record */
+    int64_t class_cells[4];      /* cells per size class (<=32, <=128, <=320, <=1024 intervals) */
+    int64_t error;               /* MTD_E_* raised on the device (capacity, cell too large) */
+} mtd_counters;
+
+int mtd_create(const mtd_config *cfg, mtd_handle *out);
+int mtd_destroy(mtd_handle h);
+const char *mtd_last_error(mtd_handle h);
+int mtd_abi_version(void);
+
+int mtd_set_params(mtd_handle h, const mtd_params *p);
+int mtd_set_cells(mtd_handle h, int64_t n_cells, const int8_t *cell_type, const int16_t *cell_indid, int mem);
+int mtd_set_static(mtd_handle h, int64_t n, const int8_t *age_bracket, const int8_t *epi_age_bracket,
+                   const double *soc_rate, const int32_t *res_cellid, int mem);
+/* any pointer may be NULL = leave that array untouched */
+int mtd_set_state(mtd_handle h, int64_t n, const int8_t *seir, const int8_t *inf_type, const int8_t *inf_sev,
+                  const int32_t *last_dose_day, const int32_t *sched, const uint8_t *sched_cnt,
+                  const int32_t *test_day, const int32_t *test_result_day, const int32_t *quarantine,
+                  const int32_t *hosp, int mem);
+int mtd_get_state(mtd_handle h, int64_t n, int8_t *seir, int8_t *inf_type, int8_t *inf_sev, int32_t *sched,
+                  uint8_t *sched_cnt, int32_t *test_day, int32_t *test_result_day, int32_t *quarantine,
+                  int32_t *hosp, int mem);
+int mtd_set_tape(mtd_handle h, const mtd_tape *tape);
+
+/* K0 (CSR build) + K1 (pairs, degrees, greedy sampling) + K2 (dense rows).  Interval stream in emission order
+ * (itinerary.py:1446-1452); iv_order may be NULL (= position in the stream) or strictly increasing global
+ * emission indices when the stream is one rank's shard. */
+int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, int64_t n_intervals, const int32_t *iv_agent,
+                                 const int32_t *iv_cell, const uint8_t *iv_start, const uint8_t *iv_end,
+                                 const uint32_t *iv_order, int mem);
+/* K3: pair evaluation, winner resolution and trajectory sampling into fixed-size delta records, then (apply != 0)
+ * application to the per-agent state.  delta_buf is a DEVICE buffer of (1 + cap_records) records of
+ * MTD_DELTA_WORDS int32 each -- record 0 is a header whose word 0 receives the record count -- or NULL to use the
+ * handle's own buffer.  Multi-GPU: pass this rank's slice of the allgather buffer with apply == 0, allgather, then
+ * mtd_apply_deltas over all n_bufs slices. */
+int mtd_simulate_direct_contacts(mtd_handle h, const mtd_day *day, int32_t *delta_buf, int64_t cap_records, int apply);
+int mtd_apply_deltas(mtd_handle h, const int32_t *delta_bufs, int64_t n_bufs, int64_t cap_records);
+/* K4: daily SEIR advance for every agent with a schedule entry dated `day`; mask (uint8[N]) may be NULL. */
+int mtd_advance_seir(mtd_handle h, int32_t day, const uint8_t *mask, int mem);
+
+/* results of the last day step */
+int mtd_get_counters(mtd_handle h, mtd_counters *out);           /* synchronises the stream */
+int mtd_get_contacts(mtd_handle h, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap, int64_t *n,
+                     int mem);                                    /* rows5: [n][5] simcelltype,a1,a2,start,end */
+int mtd_get_exposed(mtd_handle h, int32_t *agent_ids, int64_t cap, int64_t *n, int mem);   /* in reference order */
+int mtd_get_infection_prob(mtd_handle h, double *p, int64_t cap, int mem);   /* per dense row, NaN if not S-I */
+int mtd_occupancy(mtd_handle h, int64_t out[6]);                 /* dynamicstatistics.py:169-193 */
+int mtd_sync(mtd_handle h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,218 @@
+"""ctypes binding of libmtd_b200.so (C ABI declared in include/mtd_b200.h).
+
+There is no CPU fallback: if the CUDA library is missing or a call fails, a RuntimeError is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from .params import EXPO_W, MAXSCHED, NONE, ParamsStruct
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+SO = os.path.join(PKG, "libmtd_b200.so")
+MEM_HOST, MEM_DEVICE = 0, 1
+MODE_REPLAY, MODE_PHILOX = 0, 1
+DELTA_WORDS = 20
+
+EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mtd_set_params", "mtd_set_cells",
+           "mtd_set_static", "mtd_set_state", "mtd_get_state", "mtd_set_tape", "mtd_simulate_contact_network",
+           "mtd_simulate_direct_contacts", "mtd_apply_deltas", "mtd_advance_seir", "mtd_get_counters",
+           "mtd_get_contacts", "mtd_get_exposed", "mtd_get_infection_prob", "mtd_occupancy", "mtd_sync"]
+
+
+class Config(C.Structure):
+    _fields_ = [("device", C.c_int32), ("n_agents", C.c_int64), ("n_cells", C.c_int64), ("max_intervals", C.c_int64),
+                ("max_rows", C.c_int64), ("max_exposures", C.c_int64), ("stream", C.c_void_p)]
+
+
+class Day(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("seed", C.c_uint32), ("day", C.c_int32), ("mhd", C.c_double),
+                ("testing_enabled", C.c_int32), ("quarantine_enabled", C.c_int32)]
+
+
+class Tape(C.Structure):
+    _fields_ = [("n_sel", C.c_int64), ("sel_key", C.c_void_p), ("sel_off", C.c_void_p), ("sel_picks", C.c_void_p),
+                ("n_pair", C.c_int64), ("pair_k1", C.c_void_p), ("pair_k2", C.c_void_p), ("pair_u", C.c_void_p),
+                ("n_expo", C.c_int64), ("expo_agent", C.c_void_p), ("expo_row", C.c_void_p)]
+
+
+class Counters(C.Structure):
+    _fields_ = [("n_slots", C.c_int64), ("n_rows", C.c_int64), ("n_exposed", C.c_int64), ("pairs_evaluated", C.c_int64),
+                ("n_potential", C.c_int64), ("n_si_rows", C.c_int64), ("sched_overflow", C.c_int64),
+                ("tape_miss", C.c_int64), ("class_cells", C.c_int64 * 4), ("error", C.c_int64)]
+
+
+_lib = None
+
+
+def load():
+    """Load the shared library; raises if it has not been built (python -m mtdcovabm_b200.build)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO):
+            raise RuntimeError("libmtd_b200.so is missing: build it with `python mtdcovabm_b200/build.py` "
+                               "(there is no CPU fallback for this path)")
+        lib = C.CDLL(SO)
+        lib.mtd_last_error.restype = C.c_char_p
+        lib.mtd_last_error.argtypes = [C.c_void_p]
+        for name in EXPORTS:
+            getattr(lib, name)            # AttributeError if a declared symbol is not exported
+        _lib = lib
+    return _lib
+
+
+def _ptr(a):
+    """numpy array / torch tensor / int / None -> c_void_p"""
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        assert a.flags["C_CONTIGUOUS"]
+        return C.c_void_p(a.ctypes.data)
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    return C.c_void_p(a.data_ptr())       # torch tensor
+
+
+class Handle:
+    """One device + one stream (SURVEY.md section 8b threading contract)."""
+
+    def __init__(self, n_agents, n_cells, max_intervals, device=0, stream=None, max_rows=0, max_exposures=0):
+        self.lib = load()
+        cfg = Config(device, n_agents, n_cells, max_intervals, max_rows, max_exposures, stream)
+        self.h = C.c_void_p()
+        self.n_agents, self.n_cells, self.max_intervals = int(n_agents), int(n_cells), int(max_intervals)
+        rc = self.lib.mtd_create(C.byref(cfg), C.byref(self.h))
+        if rc != 0:
+            msg = self.lib.mtd_last_error(self.h).decode() if self.h else "mtd_create failed"
+            if self.h:
+                self.lib.mtd_destroy(self.h)
+                self.h = None
+            raise RuntimeError("mtd_create: rc=%d %s" % (rc, msg))
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise RuntimeError("%s: rc=%d %s" % (what, rc, self.lib.mtd_last_error(self.h).decode()))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.mtd_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- setup
+    def set_params(self, P: ParamsStruct):
+        self._keep_params = P
+        self._ck(self.lib.mtd_set_params(self.h, C.byref(P)), "mtd_set_params")
+
+    def set_cells(self, cell_type, cell_indid, mem=MEM_HOST):
+        self._ck(self.lib.mtd_set_cells(self.h, C.c_int64(self.n_cells), _ptr(cell_type), _ptr(cell_indid), mem),
+                 "mtd_set_cells")
+
+    def set_static(self, age_bracket, epi_age_bracket, soc_rate, res_cellid, mem=MEM_HOST):
+        self._ck(self.lib.mtd_set_static(self.h, C.c_int64(self.n_agents), _ptr(age_bracket), _ptr(epi_age_bracket),
+                                         _ptr(soc_rate), _ptr(res_cellid), mem), "mtd_set_static")
+
+    def set_state(self, seir=None, inf_type=None, inf_sev=None, last_dose_day=None, sched=None, sched_cnt=None,
+                  test_day=None, test_result_day=None, quarantine=None, hosp=None, mem=MEM_HOST):
+        self._ck(self.lib.mtd_set_state(self.h, C.c_int64(self.n_agents), _ptr(seir), _ptr(inf_type), _ptr(inf_sev),
+                                        _ptr(last_dose_day), _ptr(sched), _ptr(sched_cnt), _ptr(test_day),
+                                        _ptr(test_result_day), _ptr(quarantine), _ptr(hosp), mem), "mtd_set_state")
+
+    def get_state(self):
+        n = self.n_agents
+        out = dict(seir=np.zeros(n, np.int8), inf_type=np.zeros(n, np.int8), inf_sev=np.zeros(n, np.int8),
+                   sched=np.zeros((n, MAXSCHED), np.int32), sched_cnt=np.zeros(n, np.uint8),
+                   test_day=np.zeros((n, 2), np.int32), test_result_day=np.zeros((n, 2), np.int32),
+                   quarantine=np.zeros((n, 3), np.int32), hosp=np.zeros((n, 3), np.int32))
+        self._ck(self.lib.mtd_get_state(self.h, C.c_int64(n), _ptr(out["seir"]), _ptr(out["inf_type"]),
+                                        _ptr(out["inf_sev"]), _ptr(out["sched"]), _ptr(out["sched_cnt"]),
+                                        _ptr(out["test_day"]), _ptr(out["test_result_day"]), _ptr(out["quarantine"]),
+                                        _ptr(out["hosp"]), MEM_HOST), "mtd_get_state")
+        return out
+
+    def set_tape(self, sel_key, sel_off, sel_picks, pair_k1, pair_k2, pair_u, expo_agent, expo_row):
+        t = Tape()
+        arrs = [np.ascontiguousarray(sel_key, np.uint64), np.ascontiguousarray(sel_off, np.int32),
+                np.ascontiguousarray(sel_picks, np.int32), np.ascontiguousarray(pair_k1, np.uint64),
+                np.ascontiguousarray(pair_k2, np.uint32), np.ascontiguousarray(pair_u, np.float64),
+                np.ascontiguousarray(expo_agent, np.int32), np.ascontiguousarray(expo_row, np.float64)]
+        t.n_sel, t.n_pair, t.n_expo = len(arrs[0]), len(arrs[3]), len(arrs[6])
+        (t.sel_key, t.sel_off, t.sel_picks, t.pair_k1, t.pair_k2, t.pair_u, t.expo_agent, t.expo_row) = \
+            [a.ctypes.data for a in arrs]
+        self._ck(self.lib.mtd_set_tape(self.h, C.byref(t)), "mtd_set_tape")
+
+    def clear_tape(self):
+        self._ck(self.lib.mtd_set_tape(self.h, None), "mtd_set_tape")
+
+    # ---- day step
+    @staticmethod
+    def make_day(mode, day, mhd, testing_enabled=False, quarantine_enabled=False, seed=0):
+        return Day(mode, seed, day, mhd, int(testing_enabled), int(quarantine_enabled))
+
+    def simulate_contact_network(self, day: Day, iv_agent, iv_cell, iv_start, iv_end, iv_order=None, n=None,
+                                 mem=MEM_HOST):
+        n = len(iv_agent) if n is None else n
+        self._ck(self.lib.mtd_simulate_contact_network(self.h, C.byref(day), C.c_int64(n), _ptr(iv_agent), _ptr(iv_cell),
+                                                       _ptr(iv_start), _ptr(iv_end), _ptr(iv_order), mem),
+                 "mtd_simulate_contact_network")
+
+    def simulate_direct_contacts(self, day: Day, delta_buf=None, cap_records=0, apply=True):
+        self._ck(self.lib.mtd_simulate_direct_contacts(self.h, C.byref(day), _ptr(delta_buf), C.c_int64(cap_records),
+                                                       int(apply)), "mtd_simulate_direct_contacts")
+
+    def apply_deltas(self, bufs, n_bufs, cap_records):
+        self._ck(self.lib.mtd_apply_deltas(self.h, _ptr(bufs), C.c_int64(n_bufs), C.c_int64(cap_records)),
+                 "mtd_apply_deltas")
+
+    def advance_seir(self, day, mask=None, mem=MEM_HOST):
+        self._ck(self.lib.mtd_advance_seir(self.h, C.c_int32(day), _ptr(mask), mem), "mtd_advance_seir")
+
+    def sync(self):
+        self._ck(self.lib.mtd_sync(self.h), "mtd_sync")
+
+    # ---- results
+    def counters(self) -> Counters:
+        c = Counters()
+        self._ck(self.lib.mtd_get_counters(self.h, C.byref(c)), "mtd_get_counters")
+        return c
+
+    def get_contacts(self):
+        c = self.counters()
+        n = int(c.n_rows)
+        rows = np.zeros((max(n, 1), 5), np.int32); dur = np.zeros(max(n, 1), np.int32); cell = np.zeros(max(n, 1), np.int32)
+        got = C.c_int64()
+        self._ck(self.lib.mtd_get_contacts(self.h, _ptr(rows), _ptr(dur), _ptr(cell), C.c_int64(max(n, 1)), C.byref(got),
+                                           MEM_HOST), "mtd_get_contacts")
+        return rows[:n], dur[:n], cell[:n]
+
+    def get_exposed(self):
+        c = self.counters()
+        n = int(c.n_exposed)
+        ids = np.zeros(max(n, 1), np.int32)
+        got = C.c_int64()
+        self._ck(self.lib.mtd_get_exposed(self.h, _ptr(ids), C.c_int64(max(n, 1)), C.byref(got), MEM_HOST),
+                 "mtd_get_exposed")
+        return ids[:got.value]
+
+    def enable_infection_prob(self):
+        self._ck(self.lib.mtd_get_infection_prob(self.h, None, C.c_int64(0), MEM_HOST), "mtd_get_infection_prob")
+
+    def get_infection_prob(self):
+        n = int(self.counters().n_rows)
+        p = np.zeros(max(n, 1), np.float64)
+        self._ck(self.lib.mtd_get_infection_prob(self.h, _ptr(p), C.c_int64(max(n, 1)), MEM_HOST),
+                 "mtd_get_infection_prob")
+        return p[:n]
+
+    def occupancy(self):
+        out = (C.c_int64 * 6)()
+        self._ck(self.lib.mtd_occupancy(self.h, out), "mtd_occupancy")
+        return np.array(list(out), np.int64)

@@ -1,0 +1,448 @@
+// C ABI of libmtd_b200.so (include/mtd_b200.h): handle, device buffers, entry points.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "common.cuh"
+
+void launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count);
+void launch_k1(const DevCtx &c, cudaStream_t st, int sm_count);
+void launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count);
+void launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap, cudaStream_t st);
+void launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, cudaStream_t st, int sm_count);
+void launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t cap, bool resolve,
+                     unsigned long long *expo_list, cudaStream_t st, int sm_count);
+void launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count);
+void launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st, int sm_count);
+void launch_scan_nrows(const DevCtx &c, long long *scan_tmp, cudaStream_t st);
+
+struct mtd_handle_s {
+    mtd_config cfg;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int sm_count = 148;
+    std::string err;
+    std::vector<void *> allocs;
+    DevCtx c;
+    // staging buffers for host-resident day inputs
+    int32_t *d_iv_agent = nullptr, *d_iv_cell = nullptr; uint8_t *d_iv_start = nullptr, *d_iv_end = nullptr;
+    uint32_t *d_iv_order = nullptr;
+    uint8_t *d_mask = nullptr;
+    long long *scan_tmp = nullptr;
+    unsigned long long *expo_list = nullptr;     // [cap_expo][2] (key, agent)
+    unsigned long long *occ = nullptr;
+    mtd_params *d_params = nullptr;
+    int32_t *delta_own = nullptr;
+    // replay tape (device copies)
+    std::vector<void *> tape_allocs;
+    bool have_params = false, have_cells = false, have_static = false, day_ready = false;
+};
+
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
+    h->err = std::string(#call) + ": " + cudaGetErrorString(e_); return MTD_E_CUDA; } } while (0)
+
+template <typename T>
+static int dalloc(mtd_handle h, T **p, size_t n)
+{
+    void *q = nullptr;
+    cudaError_t e = cudaMalloc(&q, std::max<size_t>(n, 1) * sizeof(T));
+    if (e != cudaSuccess) { h->err = std::string("cudaMalloc: ") + cudaGetErrorString(e); return MTD_E_CUDA; }
+    h->allocs.push_back(q);
+    *p = (T *)q;
+    return 0;
+}
+#define DA(ptr, n) do { int r_ = dalloc(h, &(ptr), (size_t)(n)); if (r_) return r_; } while (0)
+
+extern "C" int mtd_abi_version(void) { return 1; }
+
+extern "C" const char *mtd_last_error(mtd_handle h) { return h ? h->err.c_str() : "null handle"; }
+
+static int create_impl(mtd_handle h)
+{
+    const mtd_config &cfg = h->cfg;
+    CK(cudaSetDevice(cfg.device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, cfg.device));
+    h->sm_count = prop.multiProcessorCount;
+    if (cfg.stream) h->stream = (cudaStream_t)cfg.stream;
+    else { CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->own_stream = true; }
+    DevCtx &c = h->c;
+    memset(&c, 0, sizeof(c));
+    const int64_t N = cfg.n_agents, C = cfg.n_cells, M = cfg.max_intervals;
+    c.n_agents = N; c.n_cells = C; c.cap_intervals = M;
+    // rows: sum over cells of (k*m + m/2)/2 + 2 with k <= 19 -> generous static bound, clipped by config
+    c.cap_scratch_rows = 10 * M + 2 * std::min(M, C) + 1024;
+    c.cap_rows = cfg.max_rows > 0 ? cfg.max_rows : (4 * M + 1024);
+    c.cap_list = std::max<int64_t>(160 * M, 1 << 22);   // u16 entries: sum of m(m-1) over cells of > 32 intervals
+    c.cap_expo = cfg.max_exposures > 0 ? cfg.max_exposures : std::max<int64_t>(N / 4, 4096);
+    const int64_t S = std::min(M, C);   // max active cells
+    int8_t *ct; int16_t *ci; int8_t *ab, *eb; double *sr; int32_t *rc;
+    DA(ct, C); DA(ci, C); DA(ab, N); DA(eb, N); DA(sr, N); DA(rc, N);
+    c.cell_type = ct; c.cell_indid = ci; c.age_bracket = ab; c.epi_age_bracket = eb; c.soc_rate = sr; c.res_cellid = rc;
+    DA(c.seir, N); DA(c.inf_type, N); DA(c.inf_sev, N); DA(c.last_dose_day, N);
+    DA(c.sched, N * MTD_MAXSCHED); DA(c.sched_cnt, N); DA(c.test_day, 2 * N); DA(c.test_result_day, 2 * N);
+    DA(c.quarantine, 3 * N); DA(c.hosp, 3 * N);
+    DA(c.cell_count, C); DA(c.cell_first, C); DA(c.slot_of_cell, C); DA(c.flag_scan, M + 2);
+    DA(c.slot_cell, S + 1); DA(c.slot_m, S + 1); DA(c.slot_first, S + 1); DA(c.slot_cursor, S + 1);
+    DA(c.slot_off, S + 2); DA(c.slot_rowoff, S + 2); DA(c.slot_listoff, S + 2); DA(c.slot_rowbound, S + 1);
+    DA(c.slot_listneed, S + 1); DA(c.slot_nrows, S + 1); DA(c.slot_denseoff, S + 2);
+    c.class_stride = S + 1;
+    DA(c.class_list, MTD_NUM_CLASSES * (S + 1));
+    DA(c.csr, M); DA(c.csr_sorted, M);
+    DA(c.scratch_rows, c.cap_scratch_rows); DA(c.lists, c.cap_list); DA(c.rows, c.cap_rows);
+    DA(c.win, N); DA(c.succ, c.cap_rows);
+    c.row_p = nullptr;
+    DA(h->delta_own, (c.cap_expo + 1) * MTD_DELTA_WORDS);
+    c.delta = h->delta_own;
+    DA(c.ctr, 1);
+    DA(h->d_params, 1);
+    c.P = h->d_params;
+    DA(h->d_iv_agent, M); DA(h->d_iv_cell, M); DA(h->d_iv_start, M); DA(h->d_iv_end, M); DA(h->d_iv_order, M);
+    DA(h->d_mask, N);
+    DA(h->scan_tmp, (std::max(M, S) + 2) / 2048 + 16);
+    DA(h->expo_list, 2 * c.cap_expo);
+    DA(h->occ, 8);
+    // initial state: nobody present
+    CK(cudaMemsetAsync(c.seir, 0, N, h->stream)); CK(cudaMemsetAsync(c.inf_type, 0, N, h->stream));
+    CK(cudaMemsetAsync(c.inf_sev, 0, N, h->stream)); CK(cudaMemsetAsync(c.sched_cnt, 0, N, h->stream));
+    CK(cudaMemsetAsync(c.sched, 0, sizeof(int32_t) * N * MTD_MAXSCHED, h->stream));
+    CK(cudaMemsetAsync(c.ctr, 0, sizeof(DevCounters), h->stream));
+    CK(cudaMemsetAsync(ci, 0xff, sizeof(int16_t) * C, h->stream));
+    std::vector<int32_t> none((size_t)std::max<int64_t>(3 * N, 1), MTD_NONE);
+    CK(cudaMemcpyAsync(c.last_dose_day, none.data(), sizeof(int32_t) * N, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(c.test_day, none.data(), sizeof(int32_t) * 2 * N, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(c.test_result_day, none.data(), sizeof(int32_t) * 2 * N, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(c.quarantine, none.data(), sizeof(int32_t) * 3 * N, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(c.hosp, none.data(), sizeof(int32_t) * 3 * N, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return MTD_OK;
+}
+
+extern "C" int mtd_create(const mtd_config *cfg, mtd_handle *out)
+{
+    if (!cfg || !out || cfg->n_agents <= 0 || cfg->n_cells <= 0 || cfg->max_intervals <= 0) return MTD_E_ARG;
+    mtd_handle h = new (std::nothrow) mtd_handle_s();
+    if (!h) return MTD_E_ARG;
+    h->cfg = *cfg;
+    *out = h;                // returned even on failure so that mtd_last_error() can be read; caller destroys it
+    return create_impl(h);
+}
+
+static void free_tape(mtd_handle h)
+{
+    for (void *p : h->tape_allocs) cudaFree(p);
+    h->tape_allocs.clear();
+    memset(&h->c.tape, 0, sizeof(h->c.tape));
+}
+
+extern "C" int mtd_destroy(mtd_handle h)
+{
+    if (!h) return MTD_E_ARG;
+    cudaSetDevice(h->cfg.device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    free_tape(h);
+    for (void *p : h->allocs) cudaFree(p);
+    if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return MTD_OK;
+}
+
+static cudaMemcpyKind kind_in(int mem) { return mem == MTD_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice; }
+static cudaMemcpyKind kind_out(int mem) { return mem == MTD_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost; }
+
+#define COPY_IN(dst, src, bytes) do { if (src) CK(cudaMemcpyAsync((void *)(dst), (src), (bytes), kind_in(mem), h->stream)); } while (0)
+#define COPY_OUT(dst, src, bytes) do { if (dst) CK(cudaMemcpyAsync((dst), (const void *)(src), (bytes), kind_out(mem), h->stream)); } while (0)
+
+extern "C" int mtd_set_params(mtd_handle h, const mtd_params *p)
+{
+    if (!h || !p) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaMemcpyAsync(h->d_params, p, sizeof(mtd_params), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    h->have_params = true;
+    return MTD_OK;
+}
+
+extern "C" int mtd_set_cells(mtd_handle h, int64_t n, const int8_t *cell_type, const int16_t *cell_indid, int mem)
+{
+    if (!h || n != h->c.n_cells || !cell_type) { if (h) h->err = "mtd_set_cells: bad arguments"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    COPY_IN(h->c.cell_type, cell_type, (size_t)n);
+    COPY_IN(h->c.cell_indid, cell_indid, sizeof(int16_t) * (size_t)n);
+    if (mem == MTD_MEM_HOST) CK(cudaStreamSynchronize(h->stream));
+    h->have_cells = true;
+    return MTD_OK;
+}
+
+extern "C" int mtd_set_static(mtd_handle h, int64_t n, const int8_t *age_bracket, const int8_t *epi_age_bracket,
+                              const double *soc_rate, const int32_t *res_cellid, int mem)
+{
+    if (!h || n != h->c.n_agents) { if (h) h->err = "mtd_set_static: n != n_agents"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    COPY_IN(h->c.age_bracket, age_bracket, (size_t)n);
+    COPY_IN(h->c.epi_age_bracket, epi_age_bracket, (size_t)n);
+    COPY_IN(h->c.soc_rate, soc_rate, sizeof(double) * (size_t)n);
+    COPY_IN(h->c.res_cellid, res_cellid, sizeof(int32_t) * (size_t)n);
+    if (mem == MTD_MEM_HOST) CK(cudaStreamSynchronize(h->stream));
+    h->have_static = true;
+    return MTD_OK;
+}
+
+extern "C" int mtd_set_state(mtd_handle h, int64_t n, const int8_t *seir, const int8_t *inf_type, const int8_t *inf_sev,
+                             const int32_t *last_dose_day, const int32_t *sched, const uint8_t *sched_cnt,
+                             const int32_t *test_day, const int32_t *test_result_day, const int32_t *quarantine,
+                             const int32_t *hosp, int mem)
+{
+    if (!h || n != h->c.n_agents) { if (h) h->err = "mtd_set_state: n != n_agents"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    size_t N = (size_t)n;
+    COPY_IN(h->c.seir, seir, N); COPY_IN(h->c.inf_type, inf_type, N); COPY_IN(h->c.inf_sev, inf_sev, N);
+    COPY_IN(h->c.last_dose_day, last_dose_day, 4 * N);
+    COPY_IN(h->c.sched, sched, 4 * N * MTD_MAXSCHED); COPY_IN(h->c.sched_cnt, sched_cnt, N);
+    COPY_IN(h->c.test_day, test_day, 8 * N); COPY_IN(h->c.test_result_day, test_result_day, 8 * N);
+    COPY_IN(h->c.quarantine, quarantine, 12 * N); COPY_IN(h->c.hosp, hosp, 12 * N);
+    if (mem == MTD_MEM_HOST) CK(cudaStreamSynchronize(h->stream));
+    return MTD_OK;
+}
+
+extern "C" int mtd_get_state(mtd_handle h, int64_t n, int8_t *seir, int8_t *inf_type, int8_t *inf_sev, int32_t *sched,
+                             uint8_t *sched_cnt, int32_t *test_day, int32_t *test_result_day, int32_t *quarantine,
+                             int32_t *hosp, int mem)
+{
+    if (!h || n != h->c.n_agents) { if (h) h->err = "mtd_get_state: n != n_agents"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    size_t N = (size_t)n;
+    COPY_OUT(seir, h->c.seir, N); COPY_OUT(inf_type, h->c.inf_type, N); COPY_OUT(inf_sev, h->c.inf_sev, N);
+    COPY_OUT(sched, h->c.sched, 4 * N * MTD_MAXSCHED); COPY_OUT(sched_cnt, h->c.sched_cnt, N);
+    COPY_OUT(test_day, h->c.test_day, 8 * N); COPY_OUT(test_result_day, h->c.test_result_day, 8 * N);
+    COPY_OUT(quarantine, h->c.quarantine, 12 * N); COPY_OUT(hosp, h->c.hosp, 12 * N);
+    CK(cudaStreamSynchronize(h->stream));
+    return MTD_OK;
+}
+
+template <typename T>
+static int tape_up(mtd_handle h, const T **dst, const T *src, size_t n)
+{
+    void *q = nullptr;
+    cudaError_t e = cudaMalloc(&q, std::max<size_t>(n, 1) * sizeof(T));
+    if (e != cudaSuccess) { h->err = std::string("cudaMalloc(tape): ") + cudaGetErrorString(e); return MTD_E_CUDA; }
+    h->tape_allocs.push_back(q);
+    if (n) {
+        e = cudaMemcpyAsync(q, src, n * sizeof(T), cudaMemcpyHostToDevice, h->stream);
+        if (e != cudaSuccess) { h->err = std::string("cudaMemcpy(tape): ") + cudaGetErrorString(e); return MTD_E_CUDA; }
+    }
+    *dst = (const T *)q;
+    return 0;
+}
+
+extern "C" int mtd_set_tape(mtd_handle h, const mtd_tape *t)
+{
+    if (!h) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    free_tape(h);
+    if (!t) return MTD_OK;
+    DevTape &d = h->c.tape;
+    d.n_sel = t->n_sel; d.n_pair = t->n_pair; d.n_expo = t->n_expo;
+    int r;
+    if ((r = tape_up(h, &d.sel_key, t->sel_key, (size_t)t->n_sel))) return r;
+    if ((r = tape_up(h, &d.sel_off, t->sel_off, (size_t)t->n_sel + 1))) return r;
+    size_t npick = t->n_sel ? (size_t)t->sel_off[t->n_sel] : 0;
+    if ((r = tape_up(h, &d.sel_picks, t->sel_picks, npick))) return r;
+    if ((r = tape_up(h, &d.pair_k1, t->pair_k1, (size_t)t->n_pair))) return r;
+    if ((r = tape_up(h, &d.pair_k2, t->pair_k2, (size_t)t->n_pair))) return r;
+    if ((r = tape_up(h, &d.pair_u, t->pair_u, (size_t)t->n_pair))) return r;
+    if ((r = tape_up(h, &d.expo_agent, t->expo_agent, (size_t)t->n_expo))) return r;
+    if ((r = tape_up(h, &d.expo_row, t->expo_row, (size_t)t->n_expo * MTD_EXPO_W))) return r;
+    CK(cudaStreamSynchronize(h->stream));
+    return MTD_OK;
+}
+
+extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, int64_t M, const int32_t *iv_agent,
+                                            const int32_t *iv_cell, const uint8_t *iv_start, const uint8_t *iv_end,
+                                            const uint32_t *iv_order, int mem)
+{
+    if (!h || !day || M < 0) return MTD_E_ARG;
+    if (!(h->have_params && h->have_cells && h->have_static)) { h->err = "params / cells / static not set"; return MTD_E_STATE; }
+    if (M > h->c.cap_intervals) { h->err = "interval stream exceeds max_intervals"; return MTD_E_CAPACITY; }
+    if (day->mode == MTD_MODE_REPLAY && M > 0 && h->c.tape.sel_key == nullptr) { h->err = "replay mode without a tape"; return MTD_E_STATE; }
+    CK(cudaSetDevice(h->cfg.device));
+    DevCtx &c = h->c;
+    c.day = *day;
+    c.M = M;
+    if (mem == MTD_MEM_HOST) {
+        size_t m = (size_t)M;
+        CK(cudaMemcpyAsync(h->d_iv_agent, iv_agent, 4 * m, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->d_iv_cell, iv_cell, 4 * m, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->d_iv_start, iv_start, m, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->d_iv_end, iv_end, m, cudaMemcpyHostToDevice, h->stream));
+        if (iv_order) CK(cudaMemcpyAsync(h->d_iv_order, iv_order, 4 * m, cudaMemcpyHostToDevice, h->stream));
+        c.iv_agent = h->d_iv_agent; c.iv_cell = h->d_iv_cell; c.iv_start = h->d_iv_start; c.iv_end = h->d_iv_end;
+        c.iv_order = iv_order ? h->d_iv_order : nullptr;
+    } else {
+        c.iv_agent = iv_agent; c.iv_cell = iv_cell; c.iv_start = iv_start; c.iv_end = iv_end; c.iv_order = iv_order;
+    }
+    CK(cudaMemsetAsync(c.ctr, 0, sizeof(DevCounters), h->stream));
+    CK(cudaMemsetAsync(c.cell_count, 0, sizeof(int32_t) * (size_t)c.n_cells, h->stream));
+    CK(cudaMemsetAsync(c.cell_first, 0xff, sizeof(uint32_t) * (size_t)c.n_cells, h->stream));
+    launch_k0(c, h->scan_tmp, h->stream, h->sm_count);
+    launch_k1(c, h->stream, h->sm_count);
+    launch_scan_nrows(c, h->scan_tmp, h->stream);
+    launch_k2_compact(c, h->stream, h->sm_count);
+    CK(cudaGetLastError());
+    h->day_ready = true;
+    return MTD_OK;
+}
+
+extern "C" int mtd_simulate_direct_contacts(mtd_handle h, const mtd_day *day, int32_t *delta_buf, int64_t cap, int apply)
+{
+    if (!h || !day) return MTD_E_ARG;
+    if (!h->day_ready) { h->err = "mtd_simulate_direct_contacts before mtd_simulate_contact_network"; return MTD_E_STATE; }
+    CK(cudaSetDevice(h->cfg.device));
+    DevCtx &c = h->c;
+    c.day = *day;
+    int32_t *buf = delta_buf ? delta_buf : h->delta_own;
+    int64_t cp = delta_buf ? cap : c.cap_expo;
+    if (cp <= 0) { h->err = "delta buffer capacity must be positive"; return MTD_E_ARG; }
+    launch_k3_eval(c, buf, cp, h->stream, h->sm_count);
+    if (apply) launch_k3_apply(c, buf, 1, cp, false, h->expo_list, h->stream, h->sm_count);
+    CK(cudaGetLastError());
+    return MTD_OK;
+}
+
+extern "C" int mtd_apply_deltas(mtd_handle h, const int32_t *bufs, int64_t n_bufs, int64_t cap)
+{
+    if (!h || !bufs || n_bufs <= 0 || cap <= 0) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    launch_k3_apply(h->c, bufs, (int)n_bufs, cap, true, h->expo_list, h->stream, h->sm_count);
+    CK(cudaGetLastError());
+    return MTD_OK;
+}
+
+extern "C" int mtd_advance_seir(mtd_handle h, int32_t day, const uint8_t *mask, int mem)
+{
+    if (!h) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    const uint8_t *dm = mask;
+    if (mask && mem == MTD_MEM_HOST) {
+        CK(cudaMemcpyAsync(h->d_mask, mask, (size_t)h->c.n_agents, cudaMemcpyHostToDevice, h->stream));
+        dm = h->d_mask;
+    }
+    launch_k4(h->c, day, dm, h->stream, h->sm_count);
+    CK(cudaGetLastError());
+    return MTD_OK;
+}
+
+extern "C" int mtd_sync(mtd_handle h)
+{
+    if (!h) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    return MTD_OK;
+}
+
+extern "C" int mtd_get_counters(mtd_handle h, mtd_counters *out)
+{
+    if (!h || !out) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    DevCounters d;
+    CK(cudaMemcpyAsync(&d, h->c.ctr, sizeof(d), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    memset(out, 0, sizeof(*out));
+    out->n_slots = d.n_slots; out->n_rows = d.n_rows; out->n_exposed = d.n_applied;
+    out->pairs_evaluated = (int64_t)d.pairs_evaluated; out->n_potential = (int64_t)d.n_potential;
+    out->n_si_rows = d.n_si_rows; out->sched_overflow = d.sched_overflow; out->tape_miss = d.tape_miss;
+    for (int k = 0; k < 4; k++) out->class_cells[k] = d.class_cells[k];
+    out->error = d.error;
+    if (d.error) {
+        char buf[256];
+        snprintf(buf, sizeof(buf), "device error %d (rows needed %llu of %lld scratch / %d of %lld dense, list %llu of %lld)",
+                 d.error, d.row_bound_total, (long long)h->c.cap_scratch_rows, d.n_rows, (long long)h->c.cap_rows,
+                 d.list_total, (long long)h->c.cap_list);
+        h->err = buf;
+        return d.error;
+    }
+    return MTD_OK;
+}
+
+extern "C" int mtd_get_contacts(mtd_handle h, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap,
+                                int64_t *n, int mem)
+{
+    if (!h || !n) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    DevCounters d;
+    CK(cudaMemcpyAsync(&d, h->c.ctr, sizeof(d), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    *n = d.n_rows;
+    if (d.n_rows > cap) { h->err = "mtd_get_contacts: cap too small"; return MTD_E_CAPACITY; }
+    if (d.n_rows == 0) return MTD_OK;
+    if (mem == MTD_MEM_DEVICE) {
+        launch_export_rows(h->c, rows5, row_dur, row_cell, cap, h->stream);
+        CK(cudaGetLastError());
+        return MTD_OK;
+    }
+    int32_t *t5 = nullptr, *td = nullptr, *tc = nullptr;
+    size_t R = (size_t)d.n_rows;
+    CK(cudaMalloc((void **)&t5, R * 5 * 4)); CK(cudaMalloc((void **)&td, R * 4)); CK(cudaMalloc((void **)&tc, R * 4));
+    launch_export_rows(h->c, t5, td, tc, (int64_t)R, h->stream);
+    if (rows5) cudaMemcpyAsync(rows5, t5, R * 5 * 4, cudaMemcpyDeviceToHost, h->stream);
+    if (row_dur) cudaMemcpyAsync(row_dur, td, R * 4, cudaMemcpyDeviceToHost, h->stream);
+    if (row_cell) cudaMemcpyAsync(row_cell, tc, R * 4, cudaMemcpyDeviceToHost, h->stream);
+    cudaError_t e = cudaStreamSynchronize(h->stream);
+    cudaFree(t5); cudaFree(td); cudaFree(tc);
+    if (e != cudaSuccess) { h->err = cudaGetErrorString(e); return MTD_E_CUDA; }
+    return MTD_OK;
+}
+
+extern "C" int mtd_get_exposed(mtd_handle h, int32_t *agent_ids, int64_t cap, int64_t *n, int mem)
+{
+    if (!h || !n) return MTD_E_ARG;
+    if (mem != MTD_MEM_HOST) { h->err = "mtd_get_exposed: host buffers only"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    DevCounters d;
+    CK(cudaMemcpyAsync(&d, h->c.ctr, sizeof(d), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    int64_t cnt = std::min<int64_t>(d.n_applied, h->c.cap_expo);
+    *n = cnt;
+    if (cnt > cap) { h->err = "mtd_get_exposed: cap too small"; return MTD_E_CAPACITY; }
+    std::vector<unsigned long long> tmp((size_t)cnt * 2);
+    if (cnt) CK(cudaMemcpy(tmp.data(), h->expo_list, sizeof(unsigned long long) * 2 * (size_t)cnt, cudaMemcpyDeviceToHost));
+    std::vector<std::pair<unsigned long long, int32_t>> v((size_t)cnt);
+    for (int64_t i = 0; i < cnt; i++) v[(size_t)i] = { tmp[2 * i], (int32_t)tmp[2 * i + 1] };
+    std::sort(v.begin(), v.end());          // order key = (cell order, row order): the reference's order of exposure
+    for (int64_t i = 0; i < cnt; i++) agent_ids[i] = v[(size_t)i].second;
+    return MTD_OK;
+}
+
+extern "C" int mtd_get_infection_prob(mtd_handle h, double *p, int64_t cap, int mem)
+{
+    // enables per-row probability capture on first use: call once with p == NULL before the day step to switch it on
+    if (!h) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    if (!h->c.row_p) {
+        double *rp; DA(rp, h->c.cap_rows); h->c.row_p = rp;
+        if (!p) return MTD_OK;
+        h->err = "probability capture was off during the last step"; return MTD_E_STATE;
+    }
+    if (!p) return MTD_OK;
+    DevCounters d;
+    CK(cudaMemcpyAsync(&d, h->c.ctr, sizeof(d), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (d.n_rows > cap) { h->err = "mtd_get_infection_prob: cap too small"; return MTD_E_CAPACITY; }
+    CK(cudaMemcpyAsync(p, h->c.row_p, sizeof(double) * (size_t)d.n_rows, kind_out(mem), h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return MTD_OK;
+}
+
+extern "C" int mtd_occupancy(mtd_handle h, int64_t out[6])
+{
+    if (!h || !out) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    launch_occupancy(h->c, h->occ, h->stream, h->sm_count);
+    unsigned long long t[6];
+    CK(cudaMemcpyAsync(t, h->occ, sizeof(t), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    for (int k = 0; k < 6; k++) out[k] = (int64_t)t[k];
+    return MTD_OK;
+}

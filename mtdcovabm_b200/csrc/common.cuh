@@ -1,0 +1,169 @@
+// mtdcovabm_b200/csrc/common.cuh -- shared device structures and helpers (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/mtd_b200.h"
+
+#define MTD_NUM_CLASSES 4
+#define FULLMASK 0xffffffffu
+
+// enums of the reference (epidemiologyclasses.py, cellsclasses.py)
+enum { S_UNDEF = 0, S_SUS = 1, S_EXP = 2, S_INF = 3, S_REC = 4, S_DEC = 5 };
+enum { IT_UNDEF = 0, IT_PREASYMP = 1, IT_PRESYMP = 2, IT_ASYMP = 3, IT_SYMP = 4 };
+enum { SV_UNDEF = 0, SV_MILD = 1, SV_SEVERE = 2, SV_CRITICAL = 3 };
+enum { T_EXP_INF = 0, T_INF_SYMP = 1, T_SYMP_SEV = 2, T_SEV_CRI = 3, T_CRI_DEATH = 4, T_ASYMP_REC = 5,
+       T_MILD_REC = 6, T_SEV_REC = 7, T_CRI_REC = 8, T_REC_SUS = 9 };
+enum { CT_HOUSEHOLD = 0, CT_WORKPLACE = 1, CT_ACCOM = 2, CT_HOSPITAL = 3, CT_ENTERTAINMENT = 4, CT_SCHOOL = 5,
+       CT_CLASSROOM = 6, CT_INSTITUTION = 7, CT_TRANSPORT = 8, CT_RELIGION = 9, CT_AIRPORT = 10 };
+enum { SCT_RESIDENCE = 0, SCT_WORKPLACE = 1, SCT_SCHOOL = 2, SCT_COMMUNITY = 3 };
+enum { SITE_SELECT = 1, SITE_PAIR = 2, SITE_EXPO = 3, SITE_TRACE = 4 };
+
+// device-side counters of one day step (copied to mtd_counters by mtd_get_counters)
+struct DevCounters {
+    unsigned long long pairs_evaluated;
+    unsigned long long n_potential;
+    unsigned long long list_total;      // total adjacency-list scratch entries requested
+    unsigned long long row_bound_total; // total scratch rows requested
+    int n_slots;
+    int n_rows;
+    int n_succ;                          // successful S-I draws (before winner resolution)
+    int n_delta;                         // delta records produced locally
+    int n_applied;                       // exposures applied
+    int n_si_rows;
+    int sched_overflow;
+    int tape_miss;
+    int class_cells[MTD_NUM_CLASSES];
+    int class_cursor[MTD_NUM_CLASSES];   // work-fetch cursors of the persistent K1 warps
+    int error;
+    int pad;
+};
+
+// one CSR record of the cell -> interval layout (16 B, one vector load)
+struct __align__(16) IvRec {
+    int32_t agent;
+    uint32_t order;      // emission index (position in the day's stream)
+    uint32_t se;         // start | end << 8
+    uint32_t pad;
+};
+
+// one dense contact row (16 B)
+struct __align__(16) RowRec {
+    int32_t a1, a2;
+    uint32_t sed;        // start | end << 8 | duration << 16
+    int32_t slot;        // active-cell slot (cell id = slot_cell[slot])
+};
+
+struct DevTape {
+    int64_t n_sel;  const uint64_t *sel_key;  const int32_t *sel_off;  const int32_t *sel_picks;
+    int64_t n_pair; const uint64_t *pair_k1;  const uint32_t *pair_k2; const double *pair_u;
+    int64_t n_expo; const int32_t *expo_agent; const double *expo_row;
+};
+
+// everything a kernel needs, passed by value
+struct DevCtx {
+    // capacities
+    int64_t n_agents, n_cells, cap_intervals, cap_rows, cap_scratch_rows, cap_list, cap_expo;
+    // day
+    mtd_day day;
+    DevTape tape;
+    // static
+    const int8_t *cell_type; const int16_t *cell_indid;
+    const int8_t *age_bracket; const int8_t *epi_age_bracket; const double *soc_rate; const int32_t *res_cellid;
+    // state
+    int8_t *seir; int8_t *inf_type; int8_t *inf_sev; int32_t *last_dose_day;
+    int32_t *sched; uint8_t *sched_cnt; int32_t *test_day; int32_t *test_result_day; int32_t *quarantine; int32_t *hosp;
+    // day inputs
+    int64_t M;
+    const int32_t *iv_agent; const int32_t *iv_cell; const uint8_t *iv_start; const uint8_t *iv_end;
+    const uint32_t *iv_order;
+    // K0 products
+    int32_t *cell_count;       // [n_cells]
+    uint32_t *cell_first;      // [n_cells] emission index of first record
+    int32_t *slot_of_cell;     // [n_cells]
+    int32_t *flag_scan;        // [M+1] scan of "first record of its cell" flags
+    int32_t *slot_cell;        // [slots]
+    int32_t *slot_m;           // [slots]
+    uint32_t *slot_first;      // [slots] order key of the cell
+    int32_t *slot_cursor;      // [slots]
+    int64_t *slot_off;         // [slots+1] CSR offsets
+    int64_t *slot_rowoff;      // [slots+1] scratch-row offsets
+    int64_t *slot_listoff;     // [slots+1] adjacency-list scratch offsets (u16 entries)
+    int32_t *slot_rowbound;    // [slots]
+    int64_t *slot_listneed;    // [slots]
+    int32_t *slot_nrows;       // [slots] rows produced
+    int64_t *slot_denseoff;    // [slots+1]
+    int32_t *class_list;       // [MTD_NUM_CLASSES][slots cap]
+    int64_t class_stride;
+    IvRec *csr;                // [M]
+    // K1 products
+    RowRec *scratch_rows;      // [cap_scratch_rows]
+    uint16_t *lists;           // [cap_list]
+    RowRec *rows;              // [cap_rows] dense
+    // K3
+    unsigned long long *win;   // [n_agents] winner key per agent
+    int32_t *succ;             // [cap_rows] dense row indices of successful draws
+    double *row_p;             // [cap_rows] optional infection probability per row (NULL = off)
+    int32_t *delta;            // [cap_expo][MTD_DELTA_WORDS]
+    DevCounters *ctr;
+    const mtd_params *P;       // device copy of the parameters
+    IvRec *csr_sorted;         // [M] CSR records in list (emission) order within each cell, written by K1
+};
+
+
+// ---------------------------------------------------------------- Philox4x32-10
+__host__ __device__ __forceinline__ void philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                                    uint32_t k1, uint32_t out[4])
+{
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+#ifdef __CUDA_ARCH__
+        uint32_t h0 = __umulhi(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
+        uint32_t h1 = __umulhi(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
+#else
+        uint64_t p0 = (uint64_t)0xD2511F53u * c0, p1 = (uint64_t)0xCD9E8D57u * c2;
+        uint32_t h0 = (uint32_t)(p0 >> 32), l0 = (uint32_t)p0, h1 = (uint32_t)(p1 >> 32), l1 = (uint32_t)p1;
+#endif
+        uint32_t n0 = h1 ^ c1 ^ k0, n2 = h0 ^ c3 ^ k1;
+        c0 = n0; c1 = l1; c2 = n2; c3 = l0;
+        k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+__device__ __forceinline__ double u53(uint32_t a, uint32_t b)
+{
+    return ((double)(a >> 5) * 67108864.0 + (double)(b >> 6)) / 9007199254740992.0;
+}
+
+// contactnetwork.py:317-347
+__device__ __forceinline__ int activity_of_celltype(int ct, int indid)
+{
+    if (indid == 9 && ct != CT_ACCOM) return 5;
+    switch (ct) {
+    case CT_HOUSEHOLD: case CT_ACCOM: case CT_INSTITUTION: return 1;
+    case CT_WORKPLACE: return 3;
+    case CT_HOSPITAL: case CT_ENTERTAINMENT: case CT_RELIGION: case CT_AIRPORT: return 5;
+    case CT_SCHOOL: return 2;
+    case CT_TRANSPORT: return 4;
+    default: return 0;   // Classroom -> "total" column (reference quirk)
+    }
+}
+
+// util.py:239-268
+__host__ __device__ __forceinline__ int simcelltype_of(int ct)
+{
+    switch (ct) {
+    case CT_HOUSEHOLD: case CT_ACCOM: case CT_INSTITUTION: return SCT_RESIDENCE;
+    case CT_WORKPLACE: return SCT_WORKPLACE;
+    case CT_SCHOOL: case CT_CLASSROOM: return SCT_SCHOOL;
+    default: return SCT_COMMUNITY;
+    }
+}
+
+__device__ __forceinline__ uint32_t lanemask_lt()
+{
+    uint32_t m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+

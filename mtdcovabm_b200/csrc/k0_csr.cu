@@ -1,0 +1,199 @@
+// K0 -- CSR cell -> interval layout of one day's emission stream (replaces the dict-of-lists
+// vars_util.cells_agents_timesteps filled at itinerary.py:1446-1452).
+//   hist     : per-cell interval count + first emission index (atomics)
+//   flags    : record is the first of its cell  -> exclusive scan = slot rank (dict order of the cells)
+//   assign   : slot tables, size class lists, per-slot scratch needs
+//   scans    : CSR offsets, scratch-row offsets, adjacency-list offsets
+//   scatter  : records into their cell segment (unordered; K1 restores list order by emission index)
+#include "common.cuh"
+
+#define SCAN_TILE 2048
+#define SCAN_THREADS 256
+
+template <typename TIn>
+__global__ void scan_reduce_kernel(const TIn *in, int64_t n_max, const int *n_dev, long long *block_sums)
+{
+    int64_t n = n_dev ? min((int64_t)*n_dev, n_max) : n_max;
+    int64_t base = (int64_t)blockIdx.x * SCAN_TILE;
+    long long s = 0;
+    for (int k = threadIdx.x; k < SCAN_TILE; k += SCAN_THREADS) {
+        int64_t i = base + k;
+        if (i < n) s += (long long)in[i];
+    }
+    __shared__ long long sh[SCAN_THREADS / 32];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(FULLMASK, s, o);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        long long t = 0;
+        for (int w = 0; w < SCAN_THREADS / 32; w++) t += sh[w];
+        block_sums[blockIdx.x] = t;
+    }
+}
+
+__global__ void scan_sums_kernel(long long *block_sums, int64_t n_blocks)
+{
+    // single block: exclusive scan of block_sums in place
+    __shared__ long long sh[SCAN_THREADS];
+    __shared__ long long carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int64_t base = 0; base < n_blocks; base += SCAN_THREADS) {
+        int64_t i = base + threadIdx.x;
+        long long v = (i < n_blocks) ? block_sums[i] : 0;
+        sh[threadIdx.x] = v;
+        __syncthreads();
+        for (int o = 1; o < SCAN_THREADS; o <<= 1) {
+            long long t = (threadIdx.x >= o) ? sh[threadIdx.x - o] : 0;
+            __syncthreads();
+            sh[threadIdx.x] += t;
+            __syncthreads();
+        }
+        long long incl = sh[threadIdx.x];
+        if (i < n_blocks) block_sums[i] = carry + incl - v;
+        __syncthreads();
+        if (threadIdx.x == SCAN_THREADS - 1) carry += incl;
+        __syncthreads();
+    }
+}
+
+template <typename TIn, typename TOut>
+__global__ void scan_apply_kernel(const TIn *in, TOut *out, int64_t n_max, const int *n_dev, const long long *block_sums)
+{
+    // exclusive scan; out[n] receives the total.  Elements past n are not written.
+    int64_t n = n_dev ? min((int64_t)*n_dev, n_max) : n_max;
+    int64_t base = (int64_t)blockIdx.x * SCAN_TILE;
+    if (base > n) return;
+    constexpr int PER = SCAN_TILE / SCAN_THREADS;
+    long long v[PER];
+    long long s = 0;
+    int64_t i0 = base + (int64_t)threadIdx.x * PER;
+#pragma unroll
+    for (int k = 0; k < PER; k++) { v[k] = (i0 + k < n) ? (long long)in[i0 + k] : 0; s += v[k]; }
+    // block exclusive scan of s
+    __shared__ long long sh[SCAN_THREADS / 32];
+    long long incl = s;
+    int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int o = 1; o < 32; o <<= 1) { long long t = __shfl_up_sync(FULLMASK, incl, o); if (lane >= o) incl += t; }
+    if (lane == 31) sh[w] = incl;
+    __syncthreads();
+    long long woff = 0;
+    for (int k = 0; k < w; k++) woff += sh[k];
+    long long run = block_sums[blockIdx.x] + woff + incl - s;
+#pragma unroll
+    for (int k = 0; k < PER; k++) {
+        if (i0 + k <= n) out[i0 + k] = (TOut)run;   // element n gets the grand total
+        run += v[k];
+    }
+}
+
+template <typename TIn, typename TOut>
+static void device_scan(const TIn *in, TOut *out, int64_t n_max, const int *n_dev, long long *block_sums, cudaStream_t st)
+{
+    int64_t nb = (n_max + 1 + SCAN_TILE - 1) / SCAN_TILE;   // +1: the total lands at out[n]
+    scan_reduce_kernel<TIn><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, n_max, n_dev, block_sums);
+    scan_sums_kernel<<<1, SCAN_THREADS, 0, st>>>(block_sums, nb);
+    scan_apply_kernel<TIn, TOut><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, out, n_max, n_dev, block_sums);
+}
+
+__device__ __forceinline__ uint32_t order_of(const DevCtx &c, int64_t i) { return c.iv_order ? c.iv_order[i] : (uint32_t)i; }
+
+__global__ void k0_hist_kernel(DevCtx c)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < c.M; i += (int64_t)gridDim.x * blockDim.x) {
+        int cell = c.iv_cell[i];
+        if (cell < 0 || cell >= c.n_cells) { c.ctr->error = MTD_E_ARG; continue; }
+        atomicAdd(&c.cell_count[cell], 1);
+        atomicMin(&c.cell_first[cell], order_of(c, i));
+    }
+}
+
+__global__ void k0_flags_kernel(DevCtx c)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < c.M; i += (int64_t)gridDim.x * blockDim.x) {
+        int cell = c.iv_cell[i];
+        int f = 0;
+        if (cell >= 0 && cell < c.n_cells) f = (c.cell_first[cell] == order_of(c, i));
+        c.flag_scan[i] = f;
+    }
+}
+
+__device__ __forceinline__ int size_class(int m) { return m <= 32 ? 0 : (m <= 128 ? 1 : (m <= 320 ? 2 : 3)); }
+
+__global__ void k0_assign_kernel(DevCtx c, const int32_t *flags_excl)
+{
+    // flags_excl: exclusive scan of the first-of-cell flags, [M+1]
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < c.M; i += (int64_t)gridDim.x * blockDim.x) {
+        if (i == 0) c.ctr->n_slots = flags_excl[c.M];
+        if (flags_excl[i + 1] == flags_excl[i]) continue;
+        int slot = flags_excl[i];
+        int cell = c.iv_cell[i];
+        int m = c.cell_count[cell];
+        c.slot_of_cell[cell] = slot;
+        c.slot_cell[slot] = cell;
+        c.slot_m[slot] = m;
+        c.slot_first[slot] = order_of(c, i);
+        c.slot_cursor[slot] = 0;
+        c.slot_nrows[slot] = 0;
+        if (m > MTD_MAX_CELL_INTERVALS) { c.ctr->error = MTD_E_CELL_TOO_LARGE; m = 0; }
+        int ct = c.cell_type[cell];
+        int indid = (ct == CT_WORKPLACE && c.cell_indid) ? c.cell_indid[cell] : -1;
+        long long k = c.P->k_by_act[activity_of_celltype(ct, indid)];
+        // rows <= sum(deg)/2, sum(deg) <= max(k*n, S) + n/2 with n <= m; and rows <= m(m-1)/2
+        long long b1 = (long long)m * (m - 1) / 2, b2 = (k * m + m / 2 + 2) / 2 + 1;
+        c.slot_rowbound[slot] = (int)(b1 < b2 ? b1 : b2);
+        c.slot_listneed[slot] = (m > 32) ? (int64_t)m * (m - 1) : 0;
+        int cls = size_class(m);
+        int idx = atomicAdd(&c.ctr->class_cells[cls], 1);
+        c.class_list[(int64_t)cls * c.class_stride + idx] = slot;
+    }
+}
+
+__global__ void k0_check_kernel(DevCtx c)
+{
+    int n = c.ctr->n_slots;
+    c.ctr->row_bound_total = (unsigned long long)c.slot_rowoff[n];
+    c.ctr->list_total = (unsigned long long)c.slot_listoff[n];
+    if (c.slot_rowoff[n] > c.cap_scratch_rows || c.slot_listoff[n] > c.cap_list) c.ctr->error = MTD_E_CAPACITY;
+}
+
+__global__ void k0_scatter_kernel(DevCtx c)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < c.M; i += (int64_t)gridDim.x * blockDim.x) {
+        int cell = c.iv_cell[i];
+        if (cell < 0 || cell >= c.n_cells) continue;
+        int slot = c.slot_of_cell[cell];
+        int p = atomicAdd(&c.slot_cursor[slot], 1);
+        IvRec r;
+        r.agent = c.iv_agent[i];
+        r.order = order_of(c, i);
+        r.se = (uint32_t)c.iv_start[i] | ((uint32_t)c.iv_end[i] << 8);
+        r.pad = 0;
+        c.csr[c.slot_off[slot] + p] = r;
+    }
+}
+
+void launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count)
+{
+    if (c.M <= 0) return;
+    int threads = 256;
+    int64_t want = (c.M + threads - 1) / threads;
+    unsigned grid = (unsigned)(want < (int64_t)sm_count * 16 ? want : (int64_t)sm_count * 16);
+    k0_hist_kernel<<<grid, threads, 0, st>>>(c);
+    k0_flags_kernel<<<grid, threads, 0, st>>>(c);
+    device_scan<int32_t, int32_t>(c.flag_scan, c.flag_scan, c.M, nullptr, scan_tmp, st);
+    k0_assign_kernel<<<grid, threads, 0, st>>>(c, c.flag_scan);
+    int64_t slots_max = c.M < c.n_cells ? c.M : c.n_cells;
+    device_scan<int32_t, int64_t>(c.slot_m, c.slot_off, slots_max, &c.ctr->n_slots, scan_tmp, st);
+    device_scan<int32_t, int64_t>(c.slot_rowbound, c.slot_rowoff, slots_max, &c.ctr->n_slots, scan_tmp, st);
+    device_scan<int64_t, int64_t>(c.slot_listneed, c.slot_listoff, slots_max, &c.ctr->n_slots, scan_tmp, st);
+    k0_check_kernel<<<1, 1, 0, st>>>(c);
+    k0_scatter_kernel<<<grid, threads, 0, st>>>(c);
+}
+
+void launch_scan_nrows(const DevCtx &c, long long *scan_tmp, cudaStream_t st)
+{
+    if (c.M <= 0) return;
+    int64_t slots_max = c.M < c.n_cells ? c.M : c.n_cells;
+    device_scan<int32_t, int64_t>(c.slot_nrows, c.slot_denseoff, slots_max, &c.ctr->n_slots, scan_tmp, st);
+}

@@ -1,0 +1,58 @@
+// K2 -- dense contact rows in the reference's order (contactnetwork.py:79-105): cells in dict order (slot order),
+// rows of a cell in creation order.  K1 wrote each cell's rows into its own scratch segment; here they are packed.
+#include "common.cuh"
+
+__global__ void k2_compact_kernel(DevCtx c)
+{
+    const int lane = threadIdx.x & 31;
+    const int n_slots = c.ctr->n_slots;
+    const int64_t total = c.slot_denseoff[n_slots];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        c.ctr->n_rows = (int)(total < c.cap_rows ? total : c.cap_rows);
+        if (total > c.cap_rows) c.ctr->error = MTD_E_CAPACITY;
+    }
+    const int warps = (gridDim.x * blockDim.x) >> 5;
+    for (int s0 = (((int)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; s0 < n_slots; s0 += warps * 32) {
+        int s = s0 + lane;
+        int cnt = 0; int64_t src = 0, dst = 0;
+        if (s < n_slots) { cnt = c.slot_nrows[s]; src = c.slot_rowoff[s]; dst = c.slot_denseoff[s]; }
+        uint32_t have = __ballot_sync(FULLMASK, cnt > 0);
+        while (have) {
+            int l = __ffs(have) - 1;
+            have &= have - 1;
+            int n = __shfl_sync(FULLMASK, cnt, l);
+            int64_t sb = __shfl_sync(FULLMASK, src, l), db = __shfl_sync(FULLMASK, dst, l);
+            for (int r = lane; r < n; r += 32)
+                if (db + r < c.cap_rows) c.rows[db + r] = c.scratch_rows[sb + r];
+        }
+    }
+}
+
+// rows -> the reference's 5-int layout [simcelltype, a1, a2, start, end] (+ duration, cell id)
+__global__ void k2_export_kernel(DevCtx c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap)
+{
+    int64_t n = c.ctr->n_rows;
+    if (n > cap) n = cap;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        RowRec r = c.rows[i];
+        int cell = c.slot_cell[r.slot];
+        if (rows5) {
+            rows5[5 * i + 0] = simcelltype_of(c.cell_type[cell]);
+            rows5[5 * i + 1] = r.a1; rows5[5 * i + 2] = r.a2;
+            rows5[5 * i + 3] = (int)(r.sed & 0xff); rows5[5 * i + 4] = (int)((r.sed >> 8) & 0xff);
+        }
+        if (row_dur) row_dur[i] = (int)(r.sed >> 16);
+        if (row_cell) row_cell[i] = cell;
+    }
+}
+
+void launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count)
+{
+    k2_compact_kernel<<<sm_count * 8, 256, 0, st>>>(c);
+}
+
+void launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap,
+                        cudaStream_t st)
+{
+    k2_export_kernel<<<148 * 4, 256, 0, st>>>(c, rows5, row_dur, row_cell, cap);
+}

@@ -1,0 +1,358 @@
+// K3 -- transmission (Epidemiology.simulate_direct_contacts, epidemiology.py:88-231), whole-trajectory sampling
+// at exposure time (simulate_seir_state_transition, epidemiology.py:233-500) and the scheduling it triggers
+// (schedule_hospitalisation :647-660, schedule_test :502-565, schedule_quarantine :568-625).
+// K4 -- daily SEIR advance (seirstateutil.update_agent_state, seirstateutil.py:38-72, table :105-136).
+//
+// The reference walks the day's contact rows sequentially; a newly exposed agent is not susceptible for later rows
+// (epidemiology.py:94,221).  Here every S-I row is evaluated independently with a draw keyed by the row, and the
+// earliest successful row (atomicMin on an order key) wins -- identical to the sequential result because draws are
+// keyed, not positional (SURVEY.md section 7 "within-day visibility").  The winners' trajectories are written as
+// fixed-size delta records straight into the buffer that is exchanged between GPUs; every rank then applies all
+// records to its replicated per-agent state.
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ void vacc_multipliers(const mtd_params *P, int last, int day, double &imm, double &asym)
+{   // util.calculate_vaccination_multipliers, util.py:117-150
+    imm = 1.0; asym = 1.0;
+    if (last == MTD_NONE) return;
+    int d = day - last;
+    if (d == 0) { imm = 1.0 - P->vacc_immunity; asym = 1.0 - P->vacc_asymptomatic; return; }
+    double x = (double)d / P->vacc_decay_interval;
+    if (x < 1) x = 1;
+    imm = 1.0 - pow(P->vacc_immunity, x);
+    asym = 1.0 - pow(P->vacc_asymptomatic, x);
+}
+
+__device__ __forceinline__ long long tape_find_pair(const DevTape &T, int cell, int a1, int a2)
+{
+    uint64_t k1 = ((uint64_t)(uint32_t)cell << 32) | (uint32_t)a1;
+    uint32_t k2 = (uint32_t)a2;
+    long long lo = 0, hi = T.n_pair;
+    while (lo < hi) {
+        long long mid = (lo + hi) >> 1;
+        if (T.pair_k1[mid] < k1 || (T.pair_k1[mid] == k1 && T.pair_k2[mid] < k2)) lo = mid + 1; else hi = mid;
+    }
+    return (lo < T.n_pair && T.pair_k1[lo] == k1 && T.pair_k2[lo] == k2) ? lo : -1;
+}
+
+__device__ __forceinline__ long long tape_find_expo(const DevTape &T, int agent)
+{
+    long long lo = 0, hi = T.n_expo;
+    while (lo < hi) { long long mid = (lo + hi) >> 1; if (T.expo_agent[mid] < agent) lo = mid + 1; else hi = mid; }
+    return (lo < T.n_expo && T.expo_agent[lo] == agent) ? lo : -1;
+}
+
+__device__ __forceinline__ unsigned long long row_key(const DevCtx &c, const RowRec &r, int64_t i)
+{
+    return ((unsigned long long)c.slot_first[r.slot] << 32) | (unsigned long long)(uint32_t)i;
+}
+
+// one thread per dense contact row
+__global__ void k3_eval_kernel(DevCtx c)
+{
+    const int64_t n = c.ctr->n_rows;
+    const mtd_params *P = c.P;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        RowRec r = c.rows[i];
+        int s1 = c.seir[r.a1], s2 = c.seir[r.a2];
+        bool si = (s1 == S_INF && s2 == S_SUS) || (s1 == S_SUS && s2 == S_INF);        // epidemiology.py:106-107
+        int dur = (int)(r.sed >> 16);
+        if (!si || dur <= 0) { if (c.row_p) c.row_p[i] = __longlong_as_double(0x7ff8000000000000LL); continue; }
+        int ex = (s1 == S_SUS) ? r.a1 : r.a2;
+        int cell = c.slot_cell[r.slot];
+        int sct = simcelltype_of(c.cell_type[cell]);
+        double base;                                                                    // epidemiology.py:998-1014
+        if (sct == SCT_RESIDENCE) base = P->p_household;
+        else if (sct == SCT_WORKPLACE) base = (cell == c.res_cellid[ex]) ? P->p_workplace : P->p_community;
+        else if (sct == SCT_SCHOOL) base = P->p_school;
+        else base = P->p_community;
+        double lg = log((double)dur);
+        double mult = lg > 1.0 ? lg : 1.0;                                              // max(1, math.log(duration))
+        double imm, asym;
+        vacc_multipliers(P, c.last_dose_day[ex], c.day.day, imm, asym);
+        double susc = P->probs_by_age[0][c.epi_age_bracket[ex]];
+        double p = base * (mult * susc * (1 - c.day.mhd) * imm);                        // epidemiology.py:196
+        if (c.row_p) c.row_p[i] = p;
+        atomicAdd(&c.ctr->n_si_rows, 1);
+        double u;
+        if (c.day.mode == MTD_MODE_REPLAY) {
+            long long t = tape_find_pair(c.tape, cell, r.a1, r.a2);
+            if (t < 0) continue;                 // the reference never evaluated this row (agent already exposed)
+            u = c.tape.pair_u[t];
+        } else {
+            uint32_t w[4];
+            philox4x32((uint32_t)c.day.day, (uint32_t)cell, (uint32_t)r.a1, (uint32_t)r.a2, c.day.seed, SITE_PAIR, w);
+            u = u53(w[0], w[1]);
+        }
+        if (u < p) {
+            atomicMin(&c.win[ex], row_key(c, r, i));
+            int idx = atomicAdd(&c.ctr->n_succ, 1);
+            c.succ[idx] = (int32_t)i;
+        }
+    }
+}
+
+struct Draws {
+    const DevCtx *c; int agent; const double *row; int miss;
+    __device__ double uniform(int slot)
+    {
+        if (c->day.mode == MTD_MODE_REPLAY) {
+            if (!row || isnan(row[slot])) { miss++; return 1.0; }
+            return row[slot];
+        }
+        uint32_t w[4];
+        philox4x32((uint32_t)c->day.day, (uint32_t)agent, (uint32_t)slot, 0u, c->day.seed, SITE_EXPO, w);
+        return u53(w[0], w[1]);
+    }
+    __device__ int lognormal_days(int slot, double mu, double sigma)
+    {   // util.sample_log_normal(..., isInt=True): np.random.lognormal then round (util.py:88-115)
+        if (c->day.mode == MTD_MODE_REPLAY) {
+            if (!row || isnan(row[slot])) { miss++; return 0; }
+            return (int)row[slot];
+        }
+        uint32_t w[4];
+        philox4x32((uint32_t)c->day.day, (uint32_t)agent, (uint32_t)slot, 0u, c->day.seed, SITE_EXPO, w);
+        double u1 = u53(w[0], w[1]), u2 = u53(w[2], w[3]);
+        double z = sqrt(-2.0 * log(1.0 - u1)) * cos(6.283185307179586 * u2);
+        return (int)rint(exp(mu + sigma * z));
+    }
+    __device__ int timestep_option(int slot)
+    {   // np.random.choice(np.arange(42, 121)) (epidemiology.py:84)
+        if (c->day.mode == MTD_MODE_REPLAY) {
+            if (!row || isnan(row[slot])) { miss++; return 42; }
+            return (int)row[slot];
+        }
+        uint32_t w[4];
+        philox4x32((uint32_t)c->day.day, (uint32_t)agent, (uint32_t)slot, 0u, c->day.seed, SITE_EXPO, w);
+        return 42 + (int)__umulhi(w[0], 79u);
+    }
+};
+
+// one thread per successful draw; only the winner of each agent samples the trajectory
+__global__ void k3_trajectory_kernel(DevCtx c, int32_t *dbuf, int64_t cap)
+{
+    const int n = c.ctr->n_succ;
+    const mtd_params *P = c.P;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+        const int64_t i = c.succ[t];
+        RowRec r = c.rows[i];
+        const int ex = (c.seir[r.a1] == S_SUS) ? r.a1 : r.a2;
+        const unsigned long long key = row_key(c, r, i);
+        if (c.win[ex] != key) continue;
+        const int cell = c.slot_cell[r.slot];
+        Draws D; D.c = &c; D.agent = ex; D.row = nullptr; D.miss = 0;
+        if (c.day.mode == MTD_MODE_REPLAY) {
+            long long e = tape_find_expo(c.tape, ex);
+            if (e >= 0) D.row = c.tape.expo_row + e * MTD_EXPO_W; else D.miss++;
+        }
+        // sampled_exposed_timestep = np.random.choice(overlapping_timesteps) (epidemiology.py:246)
+        int ts = 0;
+        if (c.day.mode == MTD_MODE_REPLAY) ts = (D.row && !isnan(D.row[0])) ? (int)D.row[0] : 0;
+        else {
+            uint32_t w[4];
+            philox4x32((uint32_t)c.day.day, (uint32_t)ex, 0u, 0u, c.day.seed, SITE_EXPO, w);
+            int idx = (int)__umulhi(w[0], (uint32_t)(r.sed >> 16));
+            // flattened overlap list of key (a1, a2): a1's intervals (outer) x a2's (inner), list order
+            const int64_t b = c.slot_off[r.slot];
+            const int m = c.slot_m[r.slot];
+            bool done = false;
+            for (int p = 0; p < m && !done; p++) {
+                IvRec ra = c.csr_sorted[b + p];
+                if (ra.agent != r.a1) continue;
+                int sa = ra.se & 0xff, ea = (ra.se >> 8) & 0xff;
+                for (int q = 0; q < m; q++) {
+                    IvRec rb = c.csr_sorted[b + q];
+                    if (rb.agent != r.a2) continue;
+                    int lo = max(sa, (int)(rb.se & 0xff)), hi = min(ea, (int)((rb.se >> 8) & 0xff));
+                    if (lo > hi) continue;
+                    int len = hi - lo + 1;
+                    if (idx < len) { ts = lo + idx; done = true; break; }
+                    idx -= len;
+                }
+            }
+        }
+        double imm, asym;
+        vacc_multipliers(P, c.last_dose_day[ex], c.day.day, imm, asym);
+        const int b = c.epi_age_bracket[ex];
+        const int current_day = c.day.day;
+        int incr = current_day;
+        int32_t rec[MTD_DELTA_WORDS];
+#pragma unroll
+        for (int k = 0; k < MTD_DELTA_WORDS; k++) rec[k] = 0;
+        int ns = 0;
+        int32_t sched[6];
+#define STEP(T) do { incr += D.lognormal_days(1 + (T), P->ln_mu[T], P->ln_sigma[T]); \
+                     if (incr >= current_day && ns < 6) sched[ns++] = (int32_t)(((uint32_t)incr << 16) | ((uint32_t)(T) << 8) | (uint32_t)ts); } while (0)
+        int symptomatic_day = -1, recovered = 0, start_hosp = MTD_NONE, end_hosp = MTD_NONE, inf_type;
+        STEP(T_EXP_INF);
+        if (D.uniform(11) < P->probs_by_age[1][b] * asym) {
+            inf_type = IT_PRESYMP;
+            STEP(T_INF_SYMP); symptomatic_day = incr;
+            if (D.uniform(12) < P->probs_by_age[2][b]) {
+                STEP(T_SYMP_SEV); start_hosp = incr;
+                if (D.uniform(13) < P->probs_by_age[3][b]) {
+                    STEP(T_SEV_CRI);
+                    if (D.uniform(14) < P->probs_by_age[4][b]) { STEP(T_CRI_DEATH); end_hosp = incr; }
+                    else { STEP(T_CRI_REC); end_hosp = incr; recovered = 1; }
+                } else { STEP(T_SEV_REC); end_hosp = incr; recovered = 1; }
+            } else { STEP(T_MILD_REC); recovered = 1; }
+        } else {
+            inf_type = IT_PREASYMP;
+            STEP(T_ASYMP_REC); recovered = 1;
+        }
+        if (recovered) STEP(T_REC_SUS);
+#undef STEP
+        int test_day = MTD_NONE, test_ts = 0, tres_day = MTD_NONE;
+        if (symptomatic_day > -1) {
+            int tts = D.timestep_option(15);                                            // epidemiology.py:480
+            if (c.day.testing_enabled && c.test_day[2 * (int64_t)ex] == MTD_NONE) {     // schedule_test :502-565
+                if (D.uniform(16) < P->testing_after_symptoms_probability) {
+                    test_day = symptomatic_day + D.lognormal_days(17, P->test_mu, P->test_sigma);
+                    test_ts = tts;
+                    tres_day = test_day + D.lognormal_days(18, P->result_mu, P->result_sigma);
+                }
+            }
+            (void)D.timestep_option(19);                                                // epidemiology.py:496
+            // schedule_quarantine(Symptomatic) draws one uniform; its result is overwritten by the caller with the
+            // value read before the call (epidemiology.py:206,216) -> no state change, only the draw is consumed.
+            if (c.day.quarantine_enabled) (void)D.uniform(20);
+        }
+        if (D.miss) atomicAdd(&c.ctr->tape_miss, D.miss);
+        rec[0] = ex; rec[1] = (int32_t)(uint32_t)key; rec[2] = (int32_t)(uint32_t)(key >> 32);
+        rec[3] = inf_type | (ns << 8);
+        for (int k = 0; k < ns; k++) rec[4 + k] = sched[k];
+        rec[10] = test_day; rec[11] = test_ts; rec[12] = tres_day; rec[13] = test_ts;
+        rec[14] = start_hosp; rec[15] = ts; rec[16] = end_hosp;
+        int slot = atomicAdd(&dbuf[0], 1);          // record 0 is the header: word 0 = number of records
+        if (slot < cap) {
+            int4 *dst = (int4 *)(dbuf + (int64_t)(slot + 1) * MTD_DELTA_WORDS);
+#pragma unroll
+            for (int k = 0; k < MTD_DELTA_WORDS / 4; k++) dst[k] = make_int4(rec[4 * k], rec[4 * k + 1], rec[4 * k + 2], rec[4 * k + 3]);
+        } else c.ctr->error = MTD_E_CAPACITY;
+    }
+}
+
+// resolution across ranks: earliest key per agent over all gathered records
+__global__ void k3_resolve_kernel(DevCtx c, const int32_t *bufs, int n_bufs, int64_t cap)
+{
+    for (int bi = 0; bi < n_bufs; bi++) {
+        const int32_t *buf = bufs + (int64_t)bi * (cap + 1) * MTD_DELTA_WORDS;
+        int n = buf[0]; if (n > cap) n = (int)cap;
+        for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+            const int32_t *rec = buf + (int64_t)(t + 1) * MTD_DELTA_WORDS;
+            unsigned long long key = ((unsigned long long)(uint32_t)rec[2] << 32) | (uint32_t)rec[1];
+            atomicMin(&c.win[rec[0]], key);
+        }
+    }
+}
+
+__global__ void k3_apply_kernel(DevCtx c, const int32_t *bufs, int n_bufs, int64_t cap, unsigned long long *expo_list)
+{
+    for (int bi = 0; bi < n_bufs; bi++) {
+        const int32_t *buf = bufs + (int64_t)bi * (cap + 1) * MTD_DELTA_WORDS;
+        int n = buf[0]; if (n > cap) n = (int)cap;
+        for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+            const int32_t *rec = buf + (int64_t)(t + 1) * MTD_DELTA_WORDS;
+            const int ag = rec[0];
+            unsigned long long key = ((unsigned long long)(uint32_t)rec[2] << 32) | (uint32_t)rec[1];
+            if (c.win[ag] != key) continue;
+            int ns = (rec[3] >> 8) & 0xff;
+            int cnt = c.sched_cnt[ag];
+            for (int k = 0; k < ns; k++) {            // agent_state_transition_by_day.append(...)
+                if (cnt < MTD_MAXSCHED) c.sched[(int64_t)ag * MTD_MAXSCHED + cnt++] = rec[4 + k];
+                else atomicAdd(&c.ctr->sched_overflow, 1);
+            }
+            c.sched_cnt[ag] = (uint8_t)cnt;
+            c.seir[ag] = S_EXP; c.inf_type[ag] = (int8_t)(rec[3] & 0xff); c.inf_sev[ag] = SV_UNDEF;   // :219-225
+            if (rec[10] != MTD_NONE) {
+                c.test_day[2 * (int64_t)ag] = rec[10]; c.test_day[2 * (int64_t)ag + 1] = rec[11];
+                c.test_result_day[2 * (int64_t)ag] = rec[12]; c.test_result_day[2 * (int64_t)ag + 1] = rec[13];
+            }
+            if (rec[14] != MTD_NONE) {                // schedule_hospitalisation keeps an earlier start day (:651-658)
+                int32_t *h = c.hosp + 3 * (int64_t)ag;
+                if (h[0] == MTD_NONE) h[0] = rec[14];
+                h[1] = rec[15]; h[2] = rec[16];
+            }
+            int idx = atomicAdd(&c.ctr->n_applied, 1);
+            if (idx < c.cap_expo) { expo_list[2 * (int64_t)idx] = key; expo_list[2 * (int64_t)idx + 1] = (unsigned long long)ag; }
+        }
+    }
+}
+
+// seirstateutil.py:105-136
+__device__ __forceinline__ void transition(int seir, int it, int sv, int trans, int &ns, int &nt, int &nv)
+{
+    switch (trans) {
+    case T_EXP_INF:  ns = S_INF; nt = (it == IT_PREASYMP) ? IT_ASYMP : it; nv = SV_MILD; return;
+    case T_INF_SYMP: ns = IT_SYMP; /* reference quirk B1: InfectionType.Symptomatic (4) returned as the SEIR state */
+                     nt = (it == IT_PRESYMP) ? IT_SYMP : it; nv = sv; return;
+    case T_SYMP_SEV: ns = seir; nt = it; nv = SV_SEVERE; return;
+    case T_SEV_CRI:  ns = seir; nt = it; nv = SV_CRITICAL; return;
+    case T_CRI_DEATH: ns = S_DEC; nt = it; nv = sv; return;
+    case T_ASYMP_REC: case T_MILD_REC: case T_SEV_REC: case T_CRI_REC: ns = S_REC; nt = IT_UNDEF; nv = SV_UNDEF; return;
+    case T_REC_SUS:  ns = S_SUS; nt = it; nv = sv; return;
+    default:         ns = S_UNDEF; nt = IT_UNDEF; nv = SV_UNDEF; return;
+    }
+}
+
+__global__ void k4_advance_kernel(DevCtx c, int day, const uint8_t *mask)
+{
+    for (int64_t ag = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; ag < c.n_agents; ag += (int64_t)gridDim.x * blockDim.x) {
+        int cnt = c.sched_cnt[ag];
+        if (cnt == 0) continue;
+        if (mask && !mask[ag]) continue;
+        int32_t *sc = c.sched + ag * MTD_MAXSCHED;
+        int today = -1;
+        for (int i = 0; i < cnt; i++) if ((sc[i] >> 16) == day) { today = i; break; }   // first entry dated today only
+        if (today < 0) continue;
+        int trans = (sc[today] >> 8) & 0xff;
+        int ns, nt, nv;
+        transition(c.seir[ag], c.inf_type[ag], c.inf_sev[ag], trans, ns, nt, nv);
+        c.seir[ag] = (int8_t)ns; c.inf_type[ag] = (int8_t)nt; c.inf_sev[ag] = (int8_t)nv;
+        for (int i = today; i + 1 < cnt; i++) sc[i] = sc[i + 1];                          // del list[today_index]
+        c.sched_cnt[ag] = (uint8_t)(cnt - 1);
+    }
+}
+
+__global__ void occupancy_kernel(DevCtx c, unsigned long long *out6)
+{
+    __shared__ unsigned int h[8];
+    if (threadIdx.x < 8) h[threadIdx.x] = 0;
+    __syncthreads();
+    for (int64_t ag = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; ag < c.n_agents; ag += (int64_t)gridDim.x * blockDim.x) {
+        int s = c.seir[ag];
+        if (s >= 0 && s < 6) atomicAdd(&h[s], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < 6 && h[threadIdx.x]) atomicAdd(&out6[threadIdx.x], (unsigned long long)h[threadIdx.x]);
+}
+
+}  // namespace
+
+void launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, cudaStream_t st, int sm_count)
+{
+    cudaMemsetAsync(c.win, 0xff, sizeof(unsigned long long) * (size_t)c.n_agents, st);
+    cudaMemsetAsync(dbuf, 0, sizeof(int32_t) * MTD_DELTA_WORDS, st);
+    k3_eval_kernel<<<sm_count * 8, 256, 0, st>>>(c);
+    k3_trajectory_kernel<<<sm_count, 128, 0, st>>>(c, dbuf, cap);
+}
+
+void launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t cap, bool resolve,
+                     unsigned long long *expo_list, cudaStream_t st, int sm_count)
+{
+    if (resolve) k3_resolve_kernel<<<sm_count, 128, 0, st>>>(c, bufs, n_bufs, cap);
+    k3_apply_kernel<<<sm_count, 128, 0, st>>>(c, bufs, n_bufs, cap, expo_list);
+}
+
+void launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count)
+{
+    k4_advance_kernel<<<sm_count * 8, 256, 0, st>>>(c, day, mask);
+}
+
+void launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st, int sm_count)
+{
+    cudaMemsetAsync(out6, 0, 6 * sizeof(unsigned long long), st);
+    occupancy_kernel<<<sm_count * 4, 256, 0, st>>>(c, out6);
+}

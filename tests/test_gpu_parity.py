@@ -1,0 +1,134 @@
+"""GPU parity tests (run on the B200 box): the CUDA path, called through the C ABI, against
+ (1) the golden days recorded from the unmodified reference (replay mode: bit-exact rows, exposures, state), and
+ (2) the CPU oracle in Philox mode on the golden inputs and on tiled synthetic populations."""
+import numpy as np
+import pytest
+
+from mtdcovabm_b200 import capi
+from mtdcovabm_b200 import params as prm
+from oracle import mtd_oracle as mo
+from tests import helpers as H
+from tests.golden import golden_io as gio
+
+pytestmark = pytest.mark.gpu
+DAYS = list(gio.all_days())
+
+
+@pytest.mark.parametrize("name,day", DAYS)
+def test_replay_day_matches_reference(name, day):
+    z = gio.load_run(name)
+    P = prm.build_params(None, prm.load_json(gio.RUNS[name]))
+    g = gio.load_day(z, day)
+    h = H.make_handle(P, g.pre, g.cell_type, g.cell_indid, len(g.iv_cell) + 16)
+    H.set_tape(h, g.tape)
+    d = h.make_day(capi.MODE_REPLAY, g.day, g.mhd, g.testing_enabled, g.quarantine_enabled)
+    h.simulate_contact_network(d, g.iv_agent, g.iv_cell, g.iv_start, g.iv_end)
+    h.simulate_direct_contacts(d)
+    c = h.counters()
+    assert c.error == 0 and c.tape_miss == 0 and c.sched_overflow == 0
+    rows, dur, cell = h.get_contacts()
+    assert np.array_equal(rows, g.contacts)              # the reference's rows, element for element, in order
+    assert np.array_equal(h.get_exposed(), g.exposed_ids)
+    assert H.state_diff(h.get_state(), g.post) == []
+    h.close()
+
+
+def _oracle_day(P, mode, g_day, mhd, te, qe, seed, s, st):
+    ctx = mo.make_ctx(mode, g_day, mhd, te, qe, seed=seed)
+    rows, dur, rc, s1 = mo.contact_network(P, ctx, s["iv_cell"], s["iv_agent"], s["iv_start"], s["iv_end"],
+                                           s["cell_type"], s["cell_indid"], st)
+    exp, p, s2 = mo.transmission(P, ctx, s["iv_cell"], s["iv_agent"], s["iv_start"], s["iv_end"], s["cell_type"], rows,
+                                 dur, rc, st, want_p=True)
+    return rows, dur, rc, exp, p, s1
+
+
+@pytest.mark.parametrize("reps,agent_major,seed", [(1, False, 1), (1, True, 2), (8, True, 3), (64, True, 4)])
+def test_philox_matches_oracle_on_tiled_population(reps, agent_major, seed):
+    z = gio.load_run("ref_1k_seed6")
+    P = prm.build_params()
+    g = gio.load_day(z, 16)
+    s = H.tile_day(g, reps, agent_major=agent_major, seed=seed, infectious_frac=0.05)
+    st = s["state"]
+    h = H.make_handle(P, st, s["cell_type"], s["cell_indid"], len(s["iv_cell"]))
+    h.enable_infection_prob()
+    d = h.make_day(capi.MODE_PHILOX, 16, 0.2, True, True, seed=seed)
+    h.simulate_contact_network(d, s["iv_agent"], s["iv_cell"], s["iv_start"], s["iv_end"])
+    h.simulate_direct_contacts(d)
+    c = h.counters()
+    assert c.error == 0
+    ost = st.copy()
+    rows, dur, rc, exp, p, s1 = _oracle_day(P, mo.MODE_PHILOX, 16, 0.2, True, True, seed, s, ost)
+    grows, gdur, gcell = h.get_contacts()
+    assert c.pairs_evaluated == s1.pairs_evaluated and c.n_potential == s1.n_potential
+    assert np.array_equal(grows, rows) and np.array_equal(gdur, dur) and np.array_equal(gcell, rc)
+    gp = h.get_infection_prob()
+    both = ~np.isnan(p)
+    # the sequential oracle skips rows of agents exposed earlier the same day; the GPU evaluates every S-I row
+    assert not np.any(np.isnan(gp) & both)
+    assert np.allclose(gp[both], p[both], rtol=1e-12, atol=0)       # north_star bar: 1e-6 relative
+    assert len(exp) > 0 and np.array_equal(h.get_exposed(), exp)
+    assert H.state_diff(h.get_state(), ost) == []
+    h.close()
+
+
+def test_seir_advance_matches_oracle():
+    z = gio.load_run("ref_1k_strict_seed7")
+    da = z["adv_day_agent"]; bo, b = z["adv_before_off"], z["adv_before"]
+    n = len(da)
+    st = mo.AgentState(n)
+    for i in range(n):
+        ent = b[bo[i]:bo[i + 1]]
+        st.sched_cnt[i] = len(ent)
+        for j, (dd, t, ts) in enumerate(ent):
+            st.sched[i, j] = mo.pack_sched(dd, t, ts)
+    st.seir[:] = z["adv_pre"][:, 0]; st.inf_type[:] = z["adv_pre"][:, 1]; st.inf_sev[:] = z["adv_pre"][:, 2]
+    h = H.make_handle(prm.build_params(), st, np.zeros(4, np.int8), np.full(4, -1, np.int16), 16)
+    for day in np.unique(da[:, 0]):
+        mask = (da[:, 0] == day).astype(np.uint8)
+        h.advance_seir(int(day), mask)
+        mo.advance(int(day), st, mask)
+    dev = h.get_state()
+    assert np.array_equal(np.stack([dev["seir"], dev["inf_type"], dev["inf_sev"]], 1), z["adv_post"])
+    assert H.state_diff(dev, st) == []
+    assert np.array_equal(h.occupancy(), np.bincount(st.seir, minlength=6)[:6])
+    h.close()
+
+
+def test_two_rank_cell_sharding_equals_single_rank():
+    """cells sharded over 2 handles on one device, delta buffers exchanged -> same state as the 1-rank run"""
+    import torch
+    z = gio.load_run("ref_1k_seed6")
+    P = prm.build_params()
+    g = gio.load_day(z, 20)
+    s = H.tile_day(g, 4, agent_major=True, seed=9, infectious_frac=0.08)
+    st = s["state"]
+    M = len(s["iv_cell"])
+    d_args = (capi.MODE_PHILOX, 20, 0.2, True, True)
+    h0 = H.make_handle(P, st, s["cell_type"], s["cell_indid"], M)
+    d = h0.make_day(*d_args, seed=5)
+    h0.simulate_contact_network(d, s["iv_agent"], s["iv_cell"], s["iv_start"], s["iv_end"])
+    h0.simulate_direct_contacts(d)
+    ref_state, ref_exp = h0.get_state(), h0.get_exposed()
+    ref_rows = h0.get_contacts()[0]
+    assert len(ref_exp) > 0
+    cap = 4096
+    bufs = torch.zeros((2, cap + 1, capi.DELTA_WORDS), dtype=torch.int32, device="cuda")
+    hs, nrows = [], 0
+    order = np.arange(M, dtype=np.uint32)
+    for r in range(2):
+        sel = (s["iv_cell"] % 2) == r
+        h = H.make_handle(P, st, s["cell_type"], s["cell_indid"], M)
+        h.simulate_contact_network(d, np.ascontiguousarray(s["iv_agent"][sel]), np.ascontiguousarray(s["iv_cell"][sel]),
+                                   np.ascontiguousarray(s["iv_start"][sel]), np.ascontiguousarray(s["iv_end"][sel]),
+                                   iv_order=np.ascontiguousarray(order[sel]))
+        h.simulate_direct_contacts(d, delta_buf=bufs[r], cap_records=cap, apply=False)
+        h.sync()
+        nrows += int(h.counters().n_rows)
+        hs.append(h)
+    assert nrows == len(ref_rows)
+    for h in hs:
+        h.apply_deltas(bufs, 2, cap)
+        assert H.state_diff(h.get_state(), type("S", (), ref_state | {"sched_cnt": ref_state["sched_cnt"]})) == []
+        assert np.array_equal(h.get_exposed(), ref_exp)
+        h.close()
+    h0.close()
