@@ -1,0 +1,359 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 contact-network + transmission + SEIR day step.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--agents A]
+
+One "step" = one simulated day of the hot path over a synthetic population (K4 SEIR advance, K0 CSR build,
+K1 per-cell contact network, K2 rows, K3 transmission + deltas [+ all-gather + apply when N > 1]).
+Workload (BASELINE.json configs[3], the configuration the metric's target is quoted on): 5M active agents =
+the reference's own 1k-agent itinerary streams tiled 5000x (mtdcovabm_b200/synth.py), cells sharded over the N
+ranks (strong scaling: the population is fixed, each rank owns 1/N of the cells), state replicated.
+
+Prints ONE JSON line (rank 0).  `value` = agent-contact pairs evaluated per second, whole job, inputs resident in
+HBM; `e2e` = the same through the public engine API with HOST buffers (H2D of the day's intervals and D2H of the
+contact rows + exposed ids inside the timed region).  `--impl reference` times the CPU oracle port of the reference
+path (the reference is pure Python and its sources do not travel to the GPU box) on all host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "agent_contact_pairs_per_s"
+UNIT = "pairs/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--agents", type=int, default=5_000_000, help="active agents of the synthetic population")
+    ap.add_argument("--cpu-sample-agents", type=int, default=0, help="agents of the CPU baseline sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--seed", type=int, default=0)
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """samples nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop = index, [], threading.Event()
+        self.t = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 7:
+                    self.rows.append(f)
+            except Exception:
+                pass
+            self.stop.wait(0.1)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.t.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "power_w_max": max(float(r[2]) for r in self.rows), "samples": len(self.rows)}
+
+
+# ------------------------------------------------------------------------------------------- CPU arm
+def cpu_day_numpy(bank, reps, k, seed):
+    """bank day k tiled `reps` times on the host (same construction as synth.SynthPopulation, numpy)"""
+    N1 = int(bank["n_agents"][0]); C1 = len(bank["cell_type"])
+    a1 = bank["d%d_iv_agent" % k].astype(np.int64); c1 = bank["d%d_iv_cell" % k].astype(np.int64)
+    M1 = len(a1)
+    r = np.repeat(np.arange(reps, dtype=np.int64), M1)
+    agent = np.tile(a1, reps) + r * N1
+    cell = (np.tile(c1, reps) + r * C1).astype(np.int32)
+    start = np.tile(bank["d%d_iv_start" % k], reps); end = np.tile(bank["d%d_iv_end" % k], reps)
+    rng = np.random.default_rng(1234 + seed)
+    perm = rng.permutation(N1 * reps)
+    agent = perm[agent]
+    o = np.argsort(agent, kind="stable")
+    return (agent[o].astype(np.int32), cell[o], start[o], end[o], perm)
+
+
+def cpu_oracle_run(args, steps, warmup, sample_agents):
+    """Times the CPU oracle port (oracle/mtd_oracle.c: contact network + transmission + SEIR advance) with one
+    worker thread per host core, cells partitioned over the workers like contactnetwork_mp.contactnetwork_parallel
+    (contactnetwork_mp.py:59-190).  -> dict(value pairs/s, cores, sample, ms_per_step)"""
+    from concurrent.futures import ThreadPoolExecutor
+    from mtdcovabm_b200 import params as prm, synth
+    from oracle import mtd_oracle as mo
+    bank = synth.load_bank()
+    P = prm.build_params()
+    N1 = int(bank["n_agents"][0])
+    n_present1 = int(bank["present"].sum())
+    reps = max(1, sample_agents // n_present1)
+    cores = os.cpu_count() or 1
+    nb = int(bank["n_days"])
+    days = []
+    for k in range(nb):
+        agent, cell, start, end, perm = cpu_day_numpy(bank, reps, k, args.seed)
+        part = (cell.astype(np.int64) * 2654435761 & 0xFFFFFFFF) >> 7
+        shards = []
+        for w in range(cores):
+            sel = (part % cores) == w
+            shards.append(tuple(np.ascontiguousarray(x[sel]) for x in (cell, agent, start, end)))
+        days.append(shards)
+    N = N1 * reps
+    st = mo.AgentState(N)
+    for name in ("age_bracket", "epi_age_bracket", "soc_rate"):
+        getattr(st, name)[perm] = np.tile(bank[name], reps)
+    present = np.zeros(N, bool); present[perm] = np.tile(bank["present"], reps)
+    rng = np.random.default_rng(99 + args.seed)
+    st.seir[:] = np.where(present, 1, 0)
+    inf = present & (rng.random(N) < 0.01)
+    st.seir[inf] = 3; st.inf_type[inf] = 3; st.inf_sev[inf] = 1
+    cell_type = np.tile(bank["cell_type"], reps); cell_indid = np.tile(bank["cell_indid"], reps)
+    mo.lib()
+
+    def worker(shard, day):
+        cell, agent, start, end = shard
+        ctx = mo.make_ctx(mo.MODE_PHILOX, day, 0.0, False, False, seed=args.seed)
+        rows, dur, rc, s1 = mo.contact_network(P, ctx, cell, agent, start, end, cell_type, cell_indid, st)
+        return rows, dur, rc, s1.pairs_evaluated, shard
+
+    total_pairs, t_total = 0, 0.0
+    with ThreadPoolExecutor(cores) as ex:
+        for step in range(warmup + steps):
+            day = 1 + step
+            shards = days[step % nb]
+            t0 = time.perf_counter()
+            mo.advance(day, st, None)
+            res = list(ex.map(lambda sh: worker(sh, day), shards))
+            # transmission mutates shared per-agent state: applied in partition order on one thread, like the
+            # reference's merge of the workers' results (daskutil.py:168)
+            ctx = mo.make_ctx(mo.MODE_PHILOX, day, 0.0, False, False, seed=args.seed)
+            for rows, dur, rc, _, (cell, agent, start, end) in res:
+                mo.transmission(P, ctx, cell, agent, start, end, cell_type, rows, dur, rc, st)
+            dt = time.perf_counter() - t0
+            if step >= warmup:
+                t_total += dt
+                total_pairs += sum(r[3] for r in res)
+    return dict(value=total_pairs / t_total, cores=cores, ms_per_step=1e3 * t_total / steps,
+                sample="%d active agents (%d replicas of the 1k itinerary bank), %d day-steps" % (n_present1 * reps, reps, steps),
+                agents=n_present1 * reps)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample = args.cpu_sample_agents or 200_000
+    r = cpu_oracle_run(args, max(1, args.steps), max(1, min(args.warmup, 2)), sample)
+    line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "int32+f64", "data": "synthetic",
+            "config": workload_config(args, r["agents"], None, None),
+            "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+                             "sample": r["sample"]},
+            "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, agents, intervals, cells):
+    return {"workload": "synthetic %d-agent population: reference 1k-agent itinerary bank tiled, ids shuffled, "
+                        "agent-major emission order (BASELINE.json configs[3])" % agents,
+            "agents": agents, "intervals_per_day": intervals, "cells": cells, "parallelism": "cells sharded x%d, state replicated" % args.gpus,
+            "rng": "philox4x32-10", "l2": "inputs larger than L2 (7 distinct day streams cycled)"}
+
+
+# ------------------------------------------------------------------------------------------- GPU arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from mtdcovabm_b200 import capi, engine, params as prm, synth
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the B200 path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    bank = synth.load_bank()
+    n_present1 = int(bank["present"].sum())
+    reps = max(1, round(args.agents / n_present1))
+    pop = synth.SynthPopulation(bank, reps, dev, seed=args.seed)
+    nb = pop.n_days
+    streams = [pop.stream(k, rank, world) for k in range(nb)]
+    max_m = max(len(s["iv_agent"]) for s in streams)
+    P = prm.build_params()
+    eng = engine.DayEngine(pop.n_agents, pop.n_cells, max_m + 16, P, device=local, rank=rank, world=world,
+                           seed=args.seed)
+    eng.set_population(pop)
+    h = eng.h
+
+    # calibration: the pairs a day's stream holds do not depend on the epidemic state -> count them once
+    pairs = []
+    d = h.make_day(capi.MODE_PHILOX, 1, 0.0, False, False, seed=args.seed)
+    for k in range(nb):
+        s = streams[k]
+        with torch.cuda.stream(eng.stream):
+            h.simulate_contact_network(d, s["iv_agent"], s["iv_cell"], s["iv_start"], s["iv_end"], iv_order=s["iv_order"],
+                                       mem=capi.MEM_DEVICE)
+        c = h.counters()
+        pairs.append((int(c.pairs_evaluated), int(c.n_rows), int(c.n_slots)))
+    eng.set_population(pop)          # reset the state
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # ---------------- device-resident timed loop
+    for step in range(args.warmup):
+        eng.step(1 + step, streams[step % nb])
+    barrier()
+    h.set_profiling(True)
+    stage_sum = {}
+    launches = 0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clocks:
+        ev0.record(eng.stream)
+        for step in range(args.warmup, args.warmup + args.steps):
+            eng.step(1 + step, streams[step % nb])
+        ev1.record(eng.stream)
+        barrier()
+    ms = allmax(ev0.elapsed_time(ev1))
+    local_pairs = sum(pairs[step % nb][0] for step in range(args.warmup, args.warmup + args.steps))
+    total_pairs = allsum(local_pairs)
+    value = total_pairs / (ms * 1e-3)
+    # per-stage device time of the last step + launches over the loop (events recorded on the engine's stream)
+    st_ms, st_launch = h.stage_ms()
+    launches = sum(st_launch.values())
+    last = (args.warmup + args.steps - 1) % nb
+    c = h.counters()
+
+    # roofline of the dominant kernel group (K1): algorithmic bytes = 10*M + 13*U + 12*D  
+    M_last = len(streams[last]["iv_agent"])
+    D_last = pairs[last][1]
+    U_last = 0.73 * M_last
+    k1_bytes = 10 * M_last + 13 * U_last + 12 * D_last
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    k1_ms = st_ms["k1_contacts"]
+    achieved = k1_bytes / (k1_ms * 1e-3) / 1e9 if k1_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": "k1_contacts (4 size-class launches)", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": "measured" if peaks else "fallback", "k1_ms": k1_ms, "stage_ms": st_ms,
+                "k1_pairs_per_s": pairs[last][0] / (k1_ms * 1e-3) if k1_ms > 0 else None}
+    h.set_profiling(False)
+
+    # ---------------- end to end: host buffers in, host results out, every step
+    e2e = None
+    if not args.no_e2e:
+        host = []
+        for s in streams:
+            hs = {k: (v.cpu().pin_memory() if v is not None else None) for k, v in s.items() if k != "n_total"}
+            host.append(hs)
+        cap_rows = max(p[1] for p in pairs) + 1024
+        rows_dev = torch.empty((cap_rows, 5), dtype=torch.int32, device=dev)
+        rows_host = torch.empty((cap_rows, 5), dtype=torch.int32).pin_memory()
+        h2d = d2h = 0
+        eng.set_population(pop)
+        for step in range(min(args.warmup, 2)):
+            eng.step(1 + step, host[step % nb], mem=capi.MEM_HOST)
+        barrier()
+        t0 = time.perf_counter()
+        for step in range(args.warmup, args.warmup + args.steps):
+            s = host[step % nb]
+            eng.step(1 + step, s, mem=capi.MEM_HOST)
+            with torch.cuda.stream(eng.stream):
+                n = h.get_contacts_device(rows_dev)
+                rows_host[:n].copy_(rows_dev[:n], non_blocking=True)
+            exposed = h.get_exposed()
+            occ = h.occupancy()
+            h2d += sum(v.numel() * v.element_size() for v in s.values() if v is not None)
+            d2h += n * 20 + exposed.nbytes + occ.nbytes
+        barrier()
+        e_ms = allmax((time.perf_counter() - t0) * 1e3)
+        e2e = {"value": total_pairs / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d // args.steps,
+               "d2h_bytes_per_step": d2h // args.steps, "ms_per_step": e_ms / args.steps,
+               "api": "engine.DayEngine.step(mem=HOST) + get_contacts + get_exposed + occupancy"}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        r = cpu_oracle_run(args, 3, 1, args.cpu_sample_agents or 200_000)
+        cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
+
+    if rank == 0:
+        agents = pop.n_present
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "int32+f64", "data": "synthetic",
+                "config": workload_config(args, agents, int(streams[0]["n_total"]), pop.n_cells),
+                "agent_days_per_s": agents * args.steps / (ms * 1e-3),
+                "pairs_per_day": total_pairs / args.steps, "contacts_per_day": allsum_rows(pairs, args, nb),
+                "exposed_last_day": int(c.n_exposed),
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
+                "clocks": clocks.summary()}
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def allsum_rows(pairs, args, nb):
+    return sum(pairs[step % nb][1] for step in range(args.warmup, args.warmup + args.steps)) / args.steps
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -142,6 +142,15 @@ int mtd_get_infection_prob(mtd_handle h, double *p, int64_t cap, int mem);   /* 
 int mtd_occupancy(mtd_handle h, int64_t out[6]);                 /* dynamicstatistics.py:169-193 */
 int mtd_sync(mtd_handle h);
 
+/* Measurement hooks (the reference's per-stage wall-clock columns, sim.py:231-244,1852-1856): with profiling on,
+ * CUDA events are recorded on the handle's stream around every stage of the day step; mtd_get_stage_ms
+ * synchronises and returns the device time of the LAST execution of each stage and the number of kernels the
+ * library launched since the previous call (per stage). */
+enum { MTD_STAGE_H2D = 0, MTD_STAGE_K0 = 1, MTD_STAGE_K1 = 2, MTD_STAGE_K2 = 3, MTD_STAGE_K3_EVAL = 4,
+       MTD_STAGE_K3_APPLY = 5, MTD_STAGE_K4 = 6, MTD_N_STAGES = 7 };
+int mtd_set_profiling(mtd_handle h, int on);
+int mtd_get_stage_ms(mtd_handle h, float ms[MTD_N_STAGES], int64_t launches[MTD_N_STAGES]);
+
 #ifdef __cplusplus
 }
 #endif

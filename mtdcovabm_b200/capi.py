@@ -20,7 +20,9 @@ DELTA_WORDS = 20
 EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mtd_set_params", "mtd_set_cells",
            "mtd_set_static", "mtd_set_state", "mtd_get_state", "mtd_set_tape", "mtd_simulate_contact_network",
            "mtd_simulate_direct_contacts", "mtd_apply_deltas", "mtd_advance_seir", "mtd_get_counters",
-           "mtd_get_contacts", "mtd_get_exposed", "mtd_get_infection_prob", "mtd_occupancy", "mtd_sync"]
+           "mtd_get_contacts", "mtd_get_exposed", "mtd_get_infection_prob", "mtd_occupancy", "mtd_sync",
+           "mtd_set_profiling", "mtd_get_stage_ms"]
+STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
 
 
 class Config(C.Structure):
@@ -178,11 +180,29 @@ class Handle:
     def sync(self):
         self._ck(self.lib.mtd_sync(self.h), "mtd_sync")
 
+    # ---- measurement hooks
+    def set_profiling(self, on=True):
+        self._ck(self.lib.mtd_set_profiling(self.h, int(on)), "mtd_set_profiling")
+
+    def stage_ms(self):
+        """-> ({stage: ms of its last execution}, {stage: kernels launched since the previous call})"""
+        ms = (C.c_float * len(STAGES))()
+        ln = (C.c_int64 * len(STAGES))()
+        self._ck(self.lib.mtd_get_stage_ms(self.h, ms, ln), "mtd_get_stage_ms")
+        return dict(zip(STAGES, [float(x) for x in ms])), dict(zip(STAGES, [int(x) for x in ln]))
+
     # ---- results
     def counters(self) -> Counters:
         c = Counters()
         self._ck(self.lib.mtd_get_counters(self.h, C.byref(c)), "mtd_get_counters")
         return c
+
+    def get_contacts_device(self, rows5, row_dur=None, row_cell=None):
+        """export the day's rows into caller-owned DEVICE tensors (int32 [cap,5], [cap], [cap]); -> row count"""
+        got = C.c_int64()
+        self._ck(self.lib.mtd_get_contacts(self.h, _ptr(rows5), _ptr(row_dur), _ptr(row_cell),
+                                           C.c_int64(rows5.shape[0]), C.byref(got), MEM_DEVICE), "mtd_get_contacts")
+        return int(got.value)
 
     def get_contacts(self):
         c = self.counters()

@@ -6,16 +6,17 @@
 #include <vector>
 #include "common.cuh"
 
-void launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count);
-void launch_k1(const DevCtx &c, cudaStream_t st, int sm_count);
-void launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count);
-void launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap, cudaStream_t st);
-void launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, cudaStream_t st, int sm_count);
-void launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t cap, bool resolve,
-                     unsigned long long *expo_list, cudaStream_t st, int sm_count);
-void launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count);
-void launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st, int sm_count);
-void launch_scan_nrows(const DevCtx &c, long long *scan_tmp, cudaStream_t st);
+// every launcher returns the number of kernels it launched
+int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count);
+int launch_k1(const DevCtx &c, cudaStream_t st, int sm_count);
+int launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count);
+int launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap, cudaStream_t st);
+int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, cudaStream_t st, int sm_count);
+int launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t cap, bool resolve,
+                    unsigned long long *expo_list, cudaStream_t st, int sm_count);
+int launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count);
+int launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st, int sm_count);
+int launch_scan_nrows(const DevCtx &c, long long *scan_tmp, cudaStream_t st);
 
 struct mtd_handle_s {
     mtd_config cfg;
@@ -37,6 +38,18 @@ struct mtd_handle_s {
     // replay tape (device copies)
     std::vector<void *> tape_allocs;
     bool have_params = false, have_cells = false, have_static = false, day_ready = false;
+    // measurement hooks
+    bool profiling = false;
+    cudaEvent_t ev[MTD_N_STAGES][2] = {};
+    bool ev_valid[MTD_N_STAGES] = {};
+    int64_t launches[MTD_N_STAGES] = {};
+};
+
+struct StageScope {     // records the stage's start/end events on the handle's stream when profiling is on
+    mtd_handle h; int stage;
+    StageScope(mtd_handle h_, int s) : h(h_), stage(s) { if (h->profiling) cudaEventRecord(h->ev[stage][0], h->stream); }
+    ~StageScope() { if (h->profiling) { cudaEventRecord(h->ev[stage][1], h->stream); h->ev_valid[stage] = true; } }
+    void add(int n) { h->launches[stage] += n; }
 };
 
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
@@ -142,6 +155,7 @@ extern "C" int mtd_destroy(mtd_handle h)
     cudaSetDevice(h->cfg.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_tape(h);
+    for (int s = 0; s < MTD_N_STAGES; s++) for (int k = 0; k < 2; k++) if (h->ev[s][k]) cudaEventDestroy(h->ev[s][k]);
     for (void *p : h->allocs) cudaFree(p);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -272,6 +286,7 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     c.day = *day;
     c.M = M;
     if (mem == MTD_MEM_HOST) {
+        StageScope sc(h, MTD_STAGE_H2D);
         size_t m = (size_t)M;
         CK(cudaMemcpyAsync(h->d_iv_agent, iv_agent, 4 * m, cudaMemcpyHostToDevice, h->stream));
         CK(cudaMemcpyAsync(h->d_iv_cell, iv_cell, 4 * m, cudaMemcpyHostToDevice, h->stream));
@@ -286,10 +301,10 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     CK(cudaMemsetAsync(c.ctr, 0, sizeof(DevCounters), h->stream));
     CK(cudaMemsetAsync(c.cell_count, 0, sizeof(int32_t) * (size_t)c.n_cells, h->stream));
     CK(cudaMemsetAsync(c.cell_first, 0xff, sizeof(uint32_t) * (size_t)c.n_cells, h->stream));
-    launch_k0(c, h->scan_tmp, h->stream, h->sm_count);
-    launch_k1(c, h->stream, h->sm_count);
-    launch_scan_nrows(c, h->scan_tmp, h->stream);
-    launch_k2_compact(c, h->stream, h->sm_count);
+    { StageScope sc(h, MTD_STAGE_K0); sc.add(launch_k0(c, h->scan_tmp, h->stream, h->sm_count)); }
+    { StageScope sc(h, MTD_STAGE_K1); sc.add(launch_k1(c, h->stream, h->sm_count)); }
+    { StageScope sc(h, MTD_STAGE_K2); sc.add(launch_scan_nrows(c, h->scan_tmp, h->stream));
+      sc.add(launch_k2_compact(c, h->stream, h->sm_count)); }
     CK(cudaGetLastError());
     h->day_ready = true;
     return MTD_OK;
@@ -305,8 +320,9 @@ extern "C" int mtd_simulate_direct_contacts(mtd_handle h, const mtd_day *day, in
     int32_t *buf = delta_buf ? delta_buf : h->delta_own;
     int64_t cp = delta_buf ? cap : c.cap_expo;
     if (cp <= 0) { h->err = "delta buffer capacity must be positive"; return MTD_E_ARG; }
-    launch_k3_eval(c, buf, cp, h->stream, h->sm_count);
-    if (apply) launch_k3_apply(c, buf, 1, cp, false, h->expo_list, h->stream, h->sm_count);
+    { StageScope sc(h, MTD_STAGE_K3_EVAL); sc.add(launch_k3_eval(c, buf, cp, h->stream, h->sm_count)); }
+    if (apply) { StageScope sc(h, MTD_STAGE_K3_APPLY);
+                 sc.add(launch_k3_apply(c, buf, 1, cp, false, h->expo_list, h->stream, h->sm_count)); }
     CK(cudaGetLastError());
     return MTD_OK;
 }
@@ -315,7 +331,8 @@ extern "C" int mtd_apply_deltas(mtd_handle h, const int32_t *bufs, int64_t n_buf
 {
     if (!h || !bufs || n_bufs <= 0 || cap <= 0) return MTD_E_ARG;
     CK(cudaSetDevice(h->cfg.device));
-    launch_k3_apply(h->c, bufs, (int)n_bufs, cap, true, h->expo_list, h->stream, h->sm_count);
+    { StageScope sc(h, MTD_STAGE_K3_APPLY);
+      sc.add(launch_k3_apply(h->c, bufs, (int)n_bufs, cap, true, h->expo_list, h->stream, h->sm_count)); }
     CK(cudaGetLastError());
     return MTD_OK;
 }
@@ -329,8 +346,34 @@ extern "C" int mtd_advance_seir(mtd_handle h, int32_t day, const uint8_t *mask, 
         CK(cudaMemcpyAsync(h->d_mask, mask, (size_t)h->c.n_agents, cudaMemcpyHostToDevice, h->stream));
         dm = h->d_mask;
     }
-    launch_k4(h->c, day, dm, h->stream, h->sm_count);
+    { StageScope sc(h, MTD_STAGE_K4); sc.add(launch_k4(h->c, day, dm, h->stream, h->sm_count)); }
     CK(cudaGetLastError());
+    return MTD_OK;
+}
+
+extern "C" int mtd_set_profiling(mtd_handle h, int on)
+{
+    if (!h) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    if (on && !h->ev[0][0])
+        for (int s = 0; s < MTD_N_STAGES; s++) { CK(cudaEventCreate(&h->ev[s][0])); CK(cudaEventCreate(&h->ev[s][1])); }
+    h->profiling = on != 0;
+    for (int s = 0; s < MTD_N_STAGES; s++) { h->ev_valid[s] = false; h->launches[s] = 0; }
+    return MTD_OK;
+}
+
+extern "C" int mtd_get_stage_ms(mtd_handle h, float ms[MTD_N_STAGES], int64_t launches[MTD_N_STAGES])
+{
+    if (!h || !ms) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    for (int s = 0; s < MTD_N_STAGES; s++) {
+        ms[s] = 0.f;
+        if (h->profiling && h->ev_valid[s]) CK(cudaEventElapsedTime(&ms[s], h->ev[s][0], h->ev[s][1]));
+        h->ev_valid[s] = false;
+        if (launches) launches[s] = h->launches[s];
+        h->launches[s] = 0;
+    }
     return MTD_OK;
 }
 

@@ -88,12 +88,13 @@ __global__ void scan_apply_kernel(const TIn *in, TOut *out, int64_t n_max, const
 }
 
 template <typename TIn, typename TOut>
-static void device_scan(const TIn *in, TOut *out, int64_t n_max, const int *n_dev, long long *block_sums, cudaStream_t st)
+static int device_scan(const TIn *in, TOut *out, int64_t n_max, const int *n_dev, long long *block_sums, cudaStream_t st)
 {
     int64_t nb = (n_max + 1 + SCAN_TILE - 1) / SCAN_TILE;   // +1: the total lands at out[n]
     scan_reduce_kernel<TIn><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, n_max, n_dev, block_sums);
     scan_sums_kernel<<<1, SCAN_THREADS, 0, st>>>(block_sums, nb);
     scan_apply_kernel<TIn, TOut><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, out, n_max, n_dev, block_sums);
+    return 3;
 }
 
 __device__ __forceinline__ uint32_t order_of(const DevCtx &c, int64_t i) { return c.iv_order ? c.iv_order[i] : (uint32_t)i; }
@@ -173,9 +174,9 @@ __global__ void k0_scatter_kernel(DevCtx c)
     }
 }
 
-void launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count)
+int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count)
 {
-    if (c.M <= 0) return;
+    if (c.M <= 0) return 0;
     int threads = 256;
     int64_t want = (c.M + threads - 1) / threads;
     unsigned grid = (unsigned)(want < (int64_t)sm_count * 16 ? want : (int64_t)sm_count * 16);
@@ -189,11 +190,12 @@ void launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_cou
     device_scan<int64_t, int64_t>(c.slot_listneed, c.slot_listoff, slots_max, &c.ctr->n_slots, scan_tmp, st);
     k0_check_kernel<<<1, 1, 0, st>>>(c);
     k0_scatter_kernel<<<grid, threads, 0, st>>>(c);
+    return 5 + 4 * 3;
 }
 
-void launch_scan_nrows(const DevCtx &c, long long *scan_tmp, cudaStream_t st)
+int launch_scan_nrows(const DevCtx &c, long long *scan_tmp, cudaStream_t st)
 {
-    if (c.M <= 0) return;
+    if (c.M <= 0) return 0;
     int64_t slots_max = c.M < c.n_cells ? c.M : c.n_cells;
-    device_scan<int32_t, int64_t>(c.slot_nrows, c.slot_denseoff, slots_max, &c.ctr->n_slots, scan_tmp, st);
+    return device_scan<int32_t, int64_t>(c.slot_nrows, c.slot_denseoff, slots_max, &c.ctr->n_slots, scan_tmp, st);
 }

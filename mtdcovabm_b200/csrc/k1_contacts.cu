@@ -482,11 +482,12 @@ void launch_class(const DevCtx &c, int cls, cudaStream_t st, int sm_count)
 
 }  // namespace
 
-void launch_k1(const DevCtx &c, cudaStream_t st, int sm_count)
+int launch_k1(const DevCtx &c, cudaStream_t st, int sm_count)
 {
     // big cells first: they are the long poles
     launch_class<1024, 1>(c, 3, st, sm_count);
     launch_class<320, 2>(c, 2, st, sm_count);
     launch_class<128, 4>(c, 1, st, sm_count);
     launch_class<32, 8>(c, 0, st, sm_count);
+    return 4;
 }

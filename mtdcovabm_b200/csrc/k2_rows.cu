@@ -46,13 +46,15 @@ __global__ void k2_export_kernel(DevCtx c, int32_t *rows5, int32_t *row_dur, int
     }
 }
 
-void launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count)
+int launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count)
 {
     k2_compact_kernel<<<sm_count * 8, 256, 0, st>>>(c);
+    return 1;
 }
 
-void launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap,
+int launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap,
                         cudaStream_t st)
 {
     k2_export_kernel<<<148 * 4, 256, 0, st>>>(c, rows5, row_dur, row_cell, cap);
+    return 1;
 }

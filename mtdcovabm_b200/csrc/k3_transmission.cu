@@ -331,28 +331,32 @@ __global__ void occupancy_kernel(DevCtx c, unsigned long long *out6)
 
 }  // namespace
 
-void launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, cudaStream_t st, int sm_count)
+int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, cudaStream_t st, int sm_count)
 {
     cudaMemsetAsync(c.win, 0xff, sizeof(unsigned long long) * (size_t)c.n_agents, st);
     cudaMemsetAsync(dbuf, 0, sizeof(int32_t) * MTD_DELTA_WORDS, st);
     k3_eval_kernel<<<sm_count * 8, 256, 0, st>>>(c);
     k3_trajectory_kernel<<<sm_count, 128, 0, st>>>(c, dbuf, cap);
+    return 2;
 }
 
-void launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t cap, bool resolve,
+int launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t cap, bool resolve,
                      unsigned long long *expo_list, cudaStream_t st, int sm_count)
 {
     if (resolve) k3_resolve_kernel<<<sm_count, 128, 0, st>>>(c, bufs, n_bufs, cap);
     k3_apply_kernel<<<sm_count, 128, 0, st>>>(c, bufs, n_bufs, cap, expo_list);
+    return resolve ? 2 : 1;
 }
 
-void launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count)
+int launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count)
 {
     k4_advance_kernel<<<sm_count * 8, 256, 0, st>>>(c, day, mask);
+    return 1;
 }
 
-void launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st, int sm_count)
+int launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st, int sm_count)
 {
     cudaMemsetAsync(out6, 0, 6 * sizeof(unsigned long long), st);
     occupancy_kernel<<<sm_count * 4, 256, 0, st>>>(c, out6);
+    return 1;
 }

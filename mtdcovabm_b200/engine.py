@@ -1,0 +1,80 @@
+"""Tensor-native day engine: the per-day sequence of the hot path over device-resident (or pinned-host) arrays.
+
+One engine = one rank = one GPU = one `capi.Handle` on one torch stream.  The order of a day follows the reference's
+day loop (sim.py:1392-2125): SEIR advance (seirstateutil.update_agent_state runs inside the itinerary stage at the
+start of the day, itinerary.py:399) -> contact network (contactnetwork.py:65) -> transmission (epidemiology.py:88).
+With `world > 1` cells are sharded over the ranks and the per-agent exposure deltas are exchanged once per day
+(the reference's stateful-actor strategy, actor_dist.py:491-518): K3 writes this rank's records
+straight into its slice of the gather buffer, one all-gather over NCCL, every rank applies all records to its replica
+of the per-agent state.
+
+torch is used for device memory, streams and torch.distributed only; every computation is a kernel of libmtd_b200.so.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import capi
+
+
+def exchange_deltas(gather: torch.Tensor, rank: int, group=None):
+    """one all-gather per day of the fixed-capacity delta slices: gather[r] <- rank r's records (in place: every
+    rank contributes gather[rank]).  Works on CUDA tensors over NCCL and on CPU tensors over gloo (tests)."""
+    torch.distributed.all_gather_into_tensor(gather, gather[rank].clone(), group=group)
+
+
+class DayEngine:
+    def __init__(self, n_agents, n_cells, max_intervals, params, device=0, rank=0, world=1, delta_cap=0,
+                 max_rows=0, mode=capi.MODE_PHILOX, seed=0, group=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("mtdcovabm_b200 needs a CUDA device: there is no CPU fallback for this path")
+        self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
+        self.rank, self.world, self.group = rank, world, group
+        self.mode, self.seed = mode, seed
+        self.stream = torch.cuda.Stream(self.device)
+        self.delta_cap = int(delta_cap) if delta_cap else max(4096, n_agents // 64)
+        self.h = capi.Handle(n_agents, n_cells, max_intervals, device=self.device.index or 0,
+                             stream=self.stream.cuda_stream, max_rows=max_rows, max_exposures=self.delta_cap)
+        self.h.set_params(params)
+        self.gather = None
+        if world > 1:
+            with torch.cuda.device(self.device):
+                self.gather = torch.zeros((world, self.delta_cap + 1, capi.DELTA_WORDS), dtype=torch.int32,
+                                         device=self.device)
+        self.n_agents, self.n_cells = n_agents, n_cells
+
+    # ---- population
+    def set_population(self, pop):
+        """pop: object with device tensors cell_type, cell_indid, age_bracket, epi_age_bracket, soc_rate, res_cellid,
+        seir, inf_type, inf_sev, sched, sched_cnt (e.g. synth.SynthPopulation)"""
+        D = capi.MEM_DEVICE
+        with torch.cuda.stream(self.stream):
+            self.h.set_cells(pop.cell_type, pop.cell_indid, mem=D)
+            self.h.set_static(pop.age_bracket, pop.epi_age_bracket, pop.soc_rate, pop.res_cellid, mem=D)
+            self.h.set_state(seir=pop.seir, inf_type=pop.inf_type, inf_sev=pop.inf_sev, sched=pop.sched,
+                             sched_cnt=pop.sched_cnt, mem=D)
+        self.h.sync()
+
+    # ---- one day
+    def step(self, day, s, mhd=0.0, testing=False, quarantine=False, mem=capi.MEM_DEVICE, n=None):
+        """s: dict(iv_agent, iv_cell, iv_start, iv_end, iv_order) -- device tensors (mem=MEM_DEVICE) or pinned host
+        tensors / numpy arrays (mem=MEM_HOST).  Enqueues the whole day on the engine's stream; returns nothing."""
+        h = self.h
+        d = h.make_day(self.mode, day, mhd, testing, quarantine, seed=self.seed)
+        with torch.cuda.stream(self.stream):
+            h.advance_seir(day, None)
+            h.simulate_contact_network(d, s["iv_agent"], s["iv_cell"], s["iv_start"], s["iv_end"],
+                                       iv_order=s.get("iv_order"), n=n if n is not None else len(s["iv_agent"]),
+                                       mem=mem)
+            if self.world == 1:
+                h.simulate_direct_contacts(d)
+            else:
+                h.simulate_direct_contacts(d, delta_buf=self.gather[self.rank], cap_records=self.delta_cap, apply=False)
+                exchange_deltas(self.gather, self.rank, self.group)
+                h.apply_deltas(self.gather, self.world, self.delta_cap)
+
+    def sync(self):
+        self.h.sync()
+
+    def close(self):
+        self.h.close()
