@@ -80,6 +80,8 @@ typedef struct {
 
 /* replay tape of one day (host pointers; sorted by key) */
 typedef struct {
+    /* selections: key = cell << 32 | main agent; sel_picks[sel_off[i] .. sel_off[i+1]) = the partner AGENT IDS the
+     * reference selected for that main agent, in order (contactnetwork.py:299) */
     int64_t n_sel;  const uint64_t *sel_key;  const int32_t *sel_off;  const int32_t *sel_picks;
     int64_t n_pair; const uint64_t *pair_k1;  const uint32_t *pair_k2; const double *pair_u;
     int64_t n_expo; const int32_t *expo_agent; const double *expo_row;
@@ -94,7 +96,7 @@ typedef struct {
     int64_t n_si_rows;           /* rows with exactly one Susceptible and one Infectious endpoint */
     int64_t sched_overflow;      /* schedule entries dropped (MTD_MAXSCHED reached) */
     int64_t tape_miss;           /* replay lookups without a record */
-    int64_t class_cells[4];      /* cells per size class (<=32, <=128, <=320, <=1024 intervals) */
+    int64_t class_cells[6];      /* cells per size class (<=8, <=16, <=32, <=128, <=320, <=1024 intervals) */
     int64_t error;               /* MTD_E_* raised on the device (capacity, cell too large) */
 } mtd_counters;
 

@@ -44,7 +44,7 @@ class Tape(C.Structure):
 class Counters(C.Structure):
     _fields_ = [("n_slots", C.c_int64), ("n_rows", C.c_int64), ("n_exposed", C.c_int64), ("pairs_evaluated", C.c_int64),
                 ("n_potential", C.c_int64), ("n_si_rows", C.c_int64), ("sched_overflow", C.c_int64),
-                ("tape_miss", C.c_int64), ("class_cells", C.c_int64 * 4), ("error", C.c_int64)]
+                ("tape_miss", C.c_int64), ("class_cells", C.c_int64 * 6), ("error", C.c_int64)]
 
 
 _lib = None

@@ -1,5 +1,6 @@
 // C ABI of libmtd_b200.so (include/mtd_b200.h): handle, device buffers, entry points.
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -87,7 +88,7 @@ static int create_impl(mtd_handle h)
     // rows: sum over cells of (k*m + m/2)/2 + 2 with k <= 19 -> generous static bound, clipped by config
     c.cap_scratch_rows = 10 * M + 2 * std::min(M, C) + 1024;
     c.cap_rows = cfg.max_rows > 0 ? cfg.max_rows : (4 * M + 1024);
-    c.cap_list = std::max<int64_t>(160 * M, 1 << 22);   // u16 entries: sum of m(m-1) over cells of > 32 intervals
+    c.cap_list = 16;                                     // adjacency lists are gone (bit matrices in shared memory)
     c.cap_expo = cfg.max_exposures > 0 ? cfg.max_exposures : std::max<int64_t>(N / 4, 4096);
     const int64_t S = std::min(M, C);   // max active cells
     int8_t *ct; int16_t *ci; int8_t *ab, *eb; double *sr; int32_t *rc;
@@ -111,6 +112,14 @@ static int create_impl(mtd_handle h)
     DA(c.ctr, 1);
     DA(h->d_params, 1);
     c.P = h->d_params;
+    {   // math.log(i) for small integers, from the host libm (what CPython's math.log calls)
+        double *lt; DA(lt, MTD_LOGTAB_N);
+        std::vector<double> tab(MTD_LOGTAB_N);
+        tab[0] = -INFINITY;
+        for (int i = 1; i < MTD_LOGTAB_N; i++) tab[i] = std::log((double)i);
+        CK(cudaMemcpy(lt, tab.data(), sizeof(double) * MTD_LOGTAB_N, cudaMemcpyHostToDevice));
+        c.logtab = lt;
+    }
     DA(h->d_iv_agent, M); DA(h->d_iv_cell, M); DA(h->d_iv_start, M); DA(h->d_iv_end, M); DA(h->d_iv_order, M);
     DA(h->d_mask, N);
     DA(h->scan_tmp, (std::max(M, S) + 2) / 2048 + 16);
@@ -396,7 +405,7 @@ extern "C" int mtd_get_counters(mtd_handle h, mtd_counters *out)
     out->n_slots = d.n_slots; out->n_rows = d.n_rows; out->n_exposed = d.n_applied;
     out->pairs_evaluated = (int64_t)d.pairs_evaluated; out->n_potential = (int64_t)d.n_potential;
     out->n_si_rows = d.n_si_rows; out->sched_overflow = d.sched_overflow; out->tape_miss = d.tape_miss;
-    for (int k = 0; k < 4; k++) out->class_cells[k] = d.class_cells[k];
+    for (int k = 0; k < MTD_NUM_CLASSES; k++) out->class_cells[k] = d.class_cells[k];
     out->error = d.error;
     if (d.error) {
         char buf[256];

@@ -4,7 +4,8 @@
 #include <stdint.h>
 #include "../../include/mtd_b200.h"
 
-#define MTD_NUM_CLASSES 4
+#define MTD_NUM_CLASSES 6      // cells by interval count: <=8, <=16, <=32 (sub-warp groups), <=128, <=320, <=1024 (warp)
+#define MTD_LOGTAB_N 4096      // host-computed math.log(i) for small integers
 #define FULLMASK 0xffffffffu
 
 // enums of the reference (epidemiologyclasses.py, cellsclasses.py)
@@ -107,6 +108,7 @@ struct DevCtx {
     DevCounters *ctr;
     const mtd_params *P;       // device copy of the parameters
     IvRec *csr_sorted;         // [M] CSR records in list (emission) order within each cell, written by K1
+    const double *logtab;      // [MTD_LOGTAB_N] glibc log(i)
 };
 
 
@@ -128,6 +130,12 @@ __host__ __device__ __forceinline__ void philox4x32(uint32_t c0, uint32_t c1, ui
         k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
     }
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// w[i] without a dynamically indexed local array
+__device__ __forceinline__ uint32_t pick4(const uint32_t w[4], int i)
+{
+    return i == 0 ? w[0] : (i == 1 ? w[1] : (i == 2 ? w[2] : w[3]));
 }
 
 __device__ __forceinline__ double u53(uint32_t a, uint32_t b)

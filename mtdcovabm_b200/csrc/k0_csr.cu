@@ -119,7 +119,10 @@ __global__ void k0_flags_kernel(DevCtx c)
     }
 }
 
-__device__ __forceinline__ int size_class(int m) { return m <= 32 ? 0 : (m <= 128 ? 1 : (m <= 320 ? 2 : 3)); }
+__device__ __forceinline__ int size_class(int m)
+{
+    return m <= 8 ? 0 : (m <= 16 ? 1 : (m <= 32 ? 2 : (m <= 128 ? 3 : (m <= 320 ? 4 : 5))));
+}
 
 __global__ void k0_assign_kernel(DevCtx c, const int32_t *flags_excl)
 {
@@ -143,7 +146,7 @@ __global__ void k0_assign_kernel(DevCtx c, const int32_t *flags_excl)
         // rows <= sum(deg)/2, sum(deg) <= max(k*n, S) + n/2 with n <= m; and rows <= m(m-1)/2
         long long b1 = (long long)m * (m - 1) / 2, b2 = (k * m + m / 2 + 2) / 2 + 1;
         c.slot_rowbound[slot] = (int)(b1 < b2 ? b1 : b2);
-        c.slot_listneed[slot] = (m > 32) ? (int64_t)m * (m - 1) : 0;
+        c.slot_listneed[slot] = 0;
         int cls = size_class(m);
         int idx = atomicAdd(&c.ctr->class_cells[cls], 1);
         c.class_list[(int64_t)cls * c.class_stride + idx] = slot;

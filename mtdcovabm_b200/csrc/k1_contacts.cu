@@ -1,15 +1,25 @@
 // K1 -- per-cell contact network: ContactNetwork.generate_contact_network (contactnetwork.py:134-315) and the
 // row conversion of simulate_contact_network (contactnetwork.py:98-105).
 //
-// One warp owns one cell at a time (persistent warps fetch cells of their size class from a device cursor).
-// Everything the cell needs lives in that warp's slice of shared memory:
-//   intervals in list order, local agent index (order of first appearance), per-agent interval lists,
-//   the n x n adjacency bit matrix of potential contacts, degrees, candidate buffer.
-// The per-agent partner lists in *dict insertion order* (which fixes the candidate order seen by
-// util.get_all_contacts_ids_by_id, util.py:274-297) are produced by walking the outer interval loop of the
-// reference sequentially and the inner loop in parallel across lanes (ballot + prefix compaction), so the list
-// order is the reference's by construction.  Lists live in shared memory for cells of <= 32 intervals and in an
-// L2-resident HBM scratch otherwise.
+// B200 design (no dict, no lists): every agent of a cell gets a 144-bit occupancy mask over the day's 10-minute
+// timesteps (union of its intervals).  Two agents are potential contacts iff their masks intersect, which is exactly
+// the reference's "some pair of their intervals overlaps" test (contactnetwork.py:426-432, inclusive bounds).  The
+// potential-contact graph is therefore an n x n BIT MATRIX built with AND + ballot, potential-contact counts are
+// popcounts, and the sequential greedy sampling (contactnetwork.py:283-301, 386-424) works on bit rows:
+//   candidates(x) = adj[x] & alive,  alive = {y : remaining degree > 0}
+// The reference deletes every pair of an agent whose degree reaches 0 (delete_all_pairs_by_id); with the alive mask
+// that deletion is one bit clear.  Selected partners come from the replay tape (agent ids, keyed by cell and main
+// agent) or from Philox draws: draw t takes the r_t-th remaining candidate in canonical order (ascending order of
+// first appearance in the cell), r_t = floor(u_t * (nc - t)) -- a uniformly random ordered subset, the same
+// distribution as np.random.shuffle + np.random.choice(replace=False) (util.py:295, contactnetwork.py:299).
+// Only the SELECTED pairs (a few % of the potential ones) need the reference's dict-order details -- key orientation,
+// first overlap's start, last overlap's end, summed duration -- and those are recomputed per row from the two
+// agents' interval lists (pair_row).
+//
+// Two kernels:
+//   k1_small<G>  cells of <= G intervals (G = 8, 16, 32): G lanes per cell, 32/G cells per warp, one lane per
+//                interval and per agent, everything in registers + a few bytes of shared memory per lane.
+//   k1_large<MM> cells of <= MM intervals (128, 320, 1024): one warp per cell, bit matrix in shared memory.
 #include "common.cuh"
 
 namespace {
@@ -17,35 +27,326 @@ namespace {
 __host__ __device__ constexpr int pow2_ge(int x) { int p = 1; while (p < x) p <<= 1; return p; }
 __host__ __device__ constexpr size_t align16(size_t x) { return (x + 15) & ~(size_t)15; }
 
+// position of the (r+1)-th set bit of v (r is 0-based, popc(v) > r)
+__device__ __forceinline__ int nth_set_bit(uint32_t v, int r)
+{
+    int pos = 0, c;
+    c = __popc(v & 0xffffu); if (r >= c) { r -= c; pos += 16; v >>= 16; }
+    c = __popc(v & 0xffu);   if (r >= c) { r -= c; pos += 8;  v >>= 8; }
+    c = __popc(v & 0xfu);    if (r >= c) { r -= c; pos += 4;  v >>= 4; }
+    c = __popc(v & 0x3u);    if (r >= c) { r -= c; pos += 2;  v >>= 2; }
+    c = (int)(v & 1u);       if (r >= c) { pos += 1; }
+    return pos;
+}
+
+// word k of the occupancy mask of the inclusive timestep range [s, e] (timesteps 0..159, five 32-bit words)
+__device__ __forceinline__ uint32_t range_word(int s, int e, int k)
+{
+    int lo = max(s - 32 * k, 0), hi = min(e - 32 * k, 31);
+    if (lo > hi) return 0u;
+    return (0xffffffffu >> (31 - (hi - lo))) << lo;
+}
+
+__device__ __forceinline__ long long tape_find_sel(const DevTape &T, int cell, int agent)
+{
+    uint64_t key = ((uint64_t)(uint32_t)cell << 32) | (uint32_t)agent;
+    long long lo = 0, hi = T.n_sel;
+    while (lo < hi) { long long mid = (lo + hi) >> 1; if (T.sel_key[mid] < key) lo = mid + 1; else hi = mid; }
+    return (lo < T.n_sel && T.sel_key[lo] == key) ? lo : -1;
+}
+
+__device__ __forceinline__ double log_int(const DevCtx &g, int v)
+{   // math.log of a small integer: host (glibc) table, the same libm CPython calls
+    return (v >= 0 && v < MTD_LOGTAB_N) ? g.logtab[v] : log((double)v);
+}
+
+// contactnetwork.py:225-252: float degree of one agent
+__device__ __forceinline__ double degree_f(const DevCtx &g, const mtd_params *P, int ag, int act, int ts, int pc,
+                                           double avg_ts, double avg_pc, double log_avg_ts, double log_avg_pc,
+                                           double one_minus_mhd)
+{
+    int ab = g.age_bracket[ag];
+    if (ab < 0) ab += 16;                                   // numpy negative index
+    double cmv = P->cm[ab][act];
+    double tsm = 1.0, pcm = 1.0;
+    if ((double)ts != avg_ts && avg_ts > 1) tsm = log_int(g, ts) / log_avg_ts;       // math.log(x, base)
+    if ((double)pc != avg_pc && avg_pc > 1) pcm = log_int(g, pc) / log_avg_pc;
+    return cmv * tsm * pcm * g.soc_rate[ag] * one_minus_mhd;
+}
+
+__device__ __forceinline__ int degree_i(double d, long long deg_sum, long long max_degree, int pc)
+{   // contactnetwork.py:254-269 (Python round = rint)
+    long long r;
+    if (deg_sum > max_degree) r = (long long)rint((d / (double)deg_sum) * (double)max_degree);
+    else r = (long long)rint(d);
+    return (int)(r > pc ? pc : r);
+}
+
+// Contact row of the pair {x, y}.  ivx / ivy: bit masks (small cells) of the two agents' interval positions, in
+// list order; se[]: start | end << 8 per interval position.  Key orientation = the agent whose interval produced the
+// first overlap in the reference's loop order (contactnetwork.py:160-196); start = first overlap's start, end = last
+// overlap's end (contactnetwork.py:101); dur = summed overlap length (epidemiology.py:170).
+__device__ __forceinline__ void pair_row_bits(const uint16_t *se, uint32_t ivx, uint32_t ivy, bool &x_first, int &start,
+                                              int &end, int &dur)
+{
+    int fx = 64, fy = 64;
+    for (uint32_t bx = ivx; bx; bx &= bx - 1) {
+        int pa = __ffs(bx) - 1; int sa = se[pa] & 0xff, ea = se[pa] >> 8;
+        for (uint32_t by = ivy; by; by &= by - 1) {
+            int pb = __ffs(by) - 1; int sb = se[pb] & 0xff, eb = se[pb] >> 8;
+            if (max(sa, sb) <= min(ea, eb)) { fx = min(fx, pa); fy = min(fy, pb); }
+        }
+    }
+    x_first = fx < fy;
+    uint32_t iva = x_first ? ivx : ivy, ivb = x_first ? ivy : ivx;
+    bool first = true;
+    start = 0; end = 0; dur = 0;
+    for (uint32_t ba = iva; ba; ba &= ba - 1) {
+        int pa = __ffs(ba) - 1; int sa = se[pa] & 0xff, ea = se[pa] >> 8;
+        for (uint32_t bb = ivb; bb; bb &= bb - 1) {
+            int pb = __ffs(bb) - 1; int sb = se[pb] & 0xff, eb = se[pb] >> 8;
+            int lo = max(sa, sb), hi = min(ea, eb);
+            if (lo <= hi) { if (first) { start = lo; first = false; } end = hi; dur += hi - lo + 1; }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ small cells
+#define K1S_THREADS 256
+
+template <int G>
+__global__ void __launch_bounds__(K1S_THREADS) k1_small_kernel(DevCtx g, int cls)
+{
+    // per-lane shared slots, indexed [group base + position]
+    __shared__ int32_t sh_agent[K1S_THREADS];
+    __shared__ uint16_t sh_se[K1S_THREADS];
+    __shared__ __align__(16) uint32_t sh_mask[K1S_THREADS][6];     // agent occupancy masks (5 words used)
+
+    const int lane = threadIdx.x & 31;
+    const int gl = lane & (G - 1);                  // lane in group
+    const int gbase = lane & ~(G - 1);              // first lane of the group inside the warp
+    const uint32_t gbits = (G == 32) ? 0xffffffffu : ((1u << G) - 1u);
+    const uint32_t gmask = gbits << gbase;
+    const int tb = (int)threadIdx.x - gl;           // group base in the block-wide shared arrays
+    if (g.ctr->error) return;
+    const int total = g.ctr->class_cells[cls];
+    const int32_t *list = g.class_list + (int64_t)cls * g.class_stride;
+    const int n_groups = (gridDim.x * K1S_THREADS) / G;
+    const mtd_params *P = g.P;
+    const double one_minus_mhd = 1 - g.day.mhd;
+    unsigned long long acc_pairs = 0, acc_pot = 0;
+
+    for (int w = (blockIdx.x * K1S_THREADS + (int)threadIdx.x) / G; w < total; w += n_groups) {
+        const int slot = list[w];
+        const int m = g.slot_m[slot];
+        const int64_t base = g.slot_off[slot];
+        const int cell = g.slot_cell[slot];
+        const int ctype = g.cell_type[cell];
+        const int indid = (ctype == CT_WORKPLACE && g.cell_indid) ? g.cell_indid[cell] : -1;
+        const int act = activity_of_celltype(ctype, indid);
+
+        // ---- 1. my interval; restore list (emission) order by ranking the emission indices ----
+        const bool have = gl < m;
+        IvRec rec; rec.agent = 0; rec.order = 0xffffffffu; rec.se = 0; rec.pad = 0;
+        if (have) rec = g.csr[base + gl];
+        int rank = 0;
+#pragma unroll
+        for (int j = 0; j < G; j++) {
+            uint32_t kj = __shfl_sync(gmask, rec.order, gbase + j);
+            rank += (kj < rec.order) || (kj == rec.order && j < gl);
+        }
+        __syncwarp(gmask);                          // previous cell's readers of the shared slots are done
+        if (have) {
+            sh_agent[tb + rank] = rec.agent; sh_se[tb + rank] = (uint16_t)(rec.se & 0xffffu);
+            g.csr_sorted[base + rank] = rec;
+        }
+        __syncwarp(gmask);
+        const int agent = have ? sh_agent[tb + gl] : (-1 - gl);
+        const uint16_t *se = sh_se + tb;
+
+        // ---- 2. agents = first appearances (contactnetwork.py:161-163); an agent lives on its first interval's lane
+        const uint32_t mm = (__match_any_sync(gmask, agent) >> gbase) & gbits;      // my agent's interval positions
+        const bool isag = have && ((__ffs(mm) - 1) == gl);
+        const uint32_t agm = (__ballot_sync(gmask, isag) >> gbase) & gbits;         // agent lanes (group-relative)
+        const int n = __popc(agm);
+        {   // metric: unordered interval pairs of different agents = (m^2 - sum_a cnt_a^2) / 2
+            int sq = have ? __popc(mm) : 0;
+#pragma unroll
+            for (int o = G / 2; o > 0; o >>= 1) sq += __shfl_xor_sync(gmask, sq, o);
+            if (gl == 0) acc_pairs += (unsigned long long)(m * m - sq) / 2;
+        }
+        // per-agent occupancy mask and total timesteps (contactnetwork.py:171-174)
+        uint32_t mk[5] = { 0, 0, 0, 0, 0 };
+        int ts = 0;
+        if (isag) {
+            for (uint32_t b = mm; b; b &= b - 1) {
+                int p = __ffs(b) - 1; int s = se[p] & 0xff, e = se[p] >> 8;
+                int len = e - s + 1; ts += len > 0 ? len : 0;
+#pragma unroll
+                for (int k = 0; k < 5; k++) mk[k] |= range_word(s, e, k);
+            }
+#pragma unroll
+            for (int k = 0; k < 5; k++) sh_mask[tb + gl][k] = mk[k];
+        }
+        __syncwarp(gmask);
+
+        // ---- 3. potential contacts: bit row per agent (contactnetwork.py:160-196) ----
+        uint32_t adj = 0;
+        if (isag) {
+            for (uint32_t b = agm & ~(1u << gl); b; b &= b - 1) {
+                int q = __ffs(b) - 1;
+                const uint32_t *o = sh_mask[tb + q];
+                uint32_t hit = (mk[0] & o[0]) | (mk[1] & o[1]) | (mk[2] & o[2]) | (mk[3] & o[3]) | (mk[4] & o[4]);
+                if (hit) adj |= 1u << q;
+            }
+        }
+        const int pc = __popc(adj);
+        int pc_sum = pc, ts_sum = ts;
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) {
+            pc_sum += __shfl_xor_sync(gmask, pc_sum, o); ts_sum += __shfl_xor_sync(gmask, ts_sum, o);
+        }
+        if (gl == 0) acc_pot += (unsigned)pc_sum / 2;
+        if (pc_sum == 0) {                                      // contactnetwork.py:198
+            if (gl == 0) g.slot_nrows[slot] = 0;
+            continue;
+        }
+
+        // ---- 4. degrees (contactnetwork.py:210-269) ----
+        const long long max_degree = (long long)P->k_by_act[act] * n;
+        const double avg_ts = (double)ts_sum / (double)n, avg_pc = (double)pc_sum / (double)n;
+        const double log_avg_ts = log(avg_ts), log_avg_pc = log(avg_pc);
+        double degf = 0.0;
+        if (isag && pc > 0) degf = degree_f(g, P, agent, act, ts, pc, avg_ts, avg_pc, log_avg_ts, log_avg_pc, one_minus_mhd);
+        double dsum;
+        {   // numpy float64 add.reduce over the agents in order of first appearance (n <= 32 < 128: one block)
+            uint32_t b = agm;
+            if (n < 8) {
+                dsum = -0.0;
+                for (; b; b &= b - 1) dsum += __shfl_sync(gmask, degf, gbase + __ffs(b) - 1);
+            } else {
+                double r[8];
+                const int nfull = n - (n % 8);
+#pragma unroll
+                for (int k = 0; k < 8; k++) { r[k] = __shfl_sync(gmask, degf, gbase + __ffs(b) - 1); b &= b - 1; }
+                for (int i = 8; i < nfull; i += 8) {
+#pragma unroll
+                    for (int k = 0; k < 8; k++) { r[k] += __shfl_sync(gmask, degf, gbase + __ffs(b) - 1); b &= b - 1; }
+                }
+                dsum = ((r[0] + r[1]) + (r[2] + r[3])) + ((r[4] + r[5]) + (r[6] + r[7]));
+                for (; b; b &= b - 1) dsum += __shfl_sync(gmask, degf, gbase + __ffs(b) - 1);
+            }
+        }
+        const long long deg_sum = (long long)rint(dsum);
+        int deg = isag ? degree_i(degf, deg_sum, max_degree, pc) : 0;
+
+        // ---- 5. greedy order: sorted(zip(deg, id), reverse=True) (contactnetwork.py:283) ----
+        int ord = 0;
+        for (uint32_t b = agm; b; b &= b - 1) {
+            int q = gbase + __ffs(b) - 1;
+            int dq = __shfl_sync(gmask, deg, q), aq = __shfl_sync(gmask, agent, q);
+            ord += (dq > deg) || (dq == deg && aq > agent);
+        }
+
+        // ---- 6. greedy sampling + create_contacts (contactnetwork.py:287-301, 386-424) ----
+        RowRec *rows = g.scratch_rows + g.slot_rowoff[slot];
+        const int row_cap = g.slot_rowbound[slot];
+        int n_rows = 0;
+        for (int r = 0; r < n; r++) {
+            const uint32_t xb = __ballot_sync(gmask, isag && ord == r);
+            const int x = __ffs(xb) - 1;                           // absolute lane of the main agent
+            const int dx = __shfl_sync(gmask, deg, x);
+            const uint32_t alive = (__ballot_sync(gmask, isag && deg > 0) >> gbase) & gbits;
+            uint32_t cand = __shfl_sync(gmask, adj, x) & alive;     // util.get_all_contacts_ids_by_id
+            const int agx = __shfl_sync(gmask, agent, x);
+            const uint32_t ivx = __shfl_sync(gmask, mm, x);
+            if (dx <= 0) continue;
+            const int nc = __popc(cand);
+            if (nc == 0) continue;                                  // returned None (contactnetwork.py:294)
+            int d = dx < nc ? dx : nc;
+            int npick = d, mypick = -1;
+            uint32_t picked = 0;
+            if (g.day.mode == MTD_MODE_REPLAY) {
+                long long tr = tape_find_sel(g.tape, cell, agx);
+                if (tr < 0) { if (gl == 0) atomicAdd(&g.ctr->tape_miss, 1); continue; }
+                const int toff = g.tape.sel_off[tr];
+                const int cnt = g.tape.sel_off[tr + 1] - toff;
+                if (cnt != d) { if (gl == 0) atomicAdd(&g.ctr->tape_miss, 1); if (cnt < npick) npick = cnt; }
+                for (int t = 0; t < npick; t++) {
+                    const int pid = g.tape.sel_picks[toff + t];     // selected partner's agent id
+                    const uint32_t hb = (__ballot_sync(gmask, isag && agent == pid) >> gbase) & gbits & cand;
+                    if (!hb) { if (gl == 0) atomicAdd(&g.ctr->tape_miss, 1); continue; }
+                    const int bit = __ffs(hb) - 1;
+                    cand &= ~(1u << bit); picked |= 1u << bit;
+                    if (gl == t) mypick = bit;
+                }
+            } else {
+                uint32_t wv = 0;
+                if (gl < d) {
+                    uint32_t w4[4];
+                    philox4x32((uint32_t)g.day.day, (uint32_t)cell, (uint32_t)agx, (uint32_t)(gl >> 2), g.day.seed, SITE_SELECT, w4);
+                    wv = pick4(w4, gl & 3);
+                }
+                for (int t = 0; t < d; t++) {
+                    const uint32_t wt = __shfl_sync(gmask, wv, gbase + t);
+                    const int bit = nth_set_bit(cand, (int)__umulhi(wt, (uint32_t)(nc - t)));
+                    cand &= ~(1u << bit); picked |= 1u << bit;
+                    if (gl == t) mypick = bit;
+                }
+            }
+            // rows: lane t builds the row of pick t
+            const uint32_t ivy = __shfl_sync(gmask, mm, gbase + (mypick >= 0 ? mypick : gl));
+            const int agy = __shfl_sync(gmask, agent, gbase + (mypick >= 0 ? mypick : gl));
+            if (mypick >= 0) {
+                bool x_first; int st, en, dur;
+                pair_row_bits(se, ivx, ivy, x_first, st, en, dur);
+                if (n_rows + gl < row_cap) {
+                    RowRec rr;
+                    rr.a1 = x_first ? agx : agy; rr.a2 = x_first ? agy : agx;
+                    rr.sed = (uint32_t)st | ((uint32_t)en << 8) | ((uint32_t)dur << 16);
+                    rr.slot = slot;
+                    rows[n_rows + gl] = rr;
+                } else g.ctr->error = MTD_E_CAPACITY;
+            }
+            if ((picked >> gl) & 1u) deg -= 1;                      // partner degree - 1 (dead at 0: alive mask)
+            if (lane == x) deg = d - npick;                         // the main agent's degree is spent
+            n_rows += npick;
+        }
+        if (gl == 0) g.slot_nrows[slot] = n_rows < row_cap ? n_rows : row_cap;
+    }
+    if (gl == 0 && (acc_pairs | acc_pot)) {
+        atomicAdd(&g.ctr->pairs_evaluated, acc_pairs);
+        atomicAdd(&g.ctr->n_potential, acc_pot);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ large cells
 template <int MM>
 struct Lay {
     static constexpr int P2 = pow2_ge(MM);
     static constexpr int BW = (MM + 31) / 32;              // bit-matrix words per row
     static constexpr int H = 2 * P2;                       // hash slots
-    static constexpr bool LISTS_SMEM = (MM <= 32);
-    static constexpr size_t o_u8 = 0;                      // u64[P2]: sort keys / 2 x u32[P2] temps / double[MM] degf
-    static constexpr size_t o_agent = o_u8 + align16(sizeof(uint64_t) * P2);        // i32[MM]
-    static constexpr size_t o_s = o_agent + align16(sizeof(int32_t) * MM);          // u8[MM]
-    static constexpr size_t o_e = o_s + align16(MM);                                // u8[MM]
-    static constexpr size_t o_la = o_e + align16(MM);                               // u16[MM]
-    static constexpr size_t o_apos = o_la + align16(2 * MM);                        // u16[MM]
+    static constexpr size_t o_key = 0;                     // u64[P2]: sort keys / 2 x u32[P2] temps / double[MM] degf
+    static constexpr size_t o_agent = o_key + align16(sizeof(uint64_t) * P2);       // i32[MM] agent id per interval
+    static constexpr size_t o_se = o_agent + align16(sizeof(int32_t) * MM);         // u16[MM] start | end << 8
+    static constexpr size_t o_la = o_se + align16(2 * MM);                          // u16[MM] local agent of interval
+    static constexpr size_t o_apos = o_la + align16(2 * MM);                        // u16[MM] interval lists
     static constexpr size_t o_aoff = o_apos + align16(2 * MM);                      // u16[MM+1]
-    static constexpr size_t o_first = o_aoff + align16(2 * (MM + 1));               // u16[MM]
+    static constexpr size_t o_first = o_aoff + align16(2 * (MM + 1));               // u16[MM] first interval of agent
     static constexpr size_t o_pc = o_first + align16(2 * MM);                       // u16[MM]
     static constexpr size_t o_deg = o_pc + align16(2 * MM);                         // i16[MM]
     static constexpr size_t o_ts = o_deg + align16(2 * MM);                         // u16[MM]
-    static constexpr size_t o_cand = o_ts + align16(2 * MM);                        // u16[MM]
-    static constexpr size_t o_bits = o_cand + align16(2 * MM);                      // u32[MM*BW]
-    static constexpr size_t o_hash = o_bits + align16(sizeof(uint32_t) * MM * BW);  // u32[H] (later u16 swap targets)
-    static constexpr size_t o_list = o_hash + align16(sizeof(uint32_t) * H);        // u8[MM*MM] if LISTS_SMEM
-    static constexpr size_t bytes = o_list + (LISTS_SMEM ? align16((size_t)MM * MM) : 0);
+    static constexpr size_t o_cand = o_ts + align16(2 * MM);                        // u16[MM] picks of one main agent
+    static constexpr size_t o_mask = o_cand + align16(2 * MM);                      // u32[MM][6] occupancy masks
+    static constexpr size_t o_bits = o_mask + align16(sizeof(uint32_t) * 6 * MM);   // u32[MM*BW] adjacency
+    static constexpr size_t o_hash = o_bits + align16(sizeof(uint32_t) * MM * BW);  // u32[H]
+    static constexpr size_t bytes = o_hash + align16(sizeof(uint32_t) * H);
 };
 
 struct Cell {
-    uint64_t *u8; int32_t *agent; uint8_t *s, *e; uint16_t *la, *apos, *aoff, *first, *pc; int16_t *deg;
-    uint16_t *ts, *cand; uint32_t *bits, *hash; uint8_t *slist; uint16_t *glist;
-    int bw;          // bit words per row
-    int lstride;     // list row stride
+    uint64_t *key; int32_t *agent; uint16_t *se, *la, *apos, *aoff, *first, *pc; int16_t *deg; uint16_t *ts, *cand;
+    uint32_t *mask, *bits, *hash;
+    int bw;
 };
 
 __device__ __forceinline__ void warp_bitonic_sort(uint64_t *k, int P2, int lane)
@@ -62,22 +363,6 @@ __device__ __forceinline__ void warp_bitonic_sort(uint64_t *k, int P2, int lane)
             __syncwarp();
         }
     }
-}
-
-__device__ __forceinline__ bool bit_get(const Cell &c, int x, int y) { return (c.bits[x * c.bw + (y >> 5)] >> (y & 31)) & 1u; }
-__device__ __forceinline__ void bit_set(const Cell &c, int x, int y) { atomicOr(&c.bits[x * c.bw + (y >> 5)], 1u << (y & 31)); }
-
-template <bool SM>
-__device__ __forceinline__ int list_get(const Cell &c, int x, int i)
-{
-    if (SM) return c.slist[x * c.lstride + i];
-    return __ldcg(&c.glist[(size_t)x * c.lstride + i]);
-}
-template <bool SM>
-__device__ __forceinline__ void list_put(const Cell &c, int x, int i, int y)
-{
-    if (SM) c.slist[x * c.lstride + i] = (uint8_t)y;
-    else __stcg(&c.glist[(size_t)x * c.lstride + i], (uint16_t)y);
 }
 
 // numpy float64 add.reduce (pairwise summation, 8 accumulators, blocks of <= 128), executed by one lane.
@@ -104,59 +389,42 @@ __device__ double np_pairwise_sum(const double *a, int n)
     return np_pairwise_sum(a, n2) + np_pairwise_sum(a + n2, n - n2);
 }
 
-__device__ __forceinline__ bool overlap(const Cell &c, int p, int q) { return max(c.s[p], c.s[q]) <= min(c.e[p], c.e[q]); }
-
-// Contact row of the pair {x, y} (local agent indices): key orientation, first overlap's start, last overlap's
-// end (contactnetwork.py:101) and the summed overlap length (epidemiology.py:170).
-__device__ __forceinline__ void pair_row(const Cell &c, int x, int y, int &a, int &b, int &start, int &end, int &dur)
+// same contract as pair_row_bits, agents given by local index with interval lists aoff/apos
+__device__ __forceinline__ void pair_row_lists(const Cell &c, int x, int y, bool &x_first, int &start, int &end, int &dur)
 {
     int fx = 1 << 30, fy = 1 << 30;
     for (int qa = c.aoff[x]; qa < c.aoff[x + 1]; qa++) {
-        int pa = c.apos[qa];
+        int pa = c.apos[qa]; int sa = c.se[pa] & 0xff, ea = c.se[pa] >> 8;
         for (int qb = c.aoff[y]; qb < c.aoff[y + 1]; qb++) {
-            int pb = c.apos[qb];
-            if (overlap(c, pa, pb)) { fx = min(fx, pa); fy = min(fy, pb); }
+            int pb = c.apos[qb]; int sb = c.se[pb] & 0xff, eb = c.se[pb] >> 8;
+            if (max(sa, sb) <= min(ea, eb)) { fx = min(fx, pa); fy = min(fy, pb); }
         }
     }
-    a = (fx < fy) ? x : y;          // the key is oriented from the agent whose interval produced the first overlap
-    b = (fx < fy) ? y : x;
+    x_first = fx < fy;
+    const int a = x_first ? x : y, b = x_first ? y : x;
     bool first = true;
     start = 0; end = 0; dur = 0;
     for (int qa = c.aoff[a]; qa < c.aoff[a + 1]; qa++) {
-        int pa = c.apos[qa];
+        int pa = c.apos[qa]; int sa = c.se[pa] & 0xff, ea = c.se[pa] >> 8;
         for (int qb = c.aoff[b]; qb < c.aoff[b + 1]; qb++) {
-            int pb = c.apos[qb];
-            int lo = max(c.s[pa], c.s[pb]), hi = min(c.e[pa], c.e[pb]);
-            if (lo <= hi) {
-                if (first) { start = lo; first = false; }
-                end = hi;
-                dur += hi - lo + 1;
-            }
+            int pb = c.apos[qb]; int sb = c.se[pb] & 0xff, eb = c.se[pb] >> 8;
+            int lo = max(sa, sb), hi = min(ea, eb);
+            if (lo <= hi) { if (first) { start = lo; first = false; } end = hi; dur += hi - lo + 1; }
         }
     }
 }
 
-__device__ __forceinline__ long long tape_find_sel(const DevTape &T, int cell, int agent)
-{
-    uint64_t key = ((uint64_t)(uint32_t)cell << 32) | (uint32_t)agent;
-    long long lo = 0, hi = T.n_sel;
-    while (lo < hi) { long long mid = (lo + hi) >> 1; if (T.sel_key[mid] < key) lo = mid + 1; else hi = mid; }
-    return (lo < T.n_sel && T.sel_key[lo] == key) ? lo : -1;
-}
-
 template <int MM>
-__device__ void process_cell(const DevCtx &g, unsigned char *sm, int slot, int lane, unsigned long long &acc_pairs,
-                             unsigned long long &acc_pot)
+__device__ void process_cell_large(const DevCtx &g, unsigned char *sm, int slot, int lane, unsigned long long &acc_pairs,
+                                   unsigned long long &acc_pot)
 {
     using L = Lay<MM>;
-    constexpr bool SM = L::LISTS_SMEM;
     Cell c;
-    c.u8 = (uint64_t *)(sm + L::o_u8); c.agent = (int32_t *)(sm + L::o_agent);
-    c.s = sm + L::o_s; c.e = sm + L::o_e; c.la = (uint16_t *)(sm + L::o_la); c.apos = (uint16_t *)(sm + L::o_apos);
-    c.aoff = (uint16_t *)(sm + L::o_aoff); c.first = (uint16_t *)(sm + L::o_first); c.pc = (uint16_t *)(sm + L::o_pc);
-    c.deg = (int16_t *)(sm + L::o_deg); c.ts = (uint16_t *)(sm + L::o_ts); c.cand = (uint16_t *)(sm + L::o_cand);
+    c.key = (uint64_t *)(sm + L::o_key); c.agent = (int32_t *)(sm + L::o_agent); c.se = (uint16_t *)(sm + L::o_se);
+    c.la = (uint16_t *)(sm + L::o_la); c.apos = (uint16_t *)(sm + L::o_apos); c.aoff = (uint16_t *)(sm + L::o_aoff);
+    c.first = (uint16_t *)(sm + L::o_first); c.pc = (uint16_t *)(sm + L::o_pc); c.deg = (int16_t *)(sm + L::o_deg);
+    c.ts = (uint16_t *)(sm + L::o_ts); c.cand = (uint16_t *)(sm + L::o_cand); c.mask = (uint32_t *)(sm + L::o_mask);
     c.bits = (uint32_t *)(sm + L::o_bits); c.hash = (uint32_t *)(sm + L::o_hash);
-    c.slist = sm + L::o_list;
 
     const int m = g.slot_m[slot];
     const int64_t base = g.slot_off[slot];
@@ -164,9 +432,9 @@ __device__ void process_cell(const DevCtx &g, unsigned char *sm, int slot, int l
     const int ctype = g.cell_type[cell];
     const int indid = (ctype == CT_WORKPLACE && g.cell_indid) ? g.cell_indid[cell] : -1;
     const int act = activity_of_celltype(ctype, indid);
-    uint32_t *t32a = (uint32_t *)c.u8;            // two u32[P2] temporaries aliasing the sort-key region
+    uint32_t *t32a = (uint32_t *)c.key;           // two u32[P2] temporaries aliasing the sort-key region
     uint32_t *t32b = t32a + L::P2;
-    double *degf = (double *)c.u8;
+    double *degf = (double *)c.key;
 
     // ---- 1. restore list (emission) order inside the cell: sort by emission index ----
     int P2 = 2;
@@ -179,14 +447,14 @@ __device__ void process_cell(const DevCtx &g, unsigned char *sm, int slot, int l
             k = ((uint64_t)o << 32) | (uint32_t)p;
             if (p > 0 && g.csr[base + p - 1].order > o) sorted = false;
         }
-        c.u8[p] = k;
+        c.key[p] = k;
     }
     sorted = __all_sync(FULLMASK, sorted);
     __syncwarp();
-    if (!sorted) warp_bitonic_sort(c.u8, P2, lane);
+    if (!sorted) warp_bitonic_sort(c.key, P2, lane);
     for (int p = lane; p < m; p += 32) {
-        IvRec r = g.csr[base + (uint32_t)c.u8[p]];
-        c.agent[p] = r.agent; c.s[p] = (uint8_t)(r.se & 0xff); c.e[p] = (uint8_t)((r.se >> 8) & 0xff);
+        IvRec r = g.csr[base + (uint32_t)c.key[p]];
+        c.agent[p] = r.agent; c.se[p] = (uint16_t)(r.se & 0xffffu);
         g.csr_sorted[base + p] = r;
     }
     __syncwarp();
@@ -248,65 +516,54 @@ __device__ void process_cell(const DevCtx &g, unsigned char *sm, int slot, int l
     for (int p0 = 0; p0 < m; p0 += 32) {                 // fill the per-agent lists in position order
         int p = p0 + lane;
         int l = (p < m) ? (int)c.la[p] : (0x10000 + lane);
-        uint32_t mm = __match_any_sync(FULLMASK, l);
+        uint32_t mmm = __match_any_sync(FULLMASK, l);
         if (p < m) {
-            int rank = __popc(mm & lanemask_lt());
+            int rank = __popc(mmm & lanemask_lt());
             c.apos[t32a[l] + rank] = (uint16_t)p;
         }
         __syncwarp();
-        if (p < m && (__ffs(mm) - 1) == lane) t32a[l] += __popc(mm);
+        if (p < m && (__ffs(mmm) - 1) == lane) t32a[l] += __popc(mmm);
         __syncwarp();
     }
-    // per-agent totals, clear the adjacency matrix
+
+    // ---- 3. per-agent occupancy masks + total timesteps; adjacency bit matrix by AND + ballot ----
+    const int bw = (n + 31) >> 5;
+    c.bw = bw;
     int ts_sum = 0;
     for (int l = lane; l < n; l += 32) {
+        uint32_t mk[5] = { 0, 0, 0, 0, 0 };
         int t = 0;
-        for (int q = c.aoff[l]; q < c.aoff[l + 1]; q++) { int p = c.apos[q]; int len = (int)c.e[p] - (int)c.s[p] + 1; t += len > 0 ? len : 0; }
-        c.ts[l] = (uint16_t)t; ts_sum += t; c.pc[l] = 0; c.deg[l] = 0;
+        for (int q = c.aoff[l]; q < c.aoff[l + 1]; q++) {
+            int p = c.apos[q]; int s = c.se[p] & 0xff, e = c.se[p] >> 8;
+            int len = e - s + 1; t += len > 0 ? len : 0;
+#pragma unroll
+            for (int k = 0; k < 5; k++) mk[k] |= range_word(s, e, k);
+        }
+        c.ts[l] = (uint16_t)t; ts_sum += t;
+        uint2 *dst = (uint2 *)(c.mask + 6 * l);
+        dst[0] = make_uint2(mk[0], mk[1]); dst[1] = make_uint2(mk[2], mk[3]); dst[2] = make_uint2(mk[4], 0u);
     }
     for (int o = 16; o > 0; o >>= 1) ts_sum += __shfl_xor_sync(FULLMASK, ts_sum, o);
-    c.bw = (n + 31) >> 5;
-    c.lstride = n > 1 ? n - 1 : 1;
-    c.glist = g.lists + g.slot_listoff[slot];
-    for (int w = lane; w < n * c.bw; w += 32) c.bits[w] = 0;
     __syncwarp();
-
-    // ---- 3. pair enumeration (contactnetwork.py:160-196): outer loop sequential, inner loop across lanes ----
-    for (int i = 0; i < m; i++) {
-        const int x = c.la[i];
-        const int si = c.s[i], ei = c.e[i];
-        int cntx = c.pc[x];
-        for (int j0 = 0; j0 < m; j0 += 32) {
-            int j = j0 + lane;
-            bool f = false;
-            int y = 0;
-            if (j < m) {
-                y = c.la[j];
-                f = (y != x) && (max(si, (int)c.s[j]) <= min(ei, (int)c.e[j])) && !bit_get(c, x, y);
-                if (f) {                                  // only the first overlapping interval of y creates the key
-                    for (int q = c.aoff[y]; q < c.aoff[y + 1]; q++) {
-                        int pj = c.apos[q];
-                        if (pj >= j) break;
-                        if (max(si, (int)c.s[pj]) <= min(ei, (int)c.e[pj])) { f = false; break; }
-                    }
-                }
-            }
-            uint32_t bm = __ballot_sync(FULLMASK, f);
-            if (f) {
-                int r = cntx + __popc(bm & lanemask_lt());
-                list_put<SM>(c, x, r, y);                 // key (x, y) appended: x's partner list ...
-                int py = c.pc[y];
-                list_put<SM>(c, y, py, x);                // ... and y's, in dict insertion order
-                c.pc[y] = (uint16_t)(py + 1);
-                bit_set(c, x, y); bit_set(c, y, x);
-            }
-            cntx += __popc(bm);
+    for (int yb = 0; yb < bw; yb++) {
+        const int y = yb * 32 + lane;
+        uint2 m0 = make_uint2(0, 0), m1 = m0, m2 = m0;
+        if (y < n) { const uint2 *src = (const uint2 *)(c.mask + 6 * y); m0 = src[0]; m1 = src[1]; m2 = src[2]; }
+        for (int x = 0; x < n; x++) {
+            const uint2 *ox = (const uint2 *)(c.mask + 6 * x);
+            uint2 a0 = ox[0], a1 = ox[1], a2 = ox[2];
+            uint32_t hit = (m0.x & a0.x) | (m0.y & a0.y) | (m1.x & a1.x) | (m1.y & a1.y) | (m2.x & a2.x);
+            uint32_t word = __ballot_sync(FULLMASK, hit != 0 && y != x);
+            if (lane == 0) c.bits[x * bw + yb] = word;
         }
-        if (lane == 0) c.pc[x] = (uint16_t)cntx;
-        __syncwarp();
     }
+    __syncwarp();
     int pc_sum = 0;
-    for (int l = lane; l < n; l += 32) pc_sum += c.pc[l];
+    for (int l = lane; l < n; l += 32) {
+        int pcv = 0;
+        for (int w = 0; w < bw; w++) pcv += __popc(c.bits[l * bw + w]);
+        c.pc[l] = (uint16_t)pcv; pc_sum += pcv;
+    }
     for (int o = 16; o > 0; o >>= 1) pc_sum += __shfl_xor_sync(FULLMASK, pc_sum, o);
     acc_pot += (unsigned)pc_sum / 2;
     if (pc_sum == 0) {                                    // contactnetwork.py:198
@@ -317,40 +574,22 @@ __device__ void process_cell(const DevCtx &g, unsigned char *sm, int slot, int l
 
     // ---- 4. degrees (contactnetwork.py:210-269) ----
     const mtd_params *P = g.P;
-    const long long k = P->k_by_act[act];
-    const long long max_degree = k * n;
+    const long long max_degree = (long long)P->k_by_act[act] * n;
     const double avg_ts = (double)ts_sum / (double)n;
     const double avg_pc = (double)pc_sum / (double)n;     // every agent has an entry once n >= 2
     const double one_minus_mhd = 1 - g.day.mhd;
     const double log_avg_ts = log(avg_ts), log_avg_pc = log(avg_pc);
     for (int l = lane; l < n; l += 32) {
         double d = 0.0;
-        int pc = c.pc[l];
-        if (pc > 0) {
-            int ag = c.agent[c.first[l]];
-            int ab = g.age_bracket[ag];
-            if (ab < 0) ab += 16;
-            double cmv = P->cm[ab][act];
-            double tsm = 1.0, pcm = 1.0;
-            double tsv = (double)c.ts[l];
-            if (tsv != avg_ts && avg_ts > 1) tsm = log(tsv) / log_avg_ts;
-            if ((double)pc != avg_pc && avg_pc > 1) pcm = log((double)pc) / log_avg_pc;
-            d = cmv * tsm * pcm * g.soc_rate[ag] * one_minus_mhd;
-        }
+        int pcv = c.pc[l];
+        if (pcv > 0) d = degree_f(g, P, c.agent[c.first[l]], act, c.ts[l], pcv, avg_ts, avg_pc, log_avg_ts, log_avg_pc, one_minus_mhd);
         degf[l] = d;
     }
     __syncwarp();
     long long deg_sum = 0;
     if (lane == 0) deg_sum = (long long)rint(np_pairwise_sum(degf, n));
     deg_sum = __shfl_sync(FULLMASK, deg_sum, 0);
-    for (int l = lane; l < n; l += 32) {
-        double d = degf[l];
-        long long r;
-        if (deg_sum > max_degree) r = (long long)rint((d / (double)deg_sum) * (double)max_degree);
-        else r = (long long)rint(d);
-        int pc = c.pc[l];
-        c.deg[l] = (int16_t)(r > pc ? pc : r);
-    }
+    for (int l = lane; l < n; l += 32) c.deg[l] = (int16_t)degree_i(degf[l], deg_sum, max_degree, c.pc[l]);
     __syncwarp();
 
     // ---- 5. greedy order: sorted(zip(deg, id), reverse=True) (contactnetwork.py:283) ----
@@ -359,83 +598,107 @@ __device__ void process_cell(const DevCtx &g, unsigned char *sm, int slot, int l
     for (int l = lane; l < Pn; l += 32) {
         uint64_t key = ~0ull;
         if (l < n) key = ~(((uint64_t)(uint16_t)c.deg[l] << 48) | ((uint64_t)(uint32_t)c.agent[c.first[l]] << 16) | (uint64_t)l);
-        c.u8[l] = key;
+        c.key[l] = key;
     }
     __syncwarp();
-    warp_bitonic_sort(c.u8, Pn, lane);
+    warp_bitonic_sort(c.key, Pn, lane);
 
     // ---- 6. greedy sampling + create_contacts (contactnetwork.py:287-301, 386-424) ----
+    // lane w owns word w of the alive mask (agents with remaining degree > 0); n <= 1024 -> at most 32 words
+    uint32_t alive = 0;
+    if (lane < bw) for (int b = 0; b < 32; b++) { int y = lane * 32 + b; if (y < n && c.deg[y] > 0) alive |= 1u << b; }
     RowRec *rows = g.scratch_rows + g.slot_rowoff[slot];
     const int row_cap = g.slot_rowbound[slot];
-    uint16_t *swp = (uint16_t *)c.hash;                   // Fisher-Yates swap targets
     int n_rows = 0;
     for (int oi = 0; oi < n; oi++) {
-        const int x = (int)((~c.u8[oi]) & 0xffff);
-        int d = c.deg[x];
-        if (d <= 0) continue;
-        // candidates: partners in insertion order whose remaining degree > 0 (util.py:274-297)
-        const int pcx = c.pc[x];
-        int nc = 0;
-        for (int q0 = 0; q0 < pcx; q0 += 32) {
-            int q = q0 + lane;
-            int y = 0;
-            bool f = false;
-            if (q < pcx) { y = list_get<SM>(c, x, q); f = c.deg[y] > 0; }
-            uint32_t bm = __ballot_sync(FULLMASK, f);
-            if (f) c.cand[nc + __popc(bm & lanemask_lt())] = (uint16_t)y;
-            nc += __popc(bm);
-        }
-        __syncwarp();
-        if (nc == 0) continue;                            // get_all_contacts_ids_by_id returned None
-        if (d > nc) d = nc;
+        const int x = (int)((~c.key[oi]) & 0xffff);
+        const int dx = c.deg[x];
+        if (((~c.key[oi]) >> 48) == 0) break;                // initial degree 0: so are all that follow
+        if (dx <= 0) continue;
+        uint32_t cw = (lane < bw) ? (c.bits[x * bw + lane] & alive) : 0u;     // util.get_all_contacts_ids_by_id
+        int cnt = __popc(cw);
+        int incl = cnt;
+        for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(FULLMASK, incl, o); if (lane >= o) incl += t; }
+        const int nc = __shfl_sync(FULLMASK, incl, 31);
+        if (nc == 0) continue;                               // returned None (contactnetwork.py:294)
+        const int d = dx < nc ? dx : nc;
         const int agx = c.agent[c.first[x]];
-        long long toff = -1;
         int npick = d;
+        long long toff = -1;
         if (g.day.mode == MTD_MODE_REPLAY) {
-            long long r = tape_find_sel(g.tape, cell, agx);
-            if (r < 0) { if (lane == 0) atomicAdd(&g.ctr->tape_miss, 1); continue; }
-            toff = g.tape.sel_off[r];
-            int cnt = g.tape.sel_off[r + 1] - (int)toff;
-            if (cnt != d) { if (lane == 0) atomicAdd(&g.ctr->tape_miss, 1); if (cnt < npick) npick = cnt; }
-        } else {
-            // partial Fisher-Yates over the ordered candidate list, Philox keyed by (day, cell, main agent, draw)
-            for (int t = lane; t < d; t += 32) {
-                uint32_t w[4];
-                philox4x32((uint32_t)g.day.day, (uint32_t)cell, (uint32_t)agx, (uint32_t)(t >> 2), g.day.seed, SITE_SELECT, w);
-                swp[t] = (uint16_t)(t + (int)__umulhi(w[t & 3], (uint32_t)(nc - t)));
-            }
-            __syncwarp();
-            if (lane == 0) {
-                for (int t = 0; t < d; t++) { int r = swp[t]; uint16_t tmp = c.cand[t]; c.cand[t] = c.cand[r]; c.cand[r] = tmp; }
-            }
-            __syncwarp();
+            long long tr = tape_find_sel(g.tape, cell, agx);
+            if (tr < 0) { if (lane == 0) atomicAdd(&g.ctr->tape_miss, 1); continue; }
+            toff = g.tape.sel_off[tr];
+            int tc = g.tape.sel_off[tr + 1] - (int)toff;
+            if (tc != d) { if (lane == 0) atomicAdd(&g.ctr->tape_miss, 1); if (tc < npick) npick = tc; }
         }
+        int made = 0;
         for (int t0 = 0; t0 < npick; t0 += 32) {
-            int t = t0 + lane;
-            if (t < npick) {
-                int y;
-                bool ok = true;
+            uint32_t wv = 0;
+            if (toff < 0 && t0 + lane < npick) {
+                uint32_t w4[4];
+                const int t = t0 + lane;
+                philox4x32((uint32_t)g.day.day, (uint32_t)cell, (uint32_t)agx, (uint32_t)(t >> 2), g.day.seed, SITE_SELECT, w4);
+                wv = pick4(w4, t & 3);
+            }
+            const int tend = min(32, npick - t0);
+            for (int tt = 0; tt < tend; tt++) {
+                const int t = t0 + tt;
+                int y = -1;
                 if (toff >= 0) {
-                    int pi = g.tape.sel_picks[toff + t];
-                    if (pi < 0 || pi >= nc) { ok = false; atomicAdd(&g.ctr->tape_miss, 1); pi = 0; }
-                    y = c.cand[pi];
-                } else y = c.cand[t];
-                if (ok) {
-                    int a, b, st, en, dur;
-                    pair_row(c, x, y, a, b, st, en, dur);
-                    if (n_rows + t < row_cap) {
-                        RowRec r;
-                        r.a1 = c.agent[c.first[a]]; r.a2 = c.agent[c.first[b]];
-                        r.sed = (uint32_t)st | ((uint32_t)en << 8) | ((uint32_t)dur << 16);
-                        r.slot = slot;
-                        rows[n_rows + t] = r;
-                    } else g.ctr->error = MTD_E_CAPACITY;
-                    c.deg[y] -= 1;                        // distinct partners: no two lanes touch the same entry
+                    // replay: the reference's selected partner (agent id) -> local index through the cell's hash
+                    const int pid = g.tape.sel_picks[toff + t];
+                    uint32_t h = ((uint32_t)pid * 2654435761u) & (H - 1);
+                    while (true) {
+                        uint32_t v = c.hash[h];
+                        if (v == 0) break;
+                        if (c.agent[v - 1] == pid) { y = c.la[v - 1]; break; }
+                        h = (h + 1) & (H - 1);
+                    }
+                    bool ok = false;
+                    if (y >= 0 && lane == (y >> 5)) ok = (cw >> (y & 31)) & 1u;
+                    ok = __any_sync(FULLMASK, ok);
+                    if (!ok) { if (lane == 0) atomicAdd(&g.ctr->tape_miss, 1); continue; }
+                    if (lane == (y >> 5)) { cw &= ~(1u << (y & 31)); }
+                } else {
+                    const uint32_t wt = __shfl_sync(FULLMASK, wv, tt);
+                    const int r = (int)__umulhi(wt, (uint32_t)(nc - t));          // r-th remaining candidate
+                    const uint32_t le = __ballot_sync(FULLMASK, incl > r);
+                    const int Lw = __ffs(le) - 1;                                  // word that holds it
+                    int yy = 0;
+                    if (lane == Lw) {
+                        int bit = nth_set_bit(cw, r - (incl - cnt));
+                        cw &= ~(1u << bit); cnt -= 1;
+                        yy = Lw * 32 + bit;
+                    }
+                    if (lane >= Lw) incl -= 1;
+                    y = __shfl_sync(FULLMASK, yy, Lw);
                 }
+                if (lane == (y >> 5)) {                      // partner degree - 1; dead at 0 (delete_all_pairs_by_id)
+                    int nd = (int)c.deg[y] - 1;
+                    c.deg[y] = (int16_t)nd;
+                    if (nd == 0) alive &= ~(1u << (y & 31));
+                }
+                if (lane == 0) c.cand[made] = (uint16_t)y;
+                made++;
             }
         }
-        if (lane == 0) c.deg[x] = (int16_t)(d - npick);  // main agent's degree is spent
-        n_rows += npick;
+        if (lane == (x >> 5)) { c.deg[x] = (int16_t)(d - npick); if (d - npick == 0) alive &= ~(1u << (x & 31)); }
+        __syncwarp();
+        for (int t = lane; t < made; t += 32) {
+            const int y = c.cand[t];
+            bool x_first; int st, en, dur;
+            pair_row_lists(c, x, y, x_first, st, en, dur);
+            if (n_rows + t < row_cap) {
+                RowRec rr;
+                const int agy = c.agent[c.first[y]];
+                rr.a1 = x_first ? agx : agy; rr.a2 = x_first ? agy : agx;
+                rr.sed = (uint32_t)st | ((uint32_t)en << 8) | ((uint32_t)dur << 16);
+                rr.slot = slot;
+                rows[n_rows + t] = rr;
+            } else g.ctr->error = MTD_E_CAPACITY;
+        }
+        n_rows += made;
         __syncwarp();
     }
     if (lane == 0) g.slot_nrows[slot] = n_rows < row_cap ? n_rows : row_cap;
@@ -443,7 +706,7 @@ __device__ void process_cell(const DevCtx &g, unsigned char *sm, int slot, int l
 }
 
 template <int MM, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) k1_kernel(DevCtx g, int cls)
+__global__ void __launch_bounds__(WARPS * 32) k1_large_kernel(DevCtx g, int cls)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -457,7 +720,7 @@ __global__ void __launch_bounds__(WARPS * 32) k1_kernel(DevCtx g, int cls)
         if (lane == 0) w = atomicAdd(&g.ctr->class_cursor[cls], 1);
         w = __shfl_sync(FULLMASK, w, 0);
         if (w >= total) break;
-        process_cell<MM>(g, sm, list[w], lane, acc_pairs, acc_pot);
+        process_cell_large<MM>(g, sm, list[w], lane, acc_pairs, acc_pot);
     }
     if (lane == 0 && (acc_pairs | acc_pot)) {
         atomicAdd(&g.ctr->pairs_evaluated, acc_pairs);
@@ -466,18 +729,33 @@ __global__ void __launch_bounds__(WARPS * 32) k1_kernel(DevCtx g, int cls)
 }
 
 template <int MM, int WARPS>
-void launch_class(const DevCtx &c, int cls, cudaStream_t st, int sm_count)
+int launch_large(const DevCtx &c, int cls, cudaStream_t st, int sm_count)
 {
     size_t smem = Lay<MM>::bytes * WARPS;
     static bool configured = false;
     if (!configured) {
-        cudaFuncSetAttribute(k1_kernel<MM, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(k1_large_kernel<MM, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         configured = true;
     }
-    int per_sm = 1;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_kernel<MM, WARPS>, WARPS * 32, smem);
-    if (per_sm < 1) per_sm = 1;
-    k1_kernel<MM, WARPS><<<sm_count * per_sm, WARPS * 32, smem, st>>>(c, cls);
+    static int per_sm = 0;
+    if (per_sm == 0) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_large_kernel<MM, WARPS>, WARPS * 32, smem);
+        if (per_sm < 1) per_sm = 1;
+    }
+    k1_large_kernel<MM, WARPS><<<sm_count * per_sm, WARPS * 32, smem, st>>>(c, cls);
+    return 1;
+}
+
+template <int G>
+int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count)
+{
+    static int per_sm = 0;
+    if (per_sm == 0) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_small_kernel<G>, K1S_THREADS, 0);
+        if (per_sm < 1) per_sm = 1;
+    }
+    k1_small_kernel<G><<<sm_count * per_sm, K1S_THREADS, 0, st>>>(c, cls);
+    return 1;
 }
 
 }  // namespace
@@ -485,9 +763,12 @@ void launch_class(const DevCtx &c, int cls, cudaStream_t st, int sm_count)
 int launch_k1(const DevCtx &c, cudaStream_t st, int sm_count)
 {
     // big cells first: they are the long poles
-    launch_class<1024, 1>(c, 3, st, sm_count);
-    launch_class<320, 2>(c, 2, st, sm_count);
-    launch_class<128, 4>(c, 1, st, sm_count);
-    launch_class<32, 8>(c, 0, st, sm_count);
-    return 4;
+    int n = 0;
+    n += launch_large<1024, 1>(c, 5, st, sm_count);
+    n += launch_large<320, 2>(c, 4, st, sm_count);
+    n += launch_large<128, 4>(c, 3, st, sm_count);
+    n += launch_small<32>(c, 2, st, sm_count);
+    n += launch_small<16>(c, 1, st, sm_count);
+    n += launch_small<8>(c, 0, st, sm_count);
+    return n;
 }

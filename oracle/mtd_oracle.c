@@ -395,11 +395,22 @@ static int64_t run_cell(const mtdo_params *P, const mtdo_dayctx *D, cellws *W, i
             ntp = D->tape->sel_off[r + 1] - D->tape->sel_off[r];
             if (ntp != degree) { S->tape_miss++; if (ntp > degree) ntp = degree; }
         } else {
-            for (int64_t t = 0; t < degree; t++) {                       /* partial Fisher-Yates on the ordered list */
+            /* Philox mode (this project's own draw scheme; the distribution equals shuffle + choice(replace=False):
+             * a uniformly random ordered `degree`-subset).  The candidates are put in CANONICAL order (ascending
+             * local agent index = order of first appearance in the cell) and draw t takes the r_t-th REMAINING
+             * candidate, r_t = floor(u_t * (nc - t)); the taken candidate is removed, order kept. */
+            for (int64_t i = 1; i < nc; i++) {                           /* insertion sort by local index */
+                int32_t v = W->cand[i]; int64_t j = i - 1;
+                while (j >= 0 && W->cand[j] > v) { W->cand[j + 1] = W->cand[j]; j--; }
+                W->cand[j + 1] = v;
+            }
+            for (int64_t t = 0; t < degree; t++) {
                 uint32_t w[4];
                 philox_site(D, MTDO_SITE_SELECT, (uint32_t)cellid, (uint32_t)W->ids[x], (uint32_t)(t >> 2), w);
                 int64_t r = t + (int64_t)(((uint64_t)w[t & 3] * (uint64_t)(nc - t)) >> 32);
-                int32_t tmp = W->cand[t]; W->cand[t] = W->cand[r]; W->cand[r] = tmp;
+                int32_t y = W->cand[r];                                  /* cand[t..nc) = remaining, ascending */
+                for (int64_t j = r; j > t; j--) W->cand[j] = W->cand[j - 1];
+                W->cand[t] = y;
             }
             ntp = degree;
         }

@@ -127,7 +127,7 @@ def unpack_sched(v):
 class TapeArrays:
     """Sorted key/value arrays of one day's replay tape."""
 
-    def __init__(self, sel_cell, sel_agent, sel_off, sel_picks, pair_key, pair_u, expo_agent, expo_row):
+    def __init__(self, sel_cell, sel_agent, sel_off, sel_picks, pair_key, pair_u, expo_agent, expo_row, sel_ids=None):
         sk = (sel_cell.astype(np.uint64) << np.uint64(32)) | sel_agent.astype(np.uint32).astype(np.uint64)
         order = np.argsort(sk, kind="stable")
         self.sel_key = np.ascontiguousarray(sk[order])
@@ -136,6 +136,12 @@ class TapeArrays:
         self.sel_off[1:] = np.cumsum(lens)
         self.sel_picks = np.concatenate([sel_picks[sel_off[i]:sel_off[i + 1]] for i in order]).astype(np.int32) \
             if len(order) else np.zeros(0, np.int32)
+        # the same selections as partner AGENT IDS (what the product's tape holds; the oracle keeps the indices into the
+        # reference-ordered candidate list, which also pins its restatement of the dict insertion order)
+        self.sel_ids = None
+        if sel_ids is not None:
+            self.sel_ids = np.concatenate([sel_ids[sel_off[i]:sel_off[i + 1]] for i in order]).astype(np.int32) \
+                if len(order) else np.zeros(0, np.int32)
         k1 = (pair_key[:, 0].astype(np.uint64) << np.uint64(32)) | pair_key[:, 1].astype(np.uint32).astype(np.uint64)
         k2 = pair_key[:, 2].astype(np.uint32)
         po = np.lexsort((k2, k1))

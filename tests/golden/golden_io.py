@@ -74,9 +74,18 @@ def load_day(z, day) -> GoldenDay:
         states.append(st)
     g.pre, g.post = states
     ek = z[p + "expo_key"]
+    # selected partner ids: the reference creates one contact row per pick, in pick order (contactnetwork.py:386-424),
+    # and the tape's selection records are in call order -> walk both in step
+    so, sa = z[p + "sel_off"], z[p + "sel_agent"]
+    sel_ids = np.zeros(int(so[-1]) if len(so) else 0, np.int32)
+    assert len(sel_ids) == len(g.contacts)
+    for i in range(len(sa)):
+        r = g.contacts[so[i]:so[i + 1]]
+        assert np.all((r[:, 1] == sa[i]) | (r[:, 2] == sa[i]))
+        sel_ids[so[i]:so[i + 1]] = np.where(r[:, 1] == sa[i], r[:, 2], r[:, 1])
     g.tape = mo.TapeArrays(z[p + "sel_cell"], z[p + "sel_agent"], z[p + "sel_off"], z[p + "sel_picks"],
                            z[p + "pair_key"], z[p + "pair_u"], ek[:, 3] if len(ek) else np.zeros(0, np.int32),
-                           z[p + "expo_row"])
+                           z[p + "expo_row"], sel_ids=sel_ids)
     g.expo_key = ek
     g.expo_ts_off, g.expo_ts = z[p + "expo_ts_off"], z[p + "expo_ts"]
     g.pair_key, g.pair_u = z[p + "pair_key"], z[p + "pair_u"]

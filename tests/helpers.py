@@ -41,7 +41,7 @@ def state_diff(dev: dict, st: mo.AgentState):
 
 
 def set_tape(h, tape: mo.TapeArrays):
-    h.set_tape(tape.sel_key, tape.sel_off, tape.sel_picks, tape.pair_k1, tape.pair_k2, tape.pair_u, tape.expo_agent,
+    h.set_tape(tape.sel_key, tape.sel_off, tape.sel_ids, tape.pair_k1, tape.pair_k2, tape.pair_u, tape.expo_agent,
                tape.expo_row)
 
 
