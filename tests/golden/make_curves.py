@@ -50,7 +50,8 @@ def one(seed, out_path):
                    dyn=(d["mhd"], int(d["testing_enabled"]), int(d["quarantine_enabled"])),
                    incidence=len(d["exposed_ids"]),
                    occupancy=np.bincount(post["seir"].astype(np.int64), minlength=6)[:6],
-                   cell_type=d["all_cell_type"], cell_indid=d["all_cell_indid"])
+                   cell_type=d["all_cell_type"], cell_indid=d["all_cell_indid"], ext_ids=list(d["ext_ids"]),
+                   ext_epi={k: v.get("state_transition_by_day") or [] for k, v in d["ext_epi"].items()})
         comp["days"].append(rec)
         # drop the heavy tape of this day: only the curves are wanted here
         d["tape_sel"] = d["tape_pair_u"] = d["tape_expo"] = None
@@ -88,9 +89,13 @@ def one(seed, out_path):
         present[i, d["ids"]] = True
         new = d["ids"] if i == 0 else d["ids"][~present[i - 1, d["ids"]]]
         seir = dict(zip(d["ids"].tolist(), d["seir"].tolist()))
-        for a in new.tolist():
+        # arrivals + agents whose state the itinerary stage set outside the hot path (tourist entry infection,
+        # re-entry infection of returning locals, day-1 infectious: itinerary.py:392,645,1578,1584)
+        inject = sorted(set(new.tolist()) | set(a for a in d["ext_ids"] if a in seir))
+        for a in inject:
             arr_state.append((d["day"], a, seir[a], d["inf_type"].get(a, 0), d["inf_sev"].get(a, 0)))
-            for (dd, t, ts) in d["pre_epi"].get(a, []):
+            ent = d["ext_epi"].get(a) if a in d["ext_epi"] else d["pre_epi"].get(a, [])
+            for (dd, t, ts) in ent or []:
                 arr_sched.append((d["day"], a, dd, t, ts))
         for a, v in d["vacc"].items():
             if last.get(a) != v:

@@ -123,6 +123,8 @@ class Recorder:
         self.ctx_site = None
         self.enabled = False
         self.advance_calls = []  # KAT records of seirstateutil.update_agent_state (seirstateutil.py:38)
+        self.in_uas = False
+        self.ext_ids = set()     # agents whose SEIR state the itinerary stage set since the last boundary
         self.n_agents_total = None
 
 
@@ -206,6 +208,9 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
         d["cell_indid"] = np.array([int(self.indids_by_cellid[c]) if (c in self.indids_by_cellid and self.indids_by_cellid[c] is not None) else -1
                                     for c in ucells], dtype=np.int16)
         d["pre"] = snap_state(self)
+        d["ext_ids"] = sorted(rec.ext_ids)   # entry / re-entry / day-1 infections set by itinerary.py:392,645,1578,1584
+        d["ext_epi"] = flat_epi(self.agents_epi, d["ext_ids"])
+        rec.ext_ids.clear()
         d["pre_epi"] = flat_epi(self.agents_epi, act)
         n_before = len(vu.directcontacts_by_simcelltype_by_day)
         d["tape_sel"] = []      # (cell, main_agent, n_candidates, [indices into unshuffled candidate list])
@@ -236,6 +241,13 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
     orig_uas = ssu.update_agent_state
 
     def patched_uas(agents_seir_state, agents_infection_type, agents_infection_severity, agentid, agent, agentindex, day):
+        rec.in_uas = True
+        try:
+            return _patched_uas(agents_seir_state, agents_infection_type, agents_infection_severity, agentid, agent, agentindex, day)
+        finally:
+            rec.in_uas = False
+
+    def _patched_uas(agents_seir_state, agents_infection_type, agents_infection_severity, agentid, agent, agentindex, day):
         sched = agent["state_transition_by_day"]
         if not sched:
             return orig_uas(agents_seir_state, agents_infection_type, agents_infection_severity, agentid, agent, agentindex, day)
@@ -252,6 +264,15 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
         return out
 
     ssu.update_agent_state = patched_uas
+
+    orig_assu = ssu.agents_seir_state_update
+
+    def patched_assu(agents_seir_state, new_seir_state, agent_id_or_idx, *a, **k):
+        if not rec.enabled and not rec.in_uas:   # outside the contact-network stage and not the daily advance
+            rec.ext_ids.add(int(agent_id_or_idx))
+        return orig_assu(agents_seir_state, new_seir_state, agent_id_or_idx, *a, **k)
+
+    ssu.agents_seir_state_update = patched_assu
 
     # ---------------- per-cell context ----------------
     orig_by_cell = cn.ContactNetwork.simulate_contact_network_by_cellid
