@@ -1,0 +1,99 @@
+"""The reference-shaped Python API (mtdcovabm_b200.contactnetwork / seirstateutil) driven the way the reference drives
+its own classes (contactnetwork_mp.py:287-304, itinerary.py:399): dict containers in, dict containers mutated in place.
+Replay mode against the golden days of the unmodified reference."""
+from types import SimpleNamespace
+
+import numpy as np
+import pytest
+
+from mtdcovabm_b200 import params as prm
+from oracle import mtd_oracle as mo
+from tests.golden import golden_io as gio
+
+pytestmark = pytest.mark.gpu
+NONE = -32768
+
+
+class FakeStatic:
+    """agents_static.get(id, name) (static.py:351-363)"""
+    def __init__(self, st):
+        self.st = st
+
+    def get(self, a, name):
+        return {"age_bracket_index": self.st.age_bracket, "epi_age_bracket_index": self.st.epi_age_bracket,
+                "soc_rate": self.st.soc_rate, "res_cellid": self.st.res_cellid}[name][a]
+
+
+def _rec(row):
+    return None if row[0] == NONE else [int(x) for x in row]
+
+
+def reference_containers(g, st):
+    ids = np.nonzero(st.seir != 0)[0]
+    epi = {}
+    for a in set(ids.tolist()) | set(g.act_ids.tolist()):
+        epi[a] = {"state_transition_by_day": [list(mo.unpack_sched(v)) for v in st.sched[a, :st.sched_cnt[a]]],
+                  "test_day": _rec(st.test_day[a]), "test_result_day": _rec(st.test_result_day[a]),
+                  "quarantine_days": _rec(st.quarantine[a]), "hospitalisation_days": _rec(st.hosp[a]),
+                  "vaccination_days": None}
+    cat = {}
+    for c, a, s, e in zip(g.iv_cell, g.iv_agent, g.iv_start, g.iv_end):
+        cat.setdefault(int(c), []).append((int(a), int(s), int(e)))
+    vu = SimpleNamespace(cells_agents_timesteps=cat, directcontacts_by_simcelltype_by_day=[],
+                         agents_seir_state={int(a): int(st.seir[a]) for a in ids},
+                         agents_infection_type={int(a): int(st.inf_type[a]) for a in ids},
+                         agents_infection_severity={int(a): int(st.inf_sev[a]) for a in ids},
+                         agents_vaccination_doses={int(a): [int(st.last_dose_day[a])] for a in ids
+                                                   if st.last_dose_day[a] != NONE})
+    return epi, vu
+
+
+@pytest.mark.parametrize("name,day", list(gio.all_days()))
+def test_contactnetwork_dropin_replays_reference_day(name, day):
+    from mtdcovabm_b200.contactnetwork import ContactNetwork
+    z = gio.load_run(name)
+    g = gio.load_day(z, day)
+    epi, vu = reference_containers(g, g.pre)
+    dyn = SimpleNamespace(masks_hygiene_distancing_multiplier=g.mhd, testing_enabled=g.testing_enabled,
+                          quarantine_enabled=g.quarantine_enabled, contact_tracing_enabled=g.contact_tracing_enabled)
+    cells_type = {c: int(t) for c, t in enumerate(g.cell_type) if t >= 0}
+    indids = {c: int(v) for c, v in enumerate(g.cell_indid) if v >= 0}
+    cn = ContactNetwork(g.n_locals, g.N - g.n_locals, 1.0, FakeStatic(g.pre), epi, vu, cells_type, indids, {}, {}, {},
+                        prm.load_json("contactnetwork.json"), prm.load_json(gio.RUNS[name]), dyn, mode="replay",
+                        tape=g.tape)
+    pidx, updated, partial, vu2 = cn.simulate_contact_network(g.day, g.weekday)
+    assert pidx == -1 and vu2 is vu
+    assert vu.directcontacts_by_simcelltype_by_day == g.contacts.tolist()      # rows, in the reference's order
+    assert updated == g.exposed_ids.tolist()
+    assert set(partial) == set(updated)
+    post = g.post
+    for a in updated:
+        assert partial[a] is epi[a]
+        assert epi[a]["state_transition_by_day"] == [list(mo.unpack_sched(v)) for v in post.sched[a, :post.sched_cnt[a]]]
+        assert epi[a]["test_day"] == _rec(post.test_day[a]) and epi[a]["test_result_day"] == _rec(post.test_result_day[a])
+        assert epi[a]["hospitalisation_days"] == _rec(post.hosp[a]) and epi[a]["quarantine_days"] == _rec(post.quarantine[a])
+        assert (vu.agents_seir_state[a], vu.agents_infection_type[a], vu.agents_infection_severity[a]) == \
+            (post.seir[a], post.inf_type[a], post.inf_sev[a])
+    # everybody else is untouched
+    for a in np.nonzero(post.seir != 0)[0]:
+        assert vu.agents_seir_state[int(a)] == post.seir[a]
+
+
+def test_update_agent_state_scalar_matches_reference_calls():
+    """seirstateutil.update_agent_state, same 7 arguments and return tuple, on calls the reference made"""
+    from mtdcovabm_b200 import seirstateutil as ssu
+    z = gio.load_run("ref_1k_strict_seed7")
+    da = z["adv_day_agent"]; bo, b, ao, a = z["adv_before_off"], z["adv_before"], z["adv_after_off"], z["adv_after"]
+    pre, post, applied = z["adv_pre"], z["adv_post"], z["adv_applied"]
+    fired = np.nonzero(applied)[0][:40]
+    idle = np.nonzero(applied == 0)[0][:10]
+    for i in list(fired) + list(idle):
+        day, ag = int(da[i, 0]), int(da[i, 1])
+        agent = {"state_transition_by_day": [[int(x) for x in e] for e in b[bo[i]:bo[i + 1]]]}
+        s, t, v = {ag: int(pre[i, 0])}, {ag: int(pre[i, 1])}, {ag: int(pre[i, 2])}
+        out = ssu.update_agent_state(s, t, v, ag, agent, ag, day)
+        assert (out is not None) == bool(applied[i])
+        assert (s[ag], t[ag], v[ag]) == tuple(int(x) for x in post[i])
+        assert agent["state_transition_by_day"] == [[int(x) for x in e] for e in a[ao[i]:ao[i + 1]]]
+        if out is not None:
+            assert int(out[0]) == int(post[i, 0]) and int(out[1]) == int(pre[i, 0])
