@@ -675,3 +675,186 @@ int64_t mtdo_advance(int32_t day, mtdo_agents *A, const uint8_t *mask)
     }
     return fired;
 }
+
+/* ------------------------------------------------------------------ contact tracing (epidemiology.py:667-834)
+ * Draw slots of one primary contact p in Philox mode (site MTDO_SITE_TRACE_PRIM, counter (day, p, slot, 0)):
+ *   0 quarantine timestep, 1 quarantine uniform, 2 test timestep, 3 testing days, 4 result days,
+ *   16 + t        : t-th draw of the secondary selection (rank among the remaining members),
+ *   65536 + 8 j + {0 ts, 1 u, 2 ts, 3 testing days, 4 result days} : j-th selected secondary contact.
+ * In replay mode the same draws are consumed positionally from the primary's tape record. */
+typedef struct {
+    const mtdo_dayctx *D; const mtdo_params *P; int32_t p; const double *rec; int64_t len, pos; mtdo_trace_stats *S;
+} tracedraws;
+
+static double td_next(tracedraws *T) { if (T->pos >= T->len) { T->S->tape_miss++; return 0.0; } return T->rec[T->pos++]; }
+
+static int td_ts(tracedraws *T, uint32_t slot)
+{
+    if (T->D->mode == MTDO_MODE_REPLAY) return (int)td_next(T);
+    uint32_t w[4]; philox_site(T->D, MTDO_SITE_TRACE_PRIM, (uint32_t)T->p, slot, 0, w);
+    return 42 + (int)(((uint64_t)w[0] * 79u) >> 32);
+}
+static double td_u(tracedraws *T, uint32_t slot)
+{
+    if (T->D->mode == MTDO_MODE_REPLAY) return td_next(T);
+    uint32_t w[4]; philox_site(T->D, MTDO_SITE_TRACE_PRIM, (uint32_t)T->p, slot, 0, w);
+    return mtdo_u53(w[0], w[1]);
+}
+static int td_ln(tracedraws *T, uint32_t slot, double mu, double sigma)
+{
+    if (T->D->mode == MTDO_MODE_REPLAY) return (int)td_next(T);
+    uint32_t w[4]; philox_site(T->D, MTDO_SITE_TRACE_PRIM, (uint32_t)T->p, slot, 0, w);
+    double u1 = mtdo_u53(w[0], w[1]), u2 = mtdo_u53(w[2], w[3]);
+    double z = sqrt(-2.0 * log(1.0 - u1)) * cos(6.283185307179586 * u2);
+    return (int)py_round(exp(mu + sigma * z));
+}
+
+/* schedule_quarantine (epidemiology.py:568-625) for PositiveContact (2) / SecondaryContact (3) on record `r` */
+static void trace_quarantine(tracedraws *T, mtdo_agents *A, int32_t r, int day, int ts, int qtype, uint32_t uslot)
+{
+    if (!T->D->quarantine_enabled) return;
+    double u = td_u(T, uslot);
+    if (u < T->P->ignore_quarantine_rules_probability) return;
+    int start = day, end;
+    if (qtype == Q_POSITIVE_CONTACT) { start += T->P->contact_tracing_positive_delay_days; end = start + T->P->quarantine_positive_contact_duration; }
+    else { start += T->P->contact_tracing_secondary_delay_days; end = start + T->P->quarantine_secondary_contact_duration; }
+    int32_t *q = A->quarantine + 3 * (int64_t)r;
+    if (q[0] != MTDO_NONE && start >= q[0]) return;          /* not rescheduled at the same or a later date (:606-611) */
+    q[0] = start; q[1] = ts; q[2] = end;
+}
+
+/* schedule_test (epidemiology.py:502-565) for PositiveContact / SecondaryContact on record `r` */
+static void trace_test(tracedraws *T, mtdo_agents *A, int32_t r, int day, int ts, int qtype, uint32_t lnslot)
+{
+    if (!T->D->testing_enabled) return;
+    int32_t *td = A->test_day + 2 * (int64_t)r, *tr = A->test_result_day + 2 * (int64_t)r;
+    if (td[0] != MTDO_NONE) return;                            /* a test is already scheduled (:519-521) */
+    int days = (qtype == Q_POSITIVE_CONTACT) ? T->P->contact_tracing_positive_delay_days : T->P->contact_tracing_secondary_delay_days;
+    days += td_ln(T, lnslot, T->P->test_mu, T->P->test_sigma);
+    int tday = day + days;
+    int rday = tday + td_ln(T, lnslot + 1, T->P->result_mu, T->P->result_sigma);
+    td[0] = tday; td[1] = ts; tr[0] = rday; tr[1] = ts;
+}
+
+static int64_t trace_find_scan(const mtdo_trace_tape *T, uint64_t key)
+{
+    int64_t lo = 0, hi = T->n_scan;
+    while (lo < hi) { int64_t mid = (lo + hi) >> 1; if (T->scan_key[mid] < key) lo = mid + 1; else hi = mid; }
+    return (lo < T->n_scan && T->scan_key[lo] == key) ? lo : -1;
+}
+
+int64_t mtdo_contact_tracing(const mtdo_params *P, const mtdo_dayctx *D, const mtdo_trace_tape *T, int64_t n_traced,
+                             const int32_t *traced, int64_t n_slices, const int64_t *slice_off, const int32_t *rows3,
+                             int64_t n_res_cells, const int64_t *res_off, const int32_t *res_nres,
+                             const int32_t *res_members, mtdo_agents *A, const uint8_t *epi_present, int32_t n_locals,
+                             uint8_t *primary, uint8_t *secondary, mtdo_trace_stats *S)
+{
+    const int64_t N = A->n_agents;
+    uint8_t *is_traced = (uint8_t *)calloc((size_t)N + 1, 1);
+    for (int64_t i = 0; i < n_traced; i++) if (traced[i] >= 0 && traced[i] < N) is_traced[traced[i]] = 1;
+    memset(primary, 0, (size_t)N); memset(secondary, 0, (size_t)N);
+    memset(S, 0, sizeof(*S));
+
+    /* ---- scan of the look-back slices (:677-721) ---- */
+    for (int64_t back = 0; back < n_slices; back++) {
+        for (int64_t r = slice_off[back]; r < slice_off[back + 1]; r++) {
+            int sct = rows3[3 * r], a1 = rows3[3 * r + 1], a2 = rows3[3 * r + 2];
+            int f1 = is_traced[a1], f2 = is_traced[a2];
+            if (f1 == f2) continue;                                         /* exactly one endpoint is a traced positive */
+            double u;
+            uint64_t idx = (uint64_t)(r - slice_off[back]);
+            if (D->mode == MTDO_MODE_REPLAY) {
+                int64_t t = trace_find_scan(T, ((uint64_t)back << 32) | idx);
+                if (t < 0) { S->tape_miss++; continue; }
+                u = T->scan_u[t];
+            } else {
+                uint32_t w[4];
+                philox_site(D, MTDO_SITE_TRACE, (uint32_t)back, (uint32_t)idx, 0, w);
+                u = mtdo_u53(w[0], w[1]);
+            }
+            S->n_scan_draws++;
+            if (u < P->tracing_success_prob[sct]) primary[f1 ? a2 : a1] = 1;    /* :714-721 */
+        }
+    }
+
+    /* ---- processing order of the primary contacts: the reference iterates a Python set (:723); replay takes the
+     * recorded order, Philox mode uses ascending agent id ---- */
+    int64_t np_ = 0;
+    for (int64_t a = 0; a < N; a++) np_ += primary[a];
+    int32_t *order = (int32_t *)malloc(sizeof(int32_t) * (size_t)(np_ + 1));
+    if (D->mode == MTDO_MODE_REPLAY) {
+        int64_t k = 0;
+        for (int64_t i = 0; i < T->n_prim && k < np_; i++) {
+            if (primary[T->prim_id[i]]) order[k++] = T->prim_id[i]; else S->tape_miss++;
+        }
+        /* primaries without an epi record are skipped by the reference before any draw (:729-733): not on the tape */
+        for (int64_t a = 0; a < N && k < np_; a++) {
+            if (!primary[a]) continue;
+            int seen = 0;
+            for (int64_t i = 0; i < T->n_prim; i++) if (T->prim_id[i] == a) { seen = 1; break; }
+            if (!seen) { if (epi_present && !epi_present[a]) order[k++] = (int32_t)a; else { S->tape_miss++; order[k++] = (int32_t)a; } }
+        }
+    } else {
+        int64_t k = 0;
+        for (int64_t a = 0; a < N; a++) if (primary[a]) order[k++] = (int32_t)a;
+    }
+
+    uint8_t *res_done = (uint8_t *)calloc((size_t)n_res_cells + 1, 1);
+    int32_t *sel = NULL; int64_t sel_cap = 0;
+    for (int64_t oi = 0; oi < np_; oi++) {
+        const int32_t p = order[oi];
+        if (epi_present && !epi_present[p]) continue;                      /* agents_epi[contact_id] missing / empty */
+        tracedraws td = { D, P, p, NULL, 0, 0, S };
+        if (D->mode == MTDO_MODE_REPLAY) {
+            int64_t i = 0;
+            while (i < T->n_prim && T->prim_id[i] != p) i++;
+            if (i < T->n_prim) { td.rec = T->prim_draws + T->prim_off[i]; td.len = T->prim_off[i + 1] - T->prim_off[i]; }
+        }
+        int ts = td_ts(&td, 0);
+        trace_quarantine(&td, A, p, D->day, ts, Q_POSITIVE_CONTACT, 1);
+        ts = td_ts(&td, 2);
+        trace_test(&td, A, p, D->day, ts, Q_POSITIVE_CONTACT, 3);
+        /* secondary contacts: once per residence, triggered by its first primary contact (:737-817) */
+        int32_t res = A->res_cellid[p];
+        if (res < 0 || res >= n_res_cells || res_done[res]) { if (D->mode == MTDO_MODE_REPLAY && td.pos != td.len) S->tape_miss++; continue; }
+        res_done[res] = 1;
+        int64_t L = 0, b = res_off[res], e = res_off[res + 1];
+        if (e - b > sel_cap) { sel_cap = (e - b) * 2 + 16; sel = (int32_t *)realloc(sel, sizeof(int32_t) * (size_t)sel_cap); }
+        for (int64_t q = b; q < e; q++) {
+            int32_t m = res_members[q];
+            if (q - b < res_nres[res] && m == p) continue;                 /* np.delete(resident_ids, == contact_id) */
+            sel[L++] = m;
+        }
+        if (L == 0) { if (D->mode == MTDO_MODE_REPLAY && td.pos != td.len) S->tape_miss++; continue; }
+        int64_t k = (int64_t)py_round((double)L * P->tracing_success_prob[0]);
+        if (k > L) k = L;
+        for (int64_t t = 0; t < k; t++) {                                  /* np.random.choice(sec, k, replace=False) */
+            if (D->mode == MTDO_MODE_REPLAY) {
+                int32_t id = (int32_t)td_next(&td);
+                int64_t r = t; while (r < L && sel[r] != id) r++;
+                if (r == L) { S->tape_miss++; r = t; }
+                int32_t y = sel[r]; for (int64_t j = r; j > t; j--) sel[j] = sel[j - 1]; sel[t] = y;
+            } else {
+                uint32_t w[4];
+                philox_site(D, MTDO_SITE_TRACE_PRIM, (uint32_t)p, (uint32_t)(16 + t), 0, w);
+                int64_t r = t + (int64_t)(((uint64_t)w[0] * (uint64_t)(L - t)) >> 32);
+                int32_t y = sel[r]; for (int64_t j = r; j > t; j--) sel[j] = sel[j - 1]; sel[t] = y;
+            }
+        }
+        for (int64_t j = 0; j < k; j++) {
+            int32_t s = sel[j];
+            if (s < 0 || s >= N || secondary[s] || primary[s]) continue;   /* skip if already handled (:798) */
+            /* quirk B9: the PRIMARY's record is the one offered to schedule_quarantine / schedule_test (:800-809) */
+            uint32_t base = 65536u + 8u * (uint32_t)j;
+            int t1 = td_ts(&td, base);
+            trace_quarantine(&td, A, p, D->day, t1, Q_SECONDARY_CONTACT, base + 1);
+            int t2 = td_ts(&td, base + 2);
+            trace_test(&td, A, p, D->day, t2, Q_SECONDARY_CONTACT, base + 3);
+            secondary[s] = 1;
+        }
+        if (D->mode == MTDO_MODE_REPLAY && td.pos != td.len) S->tape_miss++;
+    }
+    for (int64_t a = 0; a < N; a++) { S->n_primary += primary[a]; S->n_secondary += secondary[a]; }
+    free(is_traced); free(order); free(res_done); free(sel);
+    return S->n_primary + S->n_secondary;
+}

@@ -220,3 +220,55 @@ def advance(day, agents: AgentState, mask=None):
     if mask is not None:
         mask = np.ascontiguousarray(mask, np.uint8)
     return lib().mtdo_advance(C.c_int32(day), C.byref(a), _p(mask))
+
+
+# ---------------------------------------------------------------------------------- contact tracing
+class TraceTape(C.Structure):
+    _fields_ = [("n_scan", C.c_int64), ("scan_key", C.c_void_p), ("scan_u", C.c_void_p),
+                ("n_prim", C.c_int64), ("prim_id", C.c_void_p), ("prim_off", C.c_void_p), ("prim_draws", C.c_void_p)]
+
+
+class TraceStats(C.Structure):
+    _fields_ = [("n_primary", C.c_int64), ("n_secondary", C.c_int64), ("n_scan_draws", C.c_int64),
+                ("tape_miss", C.c_int64)]
+
+
+class TraceTapeArrays:
+    """replay tape of one contact_tracing call (tests/golden/make_golden.py:encode_traces)"""
+
+    def __init__(self, scan_key, scan_u, prim_id, prim_off, prim_draws):
+        o = np.argsort(scan_key, kind="stable")
+        self.scan_key = np.ascontiguousarray(np.asarray(scan_key, np.uint64)[o])
+        self.scan_u = np.ascontiguousarray(np.asarray(scan_u, np.float64)[o])
+        self.prim_id = np.ascontiguousarray(prim_id, np.int32)
+        self.prim_off = np.ascontiguousarray(prim_off, np.int32)
+        self.prim_draws = np.ascontiguousarray(prim_draws, np.float64)
+
+    def struct(self):
+        t = TraceTape()
+        t.n_scan = len(self.scan_key); t.scan_key = self.scan_key.ctypes.data; t.scan_u = self.scan_u.ctypes.data
+        t.n_prim = len(self.prim_id); t.prim_id = self.prim_id.ctypes.data; t.prim_off = self.prim_off.ctypes.data
+        t.prim_draws = self.prim_draws.ctypes.data
+        return t
+
+
+def contact_tracing(params, ctx, tape, traced, slice_off, rows3, res_off, res_nres, res_members, agents: AgentState,
+                    epi_present, n_locals):
+    """Mutates agents.quarantine / test_day / test_result_day.  -> (primary flags, secondary flags, TraceStats)"""
+    L = lib()
+    L.mtdo_contact_tracing.restype = C.c_int64
+    N = agents.n
+    prim = np.zeros(N, np.uint8); sec = np.zeros(N, np.uint8)
+    st = TraceStats()
+    a = agents.struct()
+    traced = np.ascontiguousarray(traced, np.int32); slice_off = np.ascontiguousarray(slice_off, np.int64)
+    rows3 = np.ascontiguousarray(rows3, np.int32)
+    res_off = np.ascontiguousarray(res_off, np.int64); res_nres = np.ascontiguousarray(res_nres, np.int32)
+    res_members = np.ascontiguousarray(res_members, np.int32)
+    epi_present = np.ascontiguousarray(epi_present, np.uint8)
+    ts = tape.struct() if tape is not None else TraceTape()
+    L.mtdo_contact_tracing(C.byref(params), C.byref(ctx), C.byref(ts), C.c_int64(len(traced)), _p(traced),
+                           C.c_int64(len(slice_off) - 1), _p(slice_off), _p(rows3), C.c_int64(len(res_nres)),
+                           _p(res_off), _p(res_nres), _p(res_members), C.byref(a), _p(epi_present), C.c_int32(n_locals),
+                           _p(prim), _p(sec), C.byref(st))
+    return prim, sec, st

@@ -97,3 +97,38 @@ def all_days():
         z = load_run(name)
         for d in z["days"]:
             yield name, int(d)
+
+
+class GoldenTrace:
+    pass
+
+
+def load_trace(z, ti) -> GoldenTrace:
+    """one recorded Epidemiology.contact_tracing call (epidemiology.py:667-834)"""
+    p = "t%02d_" % ti
+    t = GoldenTrace()
+    sc = z[p + "scalars"]
+    t.day, t.testing_enabled, t.quarantine_enabled, t.n_locals = int(sc[0]), bool(sc[1]), bool(sc[2]), int(sc[3])
+    t.traced, t.slice_off, t.rows = z[p + "traced"], z[p + "slice_off"], z[p + "rows"]
+    t.tape = mo.TraceTapeArrays(z[p + "scan_key"], z[p + "scan_u"], z[p + "prim_id"], z[p + "prim_off"], z[p + "prim_draws"])
+    t.primary, t.secondary, t.updated = np.sort(z[p + "prim_id"]), z[p + "secondary"], z[p + "updated"]
+    t.res_off, t.res_nres, t.res_members = z[p + "res_off"], z[p + "res_nres"], z[p + "res_members"]
+    t.epi_present = z[p + "epi_present"]
+    N = len(t.epi_present)
+    states = []
+    for tag in ("pre_", "post_"):
+        st = mo.AgentState(N)
+        st.res_cellid[:] = z[p + "res_cellid"]
+        st.quarantine[:] = z[p + tag + "quar"]; st.test_day[:] = z[p + tag + "test"]
+        st.test_result_day[:] = z[p + tag + "tres"]
+        states.append(st)
+    t.pre, t.post = states
+    return t
+
+
+def all_traces():
+    for name in RUNS:
+        z = load_run(name)
+        if "trace_days" in z.files:
+            for i in range(len(z["trace_days"])):
+                yield name, i

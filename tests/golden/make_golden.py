@@ -143,7 +143,95 @@ def encode_run(rec, keep_days):
         b.extend(a[2]); af.extend(a[5]); bo[i + 1] = len(b); ao[i + 1] = len(af)
     out["adv_before_off"] = bo; out["adv_before"] = np.array(b, dtype=np.int32).reshape(-1, 3)
     out["adv_after_off"] = ao; out["adv_after"] = np.array(af, dtype=np.int32).reshape(-1, 3)
+    if rec.traces:
+        encode_traces(rec, out)
     return out
+
+
+def encode_traces(rec, out, days_back=2):
+    """contact_tracing calls (epidemiology.py:667-834) -> t%02d_* arrays.  Per call: the look-back slices of contact
+    rows exactly as the reference cuts them (start markers, off-by-one of :691-692 included), the traced ids, the keyed
+    scan uniforms, and per primary contact -- in the reference's processing order -- the ordered list of draws it
+    consumed (timesteps, uniforms, rounded log-normal days, selected secondary ids)."""
+    N = rec.days[0]["n_agents_total"]
+    out["trace_days"] = np.array([t["day"] for t in rec.traces], dtype=np.int32)
+    for ti, t in enumerate(rec.traces):
+        p = "t%02d_" % ti
+        day, rows, markers = t["day"], t["rows"], t["markers"]
+        traced = set(t["traced"])
+        ev = t["events"]
+        first_prim = next((i for i, e in enumerate(ev) if e[0] == "sq" and e[2] == 2), len(ev))
+        start_ev = first_prim - 1 if first_prim < len(ev) else len(ev)      # the timestep draw before the first sq
+        scan_us = [e[1] for e in ev[:start_ev] if e[0] == "u"]
+        assert all(e[0] == "u" for e in ev[:start_ev])
+        sl_off, sl_rows, keys, us = [0], [], [], []
+        k = 0
+        for back in range(days_back + 1):
+            d = day - back
+            lo, hi = 0, len(rows)
+            if d in markers:
+                lo = markers[d]
+                if d + 1 in markers:
+                    hi = markers[d + 1] - 1
+                sl = rows[lo:hi]
+            else:
+                sl = rows[:0]
+            for ri, (sct, a1, a2) in enumerate(sl):
+                if (int(a1) in traced) != (int(a2) in traced):
+                    keys.append((back << 32) | ri); us.append(scan_us[k]); k += 1
+            sl_rows.append(sl); sl_off.append(sl_off[-1] + len(sl))
+        assert k == len(scan_us), (k, len(scan_us))
+        out[p + "scalars"] = np.array([day, int(t["testing_enabled"]), int(t["quarantine_enabled"]), t["n_locals"]], np.int64)
+        out[p + "traced"] = np.array(sorted(traced), np.int32)
+        out[p + "slice_off"] = np.array(sl_off, np.int64)
+        out[p + "rows"] = np.concatenate(sl_rows).astype(np.int32).reshape(-1, 3)
+        out[p + "scan_key"] = np.array(keys, np.uint64); out[p + "scan_u"] = np.array(us, np.float64)
+        # per-primary draw records
+        starts = [i - 1 for i, e in enumerate(ev) if e[0] == "sq" and e[2] == 2]
+        prim, off, draws = [], [0], []
+        for j, st in enumerate(starts):
+            en = starts[j + 1] if j + 1 < len(starts) else len(ev)
+            assert ev[st][0] == "ts"
+            prim.append(ev[st + 1][1])
+            for e in ev[st:en]:
+                if e[0] in ("u", "ts", "ln"):
+                    draws.append(float(e[1]))
+                elif e[0] == "sel":
+                    draws.extend(float(x) for x in e[1])
+            off.append(len(draws))
+        out[p + "prim_id"] = np.array(prim, np.int32); out[p + "prim_off"] = np.array(off, np.int32)
+        out[p + "prim_draws"] = np.array(draws, np.float64)
+        out[p + "secondary"] = np.array(sorted({e[1] for e in ev if e[0] == "sq" and e[2] == 3}), np.int32)
+        out[p + "updated"] = np.array(sorted(t["updated"]), np.int32)
+        assert sorted(t["updated"]) == sorted(set(prim) | {e[1] for e in ev if e[0] == "sq" and e[2] == 3})
+        # static + records
+        resc = np.full(N, -1, np.int32); present = np.zeros(N, np.uint8)
+        for a, v in t["res_cellid"].items():
+            if v is not None:
+                resc[a] = v
+        recs = {}
+        for tag, epi in (("pre_", t["pre_epi"]), ("post_", t["post_epi"])):
+            quar = np.full((N, 3), NONE, np.int32); test = np.full((N, 2), NONE, np.int32); tres = np.full((N, 2), NONE, np.int32)
+            for a, e in epi.items():
+                if tag == "pre_":
+                    present[a] = 1
+                for arr, key in ((quar, "quarantine_days"), (test, "test_day"), (tres, "test_result_day")):
+                    v = e.get(key)
+                    if v is not None and len(v) > 0:
+                        arr[a, :len(v)] = v
+            out[p + tag + "quar"], out[p + tag + "test"], out[p + tag + "tres"] = quar, test, tres
+        out[p + "res_cellid"], out[p + "epi_present"] = resc, present
+        # residences CSR: members = residents (minus nobody yet) then staff; accommodation from this call's snapshot
+        cells = dict(rec.residences)
+        for cid, mem in t["accom"].items():
+            if cid in cells and cells[cid][1] == [] and cid not in getattr(rec, "_hh_inst", set()):
+                cells[cid] = (mem, [])
+        ncell = max(cells) + 1 if cells else 1
+        roff = np.zeros(ncell + 1, np.int64); nres = np.zeros(ncell, np.int32); mem = []
+        for c in range(ncell):
+            r, sfx = cells.get(c, ([], []))
+            mem.extend(r); mem.extend(sfx); nres[c] = len(r); roff[c + 1] = len(mem)
+        out[p + "res_off"], out[p + "res_nres"], out[p + "res_members"] = roff, nres, np.array(mem, np.int32)
 
 
 RUNS = [

@@ -124,6 +124,10 @@ class Recorder:
         self.enabled = False
         self.advance_calls = []  # KAT records of seirstateutil.update_agent_state (seirstateutil.py:38)
         self.in_uas = False
+        self.ct_active = False   # inside Epidemiology.contact_tracing
+        self.ct_events = []      # flat, ordered draw / call events of the current contact_tracing call
+        self.traces = []         # one record per contact_tracing call that had work to do
+        self.residences = None   # {res_cellid: (resident ids, staff ids)}
         self.ext_ids = set()     # agents whose SEIR state the itinerary stage set since the last boundary
         self.n_agents_total = None
 
@@ -309,6 +313,12 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
 
     def patched_choice(a, size=None, replace=True, p=None):
         res = orig_choice(a, size=size, replace=replace, p=p)
+        if rec.ct_active:
+            arr = np.asarray(a)
+            if arr.shape == (79,) and arr[0] == 42 and size == 1:
+                rec.ct_events.append(("ts", int(res[0])))
+            else:
+                rec.ct_events.append(("sel", [int(x) for x in res]))
         if not rec.enabled:
             return res
         if sel_state.get("shuffled") is not None and a is sel_state["shuffled"]:
@@ -354,6 +364,8 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
 
     def patched_random():
         u = orig_random()
+        if rec.ct_active:
+            rec.ct_events.append(("u", u))
         if rec.enabled:
             if rec.ctx_expo is not None:
                 site = rec.ctx_site
@@ -401,6 +413,8 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
     epi.Epidemiology.simulate_seir_state_transition = patched_trans
 
     def patched_test(self, agent, agent_id, incremental_days, start_timestep, quarantine_type):
+        if rec.ct_active:
+            rec.ct_events.append(("st", int(agent_id), int(quarantine_type)))
         if rec.ctx_expo is None:
             return orig_test(self, agent, agent_id, incremental_days, start_timestep, quarantine_type)
         rec.ctx_site = "test_u"
@@ -419,6 +433,8 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
 
     def patched_quar(self, agent_id, start_day, start_timestep, quarantine_type, end_day=None, quarantine_days=None,
                      agent=None):
+        if rec.ct_active:
+            rec.ct_events.append(("sq", int(agent_id), int(quarantine_type)))
         if rec.ctx_expo is None:
             return orig_quar(self, agent_id, start_day, start_timestep, quarantine_type, end_day, quarantine_days, agent)
         rec.ctx_site = "quar_u"
@@ -432,6 +448,8 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
 
     def patched_sln(mean, std, size, isInt=False, recomputeparams=True):
         v = orig_sln(mean, std, size, isInt, recomputeparams)
+        if rec.ct_active:
+            rec.ct_events.append(("ln", int(v)))
         if rec.enabled and rec._ln_sink is not None:
             rec._ln_sink.append(v)
         return v
@@ -455,6 +473,66 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
         return patched_choice(a, size=size, replace=replace, p=p)
 
     np.random.choice = site_aware_choice
+
+
+    # ---------------- contact tracing (epidemiology.py:667-834) ----------------
+    orig_ct = epi.Epidemiology.contact_tracing
+
+    def all_epi(self):
+        keys = [int(k) for k in (self.agents_epi.keys() if hasattr(self.agents_epi, "keys") else range(len(self.agents_epi)))]
+        return flat_epi(self.agents_epi, keys)
+
+    def patched_ct(self, day, distributed=False, f=None):
+        vu = self.vars_util
+        traced = sorted(int(x) for x in vu.contact_tracing_agent_ids)
+        if not (self.dyn_params.contact_tracing_enabled and len(traced) > 0):
+            return orig_ct(self, day, distributed, f)
+        if rec.residences is None:
+            rec.residences = {}
+            rec._hh_inst = set()
+            for cells, rk, sk in ((self.cells_households, "resident_uids", "staff_uids"),
+                                  (self.cells_institutions, "resident_uids", "staff_uids"),
+                                  (self.cells_accommodation, "member_uids", None)):
+                for cid, cellv in cells.items():
+                    if int(cid) in rec.residences:      # households win over institutions over accommodation (:752-763)
+                        continue
+                    place = cellv["place"]
+                    res = [int(x) for x in (place.get(rk) if place.get(rk) is not None else [])]
+                    stf = [int(x) for x in (place.get(sk) if sk and place.get(sk) is not None else [])]
+                    rec.residences[int(cid)] = (res, stf)
+                    if sk is not None:
+                        rec._hh_inst.add(int(cid))
+        t = {"day": int(day), "traced": traced,
+             "testing_enabled": bool(self.dyn_params.testing_enabled),
+             "quarantine_enabled": bool(self.dyn_params.quarantine_enabled),
+             "rows": np.array([[int(x) for x in r[:3]] for r in vu.directcontacts_by_simcelltype_by_day],
+                              dtype=np.int32).reshape(-1, 3),
+             "markers": {int(k): int(v) for k, v in vu.directcontacts_by_simcelltype_by_day_start_marker.items()},
+             "n_locals": int(self.n_locals)}
+        t["pre_epi"] = all_epi(self)
+        resc = {}
+        for a in t["pre_epi"].keys():
+            try:
+                resc[a] = int(self.agents_static.get(a, "res_cellid"))
+            except Exception:
+                resc[a] = None
+        t["res_cellid"] = resc
+        # accommodation member lists change as tourists come and go: snapshot them at every call
+        t["accom"] = {int(cid): [int(x) for x in cellv["place"].get("member_uids", [])]
+                      for cid, cellv in self.cells_accommodation.items()}
+        rec.ct_events = []
+        rec.ct_active = True
+        try:
+            out = orig_ct(self, day, distributed, f)
+        finally:
+            rec.ct_active = False
+        t["events"] = rec.ct_events
+        t["updated"] = [int(x) for x in out[1]]
+        t["post_epi"] = all_epi(self)
+        rec.traces.append(t)
+        return out
+
+    epi.Epidemiology.contact_tracing = patched_ct
 
     stdout = sys.stdout
     try:
