@@ -144,6 +144,27 @@ int mtd_get_infection_prob(mtd_handle h, double *p, int64_t cap, int mem);   /* 
 int mtd_occupancy(mtd_handle h, int64_t out[6]);                 /* dynamicstatistics.py:169-193 */
 int mtd_sync(mtd_handle h);
 
+/* ---- K5: contact tracing (Epidemiology.contact_tracing, epidemiology.py:667-834) ----
+ * replay tape of one call (host pointers): scan uniforms keyed by (look-back distance << 32 | row index in its slice),
+ * sorted; per primary contact, in the reference's processing order, the ordered draws it consumed. */
+typedef struct {
+    int64_t n_scan; const uint64_t *scan_key; const double *scan_u;
+    int64_t n_prim; const int32_t *prim_id; const int32_t *prim_off; const double *prim_draws;
+} mtd_trace_tape;
+typedef struct { int64_t n_primary, n_secondary, n_scan_draws, tape_miss; } mtd_trace_stats;
+/* residences (cells_households / cells_institutions / cells_accommodation, epidemiology.py:752-788): CSR over cell ids,
+ * members = residents (the first res_nres[c]) followed by staff */
+int mtd_set_residences(mtd_handle h, int64_t n_res_cells, const int64_t *res_off, const int32_t *res_nres,
+                       const int32_t *res_members, int mem);
+/* traced: vars_util.contact_tracing_agent_ids.  rows3 [n][3] = simcelltype, a1, a2 of the look-back slices the caller
+ * cut from directcontacts_by_simcelltype_by_day (slice s = s days back; slice_off is a HOST array of n_slices + 1).
+ * epi_present (uint8[N], may be NULL = everybody): agents_epi[id] exists.  Updates the quarantine / test records of
+ * the primary contacts in the handle's state. */
+int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_trace_tape *tape, int64_t n_traced,
+                        const int32_t *traced, int64_t n_slices, const int64_t *slice_off, const int32_t *rows3,
+                        const uint8_t *epi_present, int mem);
+int mtd_get_traced(mtd_handle h, uint8_t *primary, uint8_t *secondary, mtd_trace_stats *stats, int mem);
+
 /* Measurement hooks (the reference's per-stage wall-clock columns, sim.py:231-244,1852-1856): with profiling on,
  * CUDA events are recorded on the handle's stream around every stage of the day step; mtd_get_stage_ms
  * synchronises and returns the device time of the LAST execution of each stage and the number of kernels the

@@ -21,7 +21,7 @@ EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mt
            "mtd_set_static", "mtd_set_state", "mtd_get_state", "mtd_set_tape", "mtd_simulate_contact_network",
            "mtd_simulate_direct_contacts", "mtd_apply_deltas", "mtd_advance_seir", "mtd_get_counters",
            "mtd_get_contacts", "mtd_get_exposed", "mtd_get_infection_prob", "mtd_occupancy", "mtd_sync",
-           "mtd_set_profiling", "mtd_get_stage_ms"]
+           "mtd_set_profiling", "mtd_get_stage_ms", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
 
 
@@ -45,6 +45,16 @@ class Counters(C.Structure):
     _fields_ = [("n_slots", C.c_int64), ("n_rows", C.c_int64), ("n_exposed", C.c_int64), ("pairs_evaluated", C.c_int64),
                 ("n_potential", C.c_int64), ("n_si_rows", C.c_int64), ("sched_overflow", C.c_int64),
                 ("tape_miss", C.c_int64), ("class_cells", C.c_int64 * 6), ("error", C.c_int64)]
+
+
+class TraceTape(C.Structure):
+    _fields_ = [("n_scan", C.c_int64), ("scan_key", C.c_void_p), ("scan_u", C.c_void_p),
+                ("n_prim", C.c_int64), ("prim_id", C.c_void_p), ("prim_off", C.c_void_p), ("prim_draws", C.c_void_p)]
+
+
+class TraceStats(C.Structure):
+    _fields_ = [("n_primary", C.c_int64), ("n_secondary", C.c_int64), ("n_scan_draws", C.c_int64),
+                ("tape_miss", C.c_int64)]
 
 
 _lib = None
@@ -179,6 +189,34 @@ class Handle:
 
     def sync(self):
         self._ck(self.lib.mtd_sync(self.h), "mtd_sync")
+
+    # ---- K5 contact tracing
+    def set_residences(self, res_off, res_nres, res_members, mem=MEM_HOST):
+        self._ck(self.lib.mtd_set_residences(self.h, C.c_int64(len(res_nres)), _ptr(res_off), _ptr(res_nres),
+                                             _ptr(res_members), mem), "mtd_set_residences")
+
+    def contact_tracing(self, day: Day, traced, slice_off, rows3, epi_present=None, tape=None, mem=MEM_HOST):
+        """tape: object with scan_key (sorted), scan_u, prim_id, prim_off, prim_draws (numpy) or None (Philox)"""
+        t = None
+        if tape is not None:
+            t = TraceTape()
+            keep = [np.ascontiguousarray(tape.scan_key, np.uint64), np.ascontiguousarray(tape.scan_u, np.float64),
+                    np.ascontiguousarray(tape.prim_id, np.int32), np.ascontiguousarray(tape.prim_off, np.int32),
+                    np.ascontiguousarray(tape.prim_draws, np.float64)]
+            t.n_scan, t.n_prim = len(keep[0]), len(keep[2])
+            t.scan_key, t.scan_u, t.prim_id, t.prim_off, t.prim_draws = [a.ctypes.data for a in keep]
+        slice_off = np.ascontiguousarray(slice_off, np.int64)
+        self._ck(self.lib.mtd_contact_tracing(self.h, C.byref(day), C.byref(t) if t is not None else None,
+                                              C.c_int64(len(traced)), _ptr(traced), C.c_int64(len(slice_off) - 1),
+                                              _ptr(slice_off), _ptr(rows3), _ptr(epi_present), mem),
+                 "mtd_contact_tracing")
+
+    def get_traced(self):
+        """-> (primary flags uint8[N], secondary flags uint8[N], TraceStats)"""
+        prim = np.zeros(self.n_agents, np.uint8); sec = np.zeros(self.n_agents, np.uint8)
+        st = TraceStats()
+        self._ck(self.lib.mtd_get_traced(self.h, _ptr(prim), _ptr(sec), C.byref(st), MEM_HOST), "mtd_get_traced")
+        return prim, sec, st
 
     # ---- measurement hooks
     def set_profiling(self, on=True):

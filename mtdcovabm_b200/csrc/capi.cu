@@ -39,6 +39,15 @@ struct mtd_handle_s {
     // replay tape (device copies)
     std::vector<void *> tape_allocs;
     bool have_params = false, have_cells = false, have_static = false, day_ready = false;
+    // K5 (allocated on first use)
+    int64_t n_res_cells = 0, n_res_members = 0;
+    int64_t *res_off = nullptr; int32_t *res_nres = nullptr, *res_members = nullptr, *trace_sel = nullptr;
+    int32_t *res_first = nullptr, *res_k = nullptr;
+    uint8_t *is_traced = nullptr, *primary = nullptr, *secondary = nullptr, *d_epi_present = nullptr;
+    int32_t *trace_order = nullptr, *trace_cursor = nullptr, *sec_owner = nullptr, *trace_scalars = nullptr;
+    int32_t *trace_flagscan = nullptr; long long *trace_scan_tmp = nullptr;
+    int32_t *d_traced = nullptr; int64_t cap_traced = 0; int32_t *d_rows3 = nullptr; int64_t cap_rows3 = 0;
+    std::vector<void *> trace_tape_allocs;
     // measurement hooks
     bool profiling = false;
     cudaEvent_t ev[MTD_N_STAGES][2] = {};
@@ -164,6 +173,12 @@ extern "C" int mtd_destroy(mtd_handle h)
     cudaSetDevice(h->cfg.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     free_tape(h);
+    for (void *p : h->trace_tape_allocs) cudaFree(p);
+    for (void *p : { (void *)h->res_off, (void *)h->res_nres, (void *)h->res_members, (void *)h->trace_sel, (void *)h->res_first,
+                     (void *)h->res_k, (void *)h->is_traced, (void *)h->primary, (void *)h->secondary, (void *)h->d_epi_present,
+                     (void *)h->trace_order, (void *)h->trace_cursor, (void *)h->sec_owner, (void *)h->trace_scalars,
+                     (void *)h->trace_flagscan, (void *)h->trace_scan_tmp, (void *)h->d_traced, (void *)h->d_rows3 })
+        if (p) cudaFree(p);
     for (int s = 0; s < MTD_N_STAGES; s++) for (int k = 0; k < 2; k++) if (h->ev[s][k]) cudaEventDestroy(h->ev[s][k]);
     for (void *p : h->allocs) cudaFree(p);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
@@ -496,5 +511,135 @@ extern "C" int mtd_occupancy(mtd_handle h, int64_t out[6])
     CK(cudaMemcpyAsync(t, h->occ, sizeof(t), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     for (int k = 0; k < 6; k++) out[k] = (int64_t)t[k];
+    return MTD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ K5
+#include "k5_ctx.h"
+int launch_k5(const TraceCtx &c, int32_t *flag_scan, long long *scan_tmp, cudaStream_t st, int sm_count);
+
+template <typename T>
+static int regrow(mtd_handle h, T **p, int64_t *cap, int64_t need)
+{
+    if (need <= *cap) return 0;
+    if (*p) cudaFree(*p);
+    *p = nullptr; *cap = 0;
+    void *q = nullptr;
+    int64_t c = need + need / 2 + 1024;
+    cudaError_t e = cudaMalloc(&q, (size_t)c * sizeof(T));
+    if (e != cudaSuccess) { h->err = std::string("cudaMalloc: ") + cudaGetErrorString(e); return MTD_E_CUDA; }
+    *p = (T *)q; *cap = c;
+    return 0;
+}
+
+extern "C" int mtd_set_residences(mtd_handle h, int64_t n, const int64_t *res_off, const int32_t *res_nres,
+                                  const int32_t *res_members, int mem)
+{
+    if (!h || n <= 0 || !res_off || !res_nres) { if (h) h->err = "mtd_set_residences: bad arguments"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    int64_t total = 0;
+    if (mem == MTD_MEM_HOST) total = res_off[n];
+    else CK(cudaMemcpy(&total, res_off + n, sizeof(int64_t), cudaMemcpyDeviceToHost));
+    CK(cudaStreamSynchronize(h->stream));
+    for (void *p : { (void *)h->res_off, (void *)h->res_nres, (void *)h->res_members, (void *)h->trace_sel,
+                     (void *)h->res_first, (void *)h->res_k }) if (p) cudaFree(p);
+    CK(cudaMalloc((void **)&h->res_off, sizeof(int64_t) * (size_t)(n + 1)));
+    CK(cudaMalloc((void **)&h->res_nres, sizeof(int32_t) * (size_t)n));
+    CK(cudaMalloc((void **)&h->res_members, sizeof(int32_t) * (size_t)std::max<int64_t>(total, 1)));
+    CK(cudaMalloc((void **)&h->trace_sel, sizeof(int32_t) * (size_t)std::max<int64_t>(total, 1)));
+    CK(cudaMalloc((void **)&h->res_first, sizeof(int32_t) * (size_t)n));
+    CK(cudaMalloc((void **)&h->res_k, sizeof(int32_t) * (size_t)n));
+    COPY_IN(h->res_off, res_off, sizeof(int64_t) * (size_t)(n + 1));
+    COPY_IN(h->res_nres, res_nres, sizeof(int32_t) * (size_t)n);
+    if (total) COPY_IN(h->res_members, res_members, sizeof(int32_t) * (size_t)total);
+    CK(cudaStreamSynchronize(h->stream));
+    h->n_res_cells = n; h->n_res_members = total;
+    return MTD_OK;
+}
+
+static int trace_scratch(mtd_handle h)
+{
+    if (h->primary) return 0;
+    const size_t N = (size_t)h->c.n_agents;
+    CK(cudaMalloc((void **)&h->is_traced, N)); CK(cudaMalloc((void **)&h->primary, N)); CK(cudaMalloc((void **)&h->secondary, N));
+    CK(cudaMalloc((void **)&h->d_epi_present, N));
+    CK(cudaMalloc((void **)&h->trace_order, 4 * N)); CK(cudaMalloc((void **)&h->trace_cursor, 4 * N));
+    CK(cudaMalloc((void **)&h->sec_owner, 4 * N)); CK(cudaMalloc((void **)&h->trace_scalars, 64));
+    CK(cudaMalloc((void **)&h->trace_flagscan, 4 * (N + 2)));
+    CK(cudaMalloc((void **)&h->trace_scan_tmp, sizeof(long long) * ((N + 2) / 2048 + 16)));
+    return 0;
+}
+
+template <typename T>
+static int trace_up(mtd_handle h, const T **dst, const T *src, size_t n)
+{
+    void *q = nullptr;
+    cudaError_t e = cudaMalloc(&q, std::max<size_t>(n, 1) * sizeof(T));
+    if (e != cudaSuccess) { h->err = std::string("cudaMalloc(trace tape): ") + cudaGetErrorString(e); return MTD_E_CUDA; }
+    h->trace_tape_allocs.push_back(q);
+    if (n) cudaMemcpyAsync(q, src, n * sizeof(T), cudaMemcpyHostToDevice, h->stream);
+    *dst = (const T *)q;
+    return 0;
+}
+
+extern "C" int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_trace_tape *tape, int64_t n_traced,
+                                   const int32_t *traced, int64_t n_slices, const int64_t *slice_off,
+                                   const int32_t *rows3, const uint8_t *epi_present, int mem)
+{
+    if (!h || !day || n_traced < 0 || n_slices < 0 || n_slices > 8 || (n_slices && !slice_off)) {
+        if (h) h->err = "mtd_contact_tracing: bad arguments"; return MTD_E_ARG; }
+    if (!h->have_params || !h->res_off) { h->err = "mtd_contact_tracing: params / residences not set"; return MTD_E_STATE; }
+    if (day->mode == MTD_MODE_REPLAY && !tape) { h->err = "replay mode without a trace tape"; return MTD_E_STATE; }
+    CK(cudaSetDevice(h->cfg.device));
+    int r = trace_scratch(h);
+    if (r) return r;
+    CK(cudaStreamSynchronize(h->stream));
+    for (void *p : h->trace_tape_allocs) cudaFree(p);
+    h->trace_tape_allocs.clear();
+    TraceCtx t;
+    memset(&t, 0, sizeof(t));
+    t.n_agents = h->c.n_agents; t.n_res_cells = h->n_res_cells; t.day = *day; t.P = h->d_params;
+    if (tape && day->mode == MTD_MODE_REPLAY) {
+        t.n_scan = tape->n_scan; t.n_prim = tape->n_prim;
+        if ((r = trace_up(h, &t.scan_key, tape->scan_key, (size_t)tape->n_scan))) return r;
+        if ((r = trace_up(h, &t.scan_u, tape->scan_u, (size_t)tape->n_scan))) return r;
+        if ((r = trace_up(h, &t.prim_id, tape->prim_id, (size_t)tape->n_prim))) return r;
+        if ((r = trace_up(h, &t.prim_off, tape->prim_off, (size_t)tape->n_prim + 1))) return r;
+        size_t nd = tape->n_prim ? (size_t)tape->prim_off[tape->n_prim] : 0;
+        if ((r = trace_up(h, &t.prim_draws, tape->prim_draws, nd))) return r;
+    }
+    const int64_t n_rows = n_slices ? slice_off[n_slices] : 0;
+    t.n_traced = n_traced; t.n_slices = (int)n_slices;
+    for (int64_t s = 0; s <= n_slices; s++) t.slice_off[s] = slice_off[s];
+    if (mem == MTD_MEM_HOST) {
+        if ((r = regrow(h, &h->d_traced, &h->cap_traced, n_traced))) return r;
+        if ((r = regrow(h, &h->d_rows3, &h->cap_rows3, 3 * n_rows))) return r;
+        if (n_traced) CK(cudaMemcpyAsync(h->d_traced, traced, 4 * (size_t)n_traced, cudaMemcpyHostToDevice, h->stream));
+        if (n_rows) CK(cudaMemcpyAsync(h->d_rows3, rows3, 12 * (size_t)n_rows, cudaMemcpyHostToDevice, h->stream));
+        t.traced = h->d_traced; t.rows3 = h->d_rows3;
+        if (epi_present) { CK(cudaMemcpyAsync(h->d_epi_present, epi_present, (size_t)t.n_agents, cudaMemcpyHostToDevice, h->stream));
+                           t.epi_present = h->d_epi_present; }
+    } else { t.traced = traced; t.rows3 = rows3; t.epi_present = epi_present; }
+    t.res_off = h->res_off; t.res_nres = h->res_nres; t.res_members = h->res_members; t.res_cellid = h->c.res_cellid;
+    t.quarantine = h->c.quarantine; t.test_day = h->c.test_day; t.test_result_day = h->c.test_result_day;
+    t.is_traced = h->is_traced; t.primary = h->primary; t.secondary = h->secondary;
+    t.order = h->trace_order; t.n_order = h->trace_scalars + 8; t.cursor = h->trace_cursor;
+    t.res_first = h->res_first; t.res_k = h->res_k; t.sel = h->trace_sel; t.sec_owner = h->sec_owner;
+    t.stats = h->trace_scalars;
+    launch_k5(t, h->trace_flagscan, h->trace_scan_tmp, h->stream, h->sm_count);
+    CK(cudaGetLastError());
+    return MTD_OK;
+}
+
+extern "C" int mtd_get_traced(mtd_handle h, uint8_t *primary, uint8_t *secondary, mtd_trace_stats *stats, int mem)
+{
+    if (!h || !h->primary) { if (h) h->err = "mtd_get_traced before mtd_contact_tracing"; return MTD_E_STATE; }
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t N = (size_t)h->c.n_agents;
+    COPY_OUT(primary, h->primary, N); COPY_OUT(secondary, h->secondary, N);
+    int32_t s[4];
+    CK(cudaMemcpyAsync(s, h->trace_scalars, sizeof(s), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (stats) { stats->n_scan_draws = s[0]; stats->tape_miss = s[1]; stats->n_primary = s[2]; stats->n_secondary = s[3]; }
     return MTD_OK;
 }

@@ -132,3 +132,46 @@ def test_two_rank_cell_sharding_equals_single_rank():
         assert np.array_equal(h.get_exposed(), ref_exp)
         h.close()
     h0.close()
+
+
+@pytest.mark.parametrize("name,ti", list(gio.all_traces()))
+def test_contact_tracing_replay_matches_reference(name, ti):
+    """K5 through the C ABI on every contact_tracing call the reference made (epidemiology.py:667-834)"""
+    z = gio.load_run(name)
+    P = prm.build_params(None, prm.load_json(gio.RUNS[name]))
+    t = gio.load_trace(z, ti)
+    h = H.make_handle(P, t.pre, np.zeros(len(t.res_nres), np.int8), np.full(len(t.res_nres), -1, np.int16), 16)
+    h.set_residences(t.res_off, t.res_nres, t.res_members)
+    d = h.make_day(capi.MODE_REPLAY, t.day, 0.0, t.testing_enabled, t.quarantine_enabled)
+    h.contact_tracing(d, t.traced, t.slice_off, t.rows, epi_present=t.epi_present, tape=t.tape)
+    prim, sec, s = h.get_traced()
+    assert s.tape_miss == 0 and s.n_scan_draws == len(t.tape.scan_key)
+    assert np.array_equal(np.nonzero(prim)[0], t.primary) and np.array_equal(np.nonzero(sec)[0], t.secondary)
+    dev = h.get_state()
+    for f in ("quarantine", "test_day", "test_result_day"):
+        assert np.array_equal(dev[f], getattr(t.post, f)), f
+    h.close()
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_contact_tracing_philox_matches_oracle(seed):
+    z = gio.load_run("ref_1k_strict_seed7")
+    P = prm.build_params(None, prm.load_json(gio.RUNS["ref_1k_strict_seed7"]))
+    for ti in range(len(z["trace_days"])):
+        t = gio.load_trace(z, ti)
+        traced = np.unique(np.concatenate([t.traced, t.rows[seed::7, 1]])).astype(np.int32)    # more positives
+        h = H.make_handle(P, t.pre, np.zeros(len(t.res_nres), np.int8), np.full(len(t.res_nres), -1, np.int16), 16)
+        h.set_residences(t.res_off, t.res_nres, t.res_members)
+        d = h.make_day(capi.MODE_PHILOX, t.day, 0.0, True, True, seed=seed)
+        h.contact_tracing(d, traced, t.slice_off, t.rows, epi_present=t.epi_present)
+        prim, sec, s = h.get_traced()
+        ost = t.pre.copy()
+        ctx = mo.make_ctx(mo.MODE_PHILOX, t.day, 0.0, True, True, seed=seed)
+        oprim, osec, os_ = mo.contact_tracing(P, ctx, None, traced, t.slice_off, t.rows, t.res_off, t.res_nres,
+                                              t.res_members, ost, t.epi_present, t.n_locals)
+        assert s.n_scan_draws == os_.n_scan_draws and prim.sum() > 20
+        assert np.array_equal(prim, oprim) and np.array_equal(sec, osec)
+        dev = h.get_state()
+        for f in ("quarantine", "test_day", "test_result_day"):
+            assert np.array_equal(dev[f], getattr(ost, f)), f
+        h.close()
