@@ -44,3 +44,117 @@ class Epidemiology:
         (K3 consumes the contact rows K1/K2 left in HBM); a per-cell Python dict of contacts never exists."""
         raise RuntimeError("simulate_direct_contacts runs fused inside ContactNetwork.simulate_contact_network on the "
                            "B200 path (mtd_simulate_direct_contacts); call that instead")
+
+    # ------------------------------------------------------------------ contact tracing (K5)
+    def _residences(self):
+        """cells_households / cells_institutions / cells_accommodation -> CSR over cell ids: members = residents
+        (resident_uids / member_uids) followed by staff (staff_uids), as epidemiology.py:752-788 concatenates them"""
+        cells = {}
+        for src, rk, sk in ((self.cells_households, "resident_uids", "staff_uids"),
+                            (self.cells_institutions, "resident_uids", "staff_uids"),
+                            (self.cells_accommodation, "member_uids", None)):
+            for cid, cell in (src or {}).items():
+                if int(cid) in cells:                       # households before institutions before accommodation
+                    continue
+                place = cell["place"]
+                res = place.get(rk) if hasattr(place, "get") else place[rk]
+                stf = (place.get(sk) if hasattr(place, "get") else place[sk]) if sk else None
+                cells[int(cid)] = ([int(x) for x in (res if res is not None else [])],
+                                   [int(x) for x in (stf if stf is not None else [])])
+        n = (max(cells) + 1) if cells else 1
+        off = np.zeros(n + 1, np.int64); nres = np.zeros(n, np.int32); mem = []
+        for c in range(n):
+            r, s = cells.get(c, ([], []))
+            mem.extend(r); mem.extend(s); nres[c] = len(r); off[c + 1] = len(mem)
+        return off, nres, np.array(mem, np.int32)
+
+    def contact_tracing(self, day, distributed=False, f=None):
+        """epidemiology.py:667-834 -> (process_index, updated_agent_ids, agents_epi, vars_util)"""
+        from . import bridge, capi
+        vu = self.vars_util
+        updated = []
+        traced = sorted(int(x) for x in vu.contact_tracing_agent_ids)
+        if self.dyn_params.contact_tracing_enabled and len(traced) > 0:
+            if getattr(self.dyn_params, "statistics", None) is not None:
+                self.dyn_params.statistics.new_contacttraced = len(traced)
+            rows = vu.directcontacts_by_simcelltype_by_day
+            markers = vu.directcontacts_by_simcelltype_by_day_start_marker
+            slices, off = [], [0]
+            for back in range(self.contact_tracing_days_back + 1):          # :677-703, start markers as the reference
+                d = day - back
+                sl = []
+                if d in markers:
+                    lo, hi = markers[d], len(rows)
+                    if d + 1 in markers:
+                        hi = markers[d + 1] - 1                               # exclusive bound, as written (quirk B8)
+                    sl = rows[lo:hi]
+                slices.append(np.array([[int(r[0]), int(r[1]), int(r[2])] for r in sl], np.int32).reshape(-1, 3))
+                off.append(off[-1] + len(slices[-1]))
+            rows3 = np.ascontiguousarray(np.concatenate(slices)) if off[-1] else np.zeros((0, 3), np.int32)
+            n_agents = int(self.n_locals + self.n_tourists)
+            st = bridge.DenseState(n_agents)
+            present = np.zeros(n_agents, np.uint8)
+            keys = self.agents_epi.keys() if hasattr(self.agents_epi, "keys") else range(len(self.agents_epi))
+            for a in keys:
+                e = self.agents_epi[a]
+                a = int(a)
+                if e is None or len(e) == 0:
+                    continue
+                present[a] = 1
+                bridge._rec(st.quarantine, a, e.get("quarantine_days")); bridge._rec(st.test_day, a, e.get("test_day"))
+                bridge._rec(st.test_result_day, a, e.get("test_result_day"))
+                try:
+                    st.res_cellid[a] = int(self.agents_static.get(a, "res_cellid"))
+                except Exception:
+                    if a < self.n_locals:                                     # departed tourists are skipped (:744-748)
+                        raise ValueError("Agent {0} not found during contact tracing".format(str(a)))
+            off_r, nres, mem = self._residences()
+            h = bridge.get_handle(n_agents, max(len(nres), 1), 16, self.params, self.device)
+            h.set_static(st.age_bracket, st.epi_age_bracket, st.soc_rate, st.res_cellid)
+            h.set_state(quarantine=st.quarantine, test_day=st.test_day, test_result_day=st.test_result_day)
+            h.set_residences(off_r, nres, mem)
+            replay = self.mode == "replay"
+            if replay and self.tape is None:
+                raise RuntimeError("replay mode needs the reference's contact-tracing tape")
+            d = h.make_day(capi.MODE_REPLAY if replay else capi.MODE_PHILOX, int(day), 0.0,
+                           bool(self.dyn_params.testing_enabled), bool(self.dyn_params.quarantine_enabled), seed=self.seed)
+            h.contact_tracing(d, np.array(traced, np.int32), np.array(off, np.int64), rows3, epi_present=present,
+                              tape=self.tape if replay else None)
+            prim, sec, stats = h.get_traced()
+            if replay and stats.tape_miss:
+                raise RuntimeError("contact-tracing tape does not match this call (%d misses)" % stats.tape_miss)
+            if getattr(self.dyn_params, "statistics", None) is not None and len(slices) > 0:
+                self.dyn_params.statistics.num_direct_contacts = len(slices[-1])
+            dev = h.get_state()
+            prim_ids = [int(a) for a in np.nonzero(prim)[0]]
+            for a in prim_ids:                                                # only primaries' records change (quirk B9)
+                if not present[a]:
+                    continue
+                e = self.agents_epi[a]
+                e["quarantine_days"] = bridge._lst(dev["quarantine"][a])
+                e["test_day"] = bridge._lst(dev["test_day"][a]); e["test_result_day"] = bridge._lst(dev["test_result_day"][a])
+            updated = prim_ids + [int(a) for a in np.nonzero(sec)[0]]
+        if not distributed:
+            self.contact_tracing_clean_up(day, f)
+        return self.process_index, updated, self.agents_epi, vu
+
+    def contact_tracing_clean_up(self, day, f=None):
+        """epidemiology.py:838-906: drop the oldest retained day of contact rows and re-base the start markers
+        (host-side list bookkeeping on the reference's own containers)"""
+        vu = self.vars_util
+        markers = vu.directcontacts_by_simcelltype_by_day_start_marker
+        day_to_clean = day - self.contact_tracing_days_back
+        day_end_idx = 0
+        if day_to_clean + 1 in markers:
+            day_end_idx = markers[day_to_clean + 1] - 1
+        if day_end_idx > 0:
+            vu.directcontacts_by_simcelltype_by_day = vu.directcontacts_by_simcelltype_by_day[day_end_idx + 1:]
+            if day_to_clean in markers:
+                del markers[day_to_clean]
+            keys = list(markers.keys())
+            rebased = {}
+            for i in range(len(keys), 0, -1):                                 # as written at :886-900
+                cur = keys[i - 1]
+                prev = keys[i - 2] if i - 2 >= 0 else None
+                rebased[cur] = 0 if prev is None else markers[cur] - markers[prev]
+            vu.directcontacts_by_simcelltype_by_day_start_marker = rebased

@@ -97,3 +97,48 @@ def test_update_agent_state_scalar_matches_reference_calls():
         assert agent["state_transition_by_day"] == [[int(x) for x in e] for e in a[ao[i]:ao[i + 1]]]
         if out is not None:
             assert int(out[0]) == int(post[i, 0]) and int(out[1]) == int(pre[i, 0])
+
+
+@pytest.mark.parametrize("name,ti", list(gio.all_traces()))
+def test_epidemiology_contact_tracing_dropin(name, ti):
+    """Epidemiology(...).contact_tracing(day) on the reference's containers (sim.py:1929-1968), replay mode"""
+    from mtdcovabm_b200.epidemiology import Epidemiology
+    z = gio.load_run(name)
+    t = gio.load_trace(z, ti)
+    N = len(t.epi_present)
+    epi = {}
+    for a in np.nonzero(t.epi_present)[0]:
+        epi[int(a)] = {"state_transition_by_day": [], "quarantine_days": _rec(t.pre.quarantine[a]),
+                       "test_day": _rec(t.pre.test_day[a]), "test_result_day": _rec(t.pre.test_result_day[a]),
+                       "hospitalisation_days": None}
+    # rebuild a contact-row list + start markers whose look-back slices are the recorded ones (the reference drops
+    # the last row of every non-current day, quirk B8: one filler row per older day)
+    so = t.slice_off
+    rows, markers = [], {}
+    for back in range(len(so) - 2, -1, -1):
+        markers[t.day - back] = len(rows)
+        rows.extend([int(r[0]), int(r[1]), int(r[2]), 0, 0] for r in t.rows[so[back]:so[back + 1]])
+        if back > 0:
+            rows.append([3, int(t.traced[0]), int(t.traced[0]), 0, 0])      # filler: both endpoints traced -> ignored
+    vu = SimpleNamespace(contact_tracing_agent_ids=set(int(x) for x in t.traced),
+                         directcontacts_by_simcelltype_by_day=rows,
+                         directcontacts_by_simcelltype_by_day_start_marker=markers)
+    hh = {}
+    for c in range(len(t.res_nres)):
+        m = t.res_members[t.res_off[c]:t.res_off[c + 1]]
+        if len(m):
+            hh[c] = {"place": {"resident_uids": np.array(m[:t.res_nres[c]]), "staff_uids": np.array(m[t.res_nres[c]:])}}
+    dyn = SimpleNamespace(contact_tracing_enabled=True, testing_enabled=t.testing_enabled,
+                          quarantine_enabled=t.quarantine_enabled, statistics=None)
+    n_before = len(rows)
+    e = Epidemiology(prm.load_json(gio.RUNS[name]), t.n_locals, N - t.n_locals, 1.0, FakeStatic(t.pre), epi, vu, hh, {}, {},
+                     dyn, mode="replay", tape=t.tape)
+    pidx, updated, agents_epi, vu2 = e.contact_tracing(t.day)
+    assert sorted(updated) == t.updated.tolist() and agents_epi is epi
+    for a in t.primary:
+        assert epi[int(a)]["quarantine_days"] == _rec(t.post.quarantine[a])
+        assert epi[int(a)]["test_day"] == _rec(t.post.test_day[a])
+        assert epi[int(a)]["test_result_day"] == _rec(t.post.test_result_day[a])
+    # clean-up dropped the oldest day and re-based the markers
+    assert len(vu.directcontacts_by_simcelltype_by_day) < n_before
+    assert min(vu.directcontacts_by_simcelltype_by_day_start_marker.values()) == 0
