@@ -20,7 +20,7 @@ from . import capi
 def exchange_deltas(gather: torch.Tensor, rank: int, group=None):
     """one all-gather per day of the fixed-capacity delta slices: gather[r] <- rank r's records (in place: every
     rank contributes gather[rank]).  Works on CUDA tensors over NCCL and on CPU tensors over gloo (tests)."""
-    torch.distributed.all_gather_into_tensor(gather, gather[rank].clone(), group=group)
+    torch.distributed.all_gather_into_tensor(gather.view(-1), gather[rank].reshape(-1).clone(), group=group)
 
 
 class DayEngine:
