@@ -167,8 +167,8 @@ int mtd_get_traced(mtd_handle h, uint8_t *primary, uint8_t *secondary, mtd_trace
 
 /* Measurement hooks (the reference's per-stage wall-clock columns, sim.py:231-244,1852-1856): with profiling on,
  * CUDA events are recorded on the handle's stream around every stage of the day step; mtd_get_stage_ms
- * synchronises and returns the device time of the LAST execution of each stage and the number of kernels the
- * library launched since the previous call (per stage). */
+ * synchronises and returns, per stage, the MEAN device time over its executions since the previous call (the first
+ * 512 of them) and the number of kernels the library launched since the previous call. */
 enum { MTD_STAGE_H2D = 0, MTD_STAGE_K0 = 1, MTD_STAGE_K1 = 2, MTD_STAGE_K2 = 3, MTD_STAGE_K3_EVAL = 4,
        MTD_STAGE_K3_APPLY = 5, MTD_STAGE_K4 = 6, MTD_N_STAGES = 7 };
 int mtd_set_profiling(mtd_handle h, int on);

@@ -223,7 +223,7 @@ class Handle:
         self._ck(self.lib.mtd_set_profiling(self.h, int(on)), "mtd_set_profiling")
 
     def stage_ms(self):
-        """-> ({stage: ms of its last execution}, {stage: kernels launched since the previous call})"""
+        """-> ({stage: mean ms over its executions since the previous call}, {stage: kernels launched since then})"""
         ms = (C.c_float * len(STAGES))()
         ln = (C.c_int64 * len(STAGES))()
         self._ck(self.lib.mtd_get_stage_ms(self.h, ms, ln), "mtd_get_stage_ms")

@@ -10,6 +10,7 @@
 // every launcher returns the number of kernels it launched
 int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count);
 int launch_k1(const DevCtx &c, cudaStream_t st, int sm_count);
+int64_t k1_bits_words_needed(int sm_count);
 int launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count);
 int launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap, cudaStream_t st);
 int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, cudaStream_t st, int sm_count);
@@ -50,15 +51,18 @@ struct mtd_handle_s {
     std::vector<void *> trace_tape_allocs;
     // measurement hooks
     bool profiling = false;
-    cudaEvent_t ev[MTD_N_STAGES][2] = {};
-    bool ev_valid[MTD_N_STAGES] = {};
+    // ring of event pairs per stage: every execution since the last mtd_get_stage_ms is timed (up to EV_RING)
+    static constexpr int EV_RING = 512;
+    std::vector<cudaEvent_t> ev[MTD_N_STAGES];      // [2 * EV_RING], created on first use
+    int ev_n[MTD_N_STAGES] = {};                    // executions recorded since the last query
     int64_t launches[MTD_N_STAGES] = {};
 };
 
 struct StageScope {     // records the stage's start/end events on the handle's stream when profiling is on
     mtd_handle h; int stage;
-    StageScope(mtd_handle h_, int s) : h(h_), stage(s) { if (h->profiling) cudaEventRecord(h->ev[stage][0], h->stream); }
-    ~StageScope() { if (h->profiling) { cudaEventRecord(h->ev[stage][1], h->stream); h->ev_valid[stage] = true; } }
+    StageScope(mtd_handle h_, int s) : h(h_), stage(s) { if (on()) cudaEventRecord(h->ev[stage][2 * h->ev_n[stage]], h->stream); }
+    ~StageScope() { if (on()) { cudaEventRecord(h->ev[stage][2 * h->ev_n[stage] + 1], h->stream); h->ev_n[stage]++; } }
+    bool on() const { return h->profiling && h->ev_n[stage] < mtd_handle_s::EV_RING; }
     void add(int n) { h->launches[stage] += n; }
 };
 
@@ -114,6 +118,8 @@ static int create_impl(mtd_handle h)
     DA(c.class_list, MTD_NUM_CLASSES * (S + 1));
     DA(c.csr, M); DA(c.csr_sorted, M);
     DA(c.scratch_rows, c.cap_scratch_rows); DA(c.lists, c.cap_list); DA(c.rows, c.cap_rows);
+    c.k1_bits_words = k1_bits_words_needed(h->sm_count);
+    DA(c.k1_bits, c.k1_bits_words);
     DA(c.win, N); DA(c.succ, c.cap_rows);
     c.row_p = nullptr;
     DA(h->delta_own, (c.cap_expo + 1) * MTD_DELTA_WORDS);
@@ -179,7 +185,7 @@ extern "C" int mtd_destroy(mtd_handle h)
                      (void *)h->trace_order, (void *)h->trace_cursor, (void *)h->sec_owner, (void *)h->trace_scalars,
                      (void *)h->trace_flagscan, (void *)h->trace_scan_tmp, (void *)h->d_traced, (void *)h->d_rows3 })
         if (p) cudaFree(p);
-    for (int s = 0; s < MTD_N_STAGES; s++) for (int k = 0; k < 2; k++) if (h->ev[s][k]) cudaEventDestroy(h->ev[s][k]);
+    for (int s = 0; s < MTD_N_STAGES; s++) for (cudaEvent_t e : h->ev[s]) cudaEventDestroy(e);
     for (void *p : h->allocs) cudaFree(p);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -379,10 +385,13 @@ extern "C" int mtd_set_profiling(mtd_handle h, int on)
 {
     if (!h) return MTD_E_ARG;
     CK(cudaSetDevice(h->cfg.device));
-    if (on && !h->ev[0][0])
-        for (int s = 0; s < MTD_N_STAGES; s++) { CK(cudaEventCreate(&h->ev[s][0])); CK(cudaEventCreate(&h->ev[s][1])); }
+    if (on && h->ev[0].empty())
+        for (int s = 0; s < MTD_N_STAGES; s++) {
+            h->ev[s].resize(2 * mtd_handle_s::EV_RING);
+            for (cudaEvent_t &e : h->ev[s]) CK(cudaEventCreate(&e));
+        }
     h->profiling = on != 0;
-    for (int s = 0; s < MTD_N_STAGES; s++) { h->ev_valid[s] = false; h->launches[s] = 0; }
+    for (int s = 0; s < MTD_N_STAGES; s++) { h->ev_n[s] = 0; h->launches[s] = 0; }
     return MTD_OK;
 }
 
@@ -393,8 +402,14 @@ extern "C" int mtd_get_stage_ms(mtd_handle h, float ms[MTD_N_STAGES], int64_t la
     CK(cudaStreamSynchronize(h->stream));
     for (int s = 0; s < MTD_N_STAGES; s++) {
         ms[s] = 0.f;
-        if (h->profiling && h->ev_valid[s]) CK(cudaEventElapsedTime(&ms[s], h->ev[s][0], h->ev[s][1]));
-        h->ev_valid[s] = false;
+        double sum = 0.0;
+        for (int k = 0; k < h->ev_n[s]; k++) {
+            float t = 0.f;
+            CK(cudaEventElapsedTime(&t, h->ev[s][2 * k], h->ev[s][2 * k + 1]));
+            sum += t;
+        }
+        if (h->ev_n[s] > 0) ms[s] = (float)(sum / h->ev_n[s]);
+        h->ev_n[s] = 0;
         if (launches) launches[s] = h->launches[s];
         h->launches[s] = 0;
     }

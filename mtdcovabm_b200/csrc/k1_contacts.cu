@@ -88,27 +88,29 @@ __device__ __forceinline__ int degree_i(double d, long long deg_sum, long long m
 // overlap's end (contactnetwork.py:101); dur = summed overlap length (epidemiology.py:170).
 __device__ __forceinline__ void pair_row_bits(const uint16_t *se, uint32_t ivx, uint32_t ivy, bool &x_first, int &start,
                                               int &end, int &dur)
-{
+{   // one pass: orientation A = x outer / y inner (this loop's order), orientation B = lexicographic (pb, pa)
     int fx = 64, fy = 64;
+    int a_start = 0, a_end = 0; bool a_none = true;
+    int b_min = 1 << 30, b_max = -1, b_start = 0, b_end = 0;
+    dur = 0;
     for (uint32_t bx = ivx; bx; bx &= bx - 1) {
-        int pa = __ffs(bx) - 1; int sa = se[pa] & 0xff, ea = se[pa] >> 8;
+        const int pa = __ffs(bx) - 1; const int sa = se[pa] & 0xff, ea = se[pa] >> 8;
         for (uint32_t by = ivy; by; by &= by - 1) {
-            int pb = __ffs(by) - 1; int sb = se[pb] & 0xff, eb = se[pb] >> 8;
-            if (max(sa, sb) <= min(ea, eb)) { fx = min(fx, pa); fy = min(fy, pb); }
+            const int pb = __ffs(by) - 1; const int sb = se[pb] & 0xff, eb = se[pb] >> 8;
+            const int lo = max(sa, sb), hi = min(ea, eb);
+            if (lo <= hi) {
+                fx = min(fx, pa); fy = min(fy, pb); dur += hi - lo + 1;
+                if (a_none) { a_start = lo; a_none = false; }
+                a_end = hi;
+                const int kb = (pb << 6) | pa;
+                if (kb < b_min) { b_min = kb; b_start = lo; }
+                if (kb > b_max) { b_max = kb; b_end = hi; }
+            }
         }
     }
     x_first = fx < fy;
-    uint32_t iva = x_first ? ivx : ivy, ivb = x_first ? ivy : ivx;
-    bool first = true;
-    start = 0; end = 0; dur = 0;
-    for (uint32_t ba = iva; ba; ba &= ba - 1) {
-        int pa = __ffs(ba) - 1; int sa = se[pa] & 0xff, ea = se[pa] >> 8;
-        for (uint32_t bb = ivb; bb; bb &= bb - 1) {
-            int pb = __ffs(bb) - 1; int sb = se[pb] & 0xff, eb = se[pb] >> 8;
-            int lo = max(sa, sb), hi = min(ea, eb);
-            if (lo <= hi) { if (first) { start = lo; first = false; } end = hi; dur += hi - lo + 1; }
-        }
-    }
+    start = x_first ? a_start : b_start;
+    end = x_first ? a_end : b_end;
 }
 
 // ------------------------------------------------------------------------------------------------ small cells
@@ -281,18 +283,21 @@ __global__ void __launch_bounds__(K1S_THREADS) k1_small_kernel(DevCtx g, int cls
                     if (gl == t) mypick = bit;
                 }
             } else {
-                uint32_t wv = 0;
+                // draw t takes the r_t-th REMAINING candidate, r_t = floor(u_t * (nc - t)): a Lehmer code.  Lane t decodes
+                // its own pick's rank among the ORIGINAL candidates, q += (q >= r_s) for s = t-1 .. 0, all picks at once.
+                int rq = 0;
                 if (gl < d) {
                     uint32_t w4[4];
                     philox4x32((uint32_t)g.day.day, (uint32_t)cell, (uint32_t)agx, (uint32_t)(gl >> 2), g.day.seed, SITE_SELECT, w4);
-                    wv = pick4(w4, gl & 3);
+                    rq = (int)__umulhi(pick4(w4, gl & 3), (uint32_t)(nc - gl));
                 }
-                for (int t = 0; t < d; t++) {
-                    const uint32_t wt = __shfl_sync(gmask, wv, gbase + t);
-                    const int bit = nth_set_bit(cand, (int)__umulhi(wt, (uint32_t)(nc - t)));
-                    cand &= ~(1u << bit); picked |= 1u << bit;
-                    if (gl == t) mypick = bit;
+                int q = rq;
+                for (int s = d - 2; s >= 0; s--) {
+                    const int rs = __shfl_sync(gmask, rq, gbase + s);
+                    if (s < gl) q += (q >= rs);
                 }
+                if (gl < d) mypick = nth_set_bit(cand, q);
+                picked = __reduce_or_sync(gmask, gl < d ? (1u << mypick) : 0u);
             }
             // rows: lane t builds the row of pick t
             const uint32_t ivy = __shfl_sync(gmask, mm, gbase + (mypick >= 0 ? mypick : gl));
@@ -321,32 +326,43 @@ __global__ void __launch_bounds__(K1S_THREADS) k1_small_kernel(DevCtx g, int cls
 }
 
 // ------------------------------------------------------------------------------------------------ large cells
+// One warp per cell.  Shared memory per warp is kept small (about 14.5 KB for 320 intervals) so that many cells are in
+// flight per SM: the scratch region U is reused phase by phase (sort keys + agent hash -> occupancy masks -> float
+// degrees -> greedy order keys), and the adjacency bit matrix -- written once, each row read once when its agent
+// becomes the main agent -- lives in a per-warp slice of an L2-resident global scratch, word-major ([word][agent], so
+// the writes are coalesced), with the next main agent's row prefetched one iteration ahead.
 template <int MM>
 struct Lay {
     static constexpr int P2 = pow2_ge(MM);
     static constexpr int BW = (MM + 31) / 32;              // bit-matrix words per row
     static constexpr int H = 2 * P2;                       // hash slots
-    static constexpr size_t o_key = 0;                     // u64[P2]: sort keys / 2 x u32[P2] temps / double[MM] degf
-    static constexpr size_t o_agent = o_key + align16(sizeof(uint64_t) * P2);       // i32[MM] agent id per interval
+    static constexpr size_t u_sort = sizeof(uint64_t) * P2 + sizeof(uint32_t) * H;   // keys (or 2 x u32[P2]) + hash
+    static constexpr size_t u_mask = sizeof(uint32_t) * 6 * MM;                       // u32[MM][6] occupancy masks
+    static constexpr size_t u_bytes = u_sort > u_mask ? u_sort : u_mask;
+    static constexpr size_t o_u = 0;
+    static constexpr size_t o_hash = sizeof(uint64_t) * P2;                         // inside U
+    static constexpr size_t o_agent = o_u + align16(u_bytes);                       // i32[MM] agent id per interval,
+                                                                                    //   then per local agent
     static constexpr size_t o_se = o_agent + align16(sizeof(int32_t) * MM);         // u16[MM] start | end << 8
-    static constexpr size_t o_la = o_se + align16(2 * MM);                          // u16[MM] local agent of interval
+    static constexpr size_t o_la = o_se + align16(2 * MM);                          // u16[MM] local agent of interval,
+                                                                                    //   then the greedy order
     static constexpr size_t o_apos = o_la + align16(2 * MM);                        // u16[MM] interval lists
     static constexpr size_t o_aoff = o_apos + align16(2 * MM);                      // u16[MM+1]
     static constexpr size_t o_first = o_aoff + align16(2 * (MM + 1));               // u16[MM] first interval of agent
-    static constexpr size_t o_pc = o_first + align16(2 * MM);                       // u16[MM]
+    static constexpr size_t o_pc = o_first + align16(2 * MM);                       // u16[MM] potential contacts,
+                                                                                    //   then the replay picks
     static constexpr size_t o_deg = o_pc + align16(2 * MM);                         // i16[MM]
-    static constexpr size_t o_ts = o_deg + align16(2 * MM);                         // u16[MM]
-    static constexpr size_t o_cand = o_ts + align16(2 * MM);                        // u16[MM] picks of one main agent
-    static constexpr size_t o_mask = o_cand + align16(2 * MM);                      // u32[MM][6] occupancy masks
-    static constexpr size_t o_bits = o_mask + align16(sizeof(uint32_t) * 6 * MM);   // u32[MM*BW] adjacency
-    static constexpr size_t o_hash = o_bits + align16(sizeof(uint32_t) * MM * BW);  // u32[H]
-    static constexpr size_t bytes = o_hash + align16(sizeof(uint32_t) * H);
+    static constexpr size_t o_ts = o_deg + align16(2 * MM);                         // u16[MM] timesteps, then draws
+    static constexpr size_t o_alive = o_ts + align16(2 * MM);                       // u32[32] agents with degree > 0
+    static constexpr size_t o_candw = o_alive + 128;                                // u32[32] candidates of the main
+    static constexpr size_t o_ccnt = o_candw + 128;                                 // u32[32] popcounts of candw
+    static constexpr size_t bytes = o_ccnt + 128;
+    static constexpr size_t bits_words = (size_t)MM * BW;                           // global scratch per warp
 };
 
 struct Cell {
-    uint64_t *key; int32_t *agent; uint16_t *se, *la, *apos, *aoff, *first, *pc; int16_t *deg; uint16_t *ts, *cand;
-    uint32_t *mask, *bits, *hash;
-    int bw;
+    uint64_t *key; int32_t *agent; uint16_t *se, *la, *apos, *aoff, *first, *pc; int16_t *deg; uint16_t *ts;
+    uint32_t *mask, *hash, *alive, *candw, *ccnt;
 };
 
 __device__ __forceinline__ void warp_bitonic_sort(uint64_t *k, int P2, int lane)
@@ -389,42 +405,49 @@ __device__ double np_pairwise_sum(const double *a, int n)
     return np_pairwise_sum(a, n2) + np_pairwise_sum(a + n2, n - n2);
 }
 
-// same contract as pair_row_bits, agents given by local index with interval lists aoff/apos
+// Contact row of the agents with local indices x, y (interval lists aoff/apos in position order), in ONE pass over the
+// interval pairs.  The reference's key orientation is decided by whose interval is reached first by the ordered double
+// loop (contactnetwork.py:160-196): orientation A = x outer / y inner is this loop's own order; orientation B = y outer /
+// x inner is the lexicographic order of (pb, pa).  start = first overlap's start, end = last overlap's end, in the
+// chosen orientation (contactnetwork.py:101); dur = summed overlap length (epidemiology.py:170).
 __device__ __forceinline__ void pair_row_lists(const Cell &c, int x, int y, bool &x_first, int &start, int &end, int &dur)
 {
     int fx = 1 << 30, fy = 1 << 30;
-    for (int qa = c.aoff[x]; qa < c.aoff[x + 1]; qa++) {
-        int pa = c.apos[qa]; int sa = c.se[pa] & 0xff, ea = c.se[pa] >> 8;
-        for (int qb = c.aoff[y]; qb < c.aoff[y + 1]; qb++) {
-            int pb = c.apos[qb]; int sb = c.se[pb] & 0xff, eb = c.se[pb] >> 8;
-            if (max(sa, sb) <= min(ea, eb)) { fx = min(fx, pa); fy = min(fy, pb); }
+    int a_start = 0, a_end = 0; bool a_none = true;
+    int b_min = 1 << 30, b_max = -1, b_start = 0, b_end = 0;
+    dur = 0;
+    const int xa = c.aoff[x], xb = c.aoff[x + 1], ya = c.aoff[y], yb = c.aoff[y + 1];
+    for (int qa = xa; qa < xb; qa++) {
+        const int pa = c.apos[qa]; const int sa = c.se[pa] & 0xff, ea = c.se[pa] >> 8;
+        for (int qb = ya; qb < yb; qb++) {
+            const int pb = c.apos[qb]; const int sb = c.se[pb] & 0xff, eb = c.se[pb] >> 8;
+            const int lo = max(sa, sb), hi = min(ea, eb);
+            if (lo <= hi) {
+                fx = min(fx, pa); fy = min(fy, pb); dur += hi - lo + 1;
+                if (a_none) { a_start = lo; a_none = false; }
+                a_end = hi;
+                const int kb = (pb << 12) | pa;
+                if (kb < b_min) { b_min = kb; b_start = lo; }
+                if (kb > b_max) { b_max = kb; b_end = hi; }
+            }
         }
     }
     x_first = fx < fy;
-    const int a = x_first ? x : y, b = x_first ? y : x;
-    bool first = true;
-    start = 0; end = 0; dur = 0;
-    for (int qa = c.aoff[a]; qa < c.aoff[a + 1]; qa++) {
-        int pa = c.apos[qa]; int sa = c.se[pa] & 0xff, ea = c.se[pa] >> 8;
-        for (int qb = c.aoff[b]; qb < c.aoff[b + 1]; qb++) {
-            int pb = c.apos[qb]; int sb = c.se[pb] & 0xff, eb = c.se[pb] >> 8;
-            int lo = max(sa, sb), hi = min(ea, eb);
-            if (lo <= hi) { if (first) { start = lo; first = false; } end = hi; dur += hi - lo + 1; }
-        }
-    }
+    start = x_first ? a_start : b_start;
+    end = x_first ? a_end : b_end;
 }
 
 template <int MM>
-__device__ void process_cell_large(const DevCtx &g, unsigned char *sm, int slot, int lane, unsigned long long &acc_pairs,
-                                   unsigned long long &acc_pot)
+__device__ void process_cell_large(const DevCtx &g, unsigned char *sm, uint32_t *bits, int slot, int lane,
+                                   unsigned long long &acc_pairs, unsigned long long &acc_pot)
 {
     using L = Lay<MM>;
     Cell c;
-    c.key = (uint64_t *)(sm + L::o_key); c.agent = (int32_t *)(sm + L::o_agent); c.se = (uint16_t *)(sm + L::o_se);
+    c.key = (uint64_t *)(sm + L::o_u); c.agent = (int32_t *)(sm + L::o_agent); c.se = (uint16_t *)(sm + L::o_se);
     c.la = (uint16_t *)(sm + L::o_la); c.apos = (uint16_t *)(sm + L::o_apos); c.aoff = (uint16_t *)(sm + L::o_aoff);
     c.first = (uint16_t *)(sm + L::o_first); c.pc = (uint16_t *)(sm + L::o_pc); c.deg = (int16_t *)(sm + L::o_deg);
-    c.ts = (uint16_t *)(sm + L::o_ts); c.cand = (uint16_t *)(sm + L::o_cand); c.mask = (uint32_t *)(sm + L::o_mask);
-    c.bits = (uint32_t *)(sm + L::o_bits); c.hash = (uint32_t *)(sm + L::o_hash);
+    c.ts = (uint16_t *)(sm + L::o_ts); c.mask = (uint32_t *)(sm + L::o_u); c.hash = (uint32_t *)(sm + L::o_hash);
+    c.alive = (uint32_t *)(sm + L::o_alive); c.candw = (uint32_t *)(sm + L::o_candw); c.ccnt = (uint32_t *)(sm + L::o_ccnt);
 
     const int m = g.slot_m[slot];
     const int64_t base = g.slot_off[slot];
@@ -525,10 +548,17 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, int slot,
         if (p < m && (__ffs(mmm) - 1) == lane) t32a[l] += __popc(mmm);
         __syncwarp();
     }
+    // agent id per LOCAL agent, compacted in place (first[l] >= l, so a chunk never overwrites what a later one reads)
+    for (int l0 = 0; l0 < n; l0 += 32) {
+        int l = l0 + lane;
+        int v = (l < n) ? c.agent[c.first[l]] : 0;
+        __syncwarp();
+        if (l < n) c.agent[l] = v;
+    }
+    __syncwarp();
 
     // ---- 3. per-agent occupancy masks + total timesteps; adjacency bit matrix by AND + ballot ----
     const int bw = (n + 31) >> 5;
-    c.bw = bw;
     int ts_sum = 0;
     for (int l = lane; l < n; l += 32) {
         uint32_t mk[5] = { 0, 0, 0, 0, 0 };
@@ -543,28 +573,34 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, int slot,
         uint2 *dst = (uint2 *)(c.mask + 6 * l);
         dst[0] = make_uint2(mk[0], mk[1]); dst[1] = make_uint2(mk[2], mk[3]); dst[2] = make_uint2(mk[4], 0u);
     }
-    for (int o = 16; o > 0; o >>= 1) ts_sum += __shfl_xor_sync(FULLMASK, ts_sum, o);
+    ts_sum = __reduce_add_sync(FULLMASK, ts_sum);
     __syncwarp();
+    int pc_sum = 0;
     for (int yb = 0; yb < bw; yb++) {
         const int y = yb * 32 + lane;
         uint2 m0 = make_uint2(0, 0), m1 = m0, m2 = m0;
         if (y < n) { const uint2 *src = (const uint2 *)(c.mask + 6 * y); m0 = src[0]; m1 = src[1]; m2 = src[2]; }
-        for (int x = 0; x < n; x++) {
-            const uint2 *ox = (const uint2 *)(c.mask + 6 * x);
-            uint2 a0 = ox[0], a1 = ox[1], a2 = ox[2];
-            uint32_t hit = (m0.x & a0.x) | (m0.y & a0.y) | (m1.x & a1.x) | (m1.y & a1.y) | (m2.x & a2.x);
-            uint32_t word = __ballot_sync(FULLMASK, hit != 0 && y != x);
-            if (lane == 0) c.bits[x * bw + yb] = word;
+        for (int x0 = 0; x0 < n; x0 += 32) {
+            const int xe = min(32, n - x0);
+            uint32_t keep = 0;
+            for (int xi = 0; xi < xe; xi++) {
+                const uint2 *ox = (const uint2 *)(c.mask + 6 * (x0 + xi));
+                uint2 a0 = ox[0], a1 = ox[1], a2 = ox[2];
+                uint32_t hit = (m0.x & a0.x) | (m0.y & a0.y) | (m1.x & a1.x) | (m1.y & a1.y) | (m2.x & a2.x);
+                uint32_t word = __ballot_sync(FULLMASK, hit != 0 && y != x0 + xi);
+                if (lane == xi) keep = word;
+            }
+            // lane xi holds word yb of row x0 + xi: coalesced store into the word-major scratch
+            if (lane < xe) {
+                __stcg(&bits[yb * MM + x0 + lane], keep);
+                const int pcv = __popc(keep);
+                pc_sum += pcv;
+                c.pc[x0 + lane] = (uint16_t)(yb == 0 ? pcv : (int)c.pc[x0 + lane] + pcv);
+            }
         }
     }
+    pc_sum = __reduce_add_sync(FULLMASK, pc_sum);
     __syncwarp();
-    int pc_sum = 0;
-    for (int l = lane; l < n; l += 32) {
-        int pcv = 0;
-        for (int w = 0; w < bw; w++) pcv += __popc(c.bits[l * bw + w]);
-        c.pc[l] = (uint16_t)pcv; pc_sum += pcv;
-    }
-    for (int o = 16; o > 0; o >>= 1) pc_sum += __shfl_xor_sync(FULLMASK, pc_sum, o);
     acc_pot += (unsigned)pc_sum / 2;
     if (pc_sum == 0) {                                    // contactnetwork.py:198
         if (lane == 0) g.slot_nrows[slot] = 0;
@@ -582,121 +618,126 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, int slot,
     for (int l = lane; l < n; l += 32) {
         double d = 0.0;
         int pcv = c.pc[l];
-        if (pcv > 0) d = degree_f(g, P, c.agent[c.first[l]], act, c.ts[l], pcv, avg_ts, avg_pc, log_avg_ts, log_avg_pc, one_minus_mhd);
+        if (pcv > 0) d = degree_f(g, P, c.agent[l], act, c.ts[l], pcv, avg_ts, avg_pc, log_avg_ts, log_avg_pc, one_minus_mhd);
         degf[l] = d;
     }
     __syncwarp();
     long long deg_sum = 0;
     if (lane == 0) deg_sum = (long long)rint(np_pairwise_sum(degf, n));
     deg_sum = __shfl_sync(FULLMASK, deg_sum, 0);
-    for (int l = lane; l < n; l += 32) c.deg[l] = (int16_t)degree_i(degf[l], deg_sum, max_degree, c.pc[l]);
-    __syncwarp();
-
     // ---- 5. greedy order: sorted(zip(deg, id), reverse=True) (contactnetwork.py:283) ----
+    // key[l] takes the slot of degf[l] (same lane reads the float degree, then writes the key)
     int Pn = 2;
     while (Pn < n) Pn <<= 1;
-    for (int l = lane; l < Pn; l += 32) {
+    int n_act = 0;                                         // agents with initial degree > 0 lead the order
+    for (int l0 = 0; l0 < Pn; l0 += 32) {
+        const int l = l0 + lane;
+        int dg = 0;
         uint64_t key = ~0ull;
-        if (l < n) key = ~(((uint64_t)(uint16_t)c.deg[l] << 48) | ((uint64_t)(uint32_t)c.agent[c.first[l]] << 16) | (uint64_t)l);
-        c.key[l] = key;
+        if (l < n) {
+            dg = degree_i(degf[l], deg_sum, max_degree, c.pc[l]);
+            c.deg[l] = (int16_t)dg;
+            key = ~(((uint64_t)(uint16_t)dg << 48) | ((uint64_t)(uint32_t)c.agent[l] << 16) | (uint64_t)l);
+        }
+        if (l < Pn) c.key[l] = key;
+        const uint32_t al = __ballot_sync(FULLMASK, dg > 0);
+        if (lane == 0) c.alive[l0 >> 5] = al;              // word of the alive mask (remaining degree > 0)
+        n_act += __popc(al);
     }
     __syncwarp();
     warp_bitonic_sort(c.key, Pn, lane);
+    uint16_t *ord = c.la;                                  // la is dead after phase 2
+    for (int l = lane; l < n_act; l += 32) ord[l] = (uint16_t)((~c.key[l]) & 0xffff);
+    __syncwarp();
 
     // ---- 6. greedy sampling + create_contacts (contactnetwork.py:287-301, 386-424) ----
-    // lane w owns word w of the alive mask (agents with remaining degree > 0); n <= 1024 -> at most 32 words
-    uint32_t alive = 0;
-    if (lane < bw) for (int b = 0; b < 32; b++) { int y = lane * 32 + b; if (y < n && c.deg[y] > 0) alive |= 1u << b; }
+    // Per main agent x: candidates = adjacency row of x AND alive (util.get_all_contacts_ids_by_id).  Philox mode: draw t
+    // takes the r_t-th REMAINING candidate in canonical order, r_t = floor(u_t * (nc - t)).  That sequence is a Lehmer
+    // code: lane t decodes its own pick's rank among the ORIGINAL candidates by walking the earlier draws backwards,
+    // q += (q >= r_s) for s = t-1 .. 0, and selects that set bit -- all picks of the main agent in parallel.
+    uint16_t *rarr = c.ts;                                 // draws r_t (ts is dead after phase 4)
+    uint16_t *pickarr = c.pc;                              // replay: picked local agents (pc is dead after phase 4)
     RowRec *rows = g.scratch_rows + g.slot_rowoff[slot];
     const int row_cap = g.slot_rowbound[slot];
+    const bool replay = g.day.mode == MTD_MODE_REPLAY;
     int n_rows = 0;
-    for (int oi = 0; oi < n; oi++) {
-        const int x = (int)((~c.key[oi]) & 0xffff);
+    uint32_t pre = (lane < bw && n_act > 0) ? __ldcg(&bits[lane * MM + ord[0]]) : 0u;
+    for (int oi = 0; oi < n_act; oi++) {
+        const int x = ord[oi];
+        const uint32_t roww = pre;
+        if (oi + 1 < n_act) pre = (lane < bw) ? __ldcg(&bits[lane * MM + ord[oi + 1]]) : 0u;
         const int dx = c.deg[x];
-        if (((~c.key[oi]) >> 48) == 0) break;                // initial degree 0: so are all that follow
         if (dx <= 0) continue;
-        uint32_t cw = (lane < bw) ? (c.bits[x * bw + lane] & alive) : 0u;     // util.get_all_contacts_ids_by_id
-        int cnt = __popc(cw);
-        int incl = cnt;
-        for (int o = 1; o < 32; o <<= 1) { int t = __shfl_up_sync(FULLMASK, incl, o); if (lane >= o) incl += t; }
-        const int nc = __shfl_sync(FULLMASK, incl, 31);
+        const uint32_t cw = (lane < bw) ? (roww & c.alive[lane]) : 0u;
+        const int cnt = __popc(cw);
+        const int nc = __reduce_add_sync(FULLMASK, cnt);
         if (nc == 0) continue;                               // returned None (contactnetwork.py:294)
         const int d = dx < nc ? dx : nc;
-        const int agx = c.agent[c.first[x]];
-        int npick = d;
-        long long toff = -1;
-        if (g.day.mode == MTD_MODE_REPLAY) {
+        const int agx = c.agent[x];
+        if (lane < bw) { c.candw[lane] = cw; c.ccnt[lane] = (uint32_t)cnt; }
+        int made = d, spent = d;
+        if (replay) {
+            // the reference's selected partners (agent ids) -> local indices, validated against the candidate set
             long long tr = tape_find_sel(g.tape, cell, agx);
             if (tr < 0) { if (lane == 0) atomicAdd(&g.ctr->tape_miss, 1); continue; }
-            toff = g.tape.sel_off[tr];
-            int tc = g.tape.sel_off[tr + 1] - (int)toff;
+            const long long toff = g.tape.sel_off[tr];
+            const int tc = g.tape.sel_off[tr + 1] - (int)toff;
+            int npick = d;
             if (tc != d) { if (lane == 0) atomicAdd(&g.ctr->tape_miss, 1); if (tc < npick) npick = tc; }
-        }
-        int made = 0;
-        for (int t0 = 0; t0 < npick; t0 += 32) {
-            uint32_t wv = 0;
-            if (toff < 0 && t0 + lane < npick) {
-                uint32_t w4[4];
-                const int t = t0 + lane;
-                philox4x32((uint32_t)g.day.day, (uint32_t)cell, (uint32_t)agx, (uint32_t)(t >> 2), g.day.seed, SITE_SELECT, w4);
-                wv = pick4(w4, t & 3);
-            }
-            const int tend = min(32, npick - t0);
-            for (int tt = 0; tt < tend; tt++) {
-                const int t = t0 + tt;
+            spent = npick;
+            made = 0;
+            __syncwarp();
+            for (int t = 0; t < npick; t++) {
+                const int pid = g.tape.sel_picks[toff + t];
                 int y = -1;
-                if (toff >= 0) {
-                    // replay: the reference's selected partner (agent id) -> local index through the cell's hash
-                    const int pid = g.tape.sel_picks[toff + t];
-                    uint32_t h = ((uint32_t)pid * 2654435761u) & (H - 1);
-                    while (true) {
-                        uint32_t v = c.hash[h];
-                        if (v == 0) break;
-                        if (c.agent[v - 1] == pid) { y = c.la[v - 1]; break; }
-                        h = (h + 1) & (H - 1);
-                    }
-                    bool ok = false;
-                    if (y >= 0 && lane == (y >> 5)) ok = (cw >> (y & 31)) & 1u;
-                    ok = __any_sync(FULLMASK, ok);
-                    if (!ok) { if (lane == 0) atomicAdd(&g.ctr->tape_miss, 1); continue; }
-                    if (lane == (y >> 5)) { cw &= ~(1u << (y & 31)); }
-                } else {
-                    const uint32_t wt = __shfl_sync(FULLMASK, wv, tt);
-                    const int r = (int)__umulhi(wt, (uint32_t)(nc - t));          // r-th remaining candidate
-                    const uint32_t le = __ballot_sync(FULLMASK, incl > r);
-                    const int Lw = __ffs(le) - 1;                                  // word that holds it
-                    int yy = 0;
-                    if (lane == Lw) {
-                        int bit = nth_set_bit(cw, r - (incl - cnt));
-                        cw &= ~(1u << bit); cnt -= 1;
-                        yy = Lw * 32 + bit;
-                    }
-                    if (lane >= Lw) incl -= 1;
-                    y = __shfl_sync(FULLMASK, yy, Lw);
+                for (int l0 = 0; l0 < n; l0 += 32) {
+                    const int l = l0 + lane;
+                    const uint32_t hb = __ballot_sync(FULLMASK, l < n && c.agent[l] == pid);
+                    if (hb) { y = l0 + __ffs(hb) - 1; break; }
                 }
-                if (lane == (y >> 5)) {                      // partner degree - 1; dead at 0 (delete_all_pairs_by_id)
-                    int nd = (int)c.deg[y] - 1;
-                    c.deg[y] = (int16_t)nd;
-                    if (nd == 0) alive &= ~(1u << (y & 31));
-                }
-                if (lane == 0) c.cand[made] = (uint16_t)y;
+                const bool ok = y >= 0 && ((c.candw[y >> 5] >> (y & 31)) & 1u);
+                __syncwarp();
+                if (!ok) { if (lane == 0) atomicAdd(&g.ctr->tape_miss, 1); continue; }
+                if (lane == 0) { c.candw[y >> 5] &= ~(1u << (y & 31)); pickarr[made] = (uint16_t)y; }
                 made++;
+                __syncwarp();
+            }
+        } else {
+            for (int t = lane; t < d; t += 32) {
+                uint32_t w4[4];
+                philox4x32((uint32_t)g.day.day, (uint32_t)cell, (uint32_t)agx, (uint32_t)(t >> 2), g.day.seed, SITE_SELECT, w4);
+                rarr[t] = (uint16_t)__umulhi(pick4(w4, t & 3), (uint32_t)(nc - t));
             }
         }
-        if (lane == (x >> 5)) { c.deg[x] = (int16_t)(d - npick); if (d - npick == 0) alive &= ~(1u << (x & 31)); }
         __syncwarp();
         for (int t = lane; t < made; t += 32) {
-            const int y = c.cand[t];
+            int y;
+            if (replay) y = pickarr[t];
+            else {
+                int q = rarr[t];
+                for (int s = t - 1; s >= 0; s--) q += (q >= (int)rarr[s]);
+                int w = 0, cn = (int)c.ccnt[0];
+                while (q >= cn) { q -= cn; w++; cn = (int)c.ccnt[w]; }
+                y = w * 32 + nth_set_bit(c.candw[w], q);
+            }
+            // partner degree - 1; dead at 0 (delete_all_pairs_by_id).  Picks are distinct agents: no conflicts.
+            const int nd = (int)c.deg[y] - 1;
+            c.deg[y] = (int16_t)nd;
+            if (nd == 0) atomicAnd(&c.alive[y >> 5], ~(1u << (y & 31)));
             bool x_first; int st, en, dur;
             pair_row_lists(c, x, y, x_first, st, en, dur);
             if (n_rows + t < row_cap) {
                 RowRec rr;
-                const int agy = c.agent[c.first[y]];
+                const int agy = c.agent[y];
                 rr.a1 = x_first ? agx : agy; rr.a2 = x_first ? agy : agx;
                 rr.sed = (uint32_t)st | ((uint32_t)en << 8) | ((uint32_t)dur << 16);
                 rr.slot = slot;
                 rows[n_rows + t] = rr;
             } else g.ctr->error = MTD_E_CAPACITY;
+        }
+        if (lane == 0) {                                     // the main agent's degree is spent
+            c.deg[x] = (int16_t)(d - spent);
+            if (d - spent == 0) atomicAnd(&c.alive[x >> 5], ~(1u << (x & 31)));
         }
         n_rows += made;
         __syncwarp();
@@ -711,6 +752,7 @@ __global__ void __launch_bounds__(WARPS * 32) k1_large_kernel(DevCtx g, int cls)
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned char *sm = smem + (size_t)warp * Lay<MM>::bytes;
+    uint32_t *bits = g.k1_bits + ((size_t)blockIdx.x * WARPS + warp) * Lay<MM>::bits_words;
     if (g.ctr->error) return;
     const int total = g.ctr->class_cells[cls];
     const int32_t *list = g.class_list + (int64_t)cls * g.class_stride;
@@ -720,7 +762,7 @@ __global__ void __launch_bounds__(WARPS * 32) k1_large_kernel(DevCtx g, int cls)
         if (lane == 0) w = atomicAdd(&g.ctr->class_cursor[cls], 1);
         w = __shfl_sync(FULLMASK, w, 0);
         if (w >= total) break;
-        process_cell_large<MM>(g, sm, list[w], lane, acc_pairs, acc_pot);
+        process_cell_large<MM>(g, sm, bits, list[w], lane, acc_pairs, acc_pot);
     }
     if (lane == 0 && (acc_pairs | acc_pot)) {
         atomicAdd(&g.ctr->pairs_evaluated, acc_pairs);
@@ -728,21 +770,29 @@ __global__ void __launch_bounds__(WARPS * 32) k1_large_kernel(DevCtx g, int cls)
     }
 }
 
+// resident blocks per SM of one large-cell class (cap: the 1024 class is almost empty, keep its scratch small)
 template <int MM, int WARPS>
-int launch_large(const DevCtx &c, int cls, cudaStream_t st, int sm_count)
+int large_blocks_per_sm(int cap)
 {
-    size_t smem = Lay<MM>::bytes * WARPS;
-    static bool configured = false;
-    if (!configured) {
-        cudaFuncSetAttribute(k1_large_kernel<MM, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        configured = true;
-    }
     static int per_sm = 0;
     if (per_sm == 0) {
+        size_t smem = Lay<MM>::bytes * WARPS;
+        cudaFuncSetAttribute(k1_large_kernel<MM, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_large_kernel<MM, WARPS>, WARPS * 32, smem);
         if (per_sm < 1) per_sm = 1;
+        if (per_sm > cap) per_sm = cap;
     }
-    k1_large_kernel<MM, WARPS><<<sm_count * per_sm, WARPS * 32, smem, st>>>(c, cls);
+    return per_sm;
+}
+
+template <int MM, int WARPS>
+int launch_large(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int cap)
+{
+    int grid = sm_count * large_blocks_per_sm<MM, WARPS>(cap);
+    const int64_t fit = c.k1_bits_words / (int64_t)(Lay<MM>::bits_words * WARPS);
+    if (grid > fit) grid = (int)fit;
+    if (grid < 1) return 0;
+    k1_large_kernel<MM, WARPS><<<grid, WARPS * 32, Lay<MM>::bytes * WARPS, st>>>(c, cls);
     return 1;
 }
 
@@ -758,15 +808,31 @@ int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count)
     return 1;
 }
 
+#define K1_C5 1024, 1
+#define K1_C4 320, 5
+#define K1_C3 128, 4
+#define K1_C5_CAP 2
+#define K1_NOCAP 64
+
 }  // namespace
+
+// words of the adjacency scratch (DevCtx::k1_bits) the large-cell launches need on a device with sm_count SMs
+int64_t k1_bits_words_needed(int sm_count)
+{
+    int64_t w5 = (int64_t)sm_count * large_blocks_per_sm<K1_C5>(K1_C5_CAP) * 1 * (int64_t)Lay<1024>::bits_words;
+    int64_t w4 = (int64_t)sm_count * large_blocks_per_sm<K1_C4>(K1_NOCAP) * 5 * (int64_t)Lay<320>::bits_words;
+    int64_t w3 = (int64_t)sm_count * large_blocks_per_sm<K1_C3>(K1_NOCAP) * 4 * (int64_t)Lay<128>::bits_words;
+    int64_t w = w5 > w4 ? w5 : w4;
+    return w > w3 ? w : w3;
+}
 
 int launch_k1(const DevCtx &c, cudaStream_t st, int sm_count)
 {
     // big cells first: they are the long poles
     int n = 0;
-    n += launch_large<1024, 1>(c, 5, st, sm_count);
-    n += launch_large<320, 2>(c, 4, st, sm_count);
-    n += launch_large<128, 4>(c, 3, st, sm_count);
+    n += launch_large<K1_C5>(c, 5, st, sm_count, K1_C5_CAP);
+    n += launch_large<K1_C4>(c, 4, st, sm_count, K1_NOCAP);
+    n += launch_large<K1_C3>(c, 3, st, sm_count, K1_NOCAP);
     n += launch_small<32>(c, 2, st, sm_count);
     n += launch_small<16>(c, 1, st, sm_count);
     n += launch_small<8>(c, 0, st, sm_count);
