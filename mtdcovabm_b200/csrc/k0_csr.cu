@@ -36,32 +36,49 @@ __device__ __forceinline__ int size_class(int m)
     return m <= 8 ? 0 : (m <= 16 ? 1 : (m <= 32 ? 2 : (m <= 128 ? 3 : (m <= 320 ? 4 : 5))));
 }
 
-__global__ void k0_assign_kernel(DevCtx c, const int32_t *flags_excl)
+__global__ void __launch_bounds__(256) k0_assign_kernel(DevCtx c, const int32_t *flags_excl)
 {
-    // flags_excl: exclusive scan of the first-of-cell flags, [M+1]
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < c.M; i += (int64_t)gridDim.x * blockDim.x) {
-        if (i == 0) c.ctr->n_slots = flags_excl[c.M];
-        if (flags_excl[i + 1] == flags_excl[i]) continue;
-        int slot = flags_excl[i];
-        int cell = c.iv_cell[i];
-        int m = c.cell_count[cell];
-        c.slot_of_cell[cell] = slot;
-        c.slot_cell[slot] = cell;
-        c.slot_m[slot] = m;
-        c.slot_first[slot] = order_of(c, i);
-        c.slot_cursor[slot] = 0;
-        c.slot_nrows[slot] = 0;
-        if (m > MTD_MAX_CELL_INTERVALS) { c.ctr->error = MTD_E_CELL_TOO_LARGE; m = 0; }
-        int ct = c.cell_type[cell];
-        int indid = (ct == CT_WORKPLACE && c.cell_indid) ? c.cell_indid[cell] : -1;
-        long long k = c.P->k_by_act[activity_of_celltype(ct, indid)];
-        // rows <= sum(deg)/2, sum(deg) <= max(k*n, S) + n/2 with n <= m; and rows <= m(m-1)/2
-        long long b1 = (long long)m * (m - 1) / 2, b2 = (k * m + m / 2 + 2) / 2 + 1;
-        c.slot_rowbound[slot] = (int)(b1 < b2 ? b1 : b2);
-        c.slot_listneed[slot] = 0;
-        int cls = size_class(m);
-        int idx = atomicAdd(&c.ctr->class_cells[cls], 1);
-        c.class_list[(int64_t)cls * c.class_stride + idx] = slot;
+    // flags_excl: exclusive scan of the first-of-cell flags, [M+1].  The size-class lists are appended block by block:
+    // positions inside the block come from shared-memory counters, one global atomic per class per block iteration
+    // (2.2M cells on six global counters would serialise in L2 otherwise).
+    __shared__ int s_cnt[MTD_NUM_CLASSES], s_base[MTD_NUM_CLASSES];
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t rounds = (c.M + stride - 1) / stride;
+    for (int64_t rd = 0; rd < rounds; rd++) {
+        const int64_t i = rd * stride + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+        if (threadIdx.x < MTD_NUM_CLASSES) s_cnt[threadIdx.x] = 0;
+        __syncthreads();
+        int slot = -1, cls = 0, local = 0;
+        if (i < c.M) {
+            if (i == 0) c.ctr->n_slots = flags_excl[c.M];
+            if (flags_excl[i + 1] != flags_excl[i]) {
+                slot = flags_excl[i];
+                int cell = c.iv_cell[i];
+                int m = c.cell_count[cell];
+                c.slot_of_cell[cell] = slot;
+                c.slot_cell[slot] = cell;
+                c.slot_m[slot] = m;
+                c.slot_first[slot] = order_of(c, i);
+                c.slot_cursor[slot] = 0;
+                c.slot_nrows[slot] = 0;
+                if (m > MTD_MAX_CELL_INTERVALS) { c.ctr->error = MTD_E_CELL_TOO_LARGE; m = 0; }
+                int ct = c.cell_type[cell];
+                int indid = (ct == CT_WORKPLACE && c.cell_indid) ? c.cell_indid[cell] : -1;
+                long long k = c.P->k_by_act[activity_of_celltype(ct, indid)];
+                // rows <= sum(deg)/2, sum(deg) <= max(k*n, S) + n/2 with n <= m; and rows <= m(m-1)/2
+                long long b1 = (long long)m * (m - 1) / 2, b2 = (k * m + m / 2 + 2) / 2 + 1;
+                c.slot_rowbound[slot] = (int)(b1 < b2 ? b1 : b2);
+                c.slot_listneed[slot] = 0;
+                cls = size_class(m);
+                local = atomicAdd(&s_cnt[cls], 1);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < MTD_NUM_CLASSES)
+            s_base[threadIdx.x] = s_cnt[threadIdx.x] ? atomicAdd(&c.ctr->class_cells[threadIdx.x], s_cnt[threadIdx.x]) : 0;
+        __syncthreads();
+        if (slot >= 0) c.class_list[(int64_t)cls * c.class_stride + s_base[cls] + local] = slot;
+        __syncthreads();
     }
 }
 

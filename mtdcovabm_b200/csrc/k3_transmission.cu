@@ -54,12 +54,14 @@ __global__ void k3_eval_kernel(DevCtx c)
 {
     const int64_t n = c.ctr->n_rows;
     const mtd_params *P = c.P;
+    int n_si = 0;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
         RowRec r = c.rows[i];
         int s1 = c.seir[r.a1], s2 = c.seir[r.a2];
         bool si = (s1 == S_INF && s2 == S_SUS) || (s1 == S_SUS && s2 == S_INF);        // epidemiology.py:106-107
         int dur = (int)(r.sed >> 16);
         if (!si || dur <= 0) { if (c.row_p) c.row_p[i] = __longlong_as_double(0x7ff8000000000000LL); continue; }
+        n_si++;
         int ex = (s1 == S_SUS) ? r.a1 : r.a2;
         int cell = c.slot_cell[r.slot];
         int sct = simcelltype_of(c.cell_type[cell]);
@@ -75,7 +77,6 @@ __global__ void k3_eval_kernel(DevCtx c)
         double susc = P->probs_by_age[0][c.epi_age_bracket[ex]];
         double p = base * (mult * susc * (1 - c.day.mhd) * imm);                        // epidemiology.py:196
         if (c.row_p) c.row_p[i] = p;
-        atomicAdd(&c.ctr->n_si_rows, 1);
         double u;
         if (c.day.mode == MTD_MODE_REPLAY) {
             long long t = tape_find_pair(c.tape, cell, r.a1, r.a2);
@@ -92,87 +93,129 @@ __global__ void k3_eval_kernel(DevCtx c)
             c.succ[idx] = (int32_t)i;
         }
     }
+    n_si = __reduce_add_sync(FULLMASK, n_si);            // whole warps reach this point (no early return above)
+    if ((threadIdx.x & 31) == 0 && n_si) atomicAdd(&c.ctr->n_si_rows, n_si);
 }
 
+// Draw slots of one exposure (the layout of a replay-tape exposure record, tests/golden/ref_harness.py): 0 exposure
+// timestep, 1..10 lognormal day counts of transitions 0..9, 11..14 branch uniforms, 15 / 19 timestep options, 16 / 20
+// uniforms, 17 / 18 test / result delays.  Replay mode reads the reference's values; Philox mode fills the same record
+// with counter-based draws keyed by (day, agent, slot) -- one slot per lane, all at once -- and reads it the same way.
 struct Draws {
-    const DevCtx *c; int agent; const double *row; int miss;
+    const double *row; int miss;
     __device__ double uniform(int slot)
     {
-        if (c->day.mode == MTD_MODE_REPLAY) {
-            if (!row || isnan(row[slot])) { miss++; return 1.0; }
-            return row[slot];
-        }
-        uint32_t w[4];
-        philox4x32((uint32_t)c->day.day, (uint32_t)agent, (uint32_t)slot, 0u, c->day.seed, SITE_EXPO, w);
-        return u53(w[0], w[1]);
+        if (!row || isnan(row[slot])) { miss++; return 1.0; }
+        return row[slot];
     }
-    __device__ int lognormal_days(int slot, double mu, double sigma)
+    __device__ int lognormal_days(int slot)
     {   // util.sample_log_normal(..., isInt=True): np.random.lognormal then round (util.py:88-115)
-        if (c->day.mode == MTD_MODE_REPLAY) {
-            if (!row || isnan(row[slot])) { miss++; return 0; }
-            return (int)row[slot];
-        }
-        uint32_t w[4];
-        philox4x32((uint32_t)c->day.day, (uint32_t)agent, (uint32_t)slot, 0u, c->day.seed, SITE_EXPO, w);
-        double u1 = u53(w[0], w[1]), u2 = u53(w[2], w[3]);
-        double z = sqrt(-2.0 * log(1.0 - u1)) * cos(6.283185307179586 * u2);
-        return (int)rint(exp(mu + sigma * z));
+        if (!row || isnan(row[slot])) { miss++; return 0; }
+        return (int)row[slot];
     }
     __device__ int timestep_option(int slot)
     {   // np.random.choice(np.arange(42, 121)) (epidemiology.py:84)
-        if (c->day.mode == MTD_MODE_REPLAY) {
-            if (!row || isnan(row[slot])) { miss++; return 42; }
-            return (int)row[slot];
-        }
-        uint32_t w[4];
-        philox4x32((uint32_t)c->day.day, (uint32_t)agent, (uint32_t)slot, 0u, c->day.seed, SITE_EXPO, w);
-        return 42 + (int)__umulhi(w[0], 79u);
+        if (!row || isnan(row[slot])) { miss++; return 42; }
+        return (int)row[slot];
     }
 };
 
-// one thread per successful draw; only the winner of each agent samples the trajectory
-__global__ void k3_trajectory_kernel(DevCtx c, int32_t *dbuf, int64_t cap)
+__device__ __forceinline__ double philox_slot_draw(const DevCtx &c, const mtd_params *P, int agent, int slot)
 {
+    uint32_t w[4];
+    philox4x32((uint32_t)c.day.day, (uint32_t)agent, (uint32_t)slot, 0u, c.day.seed, SITE_EXPO, w);
+    if ((slot >= 1 && slot <= 10) || slot == 17 || slot == 18) {
+        double mu, sigma;
+        if (slot <= 10) { mu = P->ln_mu[slot - 1]; sigma = P->ln_sigma[slot - 1]; }
+        else if (slot == 17) { mu = P->test_mu; sigma = P->test_sigma; }
+        else { mu = P->result_mu; sigma = P->result_sigma; }
+        double u1 = u53(w[0], w[1]), u2 = u53(w[2], w[3]);
+        double z = sqrt(-2.0 * log(1.0 - u1)) * cos(6.283185307179586 * u2);
+        return rint(exp(mu + sigma * z));
+    }
+    if (slot == 15 || slot == 19) return (double)(42 + (int)__umulhi(w[0], 79u));
+    return u53(w[0], w[1]);
+}
+
+#define K3T_WARPS 4
+#define K3T_MAXIV 16
+// one WARP per successful draw; only the winner of each agent samples the trajectory
+__global__ void __launch_bounds__(K3T_WARPS * 32) k3_trajectory_kernel(DevCtx c, int32_t *dbuf, int64_t cap)
+{
+    __shared__ double s_row[K3T_WARPS][MTD_EXPO_W + 3];
+    __shared__ uint16_t s_iv[K3T_WARPS][2][K3T_MAXIV];
     const int n = c.ctr->n_succ;
     const mtd_params *P = c.P;
-    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int n_warps = gridDim.x * K3T_WARPS;
+    for (int t = blockIdx.x * K3T_WARPS + warp; t < n; t += n_warps) {
         const int64_t i = c.succ[t];
         RowRec r = c.rows[i];
         const int ex = (c.seir[r.a1] == S_SUS) ? r.a1 : r.a2;
         const unsigned long long key = row_key(c, r, i);
-        if (c.win[ex] != key) continue;
-        const int cell = c.slot_cell[r.slot];
-        Draws D; D.c = &c; D.agent = ex; D.row = nullptr; D.miss = 0;
+        if (c.win[ex] != key) continue;                      // warp-uniform
+        Draws D; D.row = nullptr; D.miss = 0;
+        int ts = 0;
+        __syncwarp();
         if (c.day.mode == MTD_MODE_REPLAY) {
             long long e = tape_find_expo(c.tape, ex);
             if (e >= 0) D.row = c.tape.expo_row + e * MTD_EXPO_W; else D.miss++;
-        }
-        // sampled_exposed_timestep = np.random.choice(overlapping_timesteps) (epidemiology.py:246)
-        int ts = 0;
-        if (c.day.mode == MTD_MODE_REPLAY) ts = (D.row && !isnan(D.row[0])) ? (int)D.row[0] : 0;
-        else {
-            uint32_t w[4];
-            philox4x32((uint32_t)c.day.day, (uint32_t)ex, 0u, 0u, c.day.seed, SITE_EXPO, w);
-            int idx = (int)__umulhi(w[0], (uint32_t)(r.sed >> 16));
-            // flattened overlap list of key (a1, a2): a1's intervals (outer) x a2's (inner), list order
+            // sampled_exposed_timestep = np.random.choice(overlapping_timesteps) (epidemiology.py:246)
+            ts = (D.row && !isnan(D.row[0])) ? (int)D.row[0] : 0;
+        } else {
+            if (lane >= 1 && lane < MTD_EXPO_W) s_row[warp][lane] = philox_slot_draw(c, P, ex, lane);
+            // the two agents' intervals in list order: lanes scan the cell's records, ranks by ballot
             const int64_t b = c.slot_off[r.slot];
             const int m = c.slot_m[r.slot];
-            bool done = false;
-            for (int p = 0; p < m && !done; p++) {
-                IvRec ra = c.csr_sorted[b + p];
-                if (ra.agent != r.a1) continue;
-                int sa = ra.se & 0xff, ea = (ra.se >> 8) & 0xff;
-                for (int q = 0; q < m; q++) {
-                    IvRec rb = c.csr_sorted[b + q];
-                    if (rb.agent != r.a2) continue;
-                    int lo = max(sa, (int)(rb.se & 0xff)), hi = min(ea, (int)((rb.se >> 8) & 0xff));
-                    if (lo > hi) continue;
-                    int len = hi - lo + 1;
-                    if (idx < len) { ts = lo + idx; done = true; break; }
-                    idx -= len;
+            int na = 0, nb = 0;
+            for (int p0 = 0; p0 < m; p0 += 32) {
+                const int p = p0 + lane;
+                IvRec rec; rec.agent = -1; rec.se = 0;
+                if (p < m) rec = c.csr_sorted[b + p];
+                const bool ia = p < m && rec.agent == r.a1, ib = p < m && rec.agent == r.a2;
+                const uint32_t ba = __ballot_sync(FULLMASK, ia), bb = __ballot_sync(FULLMASK, ib);
+                if (ia) { int k = na + __popc(ba & lanemask_lt()); if (k < K3T_MAXIV) s_iv[warp][0][k] = (uint16_t)(rec.se & 0xffffu); }
+                if (ib) { int k = nb + __popc(bb & lanemask_lt()); if (k < K3T_MAXIV) s_iv[warp][1][k] = (uint16_t)(rec.se & 0xffffu); }
+                na += __popc(ba); nb += __popc(bb);
+            }
+            __syncwarp();
+            if (lane == 0) {
+                uint32_t w[4];
+                philox4x32((uint32_t)c.day.day, (uint32_t)ex, 0u, 0u, c.day.seed, SITE_EXPO, w);
+                int idx = (int)__umulhi(w[0], (uint32_t)(r.sed >> 16));
+                // flattened overlap list of key (a1, a2): a1's intervals (outer) x a2's (inner), list order
+                bool done = false;
+                if (na <= K3T_MAXIV && nb <= K3T_MAXIV) {
+                    for (int p = 0; p < na && !done; p++) {
+                        const int sa = s_iv[warp][0][p] & 0xff, ea = s_iv[warp][0][p] >> 8;
+                        for (int q = 0; q < nb; q++) {
+                            const int lo = max(sa, (int)(s_iv[warp][1][q] & 0xff)), hi = min(ea, (int)(s_iv[warp][1][q] >> 8));
+                            if (lo > hi) continue;
+                            const int len = hi - lo + 1;
+                            if (idx < len) { ts = lo + idx; done = true; break; }
+                            idx -= len;
+                        }
+                    }
+                } else {                                     // more intervals than the staging holds: walk the records
+                    for (int p = 0; p < m && !done; p++) {
+                        IvRec ra = c.csr_sorted[b + p];
+                        if (ra.agent != r.a1) continue;
+                        int sa = ra.se & 0xff, ea = (ra.se >> 8) & 0xff;
+                        for (int q = 0; q < m; q++) {
+                            IvRec rb = c.csr_sorted[b + q];
+                            if (rb.agent != r.a2) continue;
+                            int lo = max(sa, (int)(rb.se & 0xff)), hi = min(ea, (int)((rb.se >> 8) & 0xff));
+                            if (lo > hi) continue;
+                            int len = hi - lo + 1;
+                            if (idx < len) { ts = lo + idx; done = true; break; }
+                            idx -= len;
+                        }
+                    }
                 }
             }
+            D.row = s_row[warp];
         }
+        if (lane != 0) continue;                             // the branchy remainder is one lane's work
         double imm, asym;
         vacc_multipliers(P, c.last_dose_day[ex], c.day.day, imm, asym);
         const int b = c.epi_age_bracket[ex];
@@ -183,7 +226,7 @@ __global__ void k3_trajectory_kernel(DevCtx c, int32_t *dbuf, int64_t cap)
         for (int k = 0; k < MTD_DELTA_WORDS; k++) rec[k] = 0;
         int ns = 0;
         int32_t sched[6];
-#define STEP(T) do { incr += D.lognormal_days(1 + (T), P->ln_mu[T], P->ln_sigma[T]); \
+#define STEP(T) do { incr += D.lognormal_days(1 + (T)); \
                      if (incr >= current_day && ns < 6) sched[ns++] = (int32_t)(((uint32_t)incr << 16) | ((uint32_t)(T) << 8) | (uint32_t)ts); } while (0)
         int symptomatic_day = -1, recovered = 0, start_hosp = MTD_NONE, end_hosp = MTD_NONE, inf_type;
         STEP(T_EXP_INF);
@@ -209,9 +252,9 @@ __global__ void k3_trajectory_kernel(DevCtx c, int32_t *dbuf, int64_t cap)
             int tts = D.timestep_option(15);                                            // epidemiology.py:480
             if (c.day.testing_enabled && c.test_day[2 * (int64_t)ex] == MTD_NONE) {     // schedule_test :502-565
                 if (D.uniform(16) < P->testing_after_symptoms_probability) {
-                    test_day = symptomatic_day + D.lognormal_days(17, P->test_mu, P->test_sigma);
+                    test_day = symptomatic_day + D.lognormal_days(17);
                     test_ts = tts;
-                    tres_day = test_day + D.lognormal_days(18, P->result_mu, P->result_sigma);
+                    tres_day = test_day + D.lognormal_days(18);
                 }
             }
             (void)D.timestep_option(19);                                                // epidemiology.py:496
@@ -336,7 +379,7 @@ int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, cudaStream_t st,
     cudaMemsetAsync(c.win, 0xff, sizeof(unsigned long long) * (size_t)c.n_agents, st);
     cudaMemsetAsync(dbuf, 0, sizeof(int32_t) * MTD_DELTA_WORDS, st);
     k3_eval_kernel<<<sm_count * 8, 256, 0, st>>>(c);
-    k3_trajectory_kernel<<<sm_count, 128, 0, st>>>(c, dbuf, cap);
+    k3_trajectory_kernel<<<sm_count * 8, K3T_WARPS * 32, 0, st>>>(c, dbuf, cap);
     return 2;
 }
 
