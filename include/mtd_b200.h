@@ -38,7 +38,7 @@ extern "C" {
 #define MTD_MAX_CELL_INTERVALS 1024  /* largest cell (intervals) the on-chip path handles */
 
 enum { MTD_OK = 0, MTD_E_ARG = 1, MTD_E_CUDA = 2, MTD_E_CAPACITY = 3, MTD_E_CELL_TOO_LARGE = 4, MTD_E_STATE = 5 };
-enum { MTD_MEM_HOST = 0, MTD_MEM_DEVICE = 1 };
+enum { MTD_MEM_HOST = 0, MTD_MEM_DEVICE = 1, MTD_MEM_STAGED = 2 /* the stream given to mtd_prefetch_intervals */ };
 enum { MTD_MODE_REPLAY = 0, MTD_MODE_PHILOX = 1 };
 
 typedef struct mtd_handle_s *mtd_handle;
@@ -164,6 +164,33 @@ int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_trace_tape *
                         const int32_t *traced, int64_t n_slices, const int64_t *slice_off, const int32_t *rows3,
                         const uint8_t *epi_present, int mem);
 int mtd_get_traced(mtd_handle h, uint8_t *primary, uint8_t *secondary, mtd_trace_stats *stats, int mem);
+
+/* ---- pipelined boundary (the day loop of sim.py:1392-2125 driven from host memory without stalling the device) ----
+ * The reference hands the stage host containers and gets host containers back (contactnetwork.py:65-124).  These three
+ * calls keep that contract -- pinned HOST buffers in, pinned HOST buffers out -- while the copies run beside the
+ * kernels: day d+1's intervals are uploaded by a copy stream during day d, and day d's results are written straight
+ * into the caller's pinned memory by a low-occupancy export kernel on a side stream during day d+1.
+ *   mtd_prefetch_intervals    enqueue the upload of the NEXT day's stream (pinned host pointers); the next
+ *                             mtd_simulate_contact_network call passes mem = MTD_MEM_STAGED (pointers ignored).
+ *   mtd_export_day_async      enqueue the export of the day just computed; needs mtd_set_export(h, 1) before that
+ *                             day's mtd_simulate_contact_network.  rows12: packed contact rows, 12 bytes each
+ *                             {int32 a1, int32 a2, uint8 start, uint8 end, uint8 simcelltype, uint8 0} in the
+ *                             reference's row order (contactnetwork.py:98-105); exposed_kv: n_exposed pairs
+ *                             {uint64 order key, uint64 agent id} (sort by key for the reference's order);
+ *                             result: counts + occupancy, written last.  mem = MTD_MEM_HOST: the buffers are pinned
+ *                             (page-locked, device-mapped) host memory; MTD_MEM_DEVICE: device memory.
+ *   mtd_export_wait           block the host until the export with that ticket has landed. */
+typedef struct {
+    int64_t day, n_rows, n_exposed;
+    int64_t occupancy[6];            /* agents per SEIR state after the day (dynamicstatistics.py:169-193) */
+    int64_t pairs_evaluated, error, ticket;
+} mtd_day_result;
+int mtd_set_export(mtd_handle h, int on);
+int mtd_prefetch_intervals(mtd_handle h, int64_t n_intervals, const int32_t *iv_agent, const int32_t *iv_cell,
+                           const uint8_t *iv_start, const uint8_t *iv_end, const uint32_t *iv_order);
+int mtd_export_day_async(mtd_handle h, void *rows12, int64_t cap_rows, uint64_t *exposed_kv, int64_t cap_exposed,
+                         mtd_day_result *result, int mem, int64_t *ticket);
+int mtd_export_wait(mtd_handle h, int64_t ticket);
 
 /* Measurement hooks (the reference's per-stage wall-clock columns, sim.py:231-244,1852-1856): with profiling on,
  * CUDA events are recorded on the handle's stream around every stage of the day step; mtd_get_stage_ms

@@ -13,7 +13,7 @@ from .params import EXPO_W, MAXSCHED, NONE, ParamsStruct
 
 PKG = os.path.dirname(os.path.abspath(__file__))
 SO = os.path.join(PKG, "libmtd_b200.so")
-MEM_HOST, MEM_DEVICE = 0, 1
+MEM_HOST, MEM_DEVICE, MEM_STAGED = 0, 1, 2
 MODE_REPLAY, MODE_PHILOX = 0, 1
 DELTA_WORDS = 20
 
@@ -21,7 +21,8 @@ EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mt
            "mtd_set_static", "mtd_set_state", "mtd_get_state", "mtd_set_tape", "mtd_simulate_contact_network",
            "mtd_simulate_direct_contacts", "mtd_apply_deltas", "mtd_advance_seir", "mtd_get_counters",
            "mtd_get_contacts", "mtd_get_exposed", "mtd_get_infection_prob", "mtd_occupancy", "mtd_sync",
-           "mtd_set_profiling", "mtd_get_stage_ms", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced"]
+           "mtd_set_profiling", "mtd_get_stage_ms", "mtd_set_export", "mtd_prefetch_intervals",
+           "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
 
 
@@ -45,6 +46,16 @@ class Counters(C.Structure):
     _fields_ = [("n_slots", C.c_int64), ("n_rows", C.c_int64), ("n_exposed", C.c_int64), ("pairs_evaluated", C.c_int64),
                 ("n_potential", C.c_int64), ("n_si_rows", C.c_int64), ("sched_overflow", C.c_int64),
                 ("tape_miss", C.c_int64), ("class_cells", C.c_int64 * 6), ("error", C.c_int64)]
+
+
+class DayResult(C.Structure):
+    """mtd_day_result (include/mtd_b200.h): counts + occupancy of one exported day"""
+    _fields_ = [("day", C.c_int64), ("n_rows", C.c_int64), ("n_exposed", C.c_int64), ("occupancy", C.c_int64 * 6),
+                ("pairs_evaluated", C.c_int64), ("error", C.c_int64), ("ticket", C.c_int64)]
+
+
+RESULT_WORDS = 12                     # int64 words of mtd_day_result
+ROW12 = np.dtype([("a1", "<i4"), ("a2", "<i4"), ("start", "u1"), ("end", "u1"), ("simcelltype", "u1"), ("pad", "u1")])
 
 
 class TraceTape(C.Structure):
@@ -189,6 +200,27 @@ class Handle:
 
     def sync(self):
         self._ck(self.lib.mtd_sync(self.h), "mtd_sync")
+
+    # ---- pipelined boundary
+    def set_export(self, on=True):
+        self._ck(self.lib.mtd_set_export(self.h, int(on)), "mtd_set_export")
+
+    def prefetch_intervals(self, iv_agent, iv_cell, iv_start, iv_end, iv_order=None, n=None):
+        """enqueue the upload of the NEXT day's stream (pinned host buffers) on the copy stream"""
+        n = len(iv_agent) if n is None else n
+        self._ck(self.lib.mtd_prefetch_intervals(self.h, C.c_int64(n), _ptr(iv_agent), _ptr(iv_cell), _ptr(iv_start),
+                                                 _ptr(iv_end), _ptr(iv_order)), "mtd_prefetch_intervals")
+
+    def export_day_async(self, rows12, cap_rows, exposed_kv, cap_exposed, result, mem=MEM_HOST):
+        """enqueue the export of the day just computed into caller buffers (pinned host or device); -> ticket"""
+        tk = C.c_int64(0)
+        self._ck(self.lib.mtd_export_day_async(self.h, _ptr(rows12), C.c_int64(cap_rows), _ptr(exposed_kv),
+                                               C.c_int64(cap_exposed), _ptr(result), mem, C.byref(tk)),
+                 "mtd_export_day_async")
+        return int(tk.value)
+
+    def export_wait(self, ticket):
+        self._ck(self.lib.mtd_export_wait(self.h, C.c_int64(ticket)), "mtd_export_wait")
 
     # ---- K5 contact tracing
     def set_residences(self, res_off, res_nres, res_members, mem=MEM_HOST):

@@ -19,6 +19,8 @@ int launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t ca
 int launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count);
 int launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st, int sm_count);
 int launch_scan_nrows(const DevCtx &c, long long *scan_tmp, cudaStream_t st);
+int launch_stream_out(void *dst, const void *src, const int64_t *n_items, int64_t item_bytes, int64_t cap_items,
+                      int blocks, cudaStream_t st);
 
 struct mtd_handle_s {
     mtd_config cfg;
@@ -49,6 +51,19 @@ struct mtd_handle_s {
     int32_t *trace_flagscan = nullptr; long long *trace_scan_tmp = nullptr;
     int32_t *d_traced = nullptr; int64_t cap_traced = 0; int32_t *d_rows3 = nullptr; int64_t cap_rows3 = 0;
     std::vector<void *> trace_tape_allocs;
+    // pipelined boundary: staged uploads (copy stream) and streamed exports (side stream), double-buffered
+    cudaStream_t copy_stream = nullptr, export_stream = nullptr;
+    int32_t *st_agent[2] = {}, *st_cell[2] = {}; uint8_t *st_start[2] = {}, *st_end[2] = {}; uint32_t *st_order[2] = {};
+    int64_t st_n[2] = {}; bool st_has_order[2] = {};
+    int st_next = 0, st_ready = -1;                 // slot the next prefetch fills / slot holding the prefetched day
+    cudaEvent_t ev_staged[2] = {}, ev_k0_done = nullptr, ev_snap = nullptr, ev_exported[2] = {};
+    bool export_on = false;
+    uint32_t *rows12_buf[2] = {};                   // packed rows of the last two days
+    int64_t *snap[2] = {};                          // device copy of mtd_day_result per export slot
+    unsigned long long *expo_snap[2] = {};
+    int64_t day_seq = 0, export_ticket = 0;         // days computed / exports enqueued
+    bool exported_pending[2] = {};
+    int ticket_slot[2] = {};
     // measurement hooks
     bool profiling = false;
     // ring of event pairs per stage: every execution since the last mtd_get_stage_ms is timed (up to EV_RING)
@@ -186,6 +201,10 @@ extern "C" int mtd_destroy(mtd_handle h)
                      (void *)h->trace_flagscan, (void *)h->trace_scan_tmp, (void *)h->d_traced, (void *)h->d_rows3 })
         if (p) cudaFree(p);
     for (int s = 0; s < MTD_N_STAGES; s++) for (cudaEvent_t e : h->ev[s]) cudaEventDestroy(e);
+    if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
+    if (h->export_stream) { cudaStreamSynchronize(h->export_stream); cudaStreamDestroy(h->export_stream); }
+    for (cudaEvent_t e : { h->ev_staged[0], h->ev_staged[1], h->ev_k0_done, h->ev_snap, h->ev_exported[0], h->ev_exported[1] })
+        if (e) cudaEventDestroy(e);
     for (void *p : h->allocs) cudaFree(p);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -315,7 +334,14 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     DevCtx &c = h->c;
     c.day = *day;
     c.M = M;
-    if (mem == MTD_MEM_HOST) {
+    if (mem == MTD_MEM_STAGED) {
+        const int sl = h->st_ready;
+        if (sl < 0 || h->st_n[sl] != M) { h->err = "MTD_MEM_STAGED without a matching mtd_prefetch_intervals"; return MTD_E_STATE; }
+        CK(cudaStreamWaitEvent(h->stream, h->ev_staged[sl], 0));
+        c.iv_agent = h->st_agent[sl]; c.iv_cell = h->st_cell[sl]; c.iv_start = h->st_start[sl]; c.iv_end = h->st_end[sl];
+        c.iv_order = h->st_has_order[sl] ? h->st_order[sl] : nullptr;
+        h->st_ready = -1;
+    } else if (mem == MTD_MEM_HOST) {
         StageScope sc(h, MTD_STAGE_H2D);
         size_t m = (size_t)M;
         CK(cudaMemcpyAsync(h->d_iv_agent, iv_agent, 4 * m, cudaMemcpyHostToDevice, h->stream));
@@ -332,7 +358,15 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     CK(cudaMemsetAsync(c.cell_count, 0, sizeof(int32_t) * (size_t)c.n_cells, h->stream));
     CK(cudaMemsetAsync(c.cell_first, 0xff, sizeof(uint32_t) * (size_t)c.n_cells, h->stream));
     { StageScope sc(h, MTD_STAGE_K0); sc.add(launch_k0(c, h->scan_tmp, h->stream, h->sm_count)); }
+    if (h->ev_k0_done) CK(cudaEventRecord(h->ev_k0_done, h->stream));      // the interval stream has been consumed
     { StageScope sc(h, MTD_STAGE_K1); sc.add(launch_k1(c, h->stream, h->sm_count)); }
+    c.rows12 = nullptr;
+    if (h->export_on) {     // K2 also packs the rows for the export; the slot's previous export must have drained
+        const int sl = (int)(h->day_seq & 1);
+        if (h->exported_pending[sl]) { CK(cudaStreamWaitEvent(h->stream, h->ev_exported[sl], 0)); h->exported_pending[sl] = false; }
+        c.rows12 = h->rows12_buf[sl];
+    }
+    h->day_seq++;
     { StageScope sc(h, MTD_STAGE_K2); sc.add(launch_scan_nrows(c, h->scan_tmp, h->stream));
       sc.add(launch_k2_compact(c, h->stream, h->sm_count)); }
     CK(cudaGetLastError());
@@ -656,5 +690,115 @@ extern "C" int mtd_get_traced(mtd_handle h, uint8_t *primary, uint8_t *secondary
     CK(cudaMemcpyAsync(s, h->trace_scalars, sizeof(s), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     if (stats) { stats->n_scan_draws = s[0]; stats->tape_miss = s[1]; stats->n_primary = s[2]; stats->n_secondary = s[3]; }
+    return MTD_OK;
+}
+
+
+// ------------------------------------------------------------------------------------------------ pipelined boundary
+static int pipeline_init(mtd_handle h)
+{
+    if (h->copy_stream) return MTD_OK;
+    int lo = 0, hi = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CK(cudaStreamCreateWithPriority(&h->copy_stream, cudaStreamNonBlocking, hi));
+    CK(cudaStreamCreateWithPriority(&h->export_stream, cudaStreamNonBlocking, hi));
+    for (cudaEvent_t *e : { &h->ev_staged[0], &h->ev_staged[1], &h->ev_k0_done, &h->ev_snap, &h->ev_exported[0], &h->ev_exported[1] })
+        CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    return MTD_OK;
+}
+
+extern "C" int mtd_set_export(mtd_handle h, int on)
+{
+    if (!h) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    if (on && !h->rows12_buf[0]) {
+        int r = pipeline_init(h); if (r) return r;
+        for (int k = 0; k < 2; k++) {
+            DA(h->rows12_buf[k], 3 * h->c.cap_rows + 4);
+            DA(h->snap[k], sizeof(mtd_day_result) / sizeof(int64_t));
+            DA(h->expo_snap[k], 2 * h->c.cap_expo + 2);
+        }
+    }
+    h->export_on = on != 0;
+    return MTD_OK;
+}
+
+extern "C" int mtd_prefetch_intervals(mtd_handle h, int64_t M, const int32_t *iv_agent, const int32_t *iv_cell,
+                                      const uint8_t *iv_start, const uint8_t *iv_end, const uint32_t *iv_order)
+{
+    if (!h || M < 0 || !iv_agent || !iv_cell || !iv_start || !iv_end) return MTD_E_ARG;
+    if (M > h->c.cap_intervals) { h->err = "interval stream exceeds max_intervals"; return MTD_E_CAPACITY; }
+    CK(cudaSetDevice(h->cfg.device));
+    { int r = pipeline_init(h); if (r) return r; }
+    const int sl = h->st_next;
+    if (!h->st_agent[sl]) {
+        const int64_t cap = h->c.cap_intervals;
+        DA(h->st_agent[sl], cap); DA(h->st_cell[sl], cap); DA(h->st_start[sl], cap); DA(h->st_end[sl], cap); DA(h->st_order[sl], cap);
+    }
+    // this slot was last read by the K0 of two days ago; one event after the most recent K0 covers it
+    CK(cudaStreamWaitEvent(h->copy_stream, h->ev_k0_done, 0));
+    const size_t m = (size_t)M;
+    CK(cudaMemcpyAsync(h->st_agent[sl], iv_agent, 4 * m, cudaMemcpyHostToDevice, h->copy_stream));
+    CK(cudaMemcpyAsync(h->st_cell[sl], iv_cell, 4 * m, cudaMemcpyHostToDevice, h->copy_stream));
+    CK(cudaMemcpyAsync(h->st_start[sl], iv_start, m, cudaMemcpyHostToDevice, h->copy_stream));
+    CK(cudaMemcpyAsync(h->st_end[sl], iv_end, m, cudaMemcpyHostToDevice, h->copy_stream));
+    if (iv_order) CK(cudaMemcpyAsync(h->st_order[sl], iv_order, 4 * m, cudaMemcpyHostToDevice, h->copy_stream));
+    CK(cudaEventRecord(h->ev_staged[sl], h->copy_stream));
+    h->st_n[sl] = M; h->st_has_order[sl] = iv_order != nullptr;
+    h->st_ready = sl; h->st_next = sl ^ 1;
+    return MTD_OK;
+}
+
+__global__ void export_snapshot_kernel(DevCtx c, const unsigned long long *occ, const unsigned long long *expo_list,
+                                       int64_t *snap, unsigned long long *expo_snap, int64_t ticket)
+{
+    const int n = c.ctr->n_applied < (int)c.cap_expo ? c.ctr->n_applied : (int)c.cap_expo;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * n; i += gridDim.x * blockDim.x) expo_snap[i] = expo_list[i];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        snap[0] = c.day.day; snap[1] = c.ctr->n_rows; snap[2] = n;
+        for (int k = 0; k < 6; k++) snap[3 + k] = (int64_t)occ[k];
+        snap[9] = (int64_t)c.ctr->pairs_evaluated; snap[10] = c.ctr->error; snap[11] = ticket;
+    }
+}
+
+extern "C" int mtd_export_day_async(mtd_handle h, void *rows12, int64_t cap_rows, uint64_t *exposed_kv, int64_t cap_exposed,
+                                    mtd_day_result *result, int mem, int64_t *ticket)
+{
+    if (!h || !result) return MTD_E_ARG;
+    if (!h->export_on || !h->day_ready || !h->c.rows12) { h->err = "mtd_export_day_async: mtd_set_export(h, 1) before the day step"; return MTD_E_STATE; }
+    CK(cudaSetDevice(h->cfg.device));
+    void *d_rows = rows12, *d_kv = exposed_kv, *d_res = result;
+    if (mem == MTD_MEM_HOST) {      // pinned host memory, written by the device over PCIe
+        if (rows12) CK(cudaHostGetDevicePointer(&d_rows, rows12, 0));
+        if (exposed_kv) CK(cudaHostGetDevicePointer(&d_kv, exposed_kv, 0));
+        CK(cudaHostGetDevicePointer(&d_res, result, 0));
+    }
+    const int sl = (int)((h->day_seq - 1) & 1);          // slot of the day just computed
+    const int64_t tk = ++h->export_ticket;
+    // main stream: occupancy + snapshot of everything the next day step overwrites (counters, exposure list)
+    launch_occupancy(h->c, h->occ, h->stream, h->sm_count);
+    export_snapshot_kernel<<<32, 256, 0, h->stream>>>(h->c, h->occ, h->expo_list, h->snap[sl], h->expo_snap[sl], tk);
+    CK(cudaEventRecord(h->ev_snap, h->stream));
+    // side stream: rows, exposures, then the result record (its arrival says everything before it has landed)
+    CK(cudaStreamWaitEvent(h->export_stream, h->ev_snap, 0));
+    if (rows12) launch_stream_out(d_rows, h->rows12_buf[sl], h->snap[sl] + 1, 12, cap_rows, 2 * h->sm_count, h->export_stream);
+    if (exposed_kv) launch_stream_out(d_kv, h->expo_snap[sl], h->snap[sl] + 2, 16, cap_exposed, 8, h->export_stream);
+    CK(cudaMemcpyAsync(d_res, h->snap[sl], sizeof(mtd_day_result), cudaMemcpyDefault, h->export_stream));
+    CK(cudaEventRecord(h->ev_exported[sl], h->export_stream));
+    h->exported_pending[sl] = true;
+    h->ticket_slot[tk & 1] = sl;
+    h->launches[MTD_STAGE_K2] += 2 + (rows12 ? 1 : 0) + (exposed_kv ? 1 : 0);
+    CK(cudaGetLastError());
+    if (ticket) *ticket = tk;
+    return MTD_OK;
+}
+
+extern "C" int mtd_export_wait(mtd_handle h, int64_t ticket)
+{
+    if (!h) return MTD_E_ARG;
+    if (ticket <= 0 || ticket > h->export_ticket || ticket + 2 <= h->export_ticket) { h->err = "mtd_export_wait: unknown ticket"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    const int sl = h->ticket_slot[ticket & 1];
+    CK(cudaEventSynchronize(h->ev_exported[sl]));
     return MTD_OK;
 }

@@ -99,6 +99,7 @@ struct DevCtx {
     // K1 products
     RowRec *scratch_rows;      // [cap_scratch_rows]
     uint16_t *lists;           // [cap_list]
+    uint32_t *rows12;          // [3 * cap_rows] packed 12-byte rows of the day for the async export (NULL = off)
     uint32_t *k1_bits;         // [k1_bits_words] per-warp adjacency bit matrices of the large-cell K1 (L2-resident scratch)
     int64_t k1_bits_words;
     RowRec *rows;              // [cap_rows] dense

@@ -14,16 +14,27 @@ __global__ void k2_compact_kernel(DevCtx c)
     const int warps = (gridDim.x * blockDim.x) >> 5;
     for (int s0 = (((int)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; s0 < n_slots; s0 += warps * 32) {
         int s = s0 + lane;
-        int cnt = 0; int64_t src = 0, dst = 0;
-        if (s < n_slots) { cnt = c.slot_nrows[s]; src = c.slot_rowoff[s]; dst = c.slot_denseoff[s]; }
+        int cnt = 0, sct = 0; int64_t src = 0, dst = 0;
+        if (s < n_slots) {
+            cnt = c.slot_nrows[s]; src = c.slot_rowoff[s]; dst = c.slot_denseoff[s];
+            if (c.rows12 && cnt > 0) sct = simcelltype_of(c.cell_type[c.slot_cell[s]]);
+        }
         uint32_t have = __ballot_sync(FULLMASK, cnt > 0);
         while (have) {
             int l = __ffs(have) - 1;
             have &= have - 1;
             int n = __shfl_sync(FULLMASK, cnt, l);
             int64_t sb = __shfl_sync(FULLMASK, src, l), db = __shfl_sync(FULLMASK, dst, l);
+            const uint32_t sc = (uint32_t)__shfl_sync(FULLMASK, sct, l);
             for (int r = lane; r < n; r += 32)
-                if (db + r < c.cap_rows) c.rows[db + r] = c.scratch_rows[sb + r];
+                if (db + r < c.cap_rows) {
+                    const RowRec rr = c.scratch_rows[sb + r];
+                    c.rows[db + r] = rr;
+                    if (c.rows12) {     // {a1, a2, start | end << 8 | simcelltype << 16}
+                        uint32_t *o = c.rows12 + 3 * (db + r);
+                        o[0] = (uint32_t)rr.a1; o[1] = (uint32_t)rr.a2; o[2] = (rr.sed & 0xffffu) | (sc << 16);
+                    }
+                }
         }
     }
 }
@@ -49,6 +60,26 @@ __global__ void k2_export_kernel(DevCtx c, int32_t *rows5, int32_t *row_dur, int
 int launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count)
 {
     k2_compact_kernel<<<sm_count * 8, 256, 0, st>>>(c);
+    return 1;
+}
+
+// device -> caller memory (device, or pinned host memory written over PCIe): 16-byte words, count read on the device
+__global__ void k2_stream_out_kernel(uint4 *dst, const uint4 *src, const int64_t *n_items, int64_t item_bytes, int64_t cap_items)
+{
+    int64_t n = *n_items;
+    if (n > cap_items) n = cap_items;
+    const int64_t bytes = n * item_bytes;
+    const int64_t n16 = bytes >> 4;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (int64_t)gridDim.x * blockDim.x)
+        dst[i] = src[i];
+    if (blockIdx.x == 0 && threadIdx.x == 0)            // tail (< 16 bytes; item sizes are multiples of 4)
+        for (int64_t b = n16 << 4; b < bytes; b += 4) ((uint32_t *)dst)[b >> 2] = ((const uint32_t *)src)[b >> 2];
+}
+
+int launch_stream_out(void *dst, const void *src, const int64_t *n_items, int64_t item_bytes, int64_t cap_items,
+                      int blocks, cudaStream_t st)
+{
+    k2_stream_out_kernel<<<blocks, 256, 0, st>>>((uint4 *)dst, (const uint4 *)src, n_items, item_bytes, cap_items);
     return 1;
 }
 

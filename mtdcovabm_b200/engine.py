@@ -73,8 +73,103 @@ class DayEngine:
                 exchange_deltas(self.gather, self.rank, self.group)
                 h.apply_deltas(self.gather, self.world, self.delta_cap)
 
+    # ---- host boundary, pipelined: pinned host buffers in, pinned host buffers out, copies beside the kernels
+    def enable_host_pipeline(self, cap_rows, cap_exposed=None):
+        """two sets of pinned result buffers (day d's results stay valid until day d+2 is submitted)"""
+        import numpy as np
+        cap_exposed = int(cap_exposed or self.delta_cap)
+        self.h.set_export(True)
+        self._res = []
+        for _ in range(2):
+            rows = torch.empty((int(cap_rows), 3), dtype=torch.int32).pin_memory()
+            kv = torch.empty((cap_exposed, 2), dtype=torch.int64).pin_memory()
+            res = torch.zeros(capi.RESULT_WORDS, dtype=torch.int64).pin_memory()
+            self._res.append((rows, kv, res))
+        self._cap_rows, self._cap_exposed = int(cap_rows), cap_exposed
+        self._k = 0
+        self._staged = None
+
+    def step_host(self, day, s, next_s=None, mhd=0.0, testing=False, quarantine=False):
+        """One day from pinned HOST interval arrays `s`; `next_s` (the following day's arrays, if already known) is
+        uploaded by the copy stream while this day computes.  Returns a HostDayResult whose buffers are filled
+        asynchronously by the export stream: call .wait() before reading them."""
+        h = self.h
+        if self.world != 1:
+            raise RuntimeError("step_host: the pipelined host boundary is single-rank (use step() under torch.distributed)")
+        d = h.make_day(self.mode, day, mhd, testing, quarantine, seed=self.seed)
+        n = len(s["iv_agent"])
+        with torch.cuda.stream(self.stream):
+            h.advance_seir(day, None)
+            if self._staged is s:
+                h.simulate_contact_network(d, None, None, None, None, n=n, mem=capi.MEM_STAGED)
+            else:
+                h.simulate_contact_network(d, s["iv_agent"], s["iv_cell"], s["iv_start"], s["iv_end"],
+                                           iv_order=s.get("iv_order"), n=n, mem=capi.MEM_HOST)
+            self._staged = None
+            if next_s is not None:
+                h.prefetch_intervals(next_s["iv_agent"], next_s["iv_cell"], next_s["iv_start"], next_s["iv_end"],
+                                     next_s.get("iv_order"))
+                self._staged = next_s
+            h.simulate_direct_contacts(d)
+            rows, kv, res = self._res[self._k]
+            self._k ^= 1
+            ticket = h.export_day_async(rows, self._cap_rows, kv, self._cap_exposed, res, mem=capi.MEM_HOST)
+        return HostDayResult(h, ticket, rows, kv, res)
+
     def sync(self):
         self.h.sync()
 
     def close(self):
         self.h.close()
+
+
+class HostDayResult:
+    """Results of one day in pinned host memory (written by the device over PCIe while the next day computes)."""
+
+    def __init__(self, h, ticket, rows, kv, res):
+        self._h, self.ticket, self._rows, self._kv, self._res = h, ticket, rows, kv, res
+        self._done = False
+
+    def wait(self):
+        if not self._done:
+            self._h.export_wait(self.ticket)
+            self._done = True
+            if int(self._res[11]) != self.ticket:
+                raise RuntimeError("export record carries ticket %d, expected %d" % (int(self._res[11]), self.ticket))
+            if int(self._res[10]) != 0:
+                raise RuntimeError("device error %d during the day step" % int(self._res[10]))
+        return self
+
+    @property
+    def n_rows(self):
+        return int(self.wait()._res[1])
+
+    @property
+    def n_exposed(self):
+        return int(self.wait()._res[2])
+
+    @property
+    def occupancy(self):
+        return self.wait()._res[3:9].numpy()
+
+    @property
+    def pairs_evaluated(self):
+        return int(self.wait()._res[9])
+
+    @property
+    def rows(self):
+        """structured view (capi.ROW12) of the contact rows, in the reference's row order"""
+        n = self.n_rows
+        return self._rows.numpy()[:n].view(capi.ROW12).reshape(n)
+
+    def exposed(self, reference_order=True):
+        """exposed agent ids; reference_order sorts by the (cell order, row order) key"""
+        import numpy as np
+        kv = self._kv.numpy()[:self.n_exposed]
+        if reference_order:
+            kv = kv[np.argsort(kv[:, 0].view(np.uint64), kind="stable")]
+        return kv[:, 1].astype(np.int32)
+
+    @property
+    def nbytes(self):
+        return 12 * self.n_rows + 16 * self.n_exposed + 8 * capi.RESULT_WORDS

@@ -175,3 +175,63 @@ def test_contact_tracing_philox_matches_oracle(seed):
         for f in ("quarantine", "test_day", "test_result_day"):
             assert np.array_equal(dev[f], getattr(ost, f)), f
         h.close()
+
+
+def test_pipelined_host_boundary_matches_synchronous_api():
+    """engine.step_host (prefetched uploads, results streamed into pinned host memory) == the synchronous calls"""
+    import torch
+    from mtdcovabm_b200 import engine
+    z = gio.load_run("ref_1k_seed6")
+    P = prm.build_params()
+    days = [gio.load_day(z, d) for d in (12, 16, 20)]
+    tiles = [H.tile_day(g, 6, agent_major=True, seed=4, infectious_frac=0.06) for g in days]
+    st = tiles[0]["state"]
+    N, C = st.n, len(tiles[0]["cell_type"])
+    M = max(len(t["iv_cell"]) for t in tiles)
+
+    class Pop:
+        pass
+    pop = Pop()
+    dev = torch.device("cuda", 0)
+    for name, arr in (("cell_type", np.asarray(tiles[0]["cell_type"], np.int8)), ("cell_indid", np.asarray(tiles[0]["cell_indid"], np.int16)),
+                      ("age_bracket", st.age_bracket), ("epi_age_bracket", st.epi_age_bracket), ("soc_rate", st.soc_rate),
+                      ("res_cellid", st.res_cellid), ("seir", st.seir), ("inf_type", st.inf_type), ("inf_sev", st.inf_sev),
+                      ("sched", st.sched), ("sched_cnt", st.sched_cnt)):
+        setattr(pop, name, torch.from_numpy(np.ascontiguousarray(arr)).to(dev))
+
+    def host(t):
+        return {k: torch.from_numpy(t[k]).pin_memory() for k in ("iv_agent", "iv_cell", "iv_start", "iv_end")}
+    hs = [host(t) for t in tiles]
+
+    # synchronous reference run through the plain calls
+    e0 = engine.DayEngine(N, C, M + 16, P, seed=11)
+    e0.set_population(pop)
+    want = []
+    for k, s in enumerate(hs):
+        e0.step(30 + k, s, mhd=0.1, testing=True, quarantine=True, mem=capi.MEM_HOST)
+        rows, dur, cell = e0.h.get_contacts()
+        want.append((rows, e0.h.get_exposed(), e0.h.occupancy(), int(e0.h.counters().pairs_evaluated)))
+    final0 = e0.h.get_state()
+    e0.close()
+
+    e1 = engine.DayEngine(N, C, M + 16, P, seed=11)
+    e1.set_population(pop)
+    e1.enable_host_pipeline(max(len(w[0]) for w in want) + 64)
+    got = []
+    for k, s in enumerate(hs):
+        nxt = hs[k + 1] if k + 1 < len(hs) else None
+        r = e1.step_host(30 + k, s, next_s=nxt, mhd=0.1, testing=True, quarantine=True)
+        # copy out at once: the pinned buffers are reused two days later
+        got.append((r.rows.copy(), r.exposed().copy(), r.occupancy.copy(), r.pairs_evaluated))
+    final1 = e1.h.get_state()
+    e1.close()
+    assert sum(len(w[1]) for w in want) > 0
+    for (rows, exp, occ, pairs), (r12, e12, o12, p12) in zip(want, got):
+        assert len(r12) == len(rows)
+        assert np.array_equal(r12["simcelltype"], rows[:, 0]) and np.array_equal(r12["a1"], rows[:, 1])
+        assert np.array_equal(r12["a2"], rows[:, 2]) and np.array_equal(r12["start"], rows[:, 3])
+        assert np.array_equal(r12["end"], rows[:, 4])
+        assert np.array_equal(e12, exp)
+        assert np.array_equal(o12, occ) and p12 == pairs
+    for f in H.STATE_FIELDS:
+        assert np.array_equal(final0[f], final1[f]), f
