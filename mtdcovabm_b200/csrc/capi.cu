@@ -9,7 +9,7 @@
 
 // every launcher returns the number of kernels it launched
 int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count);
-int launch_k1(const DevCtx &c, cudaStream_t st, int sm_count);
+int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaEvent_t ev_fork, cudaEvent_t ev_join, int sm_count);
 int64_t k1_bits_words_needed(int sm_count);
 int launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count);
 int launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap, cudaStream_t st);
@@ -26,6 +26,8 @@ struct mtd_handle_s {
     mtd_config cfg;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    cudaStream_t aux_stream = nullptr;           // large-cell K1 kernels run beside the small-cell ones
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     int sm_count = 148;
     std::string err;
     std::vector<void *> allocs;
@@ -109,6 +111,8 @@ static int create_impl(mtd_handle h)
     h->sm_count = prop.multiProcessorCount;
     if (cfg.stream) h->stream = (cudaStream_t)cfg.stream;
     else { CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->own_stream = true; }
+    CK(cudaStreamCreateWithFlags(&h->aux_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
     DevCtx &c = h->c;
     memset(&c, 0, sizeof(c));
     const int64_t N = cfg.n_agents, C = cfg.n_cells, M = cfg.max_intervals;
@@ -201,6 +205,9 @@ extern "C" int mtd_destroy(mtd_handle h)
                      (void *)h->trace_flagscan, (void *)h->trace_scan_tmp, (void *)h->d_traced, (void *)h->d_rows3 })
         if (p) cudaFree(p);
     for (int s = 0; s < MTD_N_STAGES; s++) for (cudaEvent_t e : h->ev[s]) cudaEventDestroy(e);
+    if (h->aux_stream) { cudaStreamSynchronize(h->aux_stream); cudaStreamDestroy(h->aux_stream); }
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
     if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
     if (h->export_stream) { cudaStreamSynchronize(h->export_stream); cudaStreamDestroy(h->export_stream); }
     for (cudaEvent_t e : { h->ev_staged[0], h->ev_staged[1], h->ev_k0_done, h->ev_snap, h->ev_exported[0], h->ev_exported[1] })
@@ -359,7 +366,7 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     CK(cudaMemsetAsync(c.cell_first, 0xff, sizeof(uint32_t) * (size_t)c.n_cells, h->stream));
     { StageScope sc(h, MTD_STAGE_K0); sc.add(launch_k0(c, h->scan_tmp, h->stream, h->sm_count)); }
     if (h->ev_k0_done) CK(cudaEventRecord(h->ev_k0_done, h->stream));      // the interval stream has been consumed
-    { StageScope sc(h, MTD_STAGE_K1); sc.add(launch_k1(c, h->stream, h->sm_count)); }
+    { StageScope sc(h, MTD_STAGE_K1); sc.add(launch_k1(c, h->stream, h->aux_stream, h->ev_fork, h->ev_join, h->sm_count)); }
     c.rows12 = nullptr;
     if (h->export_on) {     // K2 also packs the rows for the export; the slot's previous export must have drained
         const int sl = (int)(h->day_seq & 1);

@@ -21,6 +21,7 @@
 //                interval and per agent, everything in registers + a few bytes of shared memory per lane.
 //   k1_large<MM> cells of <= MM intervals (128, 320, 1024): one warp per cell, bit matrix in shared memory.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -780,9 +781,8 @@ int large_blocks_per_sm(int cap)
         cudaFuncSetAttribute(k1_large_kernel<MM, WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_large_kernel<MM, WARPS>, WARPS * 32, smem);
         if (per_sm < 1) per_sm = 1;
-        if (per_sm > cap) per_sm = cap;
     }
-    return per_sm;
+    return per_sm > cap ? cap : per_sm;
 }
 
 template <int MM, int WARPS>
@@ -826,15 +826,37 @@ int64_t k1_bits_words_needed(int sm_count)
     return w > w3 ? w : w3;
 }
 
-int launch_k1(const DevCtx &c, cudaStream_t st, int sm_count)
+static int env_int(const char *name, int dflt)
 {
-    // big cells first: they are the long poles
+    const char *v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+// The warp-per-cell kernels of the large classes are latency-bound (one sequential greedy chain per warp, about half
+// of the issue slots used), the sub-warp kernels of the small classes are issue-bound: run the two families side by
+// side -- large classes on the auxiliary stream with a capped number of resident blocks per SM, small classes on the
+// main stream in the registers and warp slots that are left -- and join before K2.
+int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaEvent_t ev_fork, cudaEvent_t ev_join, int sm_count)
+{
+    static const int cap4 = env_int("MTD_K1_CAP320", K1_NOCAP), cap3 = env_int("MTD_K1_CAP128", K1_NOCAP);
+    static const int overlap = env_int("MTD_K1_OVERLAP", 1);
+    cudaStream_t sl = st;
+    if (overlap && aux) {
+        cudaEventRecord(ev_fork, st);
+        cudaStreamWaitEvent(aux, ev_fork, 0);
+        sl = aux;
+    }
     int n = 0;
-    n += launch_large<K1_C5>(c, 5, st, sm_count, K1_C5_CAP);
-    n += launch_large<K1_C4>(c, 4, st, sm_count, K1_NOCAP);
-    n += launch_large<K1_C3>(c, 3, st, sm_count, K1_NOCAP);
-    n += launch_small<32>(c, 2, st, sm_count);
+    // big cells first: they are the long poles
+    n += launch_large<K1_C5>(c, 5, sl, sm_count, K1_C5_CAP);
+    n += launch_large<K1_C4>(c, 4, sl, sm_count, cap4);
+    n += launch_large<K1_C3>(c, 3, sl, sm_count, cap3);
     n += launch_small<16>(c, 1, st, sm_count);
     n += launch_small<8>(c, 0, st, sm_count);
+    n += launch_small<32>(c, 2, st, sm_count);
+    if (sl != st) {
+        cudaEventRecord(ev_join, sl);
+        cudaStreamWaitEvent(st, ev_join, 0);
+    }
     return n;
 }
