@@ -13,7 +13,7 @@ int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaEvent_t ev
 int64_t k1_bits_words_needed(int sm_count);
 int launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count);
 int launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap, cudaStream_t st);
-int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, cudaStream_t st, int sm_count);
+int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, bool win_clean, cudaStream_t st, int sm_count);
 int launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t cap, bool resolve,
                     unsigned long long *expo_list, cudaStream_t st, int sm_count);
 int launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count);
@@ -60,6 +60,7 @@ struct mtd_handle_s {
     int st_next = 0, st_ready = -1;                 // slot the next prefetch fills / slot holding the prefetched day
     cudaEvent_t ev_staged[2] = {}, ev_k0_done = nullptr, ev_snap = nullptr, ev_exported[2] = {};
     bool export_on = false;
+    bool win_clean = false;                         // the winner table holds no entries (cleared after the last apply)
     uint32_t *rows12_buf[2] = {};                   // packed rows of the last two days
     int64_t *snap[2] = {};                          // device copy of mtd_day_result per export slot
     unsigned long long *expo_snap[2] = {};
@@ -391,9 +392,9 @@ extern "C" int mtd_simulate_direct_contacts(mtd_handle h, const mtd_day *day, in
     int32_t *buf = delta_buf ? delta_buf : h->delta_own;
     int64_t cp = delta_buf ? cap : c.cap_expo;
     if (cp <= 0) { h->err = "delta buffer capacity must be positive"; return MTD_E_ARG; }
-    { StageScope sc(h, MTD_STAGE_K3_EVAL); sc.add(launch_k3_eval(c, buf, cp, h->stream, h->sm_count)); }
+    { StageScope sc(h, MTD_STAGE_K3_EVAL); sc.add(launch_k3_eval(c, buf, cp, h->win_clean, h->stream, h->sm_count)); h->win_clean = false; }
     if (apply) { StageScope sc(h, MTD_STAGE_K3_APPLY);
-                 sc.add(launch_k3_apply(c, buf, 1, cp, false, h->expo_list, h->stream, h->sm_count)); }
+                 sc.add(launch_k3_apply(c, buf, 1, cp, false, h->expo_list, h->stream, h->sm_count)); h->win_clean = true; }
     CK(cudaGetLastError());
     return MTD_OK;
 }
@@ -403,7 +404,7 @@ extern "C" int mtd_apply_deltas(mtd_handle h, const int32_t *bufs, int64_t n_buf
     if (!h || !bufs || n_bufs <= 0 || cap <= 0) return MTD_E_ARG;
     CK(cudaSetDevice(h->cfg.device));
     { StageScope sc(h, MTD_STAGE_K3_APPLY);
-      sc.add(launch_k3_apply(h->c, bufs, (int)n_bufs, cap, true, h->expo_list, h->stream, h->sm_count)); }
+      sc.add(launch_k3_apply(h->c, bufs, (int)n_bufs, cap, true, h->expo_list, h->stream, h->sm_count)); h->win_clean = true; }
     CK(cudaGetLastError());
     return MTD_OK;
 }

@@ -324,6 +324,23 @@ __global__ void k3_apply_kernel(DevCtx c, const int32_t *bufs, int n_bufs, int64
     }
 }
 
+// The winner table is only meaningful within a day: clear exactly the entries this day touched (the endpoints of the
+// successful rows and the agents of every gathered record) instead of refilling all N entries every day.
+__global__ void k3_reset_win_kernel(DevCtx c, const int32_t *bufs, int n_bufs, int64_t cap)
+{
+    const int n = c.ctr->n_succ;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+        const RowRec r = c.rows[c.succ[t]];
+        c.win[r.a1] = ~0ull; c.win[r.a2] = ~0ull;
+    }
+    for (int bi = 0; bi < n_bufs; bi++) {
+        const int32_t *buf = bufs + (int64_t)bi * (cap + 1) * MTD_DELTA_WORDS;
+        int nr = buf[0]; if (nr > cap) nr = (int)cap;
+        for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < nr; t += gridDim.x * blockDim.x)
+            c.win[buf[(int64_t)(t + 1) * MTD_DELTA_WORDS]] = ~0ull;
+    }
+}
+
 // seirstateutil.py:105-136
 __device__ __forceinline__ void transition(int seir, int it, int sv, int trans, int &ns, int &nt, int &nv)
 {
@@ -340,22 +357,27 @@ __device__ __forceinline__ void transition(int seir, int it, int sv, int trans, 
     }
 }
 
+__device__ __forceinline__ void k4_advance_agent(const DevCtx &c, int64_t ag, int cnt, int day)
+{
+    int32_t *sc = c.sched + ag * MTD_MAXSCHED;
+    int today = -1;
+    for (int i = 0; i < cnt; i++) if ((sc[i] >> 16) == day) { today = i; break; }   // first entry dated today only
+    if (today < 0) return;
+    int trans = (sc[today] >> 8) & 0xff;
+    int ns, nt, nv;
+    transition(c.seir[ag], c.inf_type[ag], c.inf_sev[ag], trans, ns, nt, nv);
+    c.seir[ag] = (int8_t)ns; c.inf_type[ag] = (int8_t)nt; c.inf_sev[ag] = (int8_t)nv;
+    for (int i = today; i + 1 < cnt; i++) sc[i] = sc[i + 1];                          // del list[today_index]
+    c.sched_cnt[ag] = (uint8_t)(cnt - 1);
+}
+
 __global__ void k4_advance_kernel(DevCtx c, int day, const uint8_t *mask)
 {
     for (int64_t ag = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; ag < c.n_agents; ag += (int64_t)gridDim.x * blockDim.x) {
-        int cnt = c.sched_cnt[ag];
+        const int cnt = c.sched_cnt[ag];
         if (cnt == 0) continue;
         if (mask && !mask[ag]) continue;
-        int32_t *sc = c.sched + ag * MTD_MAXSCHED;
-        int today = -1;
-        for (int i = 0; i < cnt; i++) if ((sc[i] >> 16) == day) { today = i; break; }   // first entry dated today only
-        if (today < 0) continue;
-        int trans = (sc[today] >> 8) & 0xff;
-        int ns, nt, nv;
-        transition(c.seir[ag], c.inf_type[ag], c.inf_sev[ag], trans, ns, nt, nv);
-        c.seir[ag] = (int8_t)ns; c.inf_type[ag] = (int8_t)nt; c.inf_sev[ag] = (int8_t)nv;
-        for (int i = today; i + 1 < cnt; i++) sc[i] = sc[i + 1];                          // del list[today_index]
-        c.sched_cnt[ag] = (uint8_t)(cnt - 1);
+        k4_advance_agent(c, ag, cnt, day);
     }
 }
 
@@ -374,9 +396,9 @@ __global__ void occupancy_kernel(DevCtx c, unsigned long long *out6)
 
 }  // namespace
 
-int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, cudaStream_t st, int sm_count)
+int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, bool win_clean, cudaStream_t st, int sm_count)
 {
-    cudaMemsetAsync(c.win, 0xff, sizeof(unsigned long long) * (size_t)c.n_agents, st);
+    if (!win_clean) cudaMemsetAsync(c.win, 0xff, sizeof(unsigned long long) * (size_t)c.n_agents, st);
     cudaMemsetAsync(dbuf, 0, sizeof(int32_t) * MTD_DELTA_WORDS, st);
     k3_eval_kernel<<<sm_count * 8, 256, 0, st>>>(c);
     k3_trajectory_kernel<<<sm_count * 8, K3T_WARPS * 32, 0, st>>>(c, dbuf, cap);
@@ -388,7 +410,8 @@ int launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t ca
 {
     if (resolve) k3_resolve_kernel<<<sm_count, 128, 0, st>>>(c, bufs, n_bufs, cap);
     k3_apply_kernel<<<sm_count, 128, 0, st>>>(c, bufs, n_bufs, cap, expo_list);
-    return resolve ? 2 : 1;
+    k3_reset_win_kernel<<<sm_count, 128, 0, st>>>(c, bufs, n_bufs, cap);
+    return resolve ? 3 : 2;
 }
 
 int launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count)

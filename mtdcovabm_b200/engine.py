@@ -94,8 +94,6 @@ class DayEngine:
         uploaded by the copy stream while this day computes.  Returns a HostDayResult whose buffers are filled
         asynchronously by the export stream: call .wait() before reading them."""
         h = self.h
-        if self.world != 1:
-            raise RuntimeError("step_host: the pipelined host boundary is single-rank (use step() under torch.distributed)")
         d = h.make_day(self.mode, day, mhd, testing, quarantine, seed=self.seed)
         n = len(s["iv_agent"])
         with torch.cuda.stream(self.stream):
@@ -110,7 +108,12 @@ class DayEngine:
                 h.prefetch_intervals(next_s["iv_agent"], next_s["iv_cell"], next_s["iv_start"], next_s["iv_end"],
                                      next_s.get("iv_order"))
                 self._staged = next_s
-            h.simulate_direct_contacts(d)
+            if self.world == 1:
+                h.simulate_direct_contacts(d)
+            else:       # this rank's cells -> delta records -> one all-gather -> every rank applies all records
+                h.simulate_direct_contacts(d, delta_buf=self.gather[self.rank], cap_records=self.delta_cap, apply=False)
+                exchange_deltas(self.gather, self.rank, self.group)
+                h.apply_deltas(self.gather, self.world, self.delta_cap)
             rows, kv, res = self._res[self._k]
             self._k ^= 1
             ticket = h.export_day_async(rows, self._cap_rows, kv, self._cap_exposed, res, mem=capi.MEM_HOST)
