@@ -194,10 +194,13 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(args, agents, intervals, cells):
+def workload_config(args, agents, intervals, cells, exchange=None):
+    par = "cells sharded x%d, state replicated" % args.gpus
+    if exchange and args.gpus > 1:
+        par += ", exposure records exchanged by " + ("stores into NVLink peer memory" if exchange == "p2p" else "NCCL all-gather")
     return {"workload": "synthetic %d-agent population: reference 1k-agent itinerary bank tiled, ids shuffled, "
                         "agent-major emission order (BASELINE.json configs[3])" % agents,
-            "agents": agents, "intervals_per_day": intervals, "cells": cells, "parallelism": "cells sharded x%d, state replicated" % args.gpus,
+            "agents": agents, "intervals_per_day": intervals, "cells": cells, "parallelism": par,
             "rng": "philox4x32-10", "l2": "inputs larger than L2 (7 distinct day streams cycled)"}
 
 
@@ -361,7 +364,7 @@ def run_b200(args):
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "int32+f64", "data": "synthetic",
-                "config": workload_config(args, agents, int(streams[0]["n_total"]), pop.n_cells),
+                "config": workload_config(args, agents, int(streams[0]["n_total"]), pop.n_cells, eng.exchange),
                 "agent_days_per_s": agents * args.steps / (ms * 1e-3),
                 "pairs_per_day": total_pairs / args.steps, "contacts_per_day": contacts_per_day,
                 "exposed_last_day": int(c.n_exposed),

@@ -37,7 +37,7 @@ extern "C" {
 #define MTD_DELTA_WORDS 20       /* int32 words per exposure delta record */
 #define MTD_MAX_CELL_INTERVALS 1024  /* largest cell (intervals) the on-chip path handles */
 
-enum { MTD_OK = 0, MTD_E_ARG = 1, MTD_E_CUDA = 2, MTD_E_CAPACITY = 3, MTD_E_CELL_TOO_LARGE = 4, MTD_E_STATE = 5 };
+enum { MTD_OK = 0, MTD_E_ARG = 1, MTD_E_CUDA = 2, MTD_E_CAPACITY = 3, MTD_E_CELL_TOO_LARGE = 4, MTD_E_STATE = 5, MTD_E_TIMEOUT = 6 };
 enum { MTD_MEM_HOST = 0, MTD_MEM_DEVICE = 1, MTD_MEM_STAGED = 2 /* the stream given to mtd_prefetch_intervals */ };
 enum { MTD_MODE_REPLAY = 0, MTD_MODE_PHILOX = 1 };
 
@@ -132,6 +132,23 @@ int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, int64_t n_int
  * mtd_apply_deltas over all n_bufs slices. */
 int mtd_simulate_direct_contacts(mtd_handle h, const mtd_day *day, int32_t *delta_buf, int64_t cap_records, int apply);
 int mtd_apply_deltas(mtd_handle h, const int32_t *delta_bufs, int64_t n_bufs, int64_t cap_records);
+
+/* Multi-GPU exchange of the exposure records over NVLink peer memory (replaces the reference's
+ * actor-to-actor send_results / receive_results of updated agents, actor_dist.py:491-518, and the per-day NCCL
+ * all-gather of fixed-capacity buffers).  One process per GPU on one box:
+ *   mtd_exchange_init   allocate this rank's exchange buffer (two day-parity sets of `world` slices of cap_records
+ *                       records) and return its CUDA IPC handle (64 bytes) for the peers;
+ *   mtd_exchange_open   map a peer's buffer from its IPC handle (every peer, once);
+ *   mtd_exchange_ready  check that every peer is mapped and enable the path (callers barrier after this).
+ * mtd_simulate_direct_contacts(h, day, NULL, 0, MTD_APPLY_EXCHANGE) then writes the day's records into the rank's own
+ * slice, pushes exactly those records into the same slice of every peer with stores over NVLink, raises an arrival
+ * flag per peer, waits (on the device, with a 10 s timeout -> MTD_E_TIMEOUT) for every peer's flag and applies all
+ * slices in rank order with the same earliest-key rule as the single-GPU path.  No host synchronisation, no NCCL. */
+#define MTD_APPLY_EXCHANGE 2
+#define MTD_IPC_HANDLE_BYTES 64
+int mtd_exchange_init(mtd_handle h, int rank, int world, int64_t cap_records, void *ipc_handle_out);
+int mtd_exchange_open(mtd_handle h, int peer, const void *ipc_handle);
+int mtd_exchange_ready(mtd_handle h);
 /* K4: daily SEIR advance for every agent with a schedule entry dated `day`; mask (uint8[N]) may be NULL. */
 int mtd_advance_seir(mtd_handle h, int32_t day, const uint8_t *mask, int mem);
 
@@ -168,8 +185,8 @@ int mtd_get_traced(mtd_handle h, uint8_t *primary, uint8_t *secondary, mtd_trace
 /* ---- pipelined boundary (the day loop of sim.py:1392-2125 driven from host memory without stalling the device) ----
  * The reference hands the stage host containers and gets host containers back (contactnetwork.py:65-124).  These three
  * calls keep that contract -- pinned HOST buffers in, pinned HOST buffers out -- while the copies run beside the
- * kernels: day d+1's intervals are uploaded by a copy stream during day d, and day d's results are written straight
- * into the caller's pinned memory by a low-occupancy export kernel on a side stream during day d+1.
+ * kernels: day d+1's intervals are uploaded by a copy stream during day d, and day d's results are copied into the
+ * caller's pinned memory by the copy engine on a side stream during day d+1 (no SM is taken from the kernels).
  *   mtd_prefetch_intervals    enqueue the upload of the NEXT day's stream (pinned host pointers); the next
  *                             mtd_simulate_contact_network call passes mem = MTD_MEM_STAGED (pointers ignored).
  *   mtd_export_day_async      enqueue the export of the day just computed; needs mtd_set_export(h, 1) before that
@@ -177,9 +194,11 @@ int mtd_get_traced(mtd_handle h, uint8_t *primary, uint8_t *secondary, mtd_trace
  *                             {int32 a1, int32 a2, uint8 start, uint8 end, uint8 simcelltype, uint8 0} in the
  *                             reference's row order (contactnetwork.py:98-105); exposed_kv: n_exposed pairs
  *                             {uint64 order key, uint64 agent id} (sort by key for the reference's order);
- *                             result: counts + occupancy, written last.  mem = MTD_MEM_HOST: the buffers are pinned
- *                             (page-locked, device-mapped) host memory; MTD_MEM_DEVICE: device memory.
- *   mtd_export_wait           block the host until the export with that ticket has landed. */
+ *                             result: counts + occupancy.  mem = MTD_MEM_HOST: the buffers are pinned (page-locked)
+ *                             host memory; the result record is copied first, and the two bulk copies are issued
+ *                             with their exact sizes as soon as it has landed -- by mtd_export_wait, or by the next
+ *                             call that reuses the export slot (two days later).  MTD_MEM_DEVICE: device memory.
+ *   mtd_export_wait           block the host until the export with that ticket has landed (all three buffers). */
 typedef struct {
     int64_t day, n_rows, n_exposed;
     int64_t occupancy[6];            /* agents per SEIR state after the day (dynamicstatistics.py:169-193) */

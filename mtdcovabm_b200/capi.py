@@ -16,13 +16,16 @@ SO = os.path.join(PKG, "libmtd_b200.so")
 MEM_HOST, MEM_DEVICE, MEM_STAGED = 0, 1, 2
 MODE_REPLAY, MODE_PHILOX = 0, 1
 DELTA_WORDS = 20
+APPLY_NONE, APPLY_LOCAL, APPLY_EXCHANGE = 0, 1, 2
+IPC_HANDLE_BYTES = 64
 
 EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mtd_set_params", "mtd_set_cells",
            "mtd_set_static", "mtd_set_state", "mtd_get_state", "mtd_set_tape", "mtd_simulate_contact_network",
            "mtd_simulate_direct_contacts", "mtd_apply_deltas", "mtd_advance_seir", "mtd_get_counters",
            "mtd_get_contacts", "mtd_get_exposed", "mtd_get_infection_prob", "mtd_occupancy", "mtd_sync",
            "mtd_set_profiling", "mtd_get_stage_ms", "mtd_set_export", "mtd_prefetch_intervals",
-           "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced"]
+           "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced",
+           "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
 
 
@@ -194,6 +197,19 @@ class Handle:
     def apply_deltas(self, bufs, n_bufs, cap_records):
         self._ck(self.lib.mtd_apply_deltas(self.h, _ptr(bufs), C.c_int64(n_bufs), C.c_int64(cap_records)),
                  "mtd_apply_deltas")
+
+    # ---- multi-GPU exchange over NVLink peer memory
+    def exchange_init(self, rank, world, cap_records) -> bytes:
+        """allocate this rank's exchange buffer -> its CUDA IPC handle (bytes) for the peers"""
+        buf = C.create_string_buffer(IPC_HANDLE_BYTES)
+        self._ck(self.lib.mtd_exchange_init(self.h, int(rank), int(world), C.c_int64(cap_records), buf), "mtd_exchange_init")
+        return bytes(buf.raw)
+
+    def exchange_open(self, peer, ipc_handle: bytes):
+        self._ck(self.lib.mtd_exchange_open(self.h, int(peer), C.c_char_p(ipc_handle)), "mtd_exchange_open")
+
+    def exchange_ready(self):
+        self._ck(self.lib.mtd_exchange_ready(self.h), "mtd_exchange_ready")
 
     def advance_seir(self, day, mask=None, mem=MEM_HOST):
         self._ck(self.lib.mtd_advance_seir(self.h, C.c_int32(day), _ptr(mask), mem), "mtd_advance_seir")

@@ -3,6 +3,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <string>
 #include <vector>
 #include "common.cuh"
@@ -17,6 +18,8 @@ int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, bool win_clean, 
 int launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t cap, bool resolve,
                     unsigned long long *expo_list, cudaStream_t st, int sm_count);
 int launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count);
+int launch_xchg_push(const DevExchange &x, int par, unsigned long long seq, cudaStream_t st);
+int launch_xchg_wait(const DevExchange &x, int par, unsigned long long seq, StateCounters *sctr, cudaStream_t st);
 int launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st, int sm_count);
 int launch_scan_nrows(const DevCtx &c, long long *scan_tmp, cudaStream_t st);
 int launch_stream_out(void *dst, const void *src, const int64_t *n_items, int64_t item_bytes, int64_t cap_items,
@@ -28,6 +31,18 @@ struct mtd_handle_s {
     bool own_stream = false;
     cudaStream_t aux_stream = nullptr;           // large-cell K1 kernels run beside the small-cell ones
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    // The state chain -- apply of day d's exposure records (after the peer exchange), then K4 of day d+1 -- runs on its
+    // own stream beside K0/K1/K2 of day d+1, which read no per-agent state; K3 of day d+1 joins the two.
+    cudaStream_t state_stream = nullptr;
+    cudaEvent_t ev_state = nullptr, ev_main = nullptr;
+    bool state_dirty = false;                    // the state stream has work the main stream has not waited for
+    bool main_dirty = false;                     // the main stream touched per-agent state since the state stream last waited
+    // peer exchange (NVLink peer memory, one slice per source rank and day parity)
+    DevExchange x;
+    bool xchg_on = false;
+    void *xchg_alloc = nullptr;
+    std::vector<void *> xchg_peers;              // cudaIpcOpenMemHandle mappings
+    unsigned long long xchg_seq = 0;
     int sm_count = 148;
     std::string err;
     std::vector<void *> allocs;
@@ -54,7 +69,7 @@ struct mtd_handle_s {
     int32_t *d_traced = nullptr; int64_t cap_traced = 0; int32_t *d_rows3 = nullptr; int64_t cap_rows3 = 0;
     std::vector<void *> trace_tape_allocs;
     // pipelined boundary: staged uploads (copy stream) and streamed exports (side stream), double-buffered
-    cudaStream_t copy_stream = nullptr, export_stream = nullptr;
+    cudaStream_t copy_stream = nullptr, export_stream = nullptr, bulk_stream = nullptr;
     int32_t *st_agent[2] = {}, *st_cell[2] = {}; uint8_t *st_start[2] = {}, *st_end[2] = {}; uint32_t *st_order[2] = {};
     int64_t st_n[2] = {}; bool st_has_order[2] = {};
     int st_next = 0, st_ready = -1;                 // slot the next prefetch fills / slot holding the prefetched day
@@ -67,6 +82,10 @@ struct mtd_handle_s {
     int64_t day_seq = 0, export_ticket = 0;         // days computed / exports enqueued
     bool exported_pending[2] = {};
     int ticket_slot[2] = {};
+    // host exports: the result record lands first (ev_res); the bulk copies are issued with exact sizes once it has
+    struct HostExport { bool unissued = false; void *rows = nullptr; int64_t cap_rows = 0; void *kv = nullptr;
+                        int64_t cap_exposed = 0; mtd_day_result *result = nullptr; } hx[2];
+    cudaEvent_t ev_res[2] = {};
     // measurement hooks
     bool profiling = false;
     // ring of event pairs per stage: every execution since the last mtd_get_stage_ms is timed (up to EV_RING)
@@ -76,10 +95,11 @@ struct mtd_handle_s {
     int64_t launches[MTD_N_STAGES] = {};
 };
 
-struct StageScope {     // records the stage's start/end events on the handle's stream when profiling is on
-    mtd_handle h; int stage;
-    StageScope(mtd_handle h_, int s) : h(h_), stage(s) { if (on()) cudaEventRecord(h->ev[stage][2 * h->ev_n[stage]], h->stream); }
-    ~StageScope() { if (on()) { cudaEventRecord(h->ev[stage][2 * h->ev_n[stage] + 1], h->stream); h->ev_n[stage]++; } }
+struct StageScope {     // records the stage's start/end events on the stage's stream when profiling is on
+    mtd_handle h; int stage; cudaStream_t st;
+    StageScope(mtd_handle h_, int s, cudaStream_t st_ = nullptr) : h(h_), stage(s), st(st_ ? st_ : h_->stream)
+    { if (on()) cudaEventRecord(h->ev[stage][2 * h->ev_n[stage]], st); }
+    ~StageScope() { if (on()) { cudaEventRecord(h->ev[stage][2 * h->ev_n[stage] + 1], st); h->ev_n[stage]++; } }
     bool on() const { return h->profiling && h->ev_n[stage] < mtd_handle_s::EV_RING; }
     void add(int n) { h->launches[stage] += n; }
 };
@@ -99,7 +119,33 @@ static int dalloc(mtd_handle h, T **p, size_t n)
 }
 #define DA(ptr, n) do { int r_ = dalloc(h, &(ptr), (size_t)(n)); if (r_) return r_; } while (0)
 
-extern "C" int mtd_abi_version(void) { return 1; }
+// main stream waits for everything enqueued on the state stream so far
+static int main_after_state(mtd_handle h)
+{
+    if (!h->state_dirty) return MTD_OK;
+    CK(cudaEventRecord(h->ev_state, h->state_stream));
+    CK(cudaStreamWaitEvent(h->stream, h->ev_state, 0));
+    h->state_dirty = false;
+    return MTD_OK;
+}
+// state stream waits for everything enqueued on the main stream so far
+static int state_after_main(mtd_handle h)
+{
+    CK(cudaEventRecord(h->ev_main, h->stream));
+    CK(cudaStreamWaitEvent(h->state_stream, h->ev_main, 0));
+    h->main_dirty = false;
+    return MTD_OK;
+}
+// entry of every call that reads or writes per-agent state on the main stream outside the day step
+static int touch_state_on_main(mtd_handle h)
+{
+    int r = main_after_state(h);
+    h->main_dirty = true;
+    return r;
+}
+#define TOUCH() do { int r_ = touch_state_on_main(h); if (r_) return r_; } while (0)
+
+extern "C" int mtd_abi_version(void) { return 2; }
 
 extern "C" const char *mtd_last_error(mtd_handle h) { return h ? h->err.c_str() : "null handle"; }
 
@@ -113,6 +159,9 @@ static int create_impl(mtd_handle h)
     if (cfg.stream) h->stream = (cudaStream_t)cfg.stream;
     else { CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->own_stream = true; }
     CK(cudaStreamCreateWithFlags(&h->aux_stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->state_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&h->ev_state, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming));
+    memset(&h->x, 0, sizeof(h->x));
     CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
     DevCtx &c = h->c;
     memset(&c, 0, sizeof(c));
@@ -145,6 +194,7 @@ static int create_impl(mtd_handle h)
     DA(h->delta_own, (c.cap_expo + 1) * MTD_DELTA_WORDS);
     c.delta = h->delta_own;
     DA(c.ctr, 1);
+    DA(c.sctr, 1);
     DA(h->d_params, 1);
     c.P = h->d_params;
     {   // math.log(i) for small integers, from the host libm (what CPython's math.log calls)
@@ -165,6 +215,7 @@ static int create_impl(mtd_handle h)
     CK(cudaMemsetAsync(c.inf_sev, 0, N, h->stream)); CK(cudaMemsetAsync(c.sched_cnt, 0, N, h->stream));
     CK(cudaMemsetAsync(c.sched, 0, sizeof(int32_t) * N * MTD_MAXSCHED, h->stream));
     CK(cudaMemsetAsync(c.ctr, 0, sizeof(DevCounters), h->stream));
+    CK(cudaMemsetAsync(c.sctr, 0, sizeof(StateCounters), h->stream));
     CK(cudaMemsetAsync(ci, 0xff, sizeof(int16_t) * C, h->stream));
     std::vector<int32_t> none((size_t)std::max<int64_t>(3 * N, 1), MTD_NONE);
     CK(cudaMemcpyAsync(c.last_dose_day, none.data(), sizeof(int32_t) * N, cudaMemcpyHostToDevice, h->stream));
@@ -198,6 +249,11 @@ extern "C" int mtd_destroy(mtd_handle h)
     if (!h) return MTD_E_ARG;
     cudaSetDevice(h->cfg.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->state_stream) { cudaStreamSynchronize(h->state_stream); cudaStreamDestroy(h->state_stream); }
+    if (h->ev_state) cudaEventDestroy(h->ev_state);
+    if (h->ev_main) cudaEventDestroy(h->ev_main);
+    for (void *p : h->xchg_peers) cudaIpcCloseMemHandle(p);
+    if (h->xchg_alloc) cudaFree(h->xchg_alloc);
     free_tape(h);
     for (void *p : h->trace_tape_allocs) cudaFree(p);
     for (void *p : { (void *)h->res_off, (void *)h->res_nres, (void *)h->res_members, (void *)h->trace_sel, (void *)h->res_first,
@@ -211,7 +267,9 @@ extern "C" int mtd_destroy(mtd_handle h)
     if (h->ev_join) cudaEventDestroy(h->ev_join);
     if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
     if (h->export_stream) { cudaStreamSynchronize(h->export_stream); cudaStreamDestroy(h->export_stream); }
-    for (cudaEvent_t e : { h->ev_staged[0], h->ev_staged[1], h->ev_k0_done, h->ev_snap, h->ev_exported[0], h->ev_exported[1] })
+    if (h->bulk_stream) { cudaStreamSynchronize(h->bulk_stream); cudaStreamDestroy(h->bulk_stream); }
+    for (cudaEvent_t e : { h->ev_staged[0], h->ev_staged[1], h->ev_k0_done, h->ev_snap, h->ev_exported[0], h->ev_exported[1],
+                           h->ev_res[0], h->ev_res[1] })
         if (e) cudaEventDestroy(e);
     for (void *p : h->allocs) cudaFree(p);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
@@ -267,6 +325,7 @@ extern "C" int mtd_set_state(mtd_handle h, int64_t n, const int8_t *seir, const 
 {
     if (!h || n != h->c.n_agents) { if (h) h->err = "mtd_set_state: n != n_agents"; return MTD_E_ARG; }
     CK(cudaSetDevice(h->cfg.device));
+    TOUCH();
     size_t N = (size_t)n;
     COPY_IN(h->c.seir, seir, N); COPY_IN(h->c.inf_type, inf_type, N); COPY_IN(h->c.inf_sev, inf_sev, N);
     COPY_IN(h->c.last_dose_day, last_dose_day, 4 * N);
@@ -283,6 +342,7 @@ extern "C" int mtd_get_state(mtd_handle h, int64_t n, int8_t *seir, int8_t *inf_
 {
     if (!h || n != h->c.n_agents) { if (h) h->err = "mtd_get_state: n != n_agents"; return MTD_E_ARG; }
     CK(cudaSetDevice(h->cfg.device));
+    TOUCH();
     size_t N = (size_t)n;
     COPY_OUT(seir, h->c.seir, N); COPY_OUT(inf_type, h->c.inf_type, N); COPY_OUT(inf_sev, h->c.inf_sev, N);
     COPY_OUT(sched, h->c.sched, 4 * N * MTD_MAXSCHED); COPY_OUT(sched_cnt, h->c.sched_cnt, N);
@@ -330,6 +390,8 @@ extern "C" int mtd_set_tape(mtd_handle h, const mtd_tape *t)
     return MTD_OK;
 }
 
+static int issue_host_export(mtd_handle h, int sl);
+
 extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, int64_t M, const int32_t *iv_agent,
                                             const int32_t *iv_cell, const uint8_t *iv_start, const uint8_t *iv_end,
                                             const uint32_t *iv_order, int mem)
@@ -371,6 +433,7 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     c.rows12 = nullptr;
     if (h->export_on) {     // K2 also packs the rows for the export; the slot's previous export must have drained
         const int sl = (int)(h->day_seq & 1);
+        { int r = issue_host_export(h, sl); if (r) return r; }
         if (h->exported_pending[sl]) { CK(cudaStreamWaitEvent(h->stream, h->ev_exported[sl], 0)); h->exported_pending[sl] = false; }
         c.rows12 = h->rows12_buf[sl];
     }
@@ -382,19 +445,48 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     return MTD_OK;
 }
 
+// apply chain of the day's exposure records on the state stream: [peer wait] -> [resolve] -> apply -> clear winners
+static int enqueue_apply(mtd_handle h, const int32_t *bufs, int n_bufs, int64_t cap, bool resolve, bool wait_peers, int par)
+{
+    { int r = state_after_main(h); if (r) return r; }
+    cudaStream_t ss = h->state_stream;
+    CK(cudaMemsetAsync(h->c.sctr, 0, sizeof(StateCounters), ss));
+    StageScope sc(h, MTD_STAGE_K3_APPLY, ss);
+    if (wait_peers) sc.add(launch_xchg_wait(h->x, par, h->xchg_seq, h->c.sctr, ss));
+    sc.add(launch_k3_apply(h->c, bufs, n_bufs, cap, resolve, h->expo_list, ss, h->sm_count));
+    h->win_clean = true;
+    h->state_dirty = true;
+    return MTD_OK;
+}
+
 extern "C" int mtd_simulate_direct_contacts(mtd_handle h, const mtd_day *day, int32_t *delta_buf, int64_t cap, int apply)
 {
     if (!h || !day) return MTD_E_ARG;
     if (!h->day_ready) { h->err = "mtd_simulate_direct_contacts before mtd_simulate_contact_network"; return MTD_E_STATE; }
+    if (apply == MTD_APPLY_EXCHANGE && !h->xchg_on) { h->err = "MTD_APPLY_EXCHANGE before mtd_exchange_ready"; return MTD_E_STATE; }
     CK(cudaSetDevice(h->cfg.device));
     DevCtx &c = h->c;
     c.day = *day;
     int32_t *buf = delta_buf ? delta_buf : h->delta_own;
     int64_t cp = delta_buf ? cap : c.cap_expo;
+    int par = 0;
+    const int64_t slice = (h->x.cap + 1) * MTD_DELTA_WORDS;
+    if (apply == MTD_APPLY_EXCHANGE) {          // records go straight into this rank's slice of its own exchange buffer
+        par = (int)((h->xchg_seq + 1) & 1);
+        buf = h->x.buf[h->x.rank] + ((int64_t)par * h->x.world + h->x.rank) * slice;
+        cp = h->x.cap;
+    }
     if (cp <= 0) { h->err = "delta buffer capacity must be positive"; return MTD_E_ARG; }
-    { StageScope sc(h, MTD_STAGE_K3_EVAL); sc.add(launch_k3_eval(c, buf, cp, h->win_clean, h->stream, h->sm_count)); h->win_clean = false; }
-    if (apply) { StageScope sc(h, MTD_STAGE_K3_APPLY);
-                 sc.add(launch_k3_apply(c, buf, 1, cp, false, h->expo_list, h->stream, h->sm_count)); h->win_clean = true; }
+    { int r = main_after_state(h); if (r) return r; }          // K4 of today and the apply of yesterday
+    { StageScope sc(h, MTD_STAGE_K3_EVAL); sc.add(launch_k3_eval(c, buf, cp, h->win_clean, h->stream, h->sm_count)); h->win_clean = false;
+      if (apply == MTD_APPLY_EXCHANGE) { h->xchg_seq++; sc.add(launch_xchg_push(h->x, par, h->xchg_seq, h->stream)); } }
+    if (apply == MTD_APPLY_EXCHANGE) {
+        int r = enqueue_apply(h, h->x.buf[h->x.rank] + (int64_t)par * h->x.world * slice, h->x.world, h->x.cap, true, true, par);
+        if (r) return r;
+    } else if (apply) {
+        int r = enqueue_apply(h, buf, 1, cp, false, false, 0);
+        if (r) return r;
+    } else h->main_dirty = true;
     CK(cudaGetLastError());
     return MTD_OK;
 }
@@ -403,8 +495,7 @@ extern "C" int mtd_apply_deltas(mtd_handle h, const int32_t *bufs, int64_t n_buf
 {
     if (!h || !bufs || n_bufs <= 0 || cap <= 0) return MTD_E_ARG;
     CK(cudaSetDevice(h->cfg.device));
-    { StageScope sc(h, MTD_STAGE_K3_APPLY);
-      sc.add(launch_k3_apply(h->c, bufs, (int)n_bufs, cap, true, h->expo_list, h->stream, h->sm_count)); h->win_clean = true; }
+    { int r = enqueue_apply(h, bufs, (int)n_bufs, cap, true, false, 0); if (r) return r; }
     CK(cudaGetLastError());
     return MTD_OK;
 }
@@ -413,13 +504,61 @@ extern "C" int mtd_advance_seir(mtd_handle h, int32_t day, const uint8_t *mask, 
 {
     if (!h) return MTD_E_ARG;
     CK(cudaSetDevice(h->cfg.device));
+    cudaStream_t ss = h->state_stream;
+    if (h->main_dirty) { int r = state_after_main(h); if (r) return r; }
     const uint8_t *dm = mask;
     if (mask && mem == MTD_MEM_HOST) {
-        CK(cudaMemcpyAsync(h->d_mask, mask, (size_t)h->c.n_agents, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->d_mask, mask, (size_t)h->c.n_agents, cudaMemcpyHostToDevice, ss));
         dm = h->d_mask;
     }
-    { StageScope sc(h, MTD_STAGE_K4); sc.add(launch_k4(h->c, day, dm, h->stream, h->sm_count)); }
+    { StageScope sc(h, MTD_STAGE_K4, ss); sc.add(launch_k4(h->c, day, dm, ss, h->sm_count)); }
+    h->state_dirty = true;
     CK(cudaGetLastError());
+    return MTD_OK;
+}
+
+// ---- peer exchange: one allocation per rank = arrival flags [2][world] (256 bytes reserved) + slices [2][world][cap+1]
+#define XCHG_FLAG_BYTES 256
+extern "C" int mtd_exchange_init(mtd_handle h, int rank, int world, int64_t cap_records, void *ipc_handle_out)
+{
+    if (!h || rank < 0 || world < 2 || rank >= world || world > MTD_MAX_WORLD || cap_records <= 0 || !ipc_handle_out) {
+        if (h) h->err = "mtd_exchange_init: bad arguments"; return MTD_E_ARG; }
+    if (h->xchg_alloc) { h->err = "mtd_exchange_init: already initialised"; return MTD_E_STATE; }
+    CK(cudaSetDevice(h->cfg.device));
+    const size_t bytes = XCHG_FLAG_BYTES + sizeof(int32_t) * 2 * (size_t)world * (size_t)(cap_records + 1) * MTD_DELTA_WORDS;
+    CK(cudaMalloc(&h->xchg_alloc, bytes));
+    CK(cudaMemset(h->xchg_alloc, 0, bytes));
+    CK(cudaDeviceSynchronize());
+    h->x.rank = rank; h->x.world = world; h->x.cap = cap_records;
+    h->x.flags[rank] = (unsigned long long *)h->xchg_alloc;
+    h->x.buf[rank] = (int32_t *)((char *)h->xchg_alloc + XCHG_FLAG_BYTES);
+    cudaIpcMemHandle_t ipc;
+    CK(cudaIpcGetMemHandle(&ipc, h->xchg_alloc));
+    memcpy(ipc_handle_out, &ipc, sizeof(ipc));
+    return MTD_OK;
+}
+
+extern "C" int mtd_exchange_open(mtd_handle h, int peer, const void *ipc_handle)
+{
+    if (!h || !h->xchg_alloc || peer < 0 || peer >= h->x.world || peer == h->x.rank || !ipc_handle) {
+        if (h) h->err = "mtd_exchange_open: bad arguments"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    cudaIpcMemHandle_t ipc;
+    memcpy(&ipc, ipc_handle, sizeof(ipc));
+    void *p = nullptr;
+    CK(cudaIpcOpenMemHandle(&p, ipc, cudaIpcMemLazyEnablePeerAccess));
+    h->xchg_peers.push_back(p);
+    h->x.flags[peer] = (unsigned long long *)p;
+    h->x.buf[peer] = (int32_t *)((char *)p + XCHG_FLAG_BYTES);
+    return MTD_OK;
+}
+
+extern "C" int mtd_exchange_ready(mtd_handle h)
+{
+    if (!h || !h->xchg_alloc) { if (h) h->err = "mtd_exchange_ready before mtd_exchange_init"; return MTD_E_STATE; }
+    for (int r = 0; r < h->x.world; r++)
+        if (!h->x.buf[r]) { h->err = "mtd_exchange_ready: a peer's buffer has not been opened"; return MTD_E_STATE; }
+    h->xchg_on = true;
     return MTD_OK;
 }
 
@@ -442,6 +581,7 @@ extern "C" int mtd_get_stage_ms(mtd_handle h, float ms[MTD_N_STAGES], int64_t la
     if (!h || !ms) return MTD_E_ARG;
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
+    CK(cudaStreamSynchronize(h->state_stream));
     for (int s = 0; s < MTD_N_STAGES; s++) {
         ms[s] = 0.f;
         double sum = 0.0;
@@ -463,6 +603,7 @@ extern "C" int mtd_sync(mtd_handle h)
     if (!h) return MTD_E_ARG;
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
+    CK(cudaStreamSynchronize(h->state_stream));
     return MTD_OK;
 }
 
@@ -470,13 +611,16 @@ extern "C" int mtd_get_counters(mtd_handle h, mtd_counters *out)
 {
     if (!h || !out) return MTD_E_ARG;
     CK(cudaSetDevice(h->cfg.device));
-    DevCounters d;
+    TOUCH();
+    DevCounters d; StateCounters sc;
     CK(cudaMemcpyAsync(&d, h->c.ctr, sizeof(d), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(&sc, h->c.sctr, sizeof(sc), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     memset(out, 0, sizeof(*out));
-    out->n_slots = d.n_slots; out->n_rows = d.n_rows; out->n_exposed = d.n_applied;
+    if (!d.error && sc.error) d.error = sc.error;
+    out->n_slots = d.n_slots; out->n_rows = d.n_rows; out->n_exposed = sc.n_applied;
     out->pairs_evaluated = (int64_t)d.pairs_evaluated; out->n_potential = (int64_t)d.n_potential;
-    out->n_si_rows = d.n_si_rows; out->sched_overflow = d.sched_overflow; out->tape_miss = d.tape_miss;
+    out->n_si_rows = d.n_si_rows; out->sched_overflow = sc.sched_overflow; out->tape_miss = d.tape_miss;
     for (int k = 0; k < MTD_NUM_CLASSES; k++) out->class_cells[k] = d.class_cells[k];
     out->error = d.error;
     if (d.error) {
@@ -524,8 +668,9 @@ extern "C" int mtd_get_exposed(mtd_handle h, int32_t *agent_ids, int64_t cap, in
     if (!h || !n) return MTD_E_ARG;
     if (mem != MTD_MEM_HOST) { h->err = "mtd_get_exposed: host buffers only"; return MTD_E_ARG; }
     CK(cudaSetDevice(h->cfg.device));
-    DevCounters d;
-    CK(cudaMemcpyAsync(&d, h->c.ctr, sizeof(d), cudaMemcpyDeviceToHost, h->stream));
+    TOUCH();
+    StateCounters d;
+    CK(cudaMemcpyAsync(&d, h->c.sctr, sizeof(d), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     int64_t cnt = std::min<int64_t>(d.n_applied, h->c.cap_expo);
     *n = cnt;
@@ -563,6 +708,7 @@ extern "C" int mtd_occupancy(mtd_handle h, int64_t out[6])
 {
     if (!h || !out) return MTD_E_ARG;
     CK(cudaSetDevice(h->cfg.device));
+    TOUCH();
     launch_occupancy(h->c, h->occ, h->stream, h->sm_count);
     unsigned long long t[6];
     CK(cudaMemcpyAsync(t, h->occ, sizeof(t), cudaMemcpyDeviceToHost, h->stream));
@@ -648,6 +794,7 @@ extern "C" int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_t
     if (!h->have_params || !h->res_off) { h->err = "mtd_contact_tracing: params / residences not set"; return MTD_E_STATE; }
     if (day->mode == MTD_MODE_REPLAY && !tape) { h->err = "replay mode without a trace tape"; return MTD_E_STATE; }
     CK(cudaSetDevice(h->cfg.device));
+    TOUCH();
     int r = trace_scratch(h);
     if (r) return r;
     CK(cudaStreamSynchronize(h->stream));
@@ -710,7 +857,9 @@ static int pipeline_init(mtd_handle h)
     CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
     CK(cudaStreamCreateWithPriority(&h->copy_stream, cudaStreamNonBlocking, hi));
     CK(cudaStreamCreateWithPriority(&h->export_stream, cudaStreamNonBlocking, hi));
-    for (cudaEvent_t *e : { &h->ev_staged[0], &h->ev_staged[1], &h->ev_k0_done, &h->ev_snap, &h->ev_exported[0], &h->ev_exported[1] })
+    CK(cudaStreamCreateWithPriority(&h->bulk_stream, cudaStreamNonBlocking, hi));
+    for (cudaEvent_t *e : { &h->ev_staged[0], &h->ev_staged[1], &h->ev_k0_done, &h->ev_snap, &h->ev_exported[0], &h->ev_exported[1],
+                            &h->ev_res[0], &h->ev_res[1] })
         CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
     return MTD_OK;
 }
@@ -757,16 +906,45 @@ extern "C" int mtd_prefetch_intervals(mtd_handle h, int64_t M, const int32_t *iv
     return MTD_OK;
 }
 
-__global__ void export_snapshot_kernel(DevCtx c, const unsigned long long *occ, const unsigned long long *expo_list,
-                                       int64_t *snap, unsigned long long *expo_snap, int64_t ticket)
+// snapshot of what the next day step overwrites, in two halves: the contact counters (cleared by the next K0 on the main
+// stream) and the state chain's products (exposure list, applied count, occupancy; state stream, after the apply)
+__global__ void export_snap_contact_kernel(DevCtx c, int64_t *snap)
 {
-    const int n = c.ctr->n_applied < (int)c.cap_expo ? c.ctr->n_applied : (int)c.cap_expo;
+    snap[0] = c.day.day; snap[1] = c.ctr->n_rows; snap[9] = (int64_t)c.ctr->pairs_evaluated; snap[10] = c.ctr->error;
+}
+
+__global__ void export_snap_state_kernel(DevCtx c, const unsigned long long *occ, const unsigned long long *expo_list,
+                                         int64_t *snap, unsigned long long *expo_snap, int64_t ticket)
+{
+    const int n = c.sctr->n_applied < (int)c.cap_expo ? c.sctr->n_applied : (int)c.cap_expo;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 2 * n; i += gridDim.x * blockDim.x) expo_snap[i] = expo_list[i];
     if (blockIdx.x == 0 && threadIdx.x == 0) {
-        snap[0] = c.day.day; snap[1] = c.ctr->n_rows; snap[2] = n;
+        snap[2] = n;
         for (int k = 0; k < 6; k++) snap[3 + k] = (int64_t)occ[k];
-        snap[9] = (int64_t)c.ctr->pairs_evaluated; snap[10] = c.ctr->error; snap[11] = ticket;
+        if (snap[10] == 0) snap[10] = c.sctr->error;
+        snap[11] = ticket;
     }
+}
+
+// Host exports, second half: once the day's result record has landed (ev_res) the row and exposure counts are known on
+// the host, and the two bulk copies are issued with their exact sizes on the bulk stream -- copy-engine transfers
+// that leave every SM to the next day's kernels.
+static int issue_host_export(mtd_handle h, int sl)
+{
+    mtd_handle_s::HostExport &x = h->hx[sl];
+    if (!x.unissued) return MTD_OK;
+    x.unissued = false;
+    CK(cudaEventSynchronize(h->ev_res[sl]));
+    const int64_t n_rows = std::min<int64_t>(x.result->n_rows, x.cap_rows);
+    const int64_t n_exp = std::min<int64_t>(x.result->n_exposed, x.cap_exposed);
+    // the bulk copies have a stream of their own: the export stream already holds the NEXT day's result record behind a
+    // wait for that day's snapshot, and a copy queued there would start a whole day late
+    if (x.rows && n_rows > 0)
+        CK(cudaMemcpyAsync(x.rows, h->rows12_buf[sl], 12 * (size_t)n_rows, cudaMemcpyDeviceToHost, h->bulk_stream));
+    if (x.kv && n_exp > 0)
+        CK(cudaMemcpyAsync(x.kv, h->expo_snap[sl], 16 * (size_t)n_exp, cudaMemcpyDeviceToHost, h->bulk_stream));
+    CK(cudaEventRecord(h->ev_exported[sl], h->bulk_stream));
+    return MTD_OK;
 }
 
 extern "C" int mtd_export_day_async(mtd_handle h, void *rows12, int64_t cap_rows, uint64_t *exposed_kv, int64_t cap_exposed,
@@ -775,27 +953,36 @@ extern "C" int mtd_export_day_async(mtd_handle h, void *rows12, int64_t cap_rows
     if (!h || !result) return MTD_E_ARG;
     if (!h->export_on || !h->day_ready || !h->c.rows12) { h->err = "mtd_export_day_async: mtd_set_export(h, 1) before the day step"; return MTD_E_STATE; }
     CK(cudaSetDevice(h->cfg.device));
-    void *d_rows = rows12, *d_kv = exposed_kv, *d_res = result;
-    if (mem == MTD_MEM_HOST) {      // pinned host memory, written by the device over PCIe
-        if (rows12) CK(cudaHostGetDevicePointer(&d_rows, rows12, 0));
-        if (exposed_kv) CK(cudaHostGetDevicePointer(&d_kv, exposed_kv, 0));
-        CK(cudaHostGetDevicePointer(&d_res, result, 0));
-    }
     const int sl = (int)((h->day_seq - 1) & 1);          // slot of the day just computed
+    { int r = issue_host_export(h, sl); if (r) return r; }
     const int64_t tk = ++h->export_ticket;
-    // main stream: occupancy + snapshot of everything the next day step overwrites (counters, exposure list)
-    launch_occupancy(h->c, h->occ, h->stream, h->sm_count);
-    export_snapshot_kernel<<<32, 256, 0, h->stream>>>(h->c, h->occ, h->expo_list, h->snap[sl], h->expo_snap[sl], tk);
-    CK(cudaEventRecord(h->ev_snap, h->stream));
-    // side stream: rows, exposures, then the result record (its arrival says everything before it has landed)
+    // snapshot of everything the next day step overwrites: contact counters on the main stream (before the next K0),
+    // exposure list + occupancy on the state stream (after the apply)
+    export_snap_contact_kernel<<<1, 1, 0, h->stream>>>(h->c, h->snap[sl]);
+    { int r = state_after_main(h); if (r) return r; }
+    launch_occupancy(h->c, h->occ, h->state_stream, h->sm_count);
+    export_snap_state_kernel<<<32, 256, 0, h->state_stream>>>(h->c, h->occ, h->expo_list, h->snap[sl], h->expo_snap[sl], tk);
+    h->state_dirty = true;
+    CK(cudaEventRecord(h->ev_snap, h->state_stream));
     CK(cudaStreamWaitEvent(h->export_stream, h->ev_snap, 0));
-    if (rows12) launch_stream_out(d_rows, h->rows12_buf[sl], h->snap[sl] + 1, 12, cap_rows, 2 * h->sm_count, h->export_stream);
-    if (exposed_kv) launch_stream_out(d_kv, h->expo_snap[sl], h->snap[sl] + 2, 16, cap_exposed, 8, h->export_stream);
-    CK(cudaMemcpyAsync(d_res, h->snap[sl], sizeof(mtd_day_result), cudaMemcpyDefault, h->export_stream));
-    CK(cudaEventRecord(h->ev_exported[sl], h->export_stream));
+    if (mem == MTD_MEM_HOST) {
+        // the result record first; mtd_export_wait (or the next reuse of this slot) issues the bulk copies
+        CK(cudaMemcpyAsync(result, h->snap[sl], sizeof(mtd_day_result), cudaMemcpyDeviceToHost, h->export_stream));
+        CK(cudaEventRecord(h->ev_res[sl], h->export_stream));
+        mtd_handle_s::HostExport &x = h->hx[sl];
+        x.unissued = true; x.rows = rows12; x.cap_rows = cap_rows; x.kv = exposed_kv; x.cap_exposed = cap_exposed;
+        x.result = result;
+        h->launches[MTD_STAGE_K2] += 2;
+    } else {
+        // device destinations: counts are read on the device by a streaming kernel on the side stream
+        if (rows12) launch_stream_out(rows12, h->rows12_buf[sl], h->snap[sl] + 1, 12, cap_rows, 2 * h->sm_count, h->export_stream);
+        if (exposed_kv) launch_stream_out(exposed_kv, h->expo_snap[sl], h->snap[sl] + 2, 16, cap_exposed, 8, h->export_stream);
+        CK(cudaMemcpyAsync(result, h->snap[sl], sizeof(mtd_day_result), cudaMemcpyDefault, h->export_stream));
+        CK(cudaEventRecord(h->ev_exported[sl], h->export_stream));
+        h->launches[MTD_STAGE_K2] += 2 + (rows12 ? 1 : 0) + (exposed_kv ? 1 : 0);
+    }
     h->exported_pending[sl] = true;
     h->ticket_slot[tk & 1] = sl;
-    h->launches[MTD_STAGE_K2] += 2 + (rows12 ? 1 : 0) + (exposed_kv ? 1 : 0);
     CK(cudaGetLastError());
     if (ticket) *ticket = tk;
     return MTD_OK;
@@ -807,6 +994,7 @@ extern "C" int mtd_export_wait(mtd_handle h, int64_t ticket)
     if (ticket <= 0 || ticket > h->export_ticket || ticket + 2 <= h->export_ticket) { h->err = "mtd_export_wait: unknown ticket"; return MTD_E_ARG; }
     CK(cudaSetDevice(h->cfg.device));
     const int sl = h->ticket_slot[ticket & 1];
+    { int r = issue_host_export(h, sl); if (r) return r; }
     CK(cudaEventSynchronize(h->ev_exported[sl]));
     return MTD_OK;
 }

@@ -29,7 +29,7 @@ struct DevCounters {
     int n_rows;
     int n_succ;                          // successful S-I draws (before winner resolution)
     int n_delta;                         // delta records produced locally
-    int n_applied;                       // exposures applied
+    int n_applied_unused;
     int n_si_rows;
     int sched_overflow;
     int tape_miss;
@@ -37,6 +37,24 @@ struct DevCounters {
     int class_cursor[MTD_NUM_CLASSES];   // work-fetch cursors of the persistent K1 warps
     int error;
     int pad;
+};
+
+// counters of the state chain (apply of the day's exposure records), which runs on the handle's state stream beside the
+// next day's K0/K1/K2: kept apart from DevCounters, which the next day's K0 clears
+struct StateCounters {
+    int n_applied;                       // exposures applied
+    int sched_overflow;
+    int error;                           // MTD_E_TIMEOUT of the peer wait
+    int pad;
+};
+
+// multi-GPU exchange of the exposure records over NVLink peer memory (one slice per source rank and day parity)
+#define MTD_MAX_WORLD 16
+struct DevExchange {
+    int rank, world;
+    int64_t cap;                                   // records per slice (+1 header record)
+    int32_t *buf[MTD_MAX_WORLD];                   // base of rank r's exchange buffer [2][world][cap+1][MTD_DELTA_WORDS] (peer mapped)
+    unsigned long long *flags[MTD_MAX_WORLD];      // rank r's arrival flags [2][world]: sequence number of the last slice landed
 };
 
 // one CSR record of the cell -> interval layout (16 B, one vector load)
@@ -109,6 +127,7 @@ struct DevCtx {
     double *row_p;             // [cap_rows] optional infection probability per row (NULL = off)
     int32_t *delta;            // [cap_expo][MTD_DELTA_WORDS]
     DevCounters *ctr;
+    StateCounters *sctr;
     const mtd_params *P;       // device copy of the parameters
     IvRec *csr_sorted;         // [M] CSR records in list (emission) order within each cell, written by K1
     const double *logtab;      // [MTD_LOGTAB_N] glibc log(i)

@@ -62,17 +62,23 @@ __device__ __forceinline__ double log_int(const DevCtx &g, int v)
 }
 
 // contactnetwork.py:225-252: float degree of one agent
-__device__ __forceinline__ double degree_f(const DevCtx &g, const mtd_params *P, int ag, int act, int ts, int pc,
-                                           double avg_ts, double avg_pc, double log_avg_ts, double log_avg_pc,
-                                           double one_minus_mhd)
+__device__ __forceinline__ double degree_f2(const DevCtx &g, const mtd_params *P, int ab, double soc, int act, int ts, int pc,
+                                            double avg_ts, double avg_pc, double log_avg_ts, double log_avg_pc,
+                                            double one_minus_mhd)
 {
-    int ab = g.age_bracket[ag];
     if (ab < 0) ab += 16;                                   // numpy negative index
     double cmv = P->cm[ab][act];
     double tsm = 1.0, pcm = 1.0;
     if ((double)ts != avg_ts && avg_ts > 1) tsm = log_int(g, ts) / log_avg_ts;       // math.log(x, base)
     if ((double)pc != avg_pc && avg_pc > 1) pcm = log_int(g, pc) / log_avg_pc;
-    return cmv * tsm * pcm * g.soc_rate[ag] * one_minus_mhd;
+    return cmv * tsm * pcm * soc * one_minus_mhd;
+}
+
+__device__ __forceinline__ double degree_f(const DevCtx &g, const mtd_params *P, int ag, int act, int ts, int pc,
+                                           double avg_ts, double avg_pc, double log_avg_ts, double log_avg_pc,
+                                           double one_minus_mhd)
+{
+    return degree_f2(g, P, g.age_bracket[ag], g.soc_rate[ag], act, ts, pc, avg_ts, avg_pc, log_avg_ts, log_avg_pc, one_minus_mhd);
 }
 
 __device__ __forceinline__ int degree_i(double d, long long deg_sum, long long max_degree, int pc)
@@ -139,19 +145,31 @@ __global__ void __launch_bounds__(K1S_THREADS) k1_small_kernel(DevCtx g, int cls
     const double one_minus_mhd = 1 - g.day.mhd;
     unsigned long long acc_pairs = 0, acc_pot = 0;
 
-    for (int w = (blockIdx.x * K1S_THREADS + (int)threadIdx.x) / G; w < total; w += n_groups) {
-        const int slot = list[w];
-        const int m = g.slot_m[slot];
-        const int64_t base = g.slot_off[slot];
-        const int cell = g.slot_cell[slot];
+    // the next cell's descriptor and this lane's record are fetched while the current cell is processed
+    int w = (blockIdx.x * K1S_THREADS + (int)threadIdx.x) / G;
+    int nx_slot = 0, nx_m = 0, nx_cell = 0; int64_t nx_base = 0;
+    IvRec nx_rec; nx_rec.agent = 0; nx_rec.order = 0xffffffffu; nx_rec.se = 0; nx_rec.pad = 0;
+    if (w < total) {
+        nx_slot = list[w]; nx_m = g.slot_m[nx_slot]; nx_base = g.slot_off[nx_slot]; nx_cell = g.slot_cell[nx_slot];
+        if (gl < nx_m) nx_rec = g.csr[nx_base + gl];
+    }
+    for (; w < total; w += n_groups) {
+        const int slot = nx_slot;
+        const int m = nx_m;
+        const int64_t base = nx_base;
+        const int cell = nx_cell;
+        IvRec rec = nx_rec;
         const int ctype = g.cell_type[cell];
+        if (w + n_groups < total) {
+            nx_slot = list[w + n_groups]; nx_m = g.slot_m[nx_slot]; nx_base = g.slot_off[nx_slot]; nx_cell = g.slot_cell[nx_slot];
+            nx_rec.agent = 0; nx_rec.order = 0xffffffffu; nx_rec.se = 0;
+            if (gl < nx_m) nx_rec = g.csr[nx_base + gl];
+        }
         const int indid = (ctype == CT_WORKPLACE && g.cell_indid) ? g.cell_indid[cell] : -1;
         const int act = activity_of_celltype(ctype, indid);
 
         // ---- 1. my interval; restore list (emission) order by ranking the emission indices ----
         const bool have = gl < m;
-        IvRec rec; rec.agent = 0; rec.order = 0xffffffffu; rec.se = 0; rec.pad = 0;
-        if (have) rec = g.csr[base + gl];
         int rank = 0;
 #pragma unroll
         for (int j = 0; j < G; j++) {
@@ -170,6 +188,8 @@ __global__ void __launch_bounds__(K1S_THREADS) k1_small_kernel(DevCtx g, int cls
         // ---- 2. agents = first appearances (contactnetwork.py:161-163); an agent lives on its first interval's lane
         const uint32_t mm = (__match_any_sync(gmask, agent) >> gbase) & gbits;      // my agent's interval positions
         const bool isag = have && ((__ffs(mm) - 1) == gl);
+        int ab_pre = 0; double soc_pre = 0.0;                                       // gathered early, used in step 4
+        if (isag) { ab_pre = g.age_bracket[agent]; soc_pre = g.soc_rate[agent]; }
         const uint32_t agm = (__ballot_sync(gmask, isag) >> gbase) & gbits;         // agent lanes (group-relative)
         const int n = __popc(agm);
         {   // metric: unordered interval pairs of different agents = (m^2 - sum_a cnt_a^2) / 2
@@ -220,7 +240,7 @@ __global__ void __launch_bounds__(K1S_THREADS) k1_small_kernel(DevCtx g, int cls
         const double avg_ts = (double)ts_sum / (double)n, avg_pc = (double)pc_sum / (double)n;
         const double log_avg_ts = log(avg_ts), log_avg_pc = log(avg_pc);
         double degf = 0.0;
-        if (isag && pc > 0) degf = degree_f(g, P, agent, act, ts, pc, avg_ts, avg_pc, log_avg_ts, log_avg_pc, one_minus_mhd);
+        if (isag && pc > 0) degf = degree_f2(g, P, ab_pre, soc_pre, act, ts, pc, avg_ts, avg_pc, log_avg_ts, log_avg_pc, one_minus_mhd);
         double dsum;
         {   // numpy float64 add.reduce over the agents in order of first appearance (n <= 32 < 128: one block)
             uint32_t b = agm;

@@ -305,7 +305,7 @@ __global__ void k3_apply_kernel(DevCtx c, const int32_t *bufs, int n_bufs, int64
             int cnt = c.sched_cnt[ag];
             for (int k = 0; k < ns; k++) {            // agent_state_transition_by_day.append(...)
                 if (cnt < MTD_MAXSCHED) c.sched[(int64_t)ag * MTD_MAXSCHED + cnt++] = rec[4 + k];
-                else atomicAdd(&c.ctr->sched_overflow, 1);
+                else atomicAdd(&c.sctr->sched_overflow, 1);
             }
             c.sched_cnt[ag] = (uint8_t)cnt;
             c.seir[ag] = S_EXP; c.inf_type[ag] = (int8_t)(rec[3] & 0xff); c.inf_sev[ag] = SV_UNDEF;   // :219-225
@@ -318,7 +318,7 @@ __global__ void k3_apply_kernel(DevCtx c, const int32_t *bufs, int n_bufs, int64
                 if (h[0] == MTD_NONE) h[0] = rec[14];
                 h[1] = rec[15]; h[2] = rec[16];
             }
-            int idx = atomicAdd(&c.ctr->n_applied, 1);
+            int idx = atomicAdd(&c.sctr->n_applied, 1);
             if (idx < c.cap_expo) { expo_list[2 * (int64_t)idx] = key; expo_list[2 * (int64_t)idx + 1] = (unsigned long long)ag; }
         }
     }
@@ -371,27 +371,110 @@ __device__ __forceinline__ void k4_advance_agent(const DevCtx &c, int64_t ag, in
     c.sched_cnt[ag] = (uint8_t)(cnt - 1);
 }
 
+// sched_cnt is read 16 agents per load; almost every agent has an empty schedule
 __global__ void k4_advance_kernel(DevCtx c, int day, const uint8_t *mask)
 {
-    for (int64_t ag = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; ag < c.n_agents; ag += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t n16 = c.n_agents >> 4;
+    const uint4 *cnt16 = (const uint4 *)c.sched_cnt;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n16; q += (int64_t)gridDim.x * blockDim.x) {
+        const uint4 v = cnt16[q];
+        if ((v.x | v.y | v.z | v.w) == 0u) continue;
+        const uint32_t w[4] = { v.x, v.y, v.z, v.w };
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            const int cnt = (int)((w[k >> 2] >> (8 * (k & 3))) & 0xffu);
+            const int64_t ag = (q << 4) + k;
+            if (cnt == 0 || (mask && !mask[ag])) continue;
+            k4_advance_agent(c, ag, cnt, day);
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (int)(c.n_agents & 15)) {          // tail
+        const int64_t ag = (n16 << 4) + threadIdx.x;
         const int cnt = c.sched_cnt[ag];
-        if (cnt == 0) continue;
-        if (mask && !mask[ag]) continue;
-        k4_advance_agent(c, ag, cnt, day);
+        if (cnt != 0 && !(mask && !mask[ag])) k4_advance_agent(c, ag, cnt, day);
     }
 }
 
+// dynamicstatistics.py:169-193: agents per SEIR state; 16 agents per load, per-thread counters in registers
 __global__ void occupancy_kernel(DevCtx c, unsigned long long *out6)
 {
     __shared__ unsigned int h[8];
     if (threadIdx.x < 8) h[threadIdx.x] = 0;
     __syncthreads();
-    for (int64_t ag = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; ag < c.n_agents; ag += (int64_t)gridDim.x * blockDim.x) {
-        int s = c.seir[ag];
-        if (s >= 0 && s < 6) atomicAdd(&h[s], 1u);
+    unsigned int cnt[6] = { 0, 0, 0, 0, 0, 0 };
+    const int64_t n16 = c.n_agents >> 4;
+    const uint4 *s16 = (const uint4 *)c.seir;
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n16; q += (int64_t)gridDim.x * blockDim.x) {
+        const uint4 v = s16[q];
+        const uint32_t w[4] = { v.x, v.y, v.z, v.w };
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            const uint32_t st = (w[k >> 2] >> (8 * (k & 3))) & 0xffu;
+#pragma unroll
+            for (int j = 0; j < 6; j++) cnt[j] += (st == (uint32_t)j);
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (int)(c.n_agents & 15)) {
+        const int st = c.seir[(n16 << 4) + threadIdx.x];
+#pragma unroll
+        for (int j = 0; j < 6; j++) cnt[j] += (st == j);
+    }
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+        const unsigned int t = __reduce_add_sync(FULLMASK, cnt[j]);
+        if ((threadIdx.x & 31) == 0 && t) atomicAdd(&h[j], t);
     }
     __syncthreads();
     if (threadIdx.x < 6 && h[threadIdx.x]) atomicAdd(&out6[threadIdx.x], (unsigned long long)h[threadIdx.x]);
+}
+
+// ------------------------------------------------------------------------------------------------ peer exchange
+// Cells are sharded over the GPUs of one box and the per-agent state is replicated (the
+// reference's stateful-actor exchange, actor_dist.py:491-518).  Each rank PUSHES the records it produced -- a few
+// thousand 80-byte records, exactly as many as there are -- into its slice of every peer's exchange buffer with plain
+// stores over NVLink, then raises a per-source arrival flag on the peer; the apply chain of a rank starts once every
+// source's flag shows today's sequence number.  Slices are double-buffered by day parity: a rank can only push day
+// s+2 after it applied s+1, which needed every peer's push of s+1, which the peer enqueued after its own apply of s.
+__global__ void xchg_push_kernel(DevExchange x, int par)
+{
+    const int64_t slice = (x.cap + 1) * MTD_DELTA_WORDS;                // int32 words per slice
+    const int32_t *src = x.buf[x.rank] + ((int64_t)par * x.world + x.rank) * slice;
+    int n = src[0]; if (n > x.cap) n = (int)x.cap;
+    const int64_t n4 = (int64_t)(n + 1) * (MTD_DELTA_WORDS / 4);
+    const int4 *s4 = (const int4 *)src;
+    for (int p = 0; p < x.world; p++) {
+        if (p == x.rank) continue;
+        int4 *d4 = (int4 *)(x.buf[p] + ((int64_t)par * x.world + x.rank) * slice);
+        for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x)
+            d4[i] = s4[i];
+    }
+}
+
+__global__ void xchg_signal_kernel(DevExchange x, int par, unsigned long long seq)
+{
+    const int p = threadIdx.x;
+    if (p >= x.world) return;
+    __threadfence_system();
+    unsigned long long *f = x.flags[p] + (int64_t)par * x.world + x.rank;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(f), "l"(seq) : "memory");
+}
+
+__global__ void xchg_wait_kernel(DevExchange x, int par, unsigned long long seq, StateCounters *sctr, long long timeout_ns)
+{
+    const int q = threadIdx.x;
+    if (q >= x.world) return;
+    const unsigned long long *f = x.flags[x.rank] + (int64_t)par * x.world + q;
+    long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    while (true) {
+        unsigned long long v;
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+        if (v >= seq) break;
+        long long t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > timeout_ns) { sctr->error = MTD_E_TIMEOUT; break; }
+        __nanosleep(200);
+    }
 }
 
 }  // namespace
@@ -416,7 +499,22 @@ int launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t ca
 
 int launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count)
 {
-    k4_advance_kernel<<<sm_count * 8, 256, 0, st>>>(c, day, mask);
+    k4_advance_kernel<<<sm_count * 4, 256, 0, st>>>(c, day, mask);
+    return 1;
+}
+
+// push this rank's slice to every peer and raise the arrival flags (main stream, after the trajectory kernel)
+int launch_xchg_push(const DevExchange &x, int par, unsigned long long seq, cudaStream_t st)
+{
+    xchg_push_kernel<<<32, 256, 0, st>>>(x, par);
+    xchg_signal_kernel<<<1, 32, 0, st>>>(x, par, seq);
+    return 2;
+}
+
+// block the state stream until every source's slice of this parity carries sequence number seq
+int launch_xchg_wait(const DevExchange &x, int par, unsigned long long seq, StateCounters *sctr, cudaStream_t st)
+{
+    xchg_wait_kernel<<<1, 32, 0, st>>>(x, par, seq, sctr, 10000000000LL);
     return 1;
 }
 

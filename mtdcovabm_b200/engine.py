@@ -5,8 +5,10 @@ day loop (sim.py:1392-2125): SEIR advance (seirstateutil.update_agent_state runs
 start of the day, itinerary.py:399) -> contact network (contactnetwork.py:65) -> transmission (epidemiology.py:88).
 With `world > 1` cells are sharded over the ranks and the per-agent exposure deltas are exchanged once per day
 (the reference's stateful-actor strategy, actor_dist.py:491-518): K3 writes this rank's records
-straight into its slice of the gather buffer, one all-gather over NCCL, every rank applies all records to its replica
-of the per-agent state.
+straight into its slice of the exchange buffer and PUSHES exactly those records into every peer's buffer over NVLink
+peer memory (CUDA IPC mappings, arrival flags, no host synchronisation; csrc/k3_transmission.cu); every rank applies
+all records to its replica of the per-agent state on a side stream while the next day's K0/K1 already run.  If peer
+mappings cannot be established (or MTD_EXCHANGE=nccl) the records go through one NCCL all-gather per day instead.
 
 torch is used for device memory, streams and torch.distributed only; every computation is a kernel of libmtd_b200.so.
 """
@@ -37,11 +39,60 @@ class DayEngine:
                              stream=self.stream.cuda_stream, max_rows=max_rows, max_exposures=self.delta_cap)
         self.h.set_params(params)
         self.gather = None
+        self.exchange = "none"
         if world > 1:
-            with torch.cuda.device(self.device):
-                self.gather = torch.zeros((world, self.delta_cap + 1, capi.DELTA_WORDS), dtype=torch.int32,
-                                         device=self.device)
+            self.exchange = self._setup_peer_exchange()
+            if self.exchange == "nccl":
+                with torch.cuda.device(self.device):
+                    self.gather = torch.zeros((world, self.delta_cap + 1, capi.DELTA_WORDS), dtype=torch.int32,
+                                             device=self.device)
         self.n_agents, self.n_cells = n_agents, n_cells
+
+    def _setup_peer_exchange(self):
+        """map every peer's exchange buffer (CUDA IPC) -> "p2p"; "nccl" if that is not possible on this box"""
+        import os
+        import sys
+        dist = torch.distributed
+        ok, mine, why = 1, b"", ""
+        if os.environ.get("MTD_EXCHANGE", "p2p") == "nccl":
+            ok, why = 0, "MTD_EXCHANGE=nccl"
+        else:
+            try:
+                mine = self.h.exchange_init(self.rank, self.world, self.delta_cap)
+            except RuntimeError as e:
+                ok, why = 0, str(e)
+        handles = [None] * self.world
+        dist.all_gather_object(handles, (ok, mine, why), group=self.group)
+        if all(o for o, _, _ in handles):
+            try:
+                for r, (_, hb, _) in enumerate(handles):
+                    if r != self.rank:
+                        self.h.exchange_open(r, hb)
+                self.h.exchange_ready()
+            except RuntimeError as e:
+                ok, why = 0, str(e)
+        else:
+            ok = 0
+            why = why or next(w for o, _, w in handles if not o)
+        flags = [None] * self.world
+        dist.all_gather_object(flags, ok, group=self.group)        # also the barrier after the mappings
+        if all(flags):
+            return "p2p"
+        if self.rank == 0:
+            sys.stderr.write("mtdcovabm_b200: peer exchange unavailable (%s); using the NCCL all-gather\n" % why)
+        return "nccl"
+
+    def _transmission(self, d):
+        """K3 of the day + the exchange and application of the exposure records"""
+        h = self.h
+        if self.world == 1:
+            h.simulate_direct_contacts(d)
+        elif self.exchange == "p2p":
+            h.simulate_direct_contacts(d, apply=capi.APPLY_EXCHANGE)
+        else:       # this rank's cells -> delta records -> one all-gather -> every rank applies all records
+            h.simulate_direct_contacts(d, delta_buf=self.gather[self.rank], cap_records=self.delta_cap, apply=False)
+            exchange_deltas(self.gather, self.rank, self.group)
+            h.apply_deltas(self.gather, self.world, self.delta_cap)
 
     # ---- population
     def set_population(self, pop):
@@ -66,12 +117,7 @@ class DayEngine:
             h.simulate_contact_network(d, s["iv_agent"], s["iv_cell"], s["iv_start"], s["iv_end"],
                                        iv_order=s.get("iv_order"), n=n if n is not None else len(s["iv_agent"]),
                                        mem=mem)
-            if self.world == 1:
-                h.simulate_direct_contacts(d)
-            else:
-                h.simulate_direct_contacts(d, delta_buf=self.gather[self.rank], cap_records=self.delta_cap, apply=False)
-                exchange_deltas(self.gather, self.rank, self.group)
-                h.apply_deltas(self.gather, self.world, self.delta_cap)
+            self._transmission(d)
 
     # ---- host boundary, pipelined: pinned host buffers in, pinned host buffers out, copies beside the kernels
     def enable_host_pipeline(self, cap_rows, cap_exposed=None):
@@ -108,12 +154,7 @@ class DayEngine:
                 h.prefetch_intervals(next_s["iv_agent"], next_s["iv_cell"], next_s["iv_start"], next_s["iv_end"],
                                      next_s.get("iv_order"))
                 self._staged = next_s
-            if self.world == 1:
-                h.simulate_direct_contacts(d)
-            else:       # this rank's cells -> delta records -> one all-gather -> every rank applies all records
-                h.simulate_direct_contacts(d, delta_buf=self.gather[self.rank], cap_records=self.delta_cap, apply=False)
-                exchange_deltas(self.gather, self.rank, self.group)
-                h.apply_deltas(self.gather, self.world, self.delta_cap)
+            self._transmission(d)
             rows, kv, res = self._res[self._k]
             self._k ^= 1
             ticket = h.export_day_async(rows, self._cap_rows, kv, self._cap_exposed, res, mem=capi.MEM_HOST)
