@@ -300,10 +300,19 @@ def run_b200(args):
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    # measured DRAM traffic of the K1 launches of one day (ncu --set full capture, committed under profiles/), scaled to
+    # this rank's share of the day's intervals
+    traffic = None
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_k1_traffic.json")))
+        traffic = tr["dram_bytes_total"] * M_mean / tr["intervals_of_day"]
+    except Exception:
+        pass
     k1_ms = st_ms["k1_contacts"]
     achieved = k1_bytes / (k1_ms * 1e-3) / 1e9 if k1_ms > 0 else 0.0
     roofline = {"bound": "hbm", "kernel": "k1_contacts (6 size-class launches per day)", "achieved": achieved,
-                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum over the 6 K1 launches of one day (profiles/r01_k1_traffic.json)",
                 "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
                 "algorithmic_bytes_per_day": k1_bytes, "k1_ms": k1_ms, "stage_ms": st_ms,
                 "k1_pairs_per_s": P_mean / (k1_ms * 1e-3) if k1_ms > 0 else None,

@@ -131,6 +131,12 @@ int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, int64_t n_int
  * handle's own buffer.  Multi-GPU: pass this rank's slice of the allgather buffer with apply == 0, allgather, then
  * mtd_apply_deltas over all n_bufs slices. */
 int mtd_simulate_direct_contacts(mtd_handle h, const mtd_day *day, int32_t *delta_buf, int64_t cap_records, int apply);
+/* Epidemiology.simulate_direct_contacts(agents_directcontacts, cellid, cell_type, day) called on its own
+ * (epidemiology.py:88): the caller's contact pairs of ONE cell with their overlap lists [(start, end), ...]
+ * (ov_off[n_rows + 1] offsets into ov_se, two bytes per overlap) become the day's dense rows, in the order given;
+ * mtd_simulate_direct_contacts then evaluates them exactly like rows produced by mtd_simulate_contact_network. */
+int mtd_set_contacts(mtd_handle h, const mtd_day *day, int32_t cellid, int64_t n_rows, const int32_t *a1,
+                     const int32_t *a2, const int64_t *ov_off, const uint8_t *ov_se, int mem);
 int mtd_apply_deltas(mtd_handle h, const int32_t *delta_bufs, int64_t n_bufs, int64_t cap_records);
 
 /* Multi-GPU exchange of the exposure records over NVLink peer memory (replaces the reference's

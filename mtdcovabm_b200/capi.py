@@ -25,7 +25,7 @@ EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mt
            "mtd_get_contacts", "mtd_get_exposed", "mtd_get_infection_prob", "mtd_occupancy", "mtd_sync",
            "mtd_set_profiling", "mtd_get_stage_ms", "mtd_set_export", "mtd_prefetch_intervals",
            "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced",
-           "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready"]
+           "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
 
 
@@ -193,6 +193,11 @@ class Handle:
     def simulate_direct_contacts(self, day: Day, delta_buf=None, cap_records=0, apply=True):
         self._ck(self.lib.mtd_simulate_direct_contacts(self.h, C.byref(day), _ptr(delta_buf), C.c_int64(cap_records),
                                                        int(apply)), "mtd_simulate_direct_contacts")
+
+    def set_contacts(self, day: Day, cellid, a1, a2, ov_off, ov_se):
+        """the caller's contact pairs of one cell + overlap lists become the day's rows (host numpy arrays)"""
+        self._ck(self.lib.mtd_set_contacts(self.h, C.byref(day), C.c_int32(cellid), C.c_int64(len(a1)), _ptr(a1), _ptr(a2),
+                                           _ptr(ov_off), _ptr(ov_se), MEM_HOST), "mtd_set_contacts")
 
     def apply_deltas(self, bufs, n_bufs, cap_records):
         self._ck(self.lib.mtd_apply_deltas(self.h, _ptr(bufs), C.c_int64(n_bufs), C.c_int64(cap_records)),

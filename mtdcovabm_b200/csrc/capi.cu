@@ -18,6 +18,7 @@ int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, bool win_clean, 
 int launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t cap, bool resolve,
                     unsigned long long *expo_list, cudaStream_t st, int sm_count);
 int launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count);
+int launch_set_contacts(const DevCtx &c, int cell, int64_t n, const int32_t *a1, const int32_t *a2, cudaStream_t st);
 int launch_xchg_push(const DevExchange &x, int par, unsigned long long seq, cudaStream_t st);
 int launch_xchg_wait(const DevExchange &x, int par, unsigned long long seq, StateCounters *sctr, cudaStream_t st);
 int launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st, int sm_count);
@@ -43,6 +44,9 @@ struct mtd_handle_s {
     void *xchg_alloc = nullptr;
     std::vector<void *> xchg_peers;              // cudaIpcOpenMemHandle mappings
     unsigned long long xchg_seq = 0;
+    // caller-supplied contacts (mtd_set_contacts), device copies
+    int32_t *sc_a1 = nullptr, *sc_a2 = nullptr; int64_t sc_cap_rows = 0; int64_t *sc_off = nullptr; int64_t sc_cap_off = 0;
+    uint8_t *sc_se = nullptr; int64_t sc_cap_se = 0;
     int sm_count = 148;
     std::string err;
     std::vector<void *> allocs;
@@ -170,7 +174,6 @@ static int create_impl(mtd_handle h)
     // rows: sum over cells of (k*m + m/2)/2 + 2 with k <= 19 -> generous static bound, clipped by config
     c.cap_scratch_rows = 10 * M + 2 * std::min(M, C) + 1024;
     c.cap_rows = cfg.max_rows > 0 ? cfg.max_rows : (4 * M + 1024);
-    c.cap_list = 16;                                     // adjacency lists are gone (bit matrices in shared memory)
     c.cap_expo = cfg.max_exposures > 0 ? cfg.max_exposures : std::max<int64_t>(N / 4, 4096);
     const int64_t S = std::min(M, C);   // max active cells
     int8_t *ct; int16_t *ci; int8_t *ab, *eb; double *sr; int32_t *rc;
@@ -179,14 +182,14 @@ static int create_impl(mtd_handle h)
     DA(c.seir, N); DA(c.inf_type, N); DA(c.inf_sev, N); DA(c.last_dose_day, N);
     DA(c.sched, N * MTD_MAXSCHED); DA(c.sched_cnt, N); DA(c.test_day, 2 * N); DA(c.test_result_day, 2 * N);
     DA(c.quarantine, 3 * N); DA(c.hosp, 3 * N);
-    DA(c.cell_count, C); DA(c.cell_first, C); DA(c.slot_of_cell, C); DA(c.flag_scan, M + 2);
-    DA(c.slot_cell, S + 1); DA(c.slot_m, S + 1); DA(c.slot_first, S + 1); DA(c.slot_cursor, S + 1);
-    DA(c.slot_off, S + 2); DA(c.slot_rowoff, S + 2); DA(c.slot_listoff, S + 2); DA(c.slot_rowbound, S + 1);
-    DA(c.slot_listneed, S + 1); DA(c.slot_nrows, S + 1); DA(c.slot_denseoff, S + 2);
+    DA(c.cell_count, C); DA(c.cell_first, C); DA(c.cell_base, C); DA(c.iv_pos, M); DA(c.flag_scan, M + 64);
+    DA(c.slot_cell, S + 1); DA(c.slot_m, S + 1); DA(c.slot_first, S + 1);
+    DA(c.slot_off, S + 2); DA(c.slot_rowoff, S + 2); DA(c.slot_rowbound, S + 1);
+    DA(c.slot_nrows, S + 1); DA(c.slot_denseoff, S + 2);
     c.class_stride = S + 1;
     DA(c.class_list, MTD_NUM_CLASSES * (S + 1));
     DA(c.csr, M); DA(c.csr_sorted, M);
-    DA(c.scratch_rows, c.cap_scratch_rows); DA(c.lists, c.cap_list); DA(c.rows, c.cap_rows);
+    DA(c.scratch_rows, c.cap_scratch_rows); DA(c.rows, c.cap_rows);
     c.k1_bits_words = k1_bits_words_needed(h->sm_count);
     DA(c.k1_bits, c.k1_bits_words);
     DA(c.win, N); DA(c.succ, c.cap_rows);
@@ -207,7 +210,7 @@ static int create_impl(mtd_handle h)
     }
     DA(h->d_iv_agent, M); DA(h->d_iv_cell, M); DA(h->d_iv_start, M); DA(h->d_iv_end, M); DA(h->d_iv_order, M);
     DA(h->d_mask, N);
-    DA(h->scan_tmp, (std::max(M, S) + 2) / 2048 + 16);
+    DA(h->scan_tmp, 2 * ((std::max(M, S) + 2) / 2048 + 16));
     DA(h->expo_list, 2 * c.cap_expo);
     DA(h->occ, 8);
     // initial state: nobody present
@@ -252,6 +255,7 @@ extern "C" int mtd_destroy(mtd_handle h)
     if (h->state_stream) { cudaStreamSynchronize(h->state_stream); cudaStreamDestroy(h->state_stream); }
     if (h->ev_state) cudaEventDestroy(h->ev_state);
     if (h->ev_main) cudaEventDestroy(h->ev_main);
+    for (void *p : { (void *)h->sc_a1, (void *)h->sc_a2, (void *)h->sc_off, (void *)h->sc_se }) if (p) cudaFree(p);
     for (void *p : h->xchg_peers) cudaIpcCloseMemHandle(p);
     if (h->xchg_alloc) cudaFree(h->xchg_alloc);
     free_tape(h);
@@ -404,6 +408,7 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     DevCtx &c = h->c;
     c.day = *day;
     c.M = M;
+    c.ov_off = nullptr; c.ov_se = nullptr;
     if (mem == MTD_MEM_STAGED) {
         const int sl = h->st_ready;
         if (sl < 0 || h->st_n[sl] != M) { h->err = "MTD_MEM_STAGED without a matching mtd_prefetch_intervals"; return MTD_E_STATE; }
@@ -488,6 +493,53 @@ extern "C" int mtd_simulate_direct_contacts(mtd_handle h, const mtd_day *day, in
         if (r) return r;
     } else h->main_dirty = true;
     CK(cudaGetLastError());
+    return MTD_OK;
+}
+
+template <typename T>
+static int grow_buf(mtd_handle h, T **p, int64_t *cap, int64_t need)
+{
+    if (need <= *cap) return 0;
+    if (*p) cudaFree(*p);
+    *p = nullptr; *cap = 0;
+    void *q = nullptr;
+    const int64_t c = need + need / 2 + 256;
+    cudaError_t e = cudaMalloc(&q, (size_t)c * sizeof(T));
+    if (e != cudaSuccess) { h->err = std::string("cudaMalloc: ") + cudaGetErrorString(e); return MTD_E_CUDA; }
+    *p = (T *)q; *cap = c;
+    return 0;
+}
+
+extern "C" int mtd_set_contacts(mtd_handle h, const mtd_day *day, int32_t cellid, int64_t n_rows, const int32_t *a1,
+                                const int32_t *a2, const int64_t *ov_off, const uint8_t *ov_se, int mem)
+{
+    if (!h || !day || n_rows < 0 || cellid < 0 || cellid >= h->c.n_cells || (n_rows && (!a1 || !a2 || !ov_off || !ov_se))) {
+        if (h) h->err = "mtd_set_contacts: bad arguments"; return MTD_E_ARG; }
+    if (mem != MTD_MEM_HOST) { h->err = "mtd_set_contacts: host buffers only"; return MTD_E_ARG; }
+    if (!(h->have_params && h->have_cells && h->have_static)) { h->err = "params / cells / static not set"; return MTD_E_STATE; }
+    if (n_rows > h->c.cap_rows) { h->err = "mtd_set_contacts: more rows than max_rows"; return MTD_E_CAPACITY; }
+    CK(cudaSetDevice(h->cfg.device));
+    DevCtx &c = h->c;
+    c.day = *day;
+    c.M = 0;
+    const int64_t total = n_rows ? ov_off[n_rows] : 0;
+    int64_t cap2 = h->sc_cap_rows;
+    { int r; if ((r = grow_buf(h, &h->sc_a1, &h->sc_cap_rows, n_rows + 1))) return r;
+      if ((r = grow_buf(h, &h->sc_a2, &cap2, n_rows + 1))) return r;
+      if ((r = grow_buf(h, &h->sc_off, &h->sc_cap_off, n_rows + 2))) return r;
+      if ((r = grow_buf(h, &h->sc_se, &h->sc_cap_se, 2 * total + 2))) return r; }
+    CK(cudaMemsetAsync(c.ctr, 0, sizeof(DevCounters), h->stream));
+    if (n_rows) {
+        CK(cudaMemcpyAsync(h->sc_a1, a1, 4 * (size_t)n_rows, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->sc_a2, a2, 4 * (size_t)n_rows, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->sc_off, ov_off, 8 * (size_t)(n_rows + 1), cudaMemcpyHostToDevice, h->stream));
+        if (total) CK(cudaMemcpyAsync(h->sc_se, ov_se, 2 * (size_t)total, cudaMemcpyHostToDevice, h->stream));
+    }
+    c.ov_off = h->sc_off; c.ov_se = h->sc_se;
+    launch_set_contacts(c, cellid, n_rows, h->sc_a1, h->sc_a2, h->stream);
+    CK(cudaStreamSynchronize(h->stream));          // the host buffers may be released by the caller
+    CK(cudaGetLastError());
+    h->day_ready = true;
     return MTD_OK;
 }
 
@@ -625,9 +677,8 @@ extern "C" int mtd_get_counters(mtd_handle h, mtd_counters *out)
     out->error = d.error;
     if (d.error) {
         char buf[256];
-        snprintf(buf, sizeof(buf), "device error %d (rows needed %llu of %lld scratch / %d of %lld dense, list %llu of %lld)",
-                 d.error, d.row_bound_total, (long long)h->c.cap_scratch_rows, d.n_rows, (long long)h->c.cap_rows,
-                 d.list_total, (long long)h->c.cap_list);
+        snprintf(buf, sizeof(buf), "device error %d (rows needed %llu of %lld scratch / %d of %lld dense)",
+                 d.error, d.row_bound_total, (long long)h->c.cap_scratch_rows, d.n_rows, (long long)h->c.cap_rows);
         h->err = buf;
         return d.error;
     }

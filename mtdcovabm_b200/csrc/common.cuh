@@ -23,7 +23,7 @@ enum { SITE_SELECT = 1, SITE_PAIR = 2, SITE_EXPO = 3, SITE_TRACE = 4 };
 struct DevCounters {
     unsigned long long pairs_evaluated;
     unsigned long long n_potential;
-    unsigned long long list_total;      // total adjacency-list scratch entries requested
+    unsigned long long unused0;
     unsigned long long row_bound_total; // total scratch rows requested
     int n_slots;
     int n_rows;
@@ -81,7 +81,7 @@ struct DevTape {
 // everything a kernel needs, passed by value
 struct DevCtx {
     // capacities
-    int64_t n_agents, n_cells, cap_intervals, cap_rows, cap_scratch_rows, cap_list, cap_expo;
+    int64_t n_agents, n_cells, cap_intervals, cap_rows, cap_scratch_rows, cap_expo;
     // day
     mtd_day day;
     DevTape tape;
@@ -98,17 +98,15 @@ struct DevCtx {
     // K0 products
     int32_t *cell_count;       // [n_cells]
     uint32_t *cell_first;      // [n_cells] emission index of first record
-    int32_t *slot_of_cell;     // [n_cells]
-    int32_t *flag_scan;        // [M+1] scan of "first record of its cell" flags
+    int64_t *cell_base;        // [n_cells] CSR offset of the cell's segment
+    uint16_t *iv_pos;          // [M] position of the record inside its cell segment (arrival order)
+    int32_t *flag_scan;        // [M+64] scanned per-word counts of the "first record of its cell" flags + the flag words
     int32_t *slot_cell;        // [slots]
     int32_t *slot_m;           // [slots]
     uint32_t *slot_first;      // [slots] order key of the cell
-    int32_t *slot_cursor;      // [slots]
     int64_t *slot_off;         // [slots+1] CSR offsets
     int64_t *slot_rowoff;      // [slots+1] scratch-row offsets
-    int64_t *slot_listoff;     // [slots+1] adjacency-list scratch offsets (u16 entries)
     int32_t *slot_rowbound;    // [slots]
-    int64_t *slot_listneed;    // [slots]
     int32_t *slot_nrows;       // [slots] rows produced
     int64_t *slot_denseoff;    // [slots+1]
     int32_t *class_list;       // [MTD_NUM_CLASSES][slots cap]
@@ -116,7 +114,6 @@ struct DevCtx {
     IvRec *csr;                // [M]
     // K1 products
     RowRec *scratch_rows;      // [cap_scratch_rows]
-    uint16_t *lists;           // [cap_list]
     uint32_t *rows12;          // [3 * cap_rows] packed 12-byte rows of the day for the async export (NULL = off)
     uint32_t *k1_bits;         // [k1_bits_words] per-warp adjacency bit matrices of the large-cell K1 (L2-resident scratch)
     int64_t k1_bits_words;
@@ -130,6 +127,9 @@ struct DevCtx {
     StateCounters *sctr;
     const mtd_params *P;       // device copy of the parameters
     IvRec *csr_sorted;         // [M] CSR records in list (emission) order within each cell, written by K1
+    // caller-supplied contacts (mtd_set_contacts): overlap lists per dense row instead of the cell's interval records
+    const int64_t *ov_off;     // [n_rows + 1] or NULL
+    const uint8_t *ov_se;      // [2 * total] start, end per overlap
     const double *logtab;      // [MTD_LOGTAB_N] glibc log(i)
 };
 

@@ -124,7 +124,7 @@ __device__ __forceinline__ void pair_row_bits(const uint16_t *se, uint32_t ivx, 
 #define K1S_THREADS 256
 
 template <int G>
-__global__ void __launch_bounds__(K1S_THREADS) k1_small_kernel(DevCtx g, int cls)
+__global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int cls)
 {
     // per-lane shared slots, indexed [group base + position]
     __shared__ int32_t sh_agent[K1S_THREADS];

@@ -162,6 +162,22 @@ __global__ void __launch_bounds__(K3T_WARPS * 32) k3_trajectory_kernel(DevCtx c,
             if (e >= 0) D.row = c.tape.expo_row + e * MTD_EXPO_W; else D.miss++;
             // sampled_exposed_timestep = np.random.choice(overlapping_timesteps) (epidemiology.py:246)
             ts = (D.row && !isnan(D.row[0])) ? (int)D.row[0] : 0;
+        } else if (c.ov_off) {
+            // contacts handed in by the caller (Epidemiology.simulate_direct_contacts on a dict of overlap lists):
+            // the flattened timestep list is the row's own overlap list (epidemiology.py:171-174)
+            if (lane >= 1 && lane < MTD_EXPO_W) s_row[warp][lane] = philox_slot_draw(c, P, ex, lane);
+            __syncwarp();
+            if (lane == 0) {
+                uint32_t w[4];
+                philox4x32((uint32_t)c.day.day, (uint32_t)ex, 0u, 0u, c.day.seed, SITE_EXPO, w);
+                int idx = (int)__umulhi(w[0], (uint32_t)(r.sed >> 16));
+                for (int64_t k = c.ov_off[i]; k < c.ov_off[i + 1]; k++) {
+                    const int lo = c.ov_se[2 * k], len = (int)c.ov_se[2 * k + 1] - lo + 1;
+                    if (idx < len) { ts = lo + idx; break; }
+                    idx -= len;
+                }
+            }
+            D.row = s_row[warp];
         } else {
             if (lane >= 1 && lane < MTD_EXPO_W) s_row[warp][lane] = philox_slot_draw(c, P, ex, lane);
             // the two agents' intervals in list order: lanes scan the cell's records, ranks by ballot
@@ -477,7 +493,32 @@ __global__ void xchg_wait_kernel(DevExchange x, int par, unsigned long long seq,
     }
 }
 
+// mtd_set_contacts: caller's pairs + overlap lists of ONE cell -> dense rows, one slot
+__global__ void set_contacts_kernel(DevCtx c, int cell, int64_t n, const int32_t *a1, const int32_t *a2)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t k0 = c.ov_off[i], k1 = c.ov_off[i + 1];
+        int dur = 0;
+        for (int64_t k = k0; k < k1; k++) dur += (int)c.ov_se[2 * k + 1] - (int)c.ov_se[2 * k] + 1;      // epidemiology.py:170
+        RowRec r;
+        r.a1 = a1[i]; r.a2 = a2[i]; r.slot = 0;
+        const uint32_t st = k1 > k0 ? c.ov_se[2 * k0] : 0u, en = k1 > k0 ? c.ov_se[2 * (k1 - 1) + 1] : 0u;
+        r.sed = st | (en << 8) | ((uint32_t)dur << 16);
+        c.rows[i] = r;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        c.slot_cell[0] = cell; c.slot_first[0] = 0u; c.slot_m[0] = 0; c.slot_off[0] = 0;
+        c.ctr->n_slots = 1; c.ctr->n_rows = (int)n;
+    }
+}
+
 }  // namespace
+
+int launch_set_contacts(const DevCtx &c, int cell, int64_t n, const int32_t *a1, const int32_t *a2, cudaStream_t st)
+{
+    set_contacts_kernel<<<64, 256, 0, st>>>(c, cell, n, a1, a2);
+    return 1;
+}
 
 int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, bool win_clean, cudaStream_t st, int sm_count)
 {

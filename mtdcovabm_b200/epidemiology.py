@@ -1,8 +1,8 @@
 """Drop-in for the hot-path methods of the reference's `epidemiology.Epidemiology` (epidemiology.py:14-906): same
 constructor; `contact_tracing(day, distributed=False, f=None)` (epidemiology.py:667-834) and
 `contact_tracing_clean_up(day, f=None)` (:838-906) computed through libmtd_b200.so (K5).  The transmission step
-(`simulate_direct_contacts`, :88-231) runs fused behind `ContactNetwork.simulate_contact_network` (K3); there is no
-CPU fallback for any of it.
+(`simulate_direct_contacts`, :88-231) runs fused behind `ContactNetwork.simulate_contact_network` (K3) and can also be
+called on its own with a dict of contacts, like the reference's; there is no CPU fallback for any of it.
 
 Extra keyword arguments (not in the reference): `mode` ("philox" | "replay"), `seed`, `tape`, `device`.
 """
@@ -31,6 +31,7 @@ class Epidemiology:
         self.timestep_options = np.arange(42, 121)          # 7.00 - 20.00 (epidemiology.py:84)
         self.process_index = process_index
         self.mode, self.seed, self.tape, self.device = mode, seed, tape, device
+        self.cn_tape = None            # replay tape of the contact-network stage (set by ContactNetwork)
         self._params = None
 
     @property
@@ -40,10 +41,47 @@ class Epidemiology:
         return self._params
 
     def simulate_direct_contacts(self, agents_directcontacts, cellid, cell_type, day):
-        """epidemiology.py:88-231.  On the B200 path this step is fused behind ContactNetwork.simulate_contact_network
-        (K3 consumes the contact rows K1/K2 left in HBM); a per-cell Python dict of contacts never exists."""
-        raise RuntimeError("simulate_direct_contacts runs fused inside ContactNetwork.simulate_contact_network on the "
-                           "B200 path (mtd_simulate_direct_contacts); call that instead")
+        """epidemiology.py:88-231 -> list of newly exposed agent ids, in the order of the contact dict.
+        The pairs and their overlap lists go to the device as they are (mtd_set_contacts); K3 evaluates them like the
+        rows of the fused day step.  (Inside ContactNetwork.simulate_contact_network the rows never leave HBM.)"""
+        from . import bridge, capi
+        if not agents_directcontacts:
+            return []
+        vu = self.vars_util
+        pairs = list(agents_directcontacts.items())
+        a1 = np.array([int(k[0]) for k, _ in pairs], np.int32)
+        a2 = np.array([int(k[1]) for k, _ in pairs], np.int32)
+        off = np.zeros(len(pairs) + 1, np.int64)
+        se = []
+        for i, (_, ov) in enumerate(pairs):
+            for (s0, e0) in ov:
+                se.append(int(s0)); se.append(int(e0))
+            off[i + 1] = len(se) // 2
+        se = np.array(se, np.uint8)
+        n_agents = int(self.n_locals + self.n_tourists)
+        cellid = int(cellid)
+        ct = np.full(cellid + 1, -1, np.int8); ct[cellid] = int(cell_type)
+        ci = np.full(cellid + 1, -1, np.int16)
+        dense = bridge.flatten(n_agents, self.agents_static, self.agents_epi, vu, np.unique(np.concatenate([a1, a2])))
+        h = bridge.get_handle(n_agents, cellid + 1, 16, self.params, self.device)
+        bridge.upload(h, dense, ct, ci)
+        replay = self.mode == "replay"
+        if replay:
+            if self.cn_tape is None:
+                raise RuntimeError("replay mode needs the reference's draw tape")
+            t = self.cn_tape
+            h.set_tape(t.sel_key, t.sel_off, t.sel_ids, t.pair_k1, t.pair_k2, t.pair_u, t.expo_agent, t.expo_row)
+        dp = self.dyn_params
+        d = h.make_day(capi.MODE_REPLAY if replay else capi.MODE_PHILOX, int(day),
+                       float(dp.masks_hygiene_distancing_multiplier), bool(dp.testing_enabled),
+                       bool(dp.quarantine_enabled), seed=self.seed)
+        h.set_contacts(d, cellid, a1, a2, off, se)
+        h.simulate_direct_contacts(d)
+        h.counters()                                   # raises on device-side errors
+        exposed = [int(a) for a in h.get_exposed()]
+        if exposed:
+            bridge.scatter(h.get_state(), exposed, self.agents_epi, vu)
+        return exposed
 
     # ------------------------------------------------------------------ contact tracing (K5)
     def _residences(self):

@@ -79,6 +79,47 @@ def test_contactnetwork_dropin_replays_reference_day(name, day):
         assert vu.agents_seir_state[int(a)] == post.seir[a]
 
 
+def test_contactnetwork_per_cell_entry_points_replay_reference_day():
+    """simulate_contact_network_by_cellid / generate_contact_network (contactnetwork.py:127-315) cell by cell, in the
+    reference's cell order, rebuild the day's rows the way contactnetwork.py:98-105 does -> the reference's rows,
+    exposures and final state"""
+    from mtdcovabm_b200.contactnetwork import ContactNetwork
+    from mtdcovabm_b200 import util
+    name, day = "ref_1k_seed6", 16
+    z = gio.load_run(name)
+    g = gio.load_day(z, day)
+    epi, vu = reference_containers(g, g.pre)
+    dyn = SimpleNamespace(masks_hygiene_distancing_multiplier=g.mhd, testing_enabled=g.testing_enabled,
+                          quarantine_enabled=g.quarantine_enabled, contact_tracing_enabled=g.contact_tracing_enabled)
+    cells_type = {c: int(t) for c, t in enumerate(g.cell_type) if t >= 0}
+    indids = {c: int(v) for c, v in enumerate(g.cell_indid) if v >= 0}
+    cn = ContactNetwork(g.n_locals, g.N - g.n_locals, 1.0, FakeStatic(g.pre), epi, vu, cells_type, indids, {}, {}, {},
+                        prm.load_json("contactnetwork.json"), prm.load_json(gio.RUNS[name]), dyn, mode="replay",
+                        tape=g.tape)
+    rows, exposed = [], []
+    first = True
+    for cellid in list(vu.cells_agents_timesteps.keys()):
+        if first:                                   # generate_contact_network alone: same dict, nothing transmitted
+            only, ct = cn.generate_contact_network(cellid)
+            first = False
+        if len(rows) % 2:       # alternate the two routes: fused per cell / network first, then transmission on the dict
+            upd, contacts, ct = cn.simulate_contact_network_by_cellid(cellid, g.day)
+        else:
+            contacts, ct = cn.generate_contact_network(cellid)
+            upd = cn.epi_util.simulate_direct_contacts(contacts, cellid, ct, g.day)
+        assert ct == cells_type[cellid]
+        sct = int(util.convert_celltype_to_simcelltype(cellid, celltype=ct))
+        for (a, b), ov in contacts.items():
+            rows.append([sct, a, b, ov[0][0], ov[-1][1]])
+        exposed.extend(upd)
+    assert rows == g.contacts.tolist()
+    assert exposed == g.exposed_ids.tolist() and len(exposed) > 0
+    post = g.post
+    for a in exposed:
+        assert epi[a]["state_transition_by_day"] == [list(mo.unpack_sched(v)) for v in post.sched[a, :post.sched_cnt[a]]]
+        assert vu.agents_seir_state[a] == post.seir[a]
+
+
 def test_update_agent_state_scalar_matches_reference_calls():
     """seirstateutil.update_agent_state, same 7 arguments and return tuple, on calls the reference made"""
     from mtdcovabm_b200 import seirstateutil as ssu
