@@ -68,6 +68,7 @@ typedef struct {
     int32_t contact_tracing_days_back, contact_tracing_positive_delay_days, contact_tracing_secondary_delay_days;
     double tracing_success_prob[4];
     double vacc_immunity, vacc_asymptomatic, vacc_decay_interval;
+    double testing_false_positive_rate, testing_false_negative_rate;   /* epidemiology.py:59-60 */
 } mtd_params;
 
 typedef struct {
@@ -157,6 +158,11 @@ int mtd_exchange_open(mtd_handle h, int peer, const void *ipc_handle);
 int mtd_exchange_ready(mtd_handle h);
 /* K4: daily SEIR advance for every agent with a schedule entry dated `day`; mask (uint8[N]) may be NULL. */
 int mtd_advance_seir(mtd_handle h, int32_t day, const uint8_t *mask, int mem);
+/* Intervention coupling for day loops that do not run the reference's itinerary stage (tiled configurations, SURVEY.md
+ * section 8f rank 1; the stage's quarantine / hospital / deceased handling is itinerary.py:2283-2528): when on, K0
+ * drops every interval of an agent who today is deceased, inside its quarantine window or inside its hospitalisation
+ * window, unless the interval is in the agent's residence cell. */
+int mtd_set_intervention_mask(mtd_handle h, int on);
 
 /* results of the last day step */
 int mtd_get_counters(mtd_handle h, mtd_counters *out);           /* synchronises the stream */
@@ -187,6 +193,13 @@ int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_trace_tape *
                         const int32_t *traced, int64_t n_slices, const int64_t *slice_off, const int32_t *rows3,
                         const uint8_t *epi_present, int mem);
 int mtd_get_traced(mtd_handle h, uint8_t *primary, uint8_t *secondary, mtd_trace_stats *stats, int mem);
+/* K6: test-result processing of the itinerary stage (itinerary.py:2301-2332) over all
+ * agents (epi_present: optional u8[N], agents without an epi record are skipped): results due today flag the agent
+ * positive (false-negative / false-positive rates of epidemiology.py:59-60), positive agents get a Positive quarantine
+ * (epidemiology.py:568-625) and are returned, ascending, as the day's contact_tracing_agent_ids -- the `traced` input
+ * of mtd_contact_tracing; result days in the past are cleared.  Philox draws keyed (day, agent). */
+int mtd_process_test_results(mtd_handle h, const mtd_day *day, const uint8_t *epi_present, int32_t *traced_ids,
+                             int64_t cap, int64_t *n, int mem);
 
 /* ---- pipelined boundary (the day loop of sim.py:1392-2125 driven from host memory without stalling the device) ----
  * The reference hands the stage host containers and gets host containers back (contactnetwork.py:65-124).  These three

@@ -25,7 +25,8 @@ EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mt
            "mtd_get_contacts", "mtd_get_exposed", "mtd_get_infection_prob", "mtd_occupancy", "mtd_sync",
            "mtd_set_profiling", "mtd_get_stage_ms", "mtd_set_export", "mtd_prefetch_intervals",
            "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced",
-           "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts"]
+           "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts", "mtd_set_intervention_mask",
+           "mtd_process_test_results"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
 
 
@@ -216,6 +217,10 @@ class Handle:
     def exchange_ready(self):
         self._ck(self.lib.mtd_exchange_ready(self.h), "mtd_exchange_ready")
 
+    def set_intervention_mask(self, on=True):
+        """K0 keeps deceased / quarantined / hospitalised agents in their residence cell only"""
+        self._ck(self.lib.mtd_set_intervention_mask(self.h, int(on)), "mtd_set_intervention_mask")
+
     def advance_seir(self, day, mask=None, mem=MEM_HOST):
         self._ck(self.lib.mtd_advance_seir(self.h, C.c_int32(day), _ptr(mask), mem), "mtd_advance_seir")
 
@@ -263,6 +268,16 @@ class Handle:
                                               C.c_int64(len(traced)), _ptr(traced), C.c_int64(len(slice_off) - 1),
                                               _ptr(slice_off), _ptr(rows3), _ptr(epi_present), mem),
                  "mtd_contact_tracing")
+
+    def process_test_results(self, day: Day, epi_present=None):
+        """K6 (itinerary.py:2301-2332) -> ascending ids of the agents added to contact_tracing_agent_ids today"""
+        ids = np.zeros(self.n_agents, np.int32)
+        n = C.c_int64(0)
+        if epi_present is not None:
+            epi_present = np.ascontiguousarray(epi_present, np.uint8)
+        self._ck(self.lib.mtd_process_test_results(self.h, C.byref(day), _ptr(epi_present), _ptr(ids), C.c_int64(len(ids)),
+                                                   C.byref(n), MEM_HOST), "mtd_process_test_results")
+        return ids[:n.value].copy()
 
     def get_traced(self):
         """-> (primary flags uint8[N], secondary flags uint8[N], TraceStats)"""

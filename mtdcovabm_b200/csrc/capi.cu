@@ -47,6 +47,7 @@ struct mtd_handle_s {
     // caller-supplied contacts (mtd_set_contacts), device copies
     int32_t *sc_a1 = nullptr, *sc_a2 = nullptr; int64_t sc_cap_rows = 0; int64_t *sc_off = nullptr; int64_t sc_cap_off = 0;
     uint8_t *sc_se = nullptr; int64_t sc_cap_se = 0;
+    uint8_t *agent_masked = nullptr; bool mask_on = false;
     int sm_count = 148;
     std::string err;
     std::vector<void *> allocs;
@@ -409,6 +410,8 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     c.day = *day;
     c.M = M;
     c.ov_off = nullptr; c.ov_se = nullptr;
+    c.agent_masked = h->mask_on ? h->agent_masked : nullptr;
+    if (h->mask_on) TOUCH();                 // K0 reads today's state (after K4 of today and the apply of yesterday)
     if (mem == MTD_MEM_STAGED) {
         const int sl = h->st_ready;
         if (sl < 0 || h->st_n[sl] != M) { h->err = "MTD_MEM_STAGED without a matching mtd_prefetch_intervals"; return MTD_E_STATE; }
@@ -549,6 +552,15 @@ extern "C" int mtd_apply_deltas(mtd_handle h, const int32_t *bufs, int64_t n_buf
     CK(cudaSetDevice(h->cfg.device));
     { int r = enqueue_apply(h, bufs, (int)n_bufs, cap, true, false, 0); if (r) return r; }
     CK(cudaGetLastError());
+    return MTD_OK;
+}
+
+extern "C" int mtd_set_intervention_mask(mtd_handle h, int on)
+{
+    if (!h) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    if (on && !h->agent_masked) DA(h->agent_masked, h->c.n_agents);
+    h->mask_on = on != 0;
     return MTD_OK;
 }
 
@@ -882,6 +894,38 @@ extern "C" int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_t
     t.res_first = h->res_first; t.res_k = h->res_k; t.sel = h->trace_sel; t.sec_owner = h->sec_owner;
     t.stats = h->trace_scalars;
     launch_k5(t, h->trace_flagscan, h->trace_scan_tmp, h->stream, h->sm_count);
+    CK(cudaGetLastError());
+    return MTD_OK;
+}
+
+int launch_k6(const DevCtx &c, const uint8_t *epi_present, uint8_t *positive, int32_t *flag_scan, long long *scan_tmp,
+              int32_t *ids, int64_t cap, int32_t *n_out, cudaStream_t st, int sm_count);
+
+extern "C" int mtd_process_test_results(mtd_handle h, const mtd_day *day, const uint8_t *epi_present, int32_t *traced_ids,
+                                        int64_t cap, int64_t *n, int mem)
+{
+    if (!h || !day || !n || cap < 0 || (cap && !traced_ids)) { if (h) h->err = "mtd_process_test_results: bad arguments"; return MTD_E_ARG; }
+    if (!h->have_params) { h->err = "mtd_process_test_results: params not set"; return MTD_E_STATE; }
+    CK(cudaSetDevice(h->cfg.device));
+    TOUCH();
+    { int r = trace_scratch(h); if (r) return r; }
+    h->c.day = *day;
+    const size_t N = (size_t)h->c.n_agents;
+    const uint8_t *present = epi_present;
+    if (epi_present && mem == MTD_MEM_HOST) {
+        CK(cudaMemcpyAsync(h->d_epi_present, epi_present, N, cudaMemcpyHostToDevice, h->stream));
+        present = h->d_epi_present;
+    }
+    { int r = regrow(h, &h->d_traced, &h->cap_traced, (int64_t)N); if (r) return r; }
+    launch_k6(h->c, present, h->is_traced, h->trace_flagscan, h->trace_scan_tmp, h->d_traced, (int64_t)N, h->trace_scalars + 12,
+              h->stream, h->sm_count);
+    int32_t cnt = 0;
+    CK(cudaMemcpyAsync(&cnt, h->trace_scalars + 12, sizeof(cnt), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    *n = cnt;
+    if (cnt > cap) { h->err = "mtd_process_test_results: cap too small"; return MTD_E_CAPACITY; }
+    if (cnt) CK(cudaMemcpyAsync(traced_ids, h->d_traced, 4 * (size_t)cnt, kind_out(mem), h->stream));
+    CK(cudaStreamSynchronize(h->stream));
     CK(cudaGetLastError());
     return MTD_OK;
 }

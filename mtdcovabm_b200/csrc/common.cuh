@@ -127,6 +127,8 @@ struct DevCtx {
     StateCounters *sctr;
     const mtd_params *P;       // device copy of the parameters
     IvRec *csr_sorted;         // [M] CSR records in list (emission) order within each cell, written by K1
+    // intervention mask (mtd_set_intervention_mask): per-agent "stays in the residence cell today" flag, or NULL = off
+    uint8_t *agent_masked;
     // caller-supplied contacts (mtd_set_contacts): overlap lists per dense row instead of the cell's interval records
     const int64_t *ov_off;     // [n_rows + 1] or NULL
     const uint8_t *ov_se;      // [2 * total] start, end per overlap

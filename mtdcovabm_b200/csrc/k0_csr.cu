@@ -14,11 +14,31 @@
 
 __device__ __forceinline__ uint32_t order_of(const DevCtx &c, int64_t i) { return c.iv_order ? c.iv_order[i] : (uint32_t)i; }
 
+// Intervention coupling of the tiled configurations (the itinerary stage's quarantine /
+// hospital / deceased handling, itinerary.py:2283-2528, at day granularity): an agent who is deceased, inside a
+// quarantine window or inside a hospitalisation window keeps only the intervals in its residence cell.
+__global__ void k0_agent_mask_kernel(DevCtx c)
+{
+    const int day = c.day.day;
+    for (int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; a < c.n_agents; a += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t *q = c.quarantine + 3 * a, *h = c.hosp + 3 * a;
+        bool m = c.seir[a] == S_DEC;
+        const int q0 = q[0], h0 = h[0];
+        if (q0 != MTD_NONE && q0 <= day && day <= q[2]) m = true;
+        if (h0 != MTD_NONE && h0 <= day && day <= h[2]) m = true;
+        c.agent_masked[a] = m;
+    }
+}
+
 __global__ void k0_hist_kernel(DevCtx c)
 {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < c.M; i += (int64_t)gridDim.x * blockDim.x) {
         int cell = c.iv_cell[i];
         if (cell < 0 || cell >= c.n_cells) { c.ctr->error = MTD_E_ARG; c.iv_pos[i] = 0xffffu; continue; }
+        if (c.agent_masked) {
+            const int ag = c.iv_agent[i];
+            if (c.agent_masked[ag] && cell != c.res_cellid[ag]) { c.iv_pos[i] = 0xffffu; continue; }     // dropped
+        }
         const int pos = atomicAdd(&c.cell_count[cell], 1);
         c.iv_pos[i] = (uint16_t)(pos < 0xffff ? pos : 0xffff);         // cells beyond MTD_MAX_CELL_INTERVALS are rejected in assign
         atomicMin(&c.cell_first[cell], order_of(c, i));
@@ -33,7 +53,7 @@ __global__ void k0_flags_kernel(DevCtx c, uint32_t *words, int32_t *cnt)
         bool f = false;
         if (i < c.M) {
             int cell = c.iv_cell[i];
-            if (cell >= 0 && cell < c.n_cells) f = (c.cell_first[cell] == order_of(c, i));
+            if (cell >= 0 && cell < c.n_cells && c.iv_pos[i] != 0xffffu) f = (c.cell_first[cell] == order_of(c, i));
         }
         const uint32_t w = __ballot_sync(FULLMASK, f);
         if ((threadIdx.x & 31) == 0) { words[i >> 5] = w; cnt[i >> 5] = __popc(w); }
@@ -208,6 +228,8 @@ int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_coun
     const int64_t n_words = (c.M + 31) >> 5;
     int32_t *word_cnt = c.flag_scan;                                  // [n_words + 1], scanned in place
     uint32_t *words = (uint32_t *)(c.flag_scan + n_words + 2);        // [n_words]
+    int extra = 0;
+    if (c.agent_masked) { k0_agent_mask_kernel<<<sm_count * 8, threads, 0, st>>>(c); extra = 1; }
     k0_hist_kernel<<<grid, threads, 0, st>>>(c);
     k0_flags_kernel<<<grid, threads, 0, st>>>(c, words, word_cnt);
     int n = 2 + device_scan<int32_t, int32_t>(word_cnt, word_cnt, n_words, nullptr, scan_tmp, st);
@@ -220,7 +242,7 @@ int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_coun
                                                              &c.ctr->n_slots, scan_tmp);
     k0_finish_kernel<<<sm_count * 4, threads, 0, st>>>(c);
     k0_scatter_kernel<<<grid, threads, 0, st>>>(c);
-    return n + 6;
+    return n + 6 + extra;
 }
 
 int launch_scan_nrows(const DevCtx &c, long long *scan_tmp, cudaStream_t st)

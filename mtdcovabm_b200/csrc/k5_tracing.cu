@@ -257,7 +257,59 @@ __global__ void k5_count_kernel(TraceCtx c)
     if ((threadIdx.x & 31) == 0 && (np | ns)) { atomicAdd(&c.stats[ST_PRIM], np); atomicAdd(&c.stats[ST_SEC], ns); }
 }
 
+// K6 -- test-result processing of the itinerary stage (itinerary.py:2301-2332), one thread per agent: a result due
+// today flags the agent positive unless a false negative (Exposed / Infectious) or only on a false positive (everybody
+// else); a positive agent joins contact_tracing_agent_ids and gets a Positive quarantine (schedule_quarantine,
+// epidemiology.py:568-625); a result day in the past is cleared.  Draws: Philox keyed (day, agent), site 6.
+__global__ void k6_test_results_kernel(DevCtx c, const uint8_t *epi_present, uint8_t *positive)
+{
+    const mtd_params *P = c.P;
+    const int day = c.day.day;
+    for (int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; a < c.n_agents; a += (int64_t)gridDim.x * blockDim.x) {
+        positive[a] = 0;
+        if (epi_present && !epi_present[a]) continue;
+        int32_t *tr = c.test_result_day + 2 * a;
+        const int trd = tr[0];
+        if (trd == MTD_NONE) continue;
+        if (day == trd) {
+            const int ts = tr[1];
+            uint32_t w[4];
+            philox4x32((uint32_t)day, (uint32_t)a, 0u, 0u, c.day.seed, 6u, w);
+            const double u = u53(w[0], w[1]), u2 = u53(w[2], w[3]);
+            const int st = c.seir[a];
+            const bool pos = (st == S_EXP || st == S_INF) ? !(u < P->testing_false_negative_rate)
+                                                           : (u < P->testing_false_positive_rate);
+            if (!pos) continue;
+            positive[a] = 1;
+            if (!c.day.quarantine_enabled) continue;
+            if (u2 < P->ignore_quarantine_rules_probability) continue;
+            int32_t *q = c.quarantine + 3 * a;
+            const int start = day, end = day + P->quarantine_positive_duration;
+            if (q[0] != MTD_NONE && start >= q[0]) continue;            // epidemiology.py:606-611
+            q[0] = start; q[1] = ts; q[2] = end;
+        } else if (day > trd) { tr[0] = MTD_NONE; tr[1] = MTD_NONE; }
+    }
+}
+
+// flagged agents -> ascending id list (flag scan + compaction), count to n_out
+__global__ void k6_compact_kernel(int64_t n_agents, const uint8_t *positive, const int32_t *excl, int32_t *ids, int64_t cap,
+                                  int32_t *n_out)
+{
+    for (int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; a < n_agents; a += (int64_t)gridDim.x * blockDim.x)
+        if (positive[a] && excl[a] < cap) ids[excl[a]] = (int32_t)a;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *n_out = excl[n_agents];
+}
+
 }  // namespace
+
+int launch_k6(const DevCtx &c, const uint8_t *epi_present, uint8_t *positive, int32_t *flag_scan, long long *scan_tmp,
+              int32_t *ids, int64_t cap, int32_t *n_out, cudaStream_t st, int sm_count)
+{
+    k6_test_results_kernel<<<sm_count * 8, 256, 0, st>>>(c, epi_present, positive);
+    int n = 1 + device_scan<uint8_t, int32_t>(positive, flag_scan, c.n_agents, nullptr, scan_tmp, st);
+    k6_compact_kernel<<<sm_count * 8, 256, 0, st>>>(c.n_agents, positive, flag_scan, ids, cap, n_out);
+    return n + 1;
+}
 
 int launch_k5(const TraceCtx &c, int32_t *flag_scan, long long *scan_tmp, cudaStream_t st, int sm_count)
 {

@@ -39,6 +39,7 @@ class ParamsStruct(C.Structure):
         ("contact_tracing_secondary_delay_days", C.c_int32),
         ("tracing_success_prob", C.c_double * 4),
         ("vacc_immunity", C.c_double), ("vacc_asymptomatic", C.c_double), ("vacc_decay_interval", C.c_double),
+        ("testing_false_positive_rate", C.c_double), ("testing_false_negative_rate", C.c_double),
     ]
 
 
@@ -90,4 +91,6 @@ def build_params(contactnetworkparams=None, epidemiologyparams=None) -> ParamsSt
         P.tracing_success_prob[i] = v
     v = ep["vaccination_effectiveness_parameters"]
     P.vacc_immunity, P.vacc_asymptomatic, P.vacc_decay_interval = float(v[0]), float(v[1]), float(v[2])
+    fp, fn = ep["testing_false_positive_negative_rates"]                    # epidemiology.py:59-60
+    P.testing_false_positive_rate, P.testing_false_negative_rate = float(fp), float(fn)
     return P

@@ -655,6 +655,61 @@ int64_t mtdo_transmission(const mtdo_params *P, const mtdo_dayctx *D, int64_t M,
 }
 
 /* ------------------------------------------------------------------ seirstateutil.update_agent_state (seirstateutil.py:38-72) */
+/* Test-result processing of the itinerary stage (itinerary.py:2301-2332): an agent whose test result is due today is
+ * flagged positive unless a false negative (Exposed / Infectious) or only on a false positive (everybody else); a
+ * positive agent enters contact_tracing_agent_ids and gets a Positive quarantine (schedule_quarantine,
+ * epidemiology.py:568-625); a result day in the past is cleared.  Philox draws keyed (day, agent, slot), site 6.
+ * positive[a] = 1 for the agents added to contact_tracing_agent_ids.  Returns their number. */
+int64_t mtdo_process_test_results(const mtdo_params *P, const mtdo_dayctx *D, mtdo_agents *A, const uint8_t *epi_present,
+                                  uint8_t *positive)
+{
+    int64_t n = 0;
+    for (int64_t a = 0; a < A->n_agents; a++) {
+        positive[a] = 0;
+        if (epi_present && !epi_present[a]) continue;
+        int32_t *tr = A->test_result_day + 2 * a;
+        if (tr[0] == MTDO_NONE) continue;
+        if (D->day == tr[0]) {
+            const int ts = tr[1];
+            uint32_t ctr[4] = { (uint32_t)D->day, (uint32_t)a, 0u, 0u }, key[2] = { D->seed, 6u }, w[4];
+            mtdo_philox4x32(ctr, key, w);
+            const double u = mtdo_u53(w[0], w[1]), u2 = mtdo_u53(w[2], w[3]);
+            int pos;
+            if (A->seir[a] == S_EXP || A->seir[a] == S_INF) pos = !(u < P->testing_false_negative_rate);
+            else pos = (u < P->testing_false_positive_rate);
+            if (!pos) continue;
+            positive[a] = 1; n++;
+            if (!D->quarantine_enabled) continue;
+            if (u2 < P->ignore_quarantine_rules_probability) continue;
+            int32_t *q = A->quarantine + 3 * a;
+            const int start = D->day, end = D->day + P->quarantine_positive_duration;
+            if (q[0] != MTDO_NONE && start >= q[0]) continue;       /* epidemiology.py:606-611 */
+            q[0] = start; q[1] = ts; q[2] = end;
+        } else if (D->day > tr[0]) { tr[0] = MTDO_NONE; tr[1] = MTDO_NONE; }
+    }
+    return n;
+}
+
+/* Intervention coupling of the tiled configurations: the itinerary stage keeps agents
+ * who are deceased, inside a quarantine window or inside a hospitalisation window out of every cell but their residence
+ * (itinerary.py:2283-2528 works at timestep granularity; here the whole day is dropped).  keep[i] = 1 if interval i
+ * stays in the day's stream.  Returns the number of kept intervals. */
+int64_t mtdo_mask_intervals(int32_t day, int64_t M, const int32_t *iv_agent, const int32_t *iv_cell, const mtdo_agents *A,
+                            uint8_t *keep)
+{
+    int64_t n = 0;
+    for (int64_t i = 0; i < M; i++) {
+        const int32_t a = iv_agent[i];
+        const int32_t *q = A->quarantine + 3 * (int64_t)a, *h = A->hosp + 3 * (int64_t)a;
+        int masked = A->seir[a] == S_DEC;
+        if (q[0] != MTDO_NONE && q[0] <= day && day <= q[2]) masked = 1;
+        if (h[0] != MTDO_NONE && h[0] <= day && day <= h[2]) masked = 1;
+        keep[i] = !(masked && iv_cell[i] != A->res_cellid[a]);
+        n += keep[i];
+    }
+    return n;
+}
+
 int64_t mtdo_advance(int32_t day, mtdo_agents *A, const uint8_t *mask)
 {
     int64_t fired = 0;

@@ -222,6 +222,29 @@ def advance(day, agents: AgentState, mask=None):
     return lib().mtdo_advance(C.c_int32(day), C.byref(a), _p(mask))
 
 
+def process_test_results(params, ctx, agents: AgentState, epi_present=None):
+    """itinerary.py:2301-2332 over all agents -> ids added to contact_tracing_agent_ids (ascending)"""
+    a = agents.struct()
+    pos = np.zeros(agents.n, np.uint8)
+    if epi_present is not None:
+        epi_present = np.ascontiguousarray(epi_present, np.uint8)
+    L = lib()
+    L.mtdo_process_test_results.restype = C.c_int64
+    L.mtdo_process_test_results(C.byref(params), C.byref(ctx), C.byref(a), _p(epi_present), _p(pos))
+    return np.nonzero(pos)[0].astype(np.int32)
+
+
+def mask_intervals(day, iv_agent, iv_cell, agents: AgentState):
+    """keep flags of the day's intervals under the intervention mask (deceased / quarantined / hospitalised agents stay
+    in their residence cell only)"""
+    a = agents.struct()
+    keep = np.zeros(len(iv_agent), np.uint8)
+    L = lib()
+    L.mtdo_mask_intervals.restype = C.c_int64
+    L.mtdo_mask_intervals(C.c_int32(day), C.c_int64(len(iv_agent)), _p(iv_agent), _p(iv_cell), C.byref(a), _p(keep))
+    return keep.astype(bool)
+
+
 # ---------------------------------------------------------------------------------- contact tracing
 class TraceTape(C.Structure):
     _fields_ = [("n_scan", C.c_int64), ("scan_key", C.c_void_p), ("scan_u", C.c_void_p),

@@ -235,3 +235,92 @@ def test_pipelined_host_boundary_matches_synchronous_api():
         assert np.array_equal(o12, occ) and p12 == pairs
     for f in H.STATE_FIELDS:
         assert np.array_equal(final0[f], final1[f]), f
+
+
+def test_intervention_mask_matches_oracle():
+    """K0's intervention mask (deceased / quarantined / hospitalised agents keep only their residence-cell intervals;
+    SURVEY.md section 8f rank 1) == the oracle run on the stream filtered by mtdo_mask_intervals"""
+    P = prm.build_params()
+    g = gio.load_day(gio.load_run("ref_1k_seed6"), 16)
+    s = H.tile_day(g, 6, agent_major=True, seed=4, infectious_frac=0.05)
+    st = s["state"]
+    rng = np.random.default_rng(8)
+    ids = np.unique(s["iv_agent"])
+    day = 20
+    pick = rng.choice(ids, size=len(ids) // 4, replace=False)
+    q, hsp, dec, edge = np.array_split(pick, 4)
+    st.quarantine[q] = np.stack([np.full(len(q), day - 2), np.full(len(q), 50), np.full(len(q), day + 3)], 1)
+    st.hosp[hsp] = np.stack([np.full(len(hsp), day), np.full(len(hsp), 60), np.full(len(hsp), day)], 1)
+    st.seir[dec] = 5
+    st.quarantine[edge] = np.stack([np.full(len(edge), day + 1), np.full(len(edge), 50), np.full(len(edge), day + 9)], 1)  # not yet
+    keep = mo.mask_intervals(day, s["iv_agent"], s["iv_cell"], st)
+    assert 0 < keep.sum() < len(keep)
+    assert keep[np.isin(s["iv_agent"], edge)].all()
+
+    h = H.make_handle(P, st, s["cell_type"], s["cell_indid"], len(s["iv_cell"]))
+    h.set_intervention_mask(True)
+    d = h.make_day(capi.MODE_PHILOX, day, 0.1, True, True, seed=9)
+    h.simulate_contact_network(d, s["iv_agent"], s["iv_cell"], s["iv_start"], s["iv_end"])
+    h.simulate_direct_contacts(d)
+    c = h.counters()
+    assert c.error == 0
+    grow, gdur, gcell = h.get_contacts()
+
+    ost = st.copy()
+    ctx = mo.make_ctx(mo.MODE_PHILOX, day, 0.1, True, True, seed=9)
+    f = [np.ascontiguousarray(s[k][keep]) for k in ("iv_cell", "iv_agent", "iv_start", "iv_end")]
+    orow, odur, orc, s1 = mo.contact_network(P, ctx, f[0], f[1], f[2], f[3], s["cell_type"], s["cell_indid"], ost)
+    oexp, _, _ = mo.transmission(P, ctx, f[0], f[1], f[2], f[3], s["cell_type"], orow, odur, orc, ost)
+    assert np.array_equal(grow, orow) and np.array_equal(gdur, odur) and np.array_equal(gcell, orc)
+    assert c.pairs_evaluated == s1.pairs_evaluated
+    assert np.array_equal(h.get_exposed(), oexp)
+    assert H.state_diff(h.get_state(), ost) == []
+    # masked agents meet nobody outside their residence cell
+    masked = np.concatenate([q, hsp, dec])
+    res = st.res_cellid
+    for col in (1, 2):
+        m = np.isin(grow[:, col], masked)
+        assert np.all(gcell[m] == res[grow[m, col]])
+    h.set_intervention_mask(False)
+    h.close()
+
+
+@pytest.mark.parametrize("quarantine_enabled", [True, False])
+def test_test_result_processing_matches_oracle(quarantine_enabled):
+    """K6 (itinerary.py:2301-2332): positives, Positive quarantines and cleared result days == oracle, bit for bit"""
+    P = prm.build_params(None, prm.load_json("epidemiology_strict_days.json"))
+    n, day = 40_000, 23
+    rng = np.random.default_rng(12)
+    st = mo.AgentState(n)
+    st.seir[:] = rng.integers(0, 6, n)
+    due = rng.random(n) < 0.3
+    st.test_result_day[due, 0] = day
+    st.test_result_day[due, 1] = rng.integers(42, 121, due.sum())
+    past = ~due & (rng.random(n) < 0.2)
+    st.test_result_day[past, 0] = day - rng.integers(1, 5, past.sum()); st.test_result_day[past, 1] = 77
+    future = ~due & ~past & (rng.random(n) < 0.2)
+    st.test_result_day[future, 0] = day + 2; st.test_result_day[future, 1] = 50
+    hasq = rng.random(n) < 0.3                         # existing quarantines: earlier start blocks, later start is replaced
+    st.quarantine[hasq, 0] = day + rng.integers(-3, 4, hasq.sum()); st.quarantine[hasq, 1] = 60
+    st.quarantine[hasq, 2] = st.quarantine[hasq, 0] + 10
+    present = (rng.random(n) < 0.95).astype(np.uint8)
+    h = capi.Handle(n, 1, 16)
+    h.set_params(P)
+    H.upload_state(h, st)
+    d = h.make_day(capi.MODE_PHILOX, day, 0.0, True, quarantine_enabled, seed=21)
+    got = h.process_test_results(d, present)
+    ost = st.copy()
+    ctx = mo.make_ctx(mo.MODE_PHILOX, day, 0.0, True, quarantine_enabled, seed=21)
+    exp = mo.process_test_results(P, ctx, ost, present)
+    assert len(exp) > 100 and np.array_equal(got, exp)
+    assert H.state_diff(h.get_state(), ost) == []
+    # rates: ~ (1 - false negative) of the due Exposed/Infectious, ~ false positive of the others
+    ei = due & (present == 1) & np.isin(st.seir, (2, 3))
+    oth = due & (present == 1) & ~np.isin(st.seir, (2, 3))
+    flag = np.zeros(n, bool); flag[got] = True
+    assert abs(flag[ei].mean() - (1 - P.testing_false_negative_rate)) < 0.03
+    assert abs(flag[oth].mean() - P.testing_false_positive_rate) < 0.02
+    assert not flag[~due].any()
+    if not quarantine_enabled:
+        assert np.array_equal(ost.quarantine, st.quarantine)
+    h.close()
