@@ -164,6 +164,24 @@ int mtd_advance_seir(mtd_handle h, int32_t day, const uint8_t *mask, int mem);
  * window, unless the interval is in the agent's residence cell. */
 int mtd_set_intervention_mask(mtd_handle h, int on);
 
+/* K7: vaccination.
+ *   mtd_enable_vaccination     allocate the per-agent [day, timestep] vaccination record (agent["vaccination_days"][-1],
+ *                              epidemiology.py:961-967); locals are the ids [0, n_locals).  From then on
+ *                              mtd_advance_seir also does the dose bookkeeping of the vaccination day
+ *                              (itinerary.py:2489-2527): record dated today -> last_dose_day = today
+ *                              (agents_vaccination_doses[a].append(day)); record dated in the past -> cleared.
+ *   mtd_schedule_vaccinations  Epidemiology.schedule_vaccinations (epidemiology.py:911-976), device part: k =
+ *                              dyn_params.num_vaccinations_today locals without a dose are drawn without replacement
+ *                              (the k smallest of unique Philox keys, radix select) and get [day + 1, timestep in
+ *                              42..120].  Replay mode: the reference's own sample (ids + timesteps).  selected: optional
+ *                              u8[N] flags of the agents scheduled by this call; n_selected: their number.
+ *   mtd_set_vaccination / mtd_get_vaccination   last_dose_day i32[N] and the records i32[N][2] (MTD_NONE = none). */
+int mtd_enable_vaccination(mtd_handle h, int64_t n_locals);
+int mtd_schedule_vaccinations(mtd_handle h, const mtd_day *day, int64_t k, int64_t n_replay, const int32_t *replay_ids,
+                              const int32_t *replay_ts, uint8_t *selected, int64_t *n_selected, int mem);
+int mtd_set_vaccination(mtd_handle h, int64_t n, const int32_t *last_dose_day, const int32_t *vacc_day, int mem);
+int mtd_get_vaccination(mtd_handle h, int64_t n, int32_t *last_dose_day, int32_t *vacc_day, int mem);
+
 /* results of the last day step */
 int mtd_get_counters(mtd_handle h, mtd_counters *out);           /* synchronises the stream */
 int mtd_get_contacts(mtd_handle h, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap, int64_t *n,

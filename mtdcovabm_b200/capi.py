@@ -26,7 +26,8 @@ EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mt
            "mtd_set_profiling", "mtd_get_stage_ms", "mtd_set_export", "mtd_prefetch_intervals",
            "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced",
            "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts", "mtd_set_intervention_mask",
-           "mtd_process_test_results"]
+           "mtd_process_test_results", "mtd_enable_vaccination", "mtd_schedule_vaccinations", "mtd_set_vaccination",
+           "mtd_get_vaccination"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
 
 
@@ -216,6 +217,35 @@ class Handle:
 
     def exchange_ready(self):
         self._ck(self.lib.mtd_exchange_ready(self.h), "mtd_exchange_ready")
+
+    # ---- K7 vaccination
+    def enable_vaccination(self, n_locals):
+        self._ck(self.lib.mtd_enable_vaccination(self.h, C.c_int64(n_locals)), "mtd_enable_vaccination")
+
+    def schedule_vaccinations(self, day: Day, k, replay_ids=None, replay_ts=None):
+        """epidemiology.py:911-976 (device part) -> ascending ids of the agents scheduled for day + 1"""
+        sel = np.zeros(self.n_agents, np.uint8)
+        n = C.c_int64(0)
+        nr = 0 if replay_ids is None else len(replay_ids)
+        if nr:
+            replay_ids = np.ascontiguousarray(replay_ids, np.int32); replay_ts = np.ascontiguousarray(replay_ts, np.int32)
+        self._ck(self.lib.mtd_schedule_vaccinations(self.h, C.byref(day), C.c_int64(k), C.c_int64(nr), _ptr(replay_ids),
+                                                    _ptr(replay_ts), _ptr(sel), C.byref(n), MEM_HOST),
+                 "mtd_schedule_vaccinations")
+        ids = np.nonzero(sel)[0].astype(np.int32)
+        assert len(ids) == n.value or nr
+        return ids
+
+    def set_vaccination(self, last_dose_day=None, vacc_day=None):
+        self._ck(self.lib.mtd_set_vaccination(self.h, C.c_int64(self.n_agents), _ptr(last_dose_day), _ptr(vacc_day), MEM_HOST),
+                 "mtd_set_vaccination")
+
+    def get_vaccination(self, with_records=True):
+        ld = np.zeros(self.n_agents, np.int32)
+        vd = np.zeros((self.n_agents, 2), np.int32) if with_records else None
+        self._ck(self.lib.mtd_get_vaccination(self.h, C.c_int64(self.n_agents), _ptr(ld), _ptr(vd), MEM_HOST),
+                 "mtd_get_vaccination")
+        return ld, vd
 
     def set_intervention_mask(self, on=True):
         """K0 keeps deceased / quarantined / hospitalised agents in their residence cell only"""

@@ -19,6 +19,11 @@ int launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t ca
                     unsigned long long *expo_list, cudaStream_t st, int sm_count);
 int launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count);
 int launch_set_contacts(const DevCtx &c, int cell, int64_t n, const int32_t *a1, const int32_t *a2, cudaStream_t st);
+int launch_k7_schedule(const DevCtx &c, int64_t n_locals, long long k, int32_t *vacc_day, uint8_t *selected, void *scratch,
+                       unsigned int *hist, cudaStream_t st, int sm_count);
+int launch_k7_replay(const DevCtx &c, int64_t n, const int32_t *ids, const int32_t *ts, int32_t *vacc_day, uint8_t *selected,
+                     void *scratch, cudaStream_t st);
+int launch_k7_dose(const DevCtx &c, int day, int64_t n_locals, int32_t *vacc_day, cudaStream_t st, int sm_count);
 int launch_xchg_push(const DevExchange &x, int par, unsigned long long seq, cudaStream_t st);
 int launch_xchg_wait(const DevExchange &x, int par, unsigned long long seq, StateCounters *sctr, cudaStream_t st);
 int launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st, int sm_count);
@@ -48,6 +53,9 @@ struct mtd_handle_s {
     int32_t *sc_a1 = nullptr, *sc_a2 = nullptr; int64_t sc_cap_rows = 0; int64_t *sc_off = nullptr; int64_t sc_cap_off = 0;
     uint8_t *sc_se = nullptr; int64_t sc_cap_se = 0;
     uint8_t *agent_masked = nullptr; bool mask_on = false;
+    // K7 vaccination (allocated by mtd_enable_vaccination)
+    int32_t *vacc_day = nullptr; uint8_t *vacc_selected = nullptr; void *vacc_scratch = nullptr; unsigned int *vacc_hist = nullptr;
+    int64_t vacc_n_locals = 0; int32_t *vacc_ids = nullptr, *vacc_ts = nullptr; int64_t vacc_cap_ids = 0, vacc_cap_ts = 0;
     int sm_count = 148;
     std::string err;
     std::vector<void *> allocs;
@@ -256,7 +264,7 @@ extern "C" int mtd_destroy(mtd_handle h)
     if (h->state_stream) { cudaStreamSynchronize(h->state_stream); cudaStreamDestroy(h->state_stream); }
     if (h->ev_state) cudaEventDestroy(h->ev_state);
     if (h->ev_main) cudaEventDestroy(h->ev_main);
-    for (void *p : { (void *)h->sc_a1, (void *)h->sc_a2, (void *)h->sc_off, (void *)h->sc_se }) if (p) cudaFree(p);
+    for (void *p : { (void *)h->sc_a1, (void *)h->sc_a2, (void *)h->sc_off, (void *)h->sc_se, (void *)h->vacc_ids, (void *)h->vacc_ts }) if (p) cudaFree(p);
     for (void *p : h->xchg_peers) cudaIpcCloseMemHandle(p);
     if (h->xchg_alloc) cudaFree(h->xchg_alloc);
     free_tape(h);
@@ -555,6 +563,84 @@ extern "C" int mtd_apply_deltas(mtd_handle h, const int32_t *bufs, int64_t n_buf
     return MTD_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ K7 vaccination
+extern "C" int mtd_enable_vaccination(mtd_handle h, int64_t n_locals)
+{
+    if (!h || n_locals <= 0 || n_locals > h->c.n_agents) { if (h) h->err = "mtd_enable_vaccination: bad n_locals"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    if (!h->vacc_day) {
+        DA(h->vacc_day, 2 * h->c.n_agents); DA(h->vacc_selected, h->c.n_agents);
+        char *scr; DA(scr, 128); h->vacc_scratch = scr;
+        DA(h->vacc_hist, 65536);
+        TOUCH();
+        std::vector<int32_t> none((size_t)(2 * h->c.n_agents), MTD_NONE);
+        CK(cudaMemcpyAsync(h->vacc_day, none.data(), sizeof(int32_t) * none.size(), cudaMemcpyHostToDevice, h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+    }
+    h->vacc_n_locals = n_locals;
+    return MTD_OK;
+}
+
+extern "C" int mtd_set_vaccination(mtd_handle h, int64_t n, const int32_t *last_dose_day, const int32_t *vacc_day, int mem)
+{
+    if (!h || n != h->c.n_agents) { if (h) h->err = "mtd_set_vaccination: n != n_agents"; return MTD_E_ARG; }
+    if (!h->vacc_day) { h->err = "mtd_set_vaccination before mtd_enable_vaccination"; return MTD_E_STATE; }
+    CK(cudaSetDevice(h->cfg.device));
+    TOUCH();
+    COPY_IN(h->c.last_dose_day, last_dose_day, 4 * (size_t)n);
+    COPY_IN(h->vacc_day, vacc_day, 8 * (size_t)n);
+    if (mem == MTD_MEM_HOST) CK(cudaStreamSynchronize(h->stream));
+    return MTD_OK;
+}
+
+extern "C" int mtd_get_vaccination(mtd_handle h, int64_t n, int32_t *last_dose_day, int32_t *vacc_day, int mem)
+{
+    if (!h || n != h->c.n_agents) { if (h) h->err = "mtd_get_vaccination: n != n_agents"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    TOUCH();
+    COPY_OUT(last_dose_day, h->c.last_dose_day, 4 * (size_t)n);
+    if (vacc_day) {
+        if (!h->vacc_day) { h->err = "mtd_get_vaccination: vaccination is not enabled"; return MTD_E_STATE; }
+        COPY_OUT(vacc_day, h->vacc_day, 8 * (size_t)n);
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    return MTD_OK;
+}
+
+extern "C" int mtd_schedule_vaccinations(mtd_handle h, const mtd_day *day, int64_t k, int64_t n_replay, const int32_t *replay_ids,
+                                         const int32_t *replay_ts, uint8_t *selected, int64_t *n_selected, int mem)
+{
+    if (!h || !day || k < 0 || n_replay < 0) { if (h) h->err = "mtd_schedule_vaccinations: bad arguments"; return MTD_E_ARG; }
+    if (!h->vacc_day) { h->err = "mtd_schedule_vaccinations before mtd_enable_vaccination"; return MTD_E_STATE; }
+    if (day->mode == MTD_MODE_REPLAY && n_replay && (!replay_ids || !replay_ts)) { h->err = "replay mode without the reference's sample"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    TOUCH();
+    h->c.day = *day;
+    if (day->mode == MTD_MODE_REPLAY) {
+        const int32_t *ids = replay_ids, *ts = replay_ts;
+        if (mem == MTD_MEM_HOST && n_replay) {
+            { int r; if ((r = grow_buf(h, &h->vacc_ids, &h->vacc_cap_ids, n_replay))) return r;
+              if ((r = grow_buf(h, &h->vacc_ts, &h->vacc_cap_ts, n_replay))) return r; }
+            CK(cudaMemcpyAsync(h->vacc_ids, replay_ids, 4 * (size_t)n_replay, cudaMemcpyHostToDevice, h->stream));
+            CK(cudaMemcpyAsync(h->vacc_ts, replay_ts, 4 * (size_t)n_replay, cudaMemcpyHostToDevice, h->stream));
+            ids = h->vacc_ids; ts = h->vacc_ts;
+        }
+        CK(cudaMemsetAsync(h->vacc_selected, 0, (size_t)h->c.n_agents, h->stream));
+        launch_k7_replay(h->c, n_replay, ids, ts, h->vacc_day, h->vacc_selected, h->vacc_scratch, h->stream);
+    } else {
+        CK(cudaMemsetAsync(h->vacc_selected, 0, (size_t)h->c.n_agents, h->stream));
+        launch_k7_schedule(h->c, h->vacc_n_locals, (long long)k, h->vacc_day, h->vacc_selected, h->vacc_scratch, h->vacc_hist,
+                           h->stream, h->sm_count);
+    }
+    int cnt = 0;
+    CK(cudaMemcpyAsync(&cnt, (char *)h->vacc_scratch + 64, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    if (selected) CK(cudaMemcpyAsync(selected, h->vacc_selected, (size_t)h->c.n_agents, kind_out(mem), h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (n_selected) *n_selected = cnt;
+    CK(cudaGetLastError());
+    return MTD_OK;
+}
+
 extern "C" int mtd_set_intervention_mask(mtd_handle h, int on)
 {
     if (!h) return MTD_E_ARG;
@@ -575,7 +661,8 @@ extern "C" int mtd_advance_seir(mtd_handle h, int32_t day, const uint8_t *mask, 
         CK(cudaMemcpyAsync(h->d_mask, mask, (size_t)h->c.n_agents, cudaMemcpyHostToDevice, ss));
         dm = h->d_mask;
     }
-    { StageScope sc(h, MTD_STAGE_K4, ss); sc.add(launch_k4(h->c, day, dm, ss, h->sm_count)); }
+    { StageScope sc(h, MTD_STAGE_K4, ss); sc.add(launch_k4(h->c, day, dm, ss, h->sm_count));
+      if (h->vacc_day) sc.add(launch_k7_dose(h->c, day, h->vacc_n_locals, h->vacc_day, ss, h->sm_count)); }
     h->state_dirty = true;
     CK(cudaGetLastError());
     return MTD_OK;

@@ -83,6 +83,59 @@ class Epidemiology:
             bridge.scatter(h.get_state(), exposed, self.agents_epi, vu)
         return exposed
 
+    # ------------------------------------------------------------------ vaccination (K7)
+    def schedule_vaccinations(self, day):
+        """epidemiology.py:911-976 -> ids of the agents scheduled for day + 1.  The bookkeeping on dyn_params
+        (num_agents_to_be_vaccinated, num_vaccinations_today; :917-945) is host arithmetic on scalars, as in the
+        reference (one log-normal draw from the legacy stream); the draw of the agents and of their timesteps runs on
+        the device (mtd_schedule_vaccinations)."""
+        from . import bridge, capi, util
+        dp, vu = self.dyn_params, self.vars_util
+        updated = []
+        if dp.vaccination_propensity > 0:
+            doses = vu.agents_vaccination_doses
+            num_not_vaccinated = self.n_locals - len(doses)
+            num_already_vaccinated = self.n_locals - num_not_vaccinated
+            if dp.vaccination_propensity != dp.last_vaccination_propensity:
+                if dp.num_agents_to_be_vaccinated == 0:
+                    dp.num_agents_to_be_vaccinated = round(num_not_vaccinated * dp.vaccination_propensity) or 1
+                else:
+                    change = dp.vaccination_propensity - dp.last_vaccination_propensity
+                    dp.num_agents_to_be_vaccinated += round(num_not_vaccinated * change) or 1
+                dp.last_vaccination_propensity = dp.vaccination_propensity
+            mean, std = self.epidemiologyparams["vaccination_daily_parameters"]
+            dp.num_vaccinations_today = round(util.sample_log_normal(mean, std, 1, True) * self.locals_ratio_to_full_pop)
+            remaining = dp.num_agents_to_be_vaccinated - num_already_vaccinated
+            if dp.num_vaccinations_today > remaining:
+                dp.num_vaccinations_today = remaining
+            if dp.num_vaccinations_today > 0:
+                n_agents = int(self.n_locals + self.n_tourists)
+                h = bridge.get_handle(n_agents, 1, 16, self.params, self.device)
+                h.enable_vaccination(int(self.n_locals))
+                last = np.full(n_agents, prm.NONE, np.int32)
+                for a, d in doses.items():
+                    if int(a) < n_agents and len(d) > 0:
+                        last[int(a)] = int(d[-1])
+                h.set_vaccination(last, np.full((n_agents, 2), prm.NONE, np.int32))
+                replay = self.mode == "replay"
+                d = h.make_day(capi.MODE_REPLAY if replay else capi.MODE_PHILOX, int(day), 0.0, False, False, seed=self.seed)
+                if replay:
+                    if self.tape is None:
+                        raise RuntimeError("replay mode needs the reference's vaccination sample (ids, timesteps)")
+                    ids, ts = self.tape
+                    h.schedule_vaccinations(d, len(ids), ids, ts)
+                    order = [int(a) for a in ids]
+                else:
+                    order = [int(a) for a in h.schedule_vaccinations(d, int(dp.num_vaccinations_today))]
+                _, rec = h.get_vaccination()
+                for a in order:
+                    e = self.agents_epi[a]
+                    lst = e.get("vaccination_days") or []
+                    lst.append([int(rec[a, 0]), int(rec[a, 1])])           # [day + 1, sampled_timestep] (:965)
+                    e["vaccination_days"] = lst
+                    updated.append(a)
+        return updated
+
     # ------------------------------------------------------------------ contact tracing (K5)
     def _residences(self):
         """cells_households / cells_institutions / cells_accommodation -> CSR over cell ids: members = residents

@@ -655,6 +655,54 @@ int64_t mtdo_transmission(const mtdo_params *P, const mtdo_dayctx *D, int64_t M,
 }
 
 /* ------------------------------------------------------------------ seirstateutil.update_agent_state (seirstateutil.py:38-72) */
+/* Vaccination scheduling (Epidemiology.schedule_vaccinations, epidemiology.py:911-976), device part: k locals without a
+ * dose, drawn without replacement, get the record [day + 1, timestep].  Philox mode: the k smallest keys
+ * (philox(day, agent; site 7).w0 << 32 | agent) -- a uniform k-subset like np.random.choice(replace=False); timestep =
+ * 42 + floor(w1 * 79 / 2^32).  selected[a] = 1 for the agents scheduled.  Returns their number. */
+static int cmp_u64(const void *a, const void *b)
+{
+    uint64_t x = *(const uint64_t *)a, y = *(const uint64_t *)b;
+    return x < y ? -1 : (x > y ? 1 : 0);
+}
+
+int64_t mtdo_schedule_vaccinations(const mtdo_dayctx *D, int64_t n_locals, int64_t k, const int32_t *last_dose_day,
+                                   int32_t *vacc_day, uint8_t *selected)
+{
+    uint64_t *keys = (uint64_t *)malloc(sizeof(uint64_t) * (size_t)(n_locals > 0 ? n_locals : 1));
+    int64_t nc = 0;
+    for (int64_t a = 0; a < n_locals; a++) {
+        selected[a] = 0;
+        if (last_dose_day[a] != MTDO_NONE) continue;
+        uint32_t ctr[4] = { (uint32_t)D->day, (uint32_t)a, 0u, 0u }, key[2] = { D->seed, 7u }, w[4];
+        mtdo_philox4x32(ctr, key, w);
+        keys[nc++] = ((uint64_t)w[0] << 32) | (uint64_t)(uint32_t)a;
+    }
+    if (k > nc) k = nc;
+    if (k < 0) k = 0;
+    qsort(keys, (size_t)nc, sizeof(uint64_t), cmp_u64);
+    for (int64_t i = 0; i < k; i++) {
+        const int64_t a = (int64_t)(keys[i] & 0xffffffffu);
+        uint32_t ctr[4] = { (uint32_t)D->day, (uint32_t)a, 0u, 0u }, key[2] = { D->seed, 7u }, w[4];
+        mtdo_philox4x32(ctr, key, w);
+        vacc_day[2 * a] = D->day + 1;
+        vacc_day[2 * a + 1] = 42 + (int32_t)(((uint64_t)w[1] * 79u) >> 32);
+        selected[a] = 1;
+    }
+    free(keys);
+    return k;
+}
+
+/* dose bookkeeping of the vaccination day (itinerary.py:2489-2527) */
+void mtdo_vaccination_day(int32_t day, int64_t n_locals, int32_t *last_dose_day, int32_t *vacc_day)
+{
+    for (int64_t a = 0; a < n_locals; a++) {
+        const int32_t vd = vacc_day[2 * a];
+        if (vd == MTDO_NONE) continue;
+        if (day == vd) last_dose_day[a] = day;
+        else if (day > vd) { vacc_day[2 * a] = MTDO_NONE; vacc_day[2 * a + 1] = MTDO_NONE; }
+    }
+}
+
 /* Test-result processing of the itinerary stage (itinerary.py:2301-2332): an agent whose test result is due today is
  * flagged positive unless a false negative (Exposed / Infectious) or only on a false positive (everybody else); a
  * positive agent enters contact_tracing_agent_ids and gets a Positive quarantine (schedule_quarantine,

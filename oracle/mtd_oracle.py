@@ -222,6 +222,21 @@ def advance(day, agents: AgentState, mask=None):
     return lib().mtdo_advance(C.c_int32(day), C.byref(a), _p(mask))
 
 
+def schedule_vaccinations(ctx, n_locals, k, last_dose_day, vacc_day):
+    """epidemiology.py:911-976 (device part): mutates vacc_day [n][2] -> ascending ids scheduled"""
+    sel = np.zeros(len(last_dose_day), np.uint8)
+    L = lib()
+    L.mtdo_schedule_vaccinations.restype = C.c_int64
+    L.mtdo_schedule_vaccinations(C.byref(ctx), C.c_int64(n_locals), C.c_int64(k), _p(last_dose_day), _p(vacc_day), _p(sel))
+    return np.nonzero(sel)[0].astype(np.int32)
+
+
+def vaccination_day(day, n_locals, last_dose_day, vacc_day):
+    L = lib()
+    L.mtdo_vaccination_day.restype = None
+    L.mtdo_vaccination_day(C.c_int32(day), C.c_int64(n_locals), _p(last_dose_day), _p(vacc_day))
+
+
 def process_test_results(params, ctx, agents: AgentState, epi_present=None):
     """itinerary.py:2301-2332 over all agents -> ids added to contact_tracing_agent_ids (ascending)"""
     a = agents.struct()

@@ -183,3 +183,38 @@ def test_epidemiology_contact_tracing_dropin(name, ti):
     # clean-up dropped the oldest day and re-based the markers
     assert len(vu.directcontacts_by_simcelltype_by_day) < n_before
     assert min(vu.directcontacts_by_simcelltype_by_day_start_marker.values()) == 0
+
+
+def test_schedule_vaccinations_dropin_replays_reference_calls():
+    """Epidemiology.schedule_vaccinations (epidemiology.py:911-976): six consecutive reference calls
+    (tests/golden/make_vacc_kat.py); the dyn_params bookkeeping must match exactly, the reference's own sample is fed
+    in replay mode, and in Philox mode the device draws exactly num_vaccinations_today unvaccinated locals"""
+    import json, os
+    from mtdcovabm_b200.epidemiology import Epidemiology
+    K = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "vacc_kat.json")))
+    ep = prm.load_json("epidemiology.json")
+    for mode in ("replay", "philox"):
+        n_locals, n_tourists = K["n_locals"], K["n_tourists"]
+        agents_epi = {a: {"vaccination_days": None} for a in range(n_locals + n_tourists)}
+        vu = SimpleNamespace(agents_vaccination_doses={})
+        dp = SimpleNamespace(vaccination_propensity=0.0, last_vaccination_propensity=0.0, num_agents_to_be_vaccinated=0,
+                             num_vaccinations_today=0)
+        e = Epidemiology(ep, n_locals, n_tourists, K["ratio"], None, agents_epi, vu, {}, {}, {}, dp, mode=mode, seed=4)
+        for row in K["days"]:
+            dp.vaccination_propensity = row["propensity"]
+            np.random.seed(1000 + row["day"])
+            e.tape = (np.array(row["updated"], np.int32), np.array(row["ts"], np.int32))
+            upd = e.schedule_vaccinations(row["day"])
+            assert dp.num_agents_to_be_vaccinated == row["num_agents_to_be_vaccinated"]
+            assert dp.num_vaccinations_today == row["num_vaccinations_today"]
+            assert dp.last_vaccination_propensity == row["last_vaccination_propensity"]
+            assert len(upd) == len(row["updated"])
+            if mode == "replay":
+                assert upd == row["updated"]
+                assert [agents_epi[a]["vaccination_days"][-1] for a in upd] == [[row["day"] + 1, t] for t in row["ts"]]
+            else:
+                assert len(set(upd)) == len(upd) and all(a < n_locals and a not in vu.agents_vaccination_doses for a in upd)
+                assert all(agents_epi[a]["vaccination_days"][-1][0] == row["day"] + 1 and
+                           42 <= agents_epi[a]["vaccination_days"][-1][1] <= 120 for a in upd)
+            for a in upd:                                       # the next day's itinerary stage administers the doses
+                vu.agents_vaccination_doses.setdefault(a, []).append(row["day"] + 1)

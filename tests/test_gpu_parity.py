@@ -324,3 +324,57 @@ def test_test_result_processing_matches_oracle(quarantine_enabled):
     if not quarantine_enabled:
         assert np.array_equal(ost.quarantine, st.quarantine)
     h.close()
+
+
+@pytest.mark.parametrize("k", [0, 1, 777, 30_000, 10**9])
+def test_vaccination_scheduling_matches_oracle(k):
+    """K7 (epidemiology.py:911-976 device part + itinerary.py:2489-2527): exact-k radix select == oracle's sorted keys;
+    dose bookkeeping on the vaccination day through mtd_advance_seir"""
+    n, n_locals, day = 60_000, 50_000, 31
+    rng = np.random.default_rng(5)
+    last = np.full(n, prm.NONE, np.int32)
+    done = rng.random(n) < 0.4
+    last[done] = rng.integers(1, day, done.sum())
+    h = capi.Handle(n, 1, 16)
+    h.set_params(prm.build_params())
+    h.enable_vaccination(n_locals)
+    h.set_vaccination(last, np.full((n, 2), prm.NONE, np.int32))
+    d = h.make_day(capi.MODE_PHILOX, day, 0.0, False, False, seed=17)
+    got = h.schedule_vaccinations(d, k)
+    o_last, o_rec = last.copy(), np.full((n, 2), prm.NONE, np.int32)
+    ctx = mo.make_ctx(mo.MODE_PHILOX, day, 0.0, False, False, seed=17)
+    exp = mo.schedule_vaccinations(ctx, n_locals, k, o_last, o_rec)
+    n_cand = int((last[:n_locals] == prm.NONE).sum())
+    assert len(exp) == min(k, n_cand) and np.array_equal(got, exp)
+    g_last, g_rec = h.get_vaccination()
+    assert np.array_equal(g_rec, o_rec) and np.array_equal(g_last, o_last)
+    if len(exp):
+        assert np.all(g_rec[exp, 0] == day + 1) and g_rec[exp, 1].min() >= 42 and g_rec[exp, 1].max() <= 120
+        assert np.all(last[exp] == prm.NONE) and exp.max() < n_locals
+    # next day: the dose lands; the day after: the record is cleared
+    for dd in (day + 1, day + 2):
+        h.advance_seir(dd, None)
+        mo.vaccination_day(dd, n_locals, o_last, o_rec)
+        g_last, g_rec = h.get_vaccination()
+        assert np.array_equal(g_rec, o_rec) and np.array_equal(g_last, o_last)
+    if len(exp):
+        assert np.all(g_last[exp] == day + 1) and np.all(g_rec[exp, 0] == prm.NONE)
+    h.close()
+
+
+def test_vaccination_sample_is_uniform():
+    """the k-subset is uniform over the candidates: per-agent selection frequency over many days ~ k / n_candidates"""
+    n, k = 2000, 100
+    h = capi.Handle(n, 1, 16)
+    h.set_params(prm.build_params())
+    h.enable_vaccination(n)
+    cnt = np.zeros(n)
+    for day in range(1, 401):
+        h.set_vaccination(np.full(n, prm.NONE, np.int32), np.full((n, 2), prm.NONE, np.int32))
+        ids = h.schedule_vaccinations(h.make_day(capi.MODE_PHILOX, day, 0.0, False, False, seed=3), k)
+        assert len(ids) == k
+        cnt[ids] += 1
+    p = k / n
+    z = (cnt - 400 * p) / np.sqrt(400 * p * (1 - p))
+    assert abs(z.mean()) < 0.2 and 0.8 < z.std() < 1.2 and np.abs(z).max() < 5
+    h.close()
