@@ -47,6 +47,7 @@ class DayEngine:
                     self.gather = torch.zeros((world, self.delta_cap + 1, capi.DELTA_WORDS), dtype=torch.int32,
                                              device=self.device)
         self.n_agents, self.n_cells = n_agents, n_cells
+        self._vaccination = False
 
     def _setup_peer_exchange(self):
         """map every peer's exchange buffer (CUDA IPC) -> "p2p"; "nccl" if that is not possible on this box"""
@@ -159,6 +160,40 @@ class DayEngine:
             self._k ^= 1
             ticket = h.export_day_async(rows, self._cap_rows, kv, self._cap_exposed, res, mem=capi.MEM_HOST)
         return HostDayResult(h, ticket, rows, kv, res)
+
+    # ---- checkpoint / resume (the reference has none; the whole dynamic state of the path is a
+    # handful of dense per-agent arrays, so a checkpoint is their copy plus the day and the Philox seed)
+    def save_checkpoint(self, path, day):
+        """state after `day` has been stepped -> one .npz (every rank holds the same replicated state: rank 0 writes)"""
+        import numpy as np
+        self.h.sync()
+        st = self.h.get_state()
+        last, rec = self.h.get_vaccination(with_records=self._vaccination)
+        if self.rank == 0:
+            extra = {"vacc_day": rec} if rec is not None else {}
+            np.savez_compressed(path, day=np.int64(day), seed=np.int64(self.seed), mode=np.int64(self.mode),
+                                n_agents=np.int64(self.n_agents), last_dose_day=last, **st, **extra)
+
+    def load_checkpoint(self, path):
+        """-> the day the checkpoint was taken after; static attributes / cells / params are set as for a new run"""
+        import numpy as np
+        z = np.load(path)
+        if int(z["n_agents"]) != self.n_agents:
+            raise RuntimeError("checkpoint is for %d agents, engine has %d" % (int(z["n_agents"]), self.n_agents))
+        self.seed, self.mode = int(z["seed"]), int(z["mode"])
+        self.h.set_state(seir=z["seir"], inf_type=z["inf_type"], inf_sev=z["inf_sev"], last_dose_day=z["last_dose_day"],
+                         sched=z["sched"], sched_cnt=z["sched_cnt"], test_day=z["test_day"],
+                         test_result_day=z["test_result_day"], quarantine=z["quarantine"], hosp=z["hosp"])
+        if "vacc_day" in z.files:
+            if not self._vaccination:
+                raise RuntimeError("checkpoint carries vaccination records: enable_vaccination first")
+            self.h.set_vaccination(z["last_dose_day"], z["vacc_day"])
+        self.h.sync()
+        return int(z["day"])
+
+    def enable_vaccination(self, n_locals):
+        self.h.enable_vaccination(n_locals)
+        self._vaccination = True
 
     def sync(self):
         self.h.sync()

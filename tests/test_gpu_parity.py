@@ -378,3 +378,50 @@ def test_vaccination_sample_is_uniform():
     z = (cnt - 400 * p) / np.sqrt(400 * p * (1 - p))
     assert abs(z.mean()) < 0.2 and 0.8 < z.std() < 1.2 and np.abs(z).max() < 5
     h.close()
+
+
+def test_checkpoint_resume_is_bit_exact(tmp_path):
+    """8 days straight == 4 days, checkpoint, new engine, resume, 4 days (state, exposures)"""
+    import torch
+    from mtdcovabm_b200 import engine, synth
+    dev = torch.device("cuda", 0)
+    bank = synth.load_bank()
+    pop = synth.SynthPopulation(bank, 12, dev, seed=2, infectious_frac=0.05)
+    P = prm.build_params()
+    streams = [pop.stream(k) for k in range(pop.n_days)]
+    max_m = max(len(s["iv_agent"]) for s in streams) + 16
+    n_locals = pop.n_agents
+
+    def fresh():
+        e = engine.DayEngine(pop.n_agents, pop.n_cells, max_m, P, device=0, seed=9)
+        e.set_population(pop)
+        e.enable_vaccination(n_locals)
+        return e
+
+    def run(e, first, last):
+        out = []
+        for d in range(first, last + 1):
+            e.step(d, streams[d % pop.n_days], testing=True, quarantine=True)
+            out.append(int(e.h.counters().n_exposed))
+            if d % 3 == 0:
+                e.h.schedule_vaccinations(e.h.make_day(capi.MODE_PHILOX, d, 0.0, seed=9), 500)
+        return out
+
+    a = fresh()
+    exp_a = run(a, 1, 8)
+    st_a, vac_a = a.h.get_state(), a.h.get_vaccination()
+    a.close()
+    b = fresh()
+    exp_b = run(b, 1, 4)
+    ck = str(tmp_path / "day4.npz")
+    b.save_checkpoint(ck, 4)
+    b.close()
+    c = fresh()
+    assert c.load_checkpoint(ck) == 4
+    exp_b += run(c, 5, 8)
+    st_c, vac_c = c.h.get_state(), c.h.get_vaccination()
+    c.close()
+    assert exp_a == exp_b and sum(exp_a) > 0
+    for k in st_a:
+        assert np.array_equal(st_a[k], st_c[k]), k
+    assert np.array_equal(vac_a[0], vac_c[0]) and np.array_equal(vac_a[1], vac_c[1]) and (vac_a[0] != prm.NONE).sum() > 0
