@@ -10,7 +10,8 @@
 
 // every launcher returns the number of kernels it launched
 int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count);
-int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaEvent_t ev_fork, cudaEvent_t ev_join, int sm_count);
+int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t aux2, cudaEvent_t ev_fork, cudaEvent_t ev_join,
+              cudaEvent_t ev_join2, int sm_count);
 int64_t k1_bits_words_needed(int sm_count);
 int launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count);
 int launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap, cudaStream_t st);
@@ -35,8 +36,8 @@ struct mtd_handle_s {
     mtd_config cfg;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
-    cudaStream_t aux_stream = nullptr;           // large-cell K1 kernels run beside the small-cell ones
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaStream_t aux_stream = nullptr, aux2_stream = nullptr;   // large-cell K1 kernels run beside the small-cell ones
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr;
     // The state chain -- apply of day d's exposure records (after the peer exchange), then K4 of day d+1 -- runs on its
     // own stream beside K0/K1/K2 of day d+1, which read no per-agent state; K3 of day d+1 joins the two.
     cudaStream_t state_stream = nullptr;
@@ -172,6 +173,8 @@ static int create_impl(mtd_handle h)
     if (cfg.stream) h->stream = (cudaStream_t)cfg.stream;
     else { CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->own_stream = true; }
     CK(cudaStreamCreateWithFlags(&h->aux_stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->aux2_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&h->ev_join2, cudaEventDisableTiming));
     CK(cudaStreamCreateWithFlags(&h->state_stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&h->ev_state, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming));
     memset(&h->x, 0, sizeof(h->x));
@@ -276,6 +279,8 @@ extern "C" int mtd_destroy(mtd_handle h)
         if (p) cudaFree(p);
     for (int s = 0; s < MTD_N_STAGES; s++) for (cudaEvent_t e : h->ev[s]) cudaEventDestroy(e);
     if (h->aux_stream) { cudaStreamSynchronize(h->aux_stream); cudaStreamDestroy(h->aux_stream); }
+    if (h->aux2_stream) { cudaStreamSynchronize(h->aux2_stream); cudaStreamDestroy(h->aux2_stream); }
+    if (h->ev_join2) cudaEventDestroy(h->ev_join2);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_join) cudaEventDestroy(h->ev_join);
     if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
@@ -445,7 +450,7 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     CK(cudaMemsetAsync(c.cell_first, 0xff, sizeof(uint32_t) * (size_t)c.n_cells, h->stream));
     { StageScope sc(h, MTD_STAGE_K0); sc.add(launch_k0(c, h->scan_tmp, h->stream, h->sm_count)); }
     if (h->ev_k0_done) CK(cudaEventRecord(h->ev_k0_done, h->stream));      // the interval stream has been consumed
-    { StageScope sc(h, MTD_STAGE_K1); sc.add(launch_k1(c, h->stream, h->aux_stream, h->ev_fork, h->ev_join, h->sm_count)); }
+    { StageScope sc(h, MTD_STAGE_K1); sc.add(launch_k1(c, h->stream, h->aux_stream, h->aux2_stream, h->ev_fork, h->ev_join, h->ev_join2, h->sm_count)); }
     c.rows12 = nullptr;
     if (h->export_on) {     // K2 also packs the rows for the export; the slot's previous export must have drained
         const int sl = (int)(h->day_seq & 1);

@@ -768,12 +768,12 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, uint32_t 
 }
 
 template <int MM, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) k1_large_kernel(DevCtx g, int cls)
+__global__ void __launch_bounds__(WARPS * 32) k1_large_kernel(DevCtx g, int cls, int64_t bits_off)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned char *sm = smem + (size_t)warp * Lay<MM>::bytes;
-    uint32_t *bits = g.k1_bits + ((size_t)blockIdx.x * WARPS + warp) * Lay<MM>::bits_words;
+    uint32_t *bits = g.k1_bits + bits_off + ((size_t)blockIdx.x * WARPS + warp) * Lay<MM>::bits_words;
     if (g.ctr->error) return;
     const int total = g.ctr->class_cells[cls];
     const int32_t *list = g.class_list + (int64_t)cls * g.class_stride;
@@ -806,13 +806,13 @@ int large_blocks_per_sm(int cap)
 }
 
 template <int MM, int WARPS>
-int launch_large(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int cap)
+int launch_large(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int cap, int64_t bits_off)
 {
     int grid = sm_count * large_blocks_per_sm<MM, WARPS>(cap);
-    const int64_t fit = c.k1_bits_words / (int64_t)(Lay<MM>::bits_words * WARPS);
+    const int64_t fit = (c.k1_bits_words - bits_off) / (int64_t)(Lay<MM>::bits_words * WARPS);
     if (grid > fit) grid = (int)fit;
     if (grid < 1) return 0;
-    k1_large_kernel<MM, WARPS><<<grid, WARPS * 32, Lay<MM>::bytes * WARPS, st>>>(c, cls);
+    k1_large_kernel<MM, WARPS><<<grid, WARPS * 32, Lay<MM>::bytes * WARPS, st>>>(c, cls, bits_off);
     return 1;
 }
 
@@ -842,8 +842,14 @@ int64_t k1_bits_words_needed(int sm_count)
     int64_t w5 = (int64_t)sm_count * large_blocks_per_sm<K1_C5>(K1_C5_CAP) * 1 * (int64_t)Lay<1024>::bits_words;
     int64_t w4 = (int64_t)sm_count * large_blocks_per_sm<K1_C4>(K1_NOCAP) * 5 * (int64_t)Lay<320>::bits_words;
     int64_t w3 = (int64_t)sm_count * large_blocks_per_sm<K1_C3>(K1_NOCAP) * 4 * (int64_t)Lay<128>::bits_words;
-    int64_t w = w5 > w4 ? w5 : w4;
-    return w > w3 ? w : w3;
+    return w5 + w4 + w3;       // one region per class: the three launches run side by side
+}
+
+static void k1_bits_offsets(int sm_count, int64_t &o5, int64_t &o4, int64_t &o3)
+{
+    o5 = 0;
+    o4 = (int64_t)sm_count * large_blocks_per_sm<K1_C5>(K1_C5_CAP) * 1 * (int64_t)Lay<1024>::bits_words;
+    o3 = o4 + (int64_t)sm_count * large_blocks_per_sm<K1_C4>(K1_NOCAP) * 5 * (int64_t)Lay<320>::bits_words;
 }
 
 static int env_int(const char *name, int dflt)
@@ -856,27 +862,34 @@ static int env_int(const char *name, int dflt)
 // of the issue slots used), the sub-warp kernels of the small classes are issue-bound: run the two families side by
 // side -- large classes on the auxiliary stream with a capped number of resident blocks per SM, small classes on the
 // main stream in the registers and warp slots that are left -- and join before K2.
-int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaEvent_t ev_fork, cudaEvent_t ev_join, int sm_count)
+int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t aux2, cudaEvent_t ev_fork, cudaEvent_t ev_join,
+              cudaEvent_t ev_join2, int sm_count)
 {
     static const int cap4 = env_int("MTD_K1_CAP320", K1_NOCAP), cap3 = env_int("MTD_K1_CAP128", K1_NOCAP);
     static const int overlap = env_int("MTD_K1_OVERLAP", 1);
-    cudaStream_t sl = st;
-    if (overlap && aux) {
+    int64_t o5, o4, o3;
+    k1_bits_offsets(sm_count, o5, o4, o3);
+    cudaStream_t sl = st, sl2 = st;
+    if (overlap && aux && aux2) {
         cudaEventRecord(ev_fork, st);
         cudaStreamWaitEvent(aux, ev_fork, 0);
-        sl = aux;
+        cudaStreamWaitEvent(aux2, ev_fork, 0);
+        sl = aux; sl2 = aux2;
     }
     int n = 0;
-    // big cells first: they are the long poles
-    n += launch_large<K1_C5>(c, 5, sl, sm_count, K1_C5_CAP);
-    n += launch_large<K1_C4>(c, 4, sl, sm_count, cap4);
-    n += launch_large<K1_C3>(c, 3, sl, sm_count, cap3);
+    // big cells first: they are the long poles; the two big classes on streams of their own, so that the tail of one
+    // (a handful of warps finishing 300-interval cells) overlaps the other
+    n += launch_large<K1_C5>(c, 5, sl, sm_count, K1_C5_CAP, o5);
+    n += launch_large<K1_C4>(c, 4, sl, sm_count, cap4, o4);
+    n += launch_large<K1_C3>(c, 3, sl2, sm_count, cap3, o3);
     n += launch_small<16>(c, 1, st, sm_count);
     n += launch_small<8>(c, 0, st, sm_count);
     n += launch_small<32>(c, 2, st, sm_count);
     if (sl != st) {
         cudaEventRecord(ev_join, sl);
+        cudaEventRecord(ev_join2, sl2);
         cudaStreamWaitEvent(st, ev_join, 0);
+        cudaStreamWaitEvent(st, ev_join2, 0);
     }
     return n;
 }
