@@ -96,6 +96,12 @@ __device__ __forceinline__ int degree_i(double d, long long deg_sum, long long m
 __device__ __forceinline__ void pair_row_bits(const uint16_t *se, uint32_t ivx, uint32_t ivy, bool &x_first, int &start,
                                               int &end, int &dur)
 {   // one pass: orientation A = x outer / y inner (this loop's order), orientation B = lexicographic (pb, pa)
+    if ((ivx & (ivx - 1)) == 0 && (ivy & (ivy - 1)) == 0) {         // one interval each (the common case): one overlap
+        const int pa = __ffs(ivx) - 1, pb = __ffs(ivy) - 1;
+        start = max((int)(se[pa] & 0xff), (int)(se[pb] & 0xff)); end = min((int)(se[pa] >> 8), (int)(se[pb] >> 8));
+        dur = end - start + 1; x_first = pa < pb;
+        return;
+    }
     int fx = 64, fy = 64;
     int a_start = 0, a_end = 0; bool a_none = true;
     int b_min = 1 << 30, b_max = -1, b_start = 0, b_end = 0;
@@ -147,11 +153,12 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
 
     // the next cell's descriptor and this lane's record are fetched while the current cell is processed
     int w = (blockIdx.x * K1S_THREADS + (int)threadIdx.x) / G;
-    int nx_slot = 0, nx_m = 0, nx_cell = 0; int64_t nx_base = 0;
+    int nx_slot = 0, nx2_slot = 0, nx_m = 0, nx_cell = 0; int64_t nx_base = 0;
     IvRec nx_rec; nx_rec.agent = 0; nx_rec.order = 0xffffffffu; nx_rec.se = 0; nx_rec.pad = 0;
     if (w < total) {
         nx_slot = list[w]; nx_m = g.slot_m[nx_slot]; nx_base = g.slot_off[nx_slot]; nx_cell = g.slot_cell[nx_slot];
         if (gl < nx_m) nx_rec = g.csr[nx_base + gl];
+        if (w + n_groups < total) nx2_slot = list[w + n_groups];       // the slot index runs two cells ahead
     }
     for (; w < total; w += n_groups) {
         const int slot = nx_slot;
@@ -161,9 +168,10 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
         IvRec rec = nx_rec;
         const int ctype = g.cell_type[cell];
         if (w + n_groups < total) {
-            nx_slot = list[w + n_groups]; nx_m = g.slot_m[nx_slot]; nx_base = g.slot_off[nx_slot]; nx_cell = g.slot_cell[nx_slot];
+            nx_slot = nx2_slot; nx_m = g.slot_m[nx_slot]; nx_base = g.slot_off[nx_slot]; nx_cell = g.slot_cell[nx_slot];
             nx_rec.agent = 0; nx_rec.order = 0xffffffffu; nx_rec.se = 0;
             if (gl < nx_m) nx_rec = g.csr[nx_base + gl];
+            if (w + 2 * n_groups < total) nx2_slot = list[w + 2 * n_groups];
         }
         const int indid = (ctype == CT_WORKPLACE && g.cell_indid) ? g.cell_indid[cell] : -1;
         const int act = activity_of_celltype(ctype, indid);
@@ -438,6 +446,12 @@ __device__ __forceinline__ void pair_row_lists(const Cell &c, int x, int y, bool
     int b_min = 1 << 30, b_max = -1, b_start = 0, b_end = 0;
     dur = 0;
     const int xa = c.aoff[x], xb = c.aoff[x + 1], ya = c.aoff[y], yb = c.aoff[y + 1];
+    if (xb - xa == 1 && yb - ya == 1) {                             // one interval each (the common case): one overlap
+        const int pa = c.apos[xa], pb = c.apos[ya];
+        start = max((int)(c.se[pa] & 0xff), (int)(c.se[pb] & 0xff)); end = min((int)(c.se[pa] >> 8), (int)(c.se[pb] >> 8));
+        dur = end - start + 1; x_first = pa < pb;
+        return;
+    }
     for (int qa = xa; qa < xb; qa++) {
         const int pa = c.apos[qa]; const int sa = c.se[pa] & 0xff, ea = c.se[pa] >> 8;
         for (int qb = ya; qb < yb; qb++) {
