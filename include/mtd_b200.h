@@ -38,7 +38,8 @@ extern "C" {
 #define MTD_MAX_CELL_INTERVALS 1024  /* largest cell (intervals) the on-chip path handles */
 
 enum { MTD_OK = 0, MTD_E_ARG = 1, MTD_E_CUDA = 2, MTD_E_CAPACITY = 3, MTD_E_CELL_TOO_LARGE = 4, MTD_E_STATE = 5, MTD_E_TIMEOUT = 6 };
-enum { MTD_MEM_HOST = 0, MTD_MEM_DEVICE = 1, MTD_MEM_STAGED = 2 /* the stream given to mtd_prefetch_intervals */ };
+enum { MTD_MEM_HOST = 0, MTD_MEM_DEVICE = 1, MTD_MEM_STAGED = 2 /* the stream given to mtd_prefetch_intervals */,
+       MTD_MEM_BUILT = 3 /* the stream built on the device by mtd_build_intervals */ };
 enum { MTD_MODE_REPLAY = 0, MTD_MODE_PHILOX = 1 };
 
 typedef struct mtd_handle_s *mtd_handle;
@@ -119,6 +120,18 @@ int mtd_get_state(mtd_handle h, int64_t n, int8_t *seir, int8_t *inf_type, int8_
                   uint8_t *sched_cnt, int32_t *test_day, int32_t *test_result_day, int32_t *quarantine,
                   int32_t *hosp, int mem);
 int mtd_set_tape(mtd_handle h, const mtd_tape *tape);
+
+/* K8: interval builder = Itinerary.update_cell_agents_timesteps + combine_same_cell_itinerary_entries
+ * (itinerary.py:1403-1488), the producer of this path's input.  One record per itinerary: its entries
+ * {start timestep -> cell} sorted by timestep (CSR ent_off[n_itin + 1] / ent_ts / ent_cell; cell -1 = residence) and
+ * the agents sharing it (CSR grp_off[n_itin + 1] / grp_agent / grp_rescell; a local agent is a group of one).  Builds
+ * the day's interval stream on the device, in the reference's emission order; n_intervals receives its length.  Run the
+ * day on it with mtd_simulate_contact_network(h, day, n_intervals, NULL, NULL, NULL, NULL, NULL, MTD_MEM_BUILT);
+ * mtd_get_intervals copies the stream out. */
+int mtd_build_intervals(mtd_handle h, int64_t n_itin, const int64_t *ent_off, const int16_t *ent_ts, const int32_t *ent_cell,
+                        const int64_t *grp_off, const int32_t *grp_agent, const int32_t *grp_rescell, int mem,
+                        int64_t *n_intervals);
+int mtd_get_intervals(mtd_handle h, int64_t n, int32_t *iv_agent, int32_t *iv_cell, uint8_t *iv_start, uint8_t *iv_end, int mem);
 
 /* K0 (CSR build) + K1 (pairs, degrees, greedy sampling) + K2 (dense rows).  Interval stream in emission order
  * (itinerary.py:1446-1452); iv_order may be NULL (= position in the stream) or strictly increasing global

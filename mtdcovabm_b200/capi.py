@@ -13,7 +13,7 @@ from .params import EXPO_W, MAXSCHED, NONE, ParamsStruct
 
 PKG = os.path.dirname(os.path.abspath(__file__))
 SO = os.path.join(PKG, "libmtd_b200.so")
-MEM_HOST, MEM_DEVICE, MEM_STAGED = 0, 1, 2
+MEM_HOST, MEM_DEVICE, MEM_STAGED, MEM_BUILT = 0, 1, 2, 3
 MODE_REPLAY, MODE_PHILOX = 0, 1
 DELTA_WORDS = 20
 APPLY_NONE, APPLY_LOCAL, APPLY_EXCHANGE = 0, 1, 2
@@ -27,7 +27,7 @@ EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mt
            "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced",
            "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts", "mtd_set_intervention_mask",
            "mtd_process_test_results", "mtd_enable_vaccination", "mtd_schedule_vaccinations", "mtd_set_vaccination",
-           "mtd_get_vaccination"]
+           "mtd_get_vaccination", "mtd_build_intervals", "mtd_get_intervals"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
 
 
@@ -217,6 +217,21 @@ class Handle:
 
     def exchange_ready(self):
         self._ck(self.lib.mtd_exchange_ready(self.h), "mtd_exchange_ready")
+
+    # ---- K8 interval builder
+    def build_intervals(self, ent_off, ent_ts, ent_cell, grp_off, grp_agent, grp_rescell, mem=MEM_HOST):
+        """itinerary.py:1403-1488 on the device -> length of the built interval stream (use mem=MEM_BUILT next)"""
+        n = C.c_int64(0)
+        self._ck(self.lib.mtd_build_intervals(self.h, C.c_int64(len(ent_off) - 1), _ptr(ent_off), _ptr(ent_ts), _ptr(ent_cell),
+                                              _ptr(grp_off), _ptr(grp_agent), _ptr(grp_rescell), mem, C.byref(n)),
+                 "mtd_build_intervals")
+        return int(n.value)
+
+    def get_intervals(self, n):
+        a, c = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        s, e = np.zeros(n, np.uint8), np.zeros(n, np.uint8)
+        self._ck(self.lib.mtd_get_intervals(self.h, C.c_int64(n), _ptr(a), _ptr(c), _ptr(s), _ptr(e), MEM_HOST), "mtd_get_intervals")
+        return a, c, s, e
 
     # ---- K7 vaccination
     def enable_vaccination(self, n_locals):

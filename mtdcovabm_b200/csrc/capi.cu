@@ -25,6 +25,10 @@ int launch_k7_schedule(const DevCtx &c, int64_t n_locals, long long k, int32_t *
 int launch_k7_replay(const DevCtx &c, int64_t n, const int32_t *ids, const int32_t *ts, int32_t *vacc_day, uint8_t *selected,
                      void *scratch, cudaStream_t st);
 int launch_k7_dose(const DevCtx &c, int day, int64_t n_locals, int32_t *vacc_day, cudaStream_t st, int sm_count);
+int launch_k8(int64_t n_itin, const int64_t *ent_off, const int16_t *ent_ts, const int32_t *ent_cell, const int64_t *grp_off,
+              const int32_t *grp_agent, const int32_t *grp_rescell, int32_t *count, int64_t *out_off, long long *scan_tmp,
+              int32_t *iv_agent, int32_t *iv_cell, uint8_t *iv_start, uint8_t *iv_end, int64_t cap, int *error,
+              cudaStream_t st, int sm_count);
 int launch_xchg_push(const DevExchange &x, int par, unsigned long long seq, cudaStream_t st);
 int launch_xchg_wait(const DevExchange &x, int par, unsigned long long seq, StateCounters *sctr, cudaStream_t st);
 int launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st, int sm_count);
@@ -54,6 +58,10 @@ struct mtd_handle_s {
     int32_t *sc_a1 = nullptr, *sc_a2 = nullptr; int64_t sc_cap_rows = 0; int64_t *sc_off = nullptr; int64_t sc_cap_off = 0;
     uint8_t *sc_se = nullptr; int64_t sc_cap_se = 0;
     uint8_t *agent_masked = nullptr; bool mask_on = false;
+    // K8 interval builder: device copies of the itinerary CSR + scratch; the built stream lives in d_iv_*
+    int64_t *k8_ent_off = nullptr, *k8_grp_off = nullptr, *k8_out_off = nullptr; int16_t *k8_ent_ts = nullptr;
+    int32_t *k8_ent_cell = nullptr, *k8_grp_agent = nullptr, *k8_grp_res = nullptr, *k8_count = nullptr; long long *k8_scan = nullptr;
+    int64_t k8_cap[9] = {}; int64_t built_n = -1;
     // K7 vaccination (allocated by mtd_enable_vaccination)
     int32_t *vacc_day = nullptr; uint8_t *vacc_selected = nullptr; void *vacc_scratch = nullptr; unsigned int *vacc_hist = nullptr;
     int64_t vacc_n_locals = 0; int32_t *vacc_ids = nullptr, *vacc_ts = nullptr; int64_t vacc_cap_ids = 0, vacc_cap_ts = 0;
@@ -267,7 +275,9 @@ extern "C" int mtd_destroy(mtd_handle h)
     if (h->state_stream) { cudaStreamSynchronize(h->state_stream); cudaStreamDestroy(h->state_stream); }
     if (h->ev_state) cudaEventDestroy(h->ev_state);
     if (h->ev_main) cudaEventDestroy(h->ev_main);
-    for (void *p : { (void *)h->sc_a1, (void *)h->sc_a2, (void *)h->sc_off, (void *)h->sc_se, (void *)h->vacc_ids, (void *)h->vacc_ts }) if (p) cudaFree(p);
+    for (void *p : { (void *)h->sc_a1, (void *)h->sc_a2, (void *)h->sc_off, (void *)h->sc_se, (void *)h->vacc_ids, (void *)h->vacc_ts,
+                     (void *)h->k8_ent_off, (void *)h->k8_grp_off, (void *)h->k8_out_off, (void *)h->k8_ent_ts, (void *)h->k8_ent_cell,
+                     (void *)h->k8_grp_agent, (void *)h->k8_grp_res, (void *)h->k8_count, (void *)h->k8_scan }) if (p) cudaFree(p);
     for (void *p : h->xchg_peers) cudaIpcCloseMemHandle(p);
     if (h->xchg_alloc) cudaFree(h->xchg_alloc);
     free_tape(h);
@@ -432,7 +442,11 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
         c.iv_agent = h->st_agent[sl]; c.iv_cell = h->st_cell[sl]; c.iv_start = h->st_start[sl]; c.iv_end = h->st_end[sl];
         c.iv_order = h->st_has_order[sl] ? h->st_order[sl] : nullptr;
         h->st_ready = -1;
+    } else if (mem == MTD_MEM_BUILT) {
+        if (h->built_n != M) { h->err = "MTD_MEM_BUILT without a matching mtd_build_intervals"; return MTD_E_STATE; }
+        c.iv_agent = h->d_iv_agent; c.iv_cell = h->d_iv_cell; c.iv_start = h->d_iv_start; c.iv_end = h->d_iv_end; c.iv_order = nullptr;
     } else if (mem == MTD_MEM_HOST) {
+        h->built_n = -1;                      // the staging buffers are overwritten
         StageScope sc(h, MTD_STAGE_H2D);
         size_t m = (size_t)M;
         CK(cudaMemcpyAsync(h->d_iv_agent, iv_agent, 4 * m, cudaMemcpyHostToDevice, h->stream));
@@ -565,6 +579,63 @@ extern "C" int mtd_apply_deltas(mtd_handle h, const int32_t *bufs, int64_t n_buf
     CK(cudaSetDevice(h->cfg.device));
     { int r = enqueue_apply(h, bufs, (int)n_bufs, cap, true, false, 0); if (r) return r; }
     CK(cudaGetLastError());
+    return MTD_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ K8 interval builder
+extern "C" int mtd_build_intervals(mtd_handle h, int64_t n_itin, const int64_t *ent_off, const int16_t *ent_ts,
+                                   const int32_t *ent_cell, const int64_t *grp_off, const int32_t *grp_agent,
+                                   const int32_t *grp_rescell, int mem, int64_t *n_intervals)
+{
+    if (!h || n_itin < 0 || !n_intervals || (n_itin && (!ent_off || !ent_ts || !ent_cell || !grp_off || !grp_agent || !grp_rescell))) {
+        if (h) h->err = "mtd_build_intervals: bad arguments"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    *n_intervals = 0; h->built_n = -1;
+    if (n_itin == 0) { h->built_n = 0; return MTD_OK; }
+    const int64_t *d_eo = ent_off, *d_go = grp_off; const int16_t *d_ts = ent_ts;
+    const int32_t *d_ec = ent_cell, *d_ga = grp_agent, *d_gr = grp_rescell;
+    int r;
+    if (mem == MTD_MEM_HOST) {
+        const int64_t n_ent = ent_off[n_itin], n_grp = grp_off[n_itin];
+        if ((r = grow_buf(h, &h->k8_ent_off, &h->k8_cap[0], n_itin + 1))) return r;
+        if ((r = grow_buf(h, &h->k8_grp_off, &h->k8_cap[1], n_itin + 1))) return r;
+        if ((r = grow_buf(h, &h->k8_ent_ts, &h->k8_cap[2], n_ent + 1))) return r;
+        if ((r = grow_buf(h, &h->k8_ent_cell, &h->k8_cap[3], n_ent + 1))) return r;
+        if ((r = grow_buf(h, &h->k8_grp_agent, &h->k8_cap[4], n_grp + 1))) return r;
+        if ((r = grow_buf(h, &h->k8_grp_res, &h->k8_cap[5], n_grp + 1))) return r;
+        CK(cudaMemcpyAsync(h->k8_ent_off, ent_off, 8 * (size_t)(n_itin + 1), cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->k8_grp_off, grp_off, 8 * (size_t)(n_itin + 1), cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->k8_ent_ts, ent_ts, 2 * (size_t)n_ent, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->k8_ent_cell, ent_cell, 4 * (size_t)n_ent, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->k8_grp_agent, grp_agent, 4 * (size_t)n_grp, cudaMemcpyHostToDevice, h->stream));
+        CK(cudaMemcpyAsync(h->k8_grp_res, grp_rescell, 4 * (size_t)n_grp, cudaMemcpyHostToDevice, h->stream));
+        d_eo = h->k8_ent_off; d_go = h->k8_grp_off; d_ts = h->k8_ent_ts; d_ec = h->k8_ent_cell; d_ga = h->k8_grp_agent; d_gr = h->k8_grp_res;
+    }
+    if ((r = grow_buf(h, &h->k8_count, &h->k8_cap[6], n_itin + 1))) return r;
+    if ((r = grow_buf(h, &h->k8_out_off, &h->k8_cap[7], n_itin + 2))) return r;
+    if ((r = grow_buf(h, &h->k8_scan, &h->k8_cap[8], 2 * ((n_itin + 2) / 2048 + 16)))) return r;
+    int *d_err = (int *)(h->occ + 7);          // spare word behind the six occupancy counters
+    CK(cudaMemsetAsync(d_err, 0, sizeof(int), h->stream));
+    launch_k8(n_itin, d_eo, d_ts, d_ec, d_go, d_ga, d_gr, h->k8_count, h->k8_out_off, h->k8_scan, h->d_iv_agent, h->d_iv_cell,
+              h->d_iv_start, h->d_iv_end, h->c.cap_intervals, d_err, h->stream, h->sm_count);
+    int64_t total = 0; int err = 0;
+    CK(cudaMemcpyAsync(&total, h->k8_out_off + n_itin, sizeof(int64_t), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(&err, d_err, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
+    *n_intervals = total;
+    if (err || total > h->c.cap_intervals) { h->err = "mtd_build_intervals: the built stream exceeds max_intervals"; return MTD_E_CAPACITY; }
+    h->built_n = total;
+    return MTD_OK;
+}
+
+extern "C" int mtd_get_intervals(mtd_handle h, int64_t n, int32_t *iv_agent, int32_t *iv_cell, uint8_t *iv_start, uint8_t *iv_end, int mem)
+{
+    if (!h || n < 0 || n != h->built_n) { if (h) h->err = "mtd_get_intervals: n does not match the built stream"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    COPY_OUT(iv_agent, h->d_iv_agent, 4 * (size_t)n); COPY_OUT(iv_cell, h->d_iv_cell, 4 * (size_t)n);
+    COPY_OUT(iv_start, h->d_iv_start, (size_t)n); COPY_OUT(iv_end, h->d_iv_end, (size_t)n);
+    CK(cudaStreamSynchronize(h->stream));
     return MTD_OK;
 }
 

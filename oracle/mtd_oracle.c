@@ -655,6 +655,38 @@ int64_t mtdo_transmission(const mtdo_params *P, const mtdo_dayctx *D, int64_t M,
 }
 
 /* ------------------------------------------------------------------ seirstateutil.update_agent_state (seirstateutil.py:38-72) */
+/* Interval builder: Itinerary.update_cell_agents_timesteps + combine_same_cell_itinerary_entries
+ * (itinerary.py:1403-1488).  Itineraries as CSR (entries sorted by timestep; cell -1 = residence) + agent groups.
+ * Writes the interval stream in emission order; returns its length (or -1 if cap is too small). */
+int64_t mtdo_build_intervals(int64_t n_itin, const int64_t *ent_off, const int16_t *ent_ts, const int32_t *ent_cell,
+                             const int64_t *grp_off, const int32_t *grp_agent, const int32_t *grp_rescell, int64_t cap,
+                             int32_t *iv_agent, int32_t *iv_cell, uint8_t *iv_start, uint8_t *iv_end)
+{
+    int64_t out = 0;
+    for (int64_t t = 0; t < n_itin; t++) {
+        /* combine_same_cell_itinerary_entries (:1459-1488): keep the first entry of every run of equal cells */
+        int64_t kept[512]; int nk = 0;
+        for (int64_t k = ent_off[t]; k < ent_off[t + 1]; k++)
+            if (nk == 0 || ent_cell[k] != ent_cell[kept[nk - 1]]) { if (nk < 512) kept[nk++] = k; }
+        for (int i = 0; i < nk; i++) {
+            int start = ent_ts[kept[i]], end;                                /* :1413-1433 */
+            if (i == 0) { start = 0; end = 143; if (nk > 1) end = ent_ts[kept[1]]; }
+            else if (i == nk - 1) end = 143;
+            else end = ent_ts[kept[i + 1]];
+            if (start == end) continue;                                      /* :1435 */
+            int32_t cell = ent_cell[kept[i]];
+            for (int64_t g = grp_off[t]; g < grp_off[t + 1]; g++) {
+                if (cell == -1) cell = grp_rescell[g];                       /* :1439-1440: sticks after the first agent */
+                if (out >= cap) return -1;
+                iv_agent[out] = grp_agent[g]; iv_cell[out] = cell;
+                iv_start[out] = (uint8_t)(start < 0 ? 0 : start); iv_end[out] = (uint8_t)(end > 143 ? 143 : (end < 0 ? 0 : end));
+                out++;
+            }
+        }
+    }
+    return out;
+}
+
 /* Vaccination scheduling (Epidemiology.schedule_vaccinations, epidemiology.py:911-976), device part: k locals without a
  * dose, drawn without replacement, get the record [day + 1, timestep].  Philox mode: the k smallest keys
  * (philox(day, agent; site 7).w0 << 32 | agent) -- a uniform k-subset like np.random.choice(replace=False); timestep =

@@ -222,6 +222,19 @@ def advance(day, agents: AgentState, mask=None):
     return lib().mtdo_advance(C.c_int32(day), C.byref(a), _p(mask))
 
 
+def build_intervals(ent_off, ent_ts, ent_cell, grp_off, grp_agent, grp_rescell, cap):
+    """itinerary.py:1403-1488 -> (iv_agent, iv_cell, iv_start, iv_end) in emission order"""
+    a, c = np.zeros(cap, np.int32), np.zeros(cap, np.int32)
+    s, e = np.zeros(cap, np.uint8), np.zeros(cap, np.uint8)
+    L = lib()
+    L.mtdo_build_intervals.restype = C.c_int64
+    n = L.mtdo_build_intervals(C.c_int64(len(ent_off) - 1), _p(ent_off), _p(ent_ts), _p(ent_cell), _p(grp_off), _p(grp_agent),
+                               _p(grp_rescell), C.c_int64(cap), _p(a), _p(c), _p(s), _p(e))
+    if n < 0:
+        raise RuntimeError("oracle: interval capacity exceeded")
+    return a[:n].copy(), c[:n].copy(), s[:n].copy(), e[:n].copy()
+
+
 def schedule_vaccinations(ctx, n_locals, k, last_dose_day, vacc_day):
     """epidemiology.py:911-976 (device part): mutates vacc_day [n][2] -> ascending ids scheduled"""
     sel = np.zeros(len(last_dose_day), np.uint8)
