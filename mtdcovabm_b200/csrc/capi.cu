@@ -464,7 +464,8 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     CK(cudaMemsetAsync(c.cell_first, 0xff, sizeof(uint32_t) * (size_t)c.n_cells, h->stream));
     { StageScope sc(h, MTD_STAGE_K0); sc.add(launch_k0(c, h->scan_tmp, h->stream, h->sm_count)); }
     if (h->ev_k0_done) CK(cudaEventRecord(h->ev_k0_done, h->stream));      // the interval stream has been consumed
-    { StageScope sc(h, MTD_STAGE_K1); sc.add(launch_k1(c, h->stream, h->aux_stream, h->aux2_stream, h->ev_fork, h->ev_join, h->ev_join2, h->sm_count)); }
+    // an empty day (M == 0) has no cells: the zeroed counters are its result
+    if (M > 0) { StageScope sc(h, MTD_STAGE_K1); sc.add(launch_k1(c, h->stream, h->aux_stream, h->aux2_stream, h->ev_fork, h->ev_join, h->ev_join2, h->sm_count)); }
     c.rows12 = nullptr;
     if (h->export_on) {     // K2 also packs the rows for the export; the slot's previous export must have drained
         const int sl = (int)(h->day_seq & 1);
@@ -473,8 +474,8 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
         c.rows12 = h->rows12_buf[sl];
     }
     h->day_seq++;
-    { StageScope sc(h, MTD_STAGE_K2); sc.add(launch_scan_nrows(c, h->scan_tmp, h->stream));
-      sc.add(launch_k2_compact(c, h->stream, h->sm_count)); }
+    if (M > 0) { StageScope sc(h, MTD_STAGE_K2); sc.add(launch_scan_nrows(c, h->scan_tmp, h->stream));
+                 sc.add(launch_k2_compact(c, h->stream, h->sm_count)); }
     CK(cudaGetLastError());
     h->day_ready = true;
     return MTD_OK;
