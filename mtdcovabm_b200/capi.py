@@ -324,6 +324,26 @@ class Handle:
                                                    C.byref(n), MEM_HOST), "mtd_process_test_results")
         return ids[:n.value].copy()
 
+    def process_test_results_device(self, day: Day, ids_dev, epi_present_dev=None):
+        """K6 with DEVICE buffers (torch tensors): fills ids_dev (int32) -> number of traced agents"""
+        n = C.c_int64(0)
+        self._ck(self.lib.mtd_process_test_results(self.h, C.byref(day), _ptr(epi_present_dev), _ptr(ids_dev),
+                                                   C.c_int64(ids_dev.numel()), C.byref(n), MEM_DEVICE),
+                 "mtd_process_test_results")
+        return int(n.value)
+
+    def trace_stats(self) -> "TraceStats":
+        st = TraceStats()
+        self._ck(self.lib.mtd_get_traced(self.h, None, None, C.byref(st), MEM_HOST), "mtd_get_traced")
+        return st
+
+    def schedule_vaccinations_count(self, day: Day, k):
+        """K7 without copying the selection flags out -> number of agents scheduled"""
+        n = C.c_int64(0)
+        self._ck(self.lib.mtd_schedule_vaccinations(self.h, C.byref(day), C.c_int64(k), C.c_int64(0), None, None, None,
+                                                    C.byref(n), MEM_HOST), "mtd_schedule_vaccinations")
+        return int(n.value)
+
     def get_traced(self):
         """-> (primary flags uint8[N], secondary flags uint8[N], TraceStats)"""
         prim = np.zeros(self.n_agents, np.uint8); sec = np.zeros(self.n_agents, np.uint8)

@@ -782,7 +782,7 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, uint32_t 
 }
 
 template <int MM, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) k1_large_kernel(DevCtx g, int cls, int64_t bits_off)
+__global__ void __launch_bounds__(WARPS * 32, (MM == 128 ? 8 : 1)) k1_large_kernel(DevCtx g, int cls, int64_t bits_off)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
