@@ -83,6 +83,31 @@ class Epidemiology:
             bridge.scatter(h.get_state(), exposed, self.agents_epi, vu)
         return exposed
 
+    # ------------------------------------------------------------------ small host-side helpers of the class
+    def update_quarantine(self, agent, new_start_day, new_start_ts, new_end_day, new_end_ts):
+        """epidemiology.py:627-630: overwrite the agent's quarantine record [start day, timestep, end day]"""
+        agent["quarantine_days"] = [new_start_day, new_start_ts, new_end_day]
+
+    def convert_celltype_to_base_infection_prob(self, cellid, rescellid, celltype=None):
+        """epidemiology.py:998-1014 (the table K3 applies per row; quirk kept: a workplace counts as "workplace" only
+        when it is the exposed agent's RESIDENCE cell)"""
+        from . import util
+        from .epidemiologyclasses import SimCellType
+        P = self.params
+        sct = util.convert_celltype_to_simcelltype(cellid, celltype=celltype)
+        if sct == SimCellType.Residence:
+            return P.p_household
+        if sct == SimCellType.Workplace:
+            return P.p_workplace if cellid == rescellid else P.p_community
+        if sct == SimCellType.School:
+            return P.p_school
+        return P.p_community
+
+    def convert_simcelltype_to_contact_tracing_success_prob(self, simcelltype):
+        """epidemiology.py:978-996 (the table K5 applies per scanned row)"""
+        i = int(simcelltype)
+        return self.params.tracing_success_prob[i] if 0 <= i <= 3 else self.params.tracing_success_prob[3]
+
     # ------------------------------------------------------------------ vaccination (K7)
     def schedule_vaccinations(self, day):
         """epidemiology.py:911-976 -> ids of the agents scheduled for day + 1.  The bookkeeping on dyn_params

@@ -85,3 +85,23 @@ def test_k4_transition_table_matches_reference_on_every_input():
     assert np.array_equal(d["inf_sev"], T[:, 6].astype(np.int8))
     assert np.all(d["sched_cnt"] == 1) and np.all(d["sched"][:, 0] == sched[:, 1])
     h.close()
+
+
+def test_epidemiology_table_helpers():
+    """Epidemiology.convert_celltype_to_base_infection_prob / convert_simcelltype_to_contact_tracing_success_prob /
+    update_quarantine (epidemiology.py:627-630, 978-1014) against the parameter file"""
+    from types import SimpleNamespace
+    from mtdcovabm_b200 import params as prm
+    from mtdcovabm_b200.epidemiology import Epidemiology
+    ep = prm.load_json("epidemiology.json")
+    e = Epidemiology(ep, 10, 0, 1.0, None, {}, SimpleNamespace(), {}, {}, {}, SimpleNamespace())
+    hh, wp, sc, cm = e.params.p_household, e.params.p_workplace, e.params.p_school, e.params.p_community
+    assert e.convert_celltype_to_base_infection_prob(5, 5, celltype=CellType.Household) == hh
+    assert e.convert_celltype_to_base_infection_prob(5, 5, celltype=CellType.Workplace) == wp       # lives there
+    assert e.convert_celltype_to_base_infection_prob(5, 6, celltype=CellType.Workplace) == cm       # quirk: visitor
+    assert e.convert_celltype_to_base_infection_prob(5, 6, celltype=CellType.Classroom) == sc
+    assert e.convert_celltype_to_base_infection_prob(5, 6, celltype=CellType.Transport) == cm
+    assert [e.convert_simcelltype_to_contact_tracing_success_prob(k) for k in range(4)] == list(ep["contact_tracing_success_probability"])
+    agent = {"quarantine_days": None}
+    e.update_quarantine(agent, 3, 50, 17, 60)
+    assert agent["quarantine_days"] == [3, 50, 17]
