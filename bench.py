@@ -183,10 +183,17 @@ def run_reference(args):
         return
     sample = args.cpu_sample_agents or 200_000
     r = cpu_oracle_run(args, max(1, args.steps), max(1, min(args.warmup, 2)), sample)
+    # same `config` as the B200 arm (the workload the metric is quoted on); the bounded sample each step really ran is
+    # described in cpu_baseline.sample
+    from mtdcovabm_b200 import synth
+    bank = synth.load_bank()
+    n1 = int(bank["present"].sum())
+    reps_full = max(1, round(args.agents / n1))
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "int32+f64", "data": "synthetic",
-            "config": workload_config(args, r["agents"], None, None),
+            "config": workload_config(args, n1 * reps_full, int(len(bank["d0_iv_agent"])) * reps_full,
+                                      int(len(bank["cell_type"])) * reps_full),
             "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
                              "sample": r["sample"]},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
