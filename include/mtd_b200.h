@@ -145,6 +145,19 @@ int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, int64_t n_int
  * handle's own buffer.  Multi-GPU: pass this rank's slice of the allgather buffer with apply == 0, allgather, then
  * mtd_apply_deltas over all n_bufs slices. */
 int mtd_simulate_direct_contacts(mtd_handle h, const mtd_day *day, int32_t *delta_buf, int64_t cap_records, int apply);
+/* K9: Epidemiology.simulate_seir_state_transition(current_day, agent, id, incremental_days, overlapping_timesteps, ...)
+ * called on its own (epidemiology.py:233-500) -- the itinerary stage's initial cases: on simulated day 1 every agent that
+ * starts Infectious is given an exposure day in [day - pre_exposure_days, day) and its whole trajectory is sampled
+ * from there (itinerary.py:373-395), with the states reset to those preceding the first transition still ahead
+ * (reset_states, epidemiology.py:243).  n DISTINCT agent ids; exposure_day[n] or NULL (drawn on the device, Philox mode
+ * only); timesteps[n_timesteps] = the overlapping_timesteps list shared by the batch (the itinerary passes
+ * arange(144)); asym_mult[n] or NULL (1.0, the reference's default); draws: replay mode, n x MTD_EXPO_W doubles in the
+ * slot layout of the tape's exposure records, else NULL; out8 (optional): 8 int32 per case = [seir state, infection
+ * type, severity, recovered, schedule entries appended, exposure timestep, exposure day, symptomatic day or -1].
+ * HOST pointers; synchronous.  Schedule entries, states, test and hospitalisation records go to the handle's state. */
+int mtd_seed_exposures(mtd_handle h, const mtd_day *day, int64_t n, const int32_t *agent_ids, const int32_t *exposure_day,
+                       int32_t pre_exposure_days, const uint8_t *timesteps, int32_t n_timesteps, const double *asym_mult,
+                       const double *draws, int32_t *out8);
 /* Epidemiology.simulate_direct_contacts(agents_directcontacts, cellid, cell_type, day) called on its own
  * (epidemiology.py:88): the caller's contact pairs of ONE cell with their overlap lists [(start, end), ...]
  * (ov_off[n_rows + 1] offsets into ov_se, two bytes per overlap) become the day's dense rows, in the order given;

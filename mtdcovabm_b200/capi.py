@@ -25,7 +25,7 @@ EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mt
            "mtd_get_contacts", "mtd_get_exposed", "mtd_get_infection_prob", "mtd_occupancy", "mtd_sync",
            "mtd_set_profiling", "mtd_get_stage_ms", "mtd_set_export", "mtd_prefetch_intervals",
            "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced",
-           "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts", "mtd_set_intervention_mask",
+           "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts", "mtd_seed_exposures", "mtd_set_intervention_mask",
            "mtd_process_test_results", "mtd_enable_vaccination", "mtd_schedule_vaccinations", "mtd_set_vaccination",
            "mtd_get_vaccination", "mtd_build_intervals", "mtd_get_intervals"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
@@ -200,6 +200,24 @@ class Handle:
         """the caller's contact pairs of one cell + overlap lists become the day's rows (host numpy arrays)"""
         self._ck(self.lib.mtd_set_contacts(self.h, C.byref(day), C.c_int32(cellid), C.c_int64(len(a1)), _ptr(a1), _ptr(a2),
                                            _ptr(ov_off), _ptr(ov_se), MEM_HOST), "mtd_set_contacts")
+
+    def seed_exposures(self, day: Day, agent_ids, exposure_day=None, pre_exposure_days=0, timesteps=None, asym_mult=None,
+                       draws=None):
+        """K9: trajectories of agents exposed before the start of the simulation (itinerary.py:373-395 ->
+        epidemiology.py:233-500 with reset_states).  Host numpy arrays.  -> int32 [n, 8]: seir, infection type, severity,
+        recovered, entries appended, exposure timestep, exposure day, symptomatic day"""
+        ids = np.ascontiguousarray(agent_ids, np.int32)
+        n = len(ids)
+        ts = np.ascontiguousarray(np.arange(144) if timesteps is None else timesteps, np.uint8)
+        ed = None if exposure_day is None else np.ascontiguousarray(exposure_day, np.int32)
+        am = None if asym_mult is None else np.ascontiguousarray(asym_mult, np.float64)
+        dr = None if draws is None else np.ascontiguousarray(draws, np.float64)
+        if (ed is not None and len(ed) != n) or (am is not None and len(am) != n) or (dr is not None and dr.size != n * EXPO_W):
+            raise ValueError("seed_exposures: per-case arrays must have one entry (draws: EXPO_W entries) per agent id")
+        out = np.zeros((n, 8), np.int32)
+        self._ck(self.lib.mtd_seed_exposures(self.h, C.byref(day), C.c_int64(n), _ptr(ids), _ptr(ed), C.c_int32(pre_exposure_days),
+                                             _ptr(ts), C.c_int32(len(ts)), _ptr(am), _ptr(dr), _ptr(out)), "mtd_seed_exposures")
+        return out
 
     def apply_deltas(self, bufs, n_bufs, cap_records):
         self._ck(self.lib.mtd_apply_deltas(self.h, _ptr(bufs), C.c_int64(n_bufs), C.c_int64(cap_records)),

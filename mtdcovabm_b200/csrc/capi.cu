@@ -25,6 +25,8 @@ int launch_k7_schedule(const DevCtx &c, int64_t n_locals, long long k, int32_t *
 int launch_k7_replay(const DevCtx &c, int64_t n, const int32_t *ids, const int32_t *ts, int32_t *vacc_day, uint8_t *selected,
                      void *scratch, cudaStream_t st);
 int launch_k7_dose(const DevCtx &c, int day, int64_t n_locals, int32_t *vacc_day, cudaStream_t st, int sm_count);
+int launch_k9_seed(const DevCtx &c, int64_t n, const int32_t *ids, const int32_t *expo_day, int pre_days, const uint8_t *ts_list,
+                   int n_ts, const double *asym_mult, const double *draws, int32_t *out, int32_t *status, cudaStream_t st);
 int launch_k8(int64_t n_itin, const int64_t *ent_off, const int16_t *ent_ts, const int32_t *ent_cell, const int64_t *grp_off,
               const int32_t *grp_agent, const int32_t *grp_rescell, int32_t *count, int64_t *out_off, long long *scan_tmp,
               int32_t *iv_agent, int32_t *iv_cell, uint8_t *iv_start, uint8_t *iv_end, int64_t cap, int *error,
@@ -58,6 +60,7 @@ struct mtd_handle_s {
     int32_t *sc_a1 = nullptr, *sc_a2 = nullptr; int64_t sc_cap_rows = 0; int64_t *sc_off = nullptr; int64_t sc_cap_off = 0;
     uint8_t *sc_se = nullptr; int64_t sc_cap_se = 0;
     uint8_t *agent_masked = nullptr; bool mask_on = false;
+    uint8_t *seed_buf = nullptr; int64_t seed_cap = 0;        // staging of mtd_seed_exposures
     // K8 interval builder: device copies of the itinerary CSR + scratch; the built stream lives in d_iv_*
     int64_t *k8_ent_off = nullptr, *k8_grp_off = nullptr, *k8_out_off = nullptr; int16_t *k8_ent_ts = nullptr;
     int32_t *k8_ent_cell = nullptr, *k8_grp_agent = nullptr, *k8_grp_res = nullptr, *k8_count = nullptr; long long *k8_scan = nullptr;
@@ -275,7 +278,7 @@ extern "C" int mtd_destroy(mtd_handle h)
     if (h->state_stream) { cudaStreamSynchronize(h->state_stream); cudaStreamDestroy(h->state_stream); }
     if (h->ev_state) cudaEventDestroy(h->ev_state);
     if (h->ev_main) cudaEventDestroy(h->ev_main);
-    for (void *p : { (void *)h->sc_a1, (void *)h->sc_a2, (void *)h->sc_off, (void *)h->sc_se, (void *)h->vacc_ids, (void *)h->vacc_ts,
+    for (void *p : { (void *)h->seed_buf, (void *)h->sc_a1, (void *)h->sc_a2, (void *)h->sc_off, (void *)h->sc_se, (void *)h->vacc_ids, (void *)h->vacc_ts,
                      (void *)h->k8_ent_off, (void *)h->k8_grp_off, (void *)h->k8_out_off, (void *)h->k8_ent_ts, (void *)h->k8_ent_cell,
                      (void *)h->k8_grp_agent, (void *)h->k8_grp_res, (void *)h->k8_count, (void *)h->k8_scan }) if (p) cudaFree(p);
     for (void *p : h->xchg_peers) cudaIpcCloseMemHandle(p);
@@ -571,6 +574,44 @@ extern "C" int mtd_set_contacts(mtd_handle h, const mtd_day *day, int32_t cellid
     CK(cudaStreamSynchronize(h->stream));          // the host buffers may be released by the caller
     CK(cudaGetLastError());
     h->day_ready = true;
+    return MTD_OK;
+}
+
+extern "C" int mtd_seed_exposures(mtd_handle h, const mtd_day *day, int64_t n, const int32_t *agent_ids, const int32_t *exposure_day,
+                                  int32_t pre_exposure_days, const uint8_t *timesteps, int32_t n_timesteps, const double *asym_mult,
+                                  const double *draws, int32_t *out8)
+{
+    if (!h || !day || n < 0 || (n && (!agent_ids || !timesteps)) || n_timesteps <= 0) { if (h) h->err = "mtd_seed_exposures: bad arguments"; return MTD_E_ARG; }
+    if (day->mode == MTD_MODE_REPLAY && n && (!draws || !exposure_day)) { h->err = "mtd_seed_exposures: replay mode needs draws and exposure days"; return MTD_E_ARG; }
+    if (!exposure_day && pre_exposure_days <= 0) { h->err = "mtd_seed_exposures: pre_exposure_days must be positive"; return MTD_E_ARG; }
+    if (!(h->have_params && h->have_static)) { h->err = "params / static not set"; return MTD_E_STATE; }
+    if (n == 0) return MTD_OK;
+    CK(cudaSetDevice(h->cfg.device));
+    TOUCH();
+    h->c.day = *day;
+    const size_t N = (size_t)n, W = MTD_EXPO_W;
+    const size_t o_draws = 0, o_asym = o_draws + 8 * W * N, o_out = o_asym + 8 * N, o_ids = o_out + 32 * N, o_day = o_ids + 4 * N,
+                 o_status = o_day + 4 * N, o_ts = o_status + 16, total = o_ts + (size_t)n_timesteps + 16;
+    { int r = grow_buf(h, &h->seed_buf, &h->seed_cap, (int64_t)total); if (r) return r; }
+    uint8_t *B = h->seed_buf;
+    CK(cudaMemsetAsync(B + o_status, 0, 16, h->stream));
+    CK(cudaMemcpyAsync(B + o_ids, agent_ids, 4 * N, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(B + o_ts, timesteps, (size_t)n_timesteps, cudaMemcpyHostToDevice, h->stream));
+    if (exposure_day) CK(cudaMemcpyAsync(B + o_day, exposure_day, 4 * N, cudaMemcpyHostToDevice, h->stream));
+    if (asym_mult) CK(cudaMemcpyAsync(B + o_asym, asym_mult, 8 * N, cudaMemcpyHostToDevice, h->stream));
+    if (draws) CK(cudaMemcpyAsync(B + o_draws, draws, 8 * W * N, cudaMemcpyHostToDevice, h->stream));
+    { StageScope sc(h, MTD_STAGE_K3_EVAL);
+      sc.add(launch_k9_seed(h->c, n, (const int32_t *)(B + o_ids), exposure_day ? (const int32_t *)(B + o_day) : nullptr, pre_exposure_days,
+                            B + o_ts, n_timesteps, asym_mult ? (const double *)(B + o_asym) : nullptr,
+                            draws ? (const double *)(B + o_draws) : nullptr, (int32_t *)(B + o_out), (int32_t *)(B + o_status), h->stream)); }
+    int32_t status[4] = { 0, 0, 0, 0 };
+    CK(cudaMemcpyAsync(status, B + o_status, 16, cudaMemcpyDeviceToHost, h->stream));
+    if (out8) CK(cudaMemcpyAsync(out8, B + o_out, 32 * N, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
+    if (status[0]) { h->err = "mtd_seed_exposures: agent id out of range"; return status[0]; }
+    if (status[1]) { h->err = "mtd_seed_exposures: schedule overflow (MTD_MAXSCHED entries per agent)"; return MTD_E_CAPACITY; }
+    if (status[2]) { h->err = "mtd_seed_exposures: replay draws missing (NaN slot read)"; return MTD_E_STATE; }
     return MTD_OK;
 }
 

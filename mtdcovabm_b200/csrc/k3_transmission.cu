@@ -137,6 +137,64 @@ __device__ __forceinline__ double philox_slot_draw(const DevCtx &c, const mtd_pa
     return u53(w[0], w[1]);
 }
 
+
+// simulate_seir_state_transition + schedule_test / schedule_quarantine as reached from it (epidemiology.py:233-500):
+// the whole future trajectory of one exposure, sampled at once.  `incr0` is the exposure day (today for a contact of the
+// day step; a day before the start of the simulation for the itinerary's initial cases, itinerary.py:373-395); entries
+// dated before `current_day` are dropped (:255,280,...) and `first_T` remembers the first one kept, which decides the
+// states of an agent exposed before day 1 (reset_states, :243).
+struct Traj {
+    int ns, inf_type, first_T, recovered, symptomatic_day, start_hosp, end_hosp, test_day, test_ts, tres_day;
+    int32_t sched[6];
+};
+
+__device__ __forceinline__ void sample_trajectory(const mtd_params *P, Draws &D, int b, int current_day, int incr0, int ts,
+                                                  double asym, bool testing_enabled, bool quarantine_enabled, bool has_test,
+                                                  Traj &t)
+{
+    int incr = incr0, ns = 0, first_T = -1;
+#define STEP(T) do { incr += D.lognormal_days(1 + (T)); \
+                     if (incr >= current_day && ns < 6) { if (ns == 0) first_T = (T); \
+                         t.sched[ns++] = (int32_t)(((uint32_t)incr << 16) | ((uint32_t)(T) << 8) | (uint32_t)ts); } } while (0)
+    int symptomatic_day = -1, recovered = 0, start_hosp = MTD_NONE, end_hosp = MTD_NONE, inf_type;
+    STEP(T_EXP_INF);
+    if (D.uniform(11) < P->probs_by_age[1][b] * asym) {
+        inf_type = IT_PRESYMP;
+        STEP(T_INF_SYMP); symptomatic_day = incr;
+        if (D.uniform(12) < P->probs_by_age[2][b]) {
+            STEP(T_SYMP_SEV); start_hosp = incr;
+            if (D.uniform(13) < P->probs_by_age[3][b]) {
+                STEP(T_SEV_CRI);
+                if (D.uniform(14) < P->probs_by_age[4][b]) { STEP(T_CRI_DEATH); end_hosp = incr; }
+                else { STEP(T_CRI_REC); end_hosp = incr; recovered = 1; }
+            } else { STEP(T_SEV_REC); end_hosp = incr; recovered = 1; }
+        } else { STEP(T_MILD_REC); recovered = 1; }
+    } else {
+        inf_type = IT_PREASYMP;
+        STEP(T_ASYMP_REC); recovered = 1;
+    }
+    if (recovered) STEP(T_REC_SUS);
+#undef STEP
+    int test_day = MTD_NONE, test_ts = 0, tres_day = MTD_NONE;
+    if (symptomatic_day > -1) {
+        int tts = D.timestep_option(15);                                            // epidemiology.py:480
+        if (testing_enabled && !has_test) {                                         // schedule_test :502-565
+            if (D.uniform(16) < P->testing_after_symptoms_probability) {
+                test_day = symptomatic_day + D.lognormal_days(17);
+                test_ts = tts;
+                tres_day = test_day + D.lognormal_days(18);
+            }
+        }
+        (void)D.timestep_option(19);                                                // epidemiology.py:496
+        // schedule_quarantine(Symptomatic) draws one uniform; its result is overwritten by the caller with the
+        // value read before the call (epidemiology.py:206,216; itinerary.py:390) -> no state change, only the draw
+        // is consumed.
+        if (quarantine_enabled) (void)D.uniform(20);
+    }
+    t.ns = ns; t.inf_type = inf_type; t.first_T = first_T; t.recovered = recovered; t.symptomatic_day = symptomatic_day;
+    t.start_hosp = start_hosp; t.end_hosp = end_hosp; t.test_day = test_day; t.test_ts = test_ts; t.tres_day = tres_day;
+}
+
 #define K3T_WARPS 4
 #define K3T_MAXIV 16
 // one WARP per successful draw; only the winner of each agent samples the trajectory
@@ -234,50 +292,15 @@ __global__ void __launch_bounds__(K3T_WARPS * 32) k3_trajectory_kernel(DevCtx c,
         if (lane != 0) continue;                             // the branchy remainder is one lane's work
         double imm, asym;
         vacc_multipliers(P, c.last_dose_day[ex], c.day.day, imm, asym);
-        const int b = c.epi_age_bracket[ex];
-        const int current_day = c.day.day;
-        int incr = current_day;
         int32_t rec[MTD_DELTA_WORDS];
 #pragma unroll
         for (int k = 0; k < MTD_DELTA_WORDS; k++) rec[k] = 0;
-        int ns = 0;
-        int32_t sched[6];
-#define STEP(T) do { incr += D.lognormal_days(1 + (T)); \
-                     if (incr >= current_day && ns < 6) sched[ns++] = (int32_t)(((uint32_t)incr << 16) | ((uint32_t)(T) << 8) | (uint32_t)ts); } while (0)
-        int symptomatic_day = -1, recovered = 0, start_hosp = MTD_NONE, end_hosp = MTD_NONE, inf_type;
-        STEP(T_EXP_INF);
-        if (D.uniform(11) < P->probs_by_age[1][b] * asym) {
-            inf_type = IT_PRESYMP;
-            STEP(T_INF_SYMP); symptomatic_day = incr;
-            if (D.uniform(12) < P->probs_by_age[2][b]) {
-                STEP(T_SYMP_SEV); start_hosp = incr;
-                if (D.uniform(13) < P->probs_by_age[3][b]) {
-                    STEP(T_SEV_CRI);
-                    if (D.uniform(14) < P->probs_by_age[4][b]) { STEP(T_CRI_DEATH); end_hosp = incr; }
-                    else { STEP(T_CRI_REC); end_hosp = incr; recovered = 1; }
-                } else { STEP(T_SEV_REC); end_hosp = incr; recovered = 1; }
-            } else { STEP(T_MILD_REC); recovered = 1; }
-        } else {
-            inf_type = IT_PREASYMP;
-            STEP(T_ASYMP_REC); recovered = 1;
-        }
-        if (recovered) STEP(T_REC_SUS);
-#undef STEP
-        int test_day = MTD_NONE, test_ts = 0, tres_day = MTD_NONE;
-        if (symptomatic_day > -1) {
-            int tts = D.timestep_option(15);                                            // epidemiology.py:480
-            if (c.day.testing_enabled && c.test_day[2 * (int64_t)ex] == MTD_NONE) {     // schedule_test :502-565
-                if (D.uniform(16) < P->testing_after_symptoms_probability) {
-                    test_day = symptomatic_day + D.lognormal_days(17);
-                    test_ts = tts;
-                    tres_day = test_day + D.lognormal_days(18);
-                }
-            }
-            (void)D.timestep_option(19);                                                // epidemiology.py:496
-            // schedule_quarantine(Symptomatic) draws one uniform; its result is overwritten by the caller with the
-            // value read before the call (epidemiology.py:206,216) -> no state change, only the draw is consumed.
-            if (c.day.quarantine_enabled) (void)D.uniform(20);
-        }
+        Traj T;
+        sample_trajectory(P, D, c.epi_age_bracket[ex], c.day.day, c.day.day, ts, asym, c.day.testing_enabled != 0,
+                          c.day.quarantine_enabled != 0, c.test_day[2 * (int64_t)ex] != MTD_NONE, T);
+        const int ns = T.ns, inf_type = T.inf_type, test_day = T.test_day, test_ts = T.test_ts, tres_day = T.tres_day;
+        const int start_hosp = T.start_hosp, end_hosp = T.end_hosp;
+        const int32_t *sched = T.sched;
         if (D.miss) atomicAdd(&c.ctr->tape_miss, D.miss);
         rec[0] = ex; rec[1] = (int32_t)(uint32_t)key; rec[2] = (int32_t)(uint32_t)(key >> 32);
         rec[3] = inf_type | (ns << 8);
@@ -290,6 +313,77 @@ __global__ void __launch_bounds__(K3T_WARPS * 32) k3_trajectory_kernel(DevCtx c,
 #pragma unroll
             for (int k = 0; k < MTD_DELTA_WORDS / 4; k++) dst[k] = make_int4(rec[4 * k], rec[4 * k + 1], rec[4 * k + 2], rec[4 * k + 3]);
         } else c.ctr->error = MTD_E_CAPACITY;
+    }
+}
+
+// K9 -- the itinerary stage's initial cases (itinerary.py:373-395): on the first simulated day every agent that starts
+// Infectious gets an exposure day inside the last `pre_days` days and a full trajectory from it
+// (Epidemiology.simulate_seir_state_transition with incremental_days < 1, epidemiology.py:233-500).  Transitions dated
+// before today are dropped; the agent's states are reset to the states PRECEDING the first transition kept (:243,
+// :257-470, as written: an agent still waiting for ExposedToInfectious is (Exposed, PreAsymptomatic) whatever its
+// branch, and an agent whose whole trajectory lies in the past stays Exposed with an empty schedule).
+// One thread per case; the ids are distinct.  out (optional): 8 words per case
+// [seir, infection type, severity, recovered, entries appended, exposure timestep, exposure day, symptomatic day].
+__global__ void k9_seed_kernel(DevCtx c, int64_t n, const int32_t *ids, const int32_t *expo_day, int pre_days,
+                               const uint8_t *ts_list, int n_ts, const double *asym_mult, const double *draws, int32_t *out,
+                               int32_t *status /* [error, schedule overflows, tape misses] */)
+{
+    const mtd_params *P = c.P;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int ag = ids[i];
+        if (ag < 0 || ag >= c.n_agents) { status[0] = MTD_E_ARG; continue; }
+        double row[MTD_EXPO_W];
+        Draws D; D.miss = 0;
+        int ts, incr0;
+        if (c.day.mode == MTD_MODE_REPLAY) {
+            D.row = draws + i * MTD_EXPO_W;
+            ts = isnan(D.row[0]) ? 0 : (int)D.row[0];
+            incr0 = expo_day[i];
+        } else {
+            uint32_t w[4];
+            philox4x32((uint32_t)c.day.day, (uint32_t)ag, 0u, 0u, c.day.seed, SITE_EXPO, w);
+            ts = ts_list[__umulhi(w[0], (uint32_t)n_ts)];                              // np.random.choice(overlapping_timesteps)
+            incr0 = expo_day ? expo_day[i] : c.day.day - pre_days + (int)__umulhi(w[1], (uint32_t)pre_days);
+            for (int slot = 1; slot < MTD_EXPO_W; slot++) row[slot] = philox_slot_draw(c, P, ag, slot);
+            D.row = row;
+        }
+        Traj T;
+        sample_trajectory(P, D, c.epi_age_bracket[ag], c.day.day, incr0, ts, asym_mult ? asym_mult[i] : 1.0,
+                          c.day.testing_enabled != 0, c.day.quarantine_enabled != 0, c.test_day[2 * (int64_t)ag] != MTD_NONE, T);
+        if (D.miss) atomicAdd(&status[2], D.miss);
+        int cnt = c.sched_cnt[ag];
+        for (int k = 0; k < T.ns; k++) {
+            if (cnt < MTD_MAXSCHED) c.sched[(int64_t)ag * MTD_MAXSCHED + cnt++] = T.sched[k];
+            else atomicAdd(&status[1], 1);
+        }
+        c.sched_cnt[ag] = (uint8_t)cnt;
+        int seir = S_EXP, it = T.inf_type, sv = SV_UNDEF;
+        if (incr0 < 1) {
+            switch (T.first_T) {
+            case T_EXP_INF:  seir = S_EXP; it = IT_PREASYMP; sv = SV_UNDEF; break;
+            case T_INF_SYMP: seir = S_INF; it = IT_PRESYMP; sv = SV_UNDEF; break;
+            case T_SYMP_SEV: case T_MILD_REC: seir = S_INF; it = IT_SYMP; sv = SV_MILD; break;
+            case T_SEV_CRI:  case T_SEV_REC:  seir = S_INF; it = IT_SYMP; sv = SV_SEVERE; break;
+            case T_CRI_DEATH: case T_CRI_REC: seir = S_INF; it = IT_SYMP; sv = SV_CRITICAL; break;
+            case T_ASYMP_REC: seir = S_INF; it = IT_ASYMP; sv = SV_UNDEF; break;
+            case T_REC_SUS:  seir = S_REC; it = IT_UNDEF; sv = SV_UNDEF; break;
+            default: break;
+            }
+        }
+        c.seir[ag] = (int8_t)seir; c.inf_type[ag] = (int8_t)it; c.inf_sev[ag] = (int8_t)sv;
+        if (T.test_day != MTD_NONE) {
+            c.test_day[2 * (int64_t)ag] = T.test_day; c.test_day[2 * (int64_t)ag + 1] = T.test_ts;
+            c.test_result_day[2 * (int64_t)ag] = T.tres_day; c.test_result_day[2 * (int64_t)ag + 1] = T.test_ts;
+        }
+        if (T.start_hosp != MTD_NONE) {               // schedule_hospitalisation keeps an earlier start day (:651-658)
+            int32_t *hp = c.hosp + 3 * (int64_t)ag;
+            if (hp[0] == MTD_NONE) hp[0] = T.start_hosp;
+            hp[1] = ts; hp[2] = T.end_hosp;
+        }
+        if (out) {
+            int32_t *o = out + 8 * i;
+            o[0] = seir; o[1] = it; o[2] = sv; o[3] = T.recovered; o[4] = T.ns; o[5] = ts; o[6] = incr0; o[7] = T.symptomatic_day;
+        }
     }
 }
 
@@ -563,5 +657,14 @@ int launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st,
 {
     cudaMemsetAsync(out6, 0, 6 * sizeof(unsigned long long), st);
     occupancy_kernel<<<sm_count * 4, 256, 0, st>>>(c, out6);
+    return 1;
+}
+
+int launch_k9_seed(const DevCtx &c, int64_t n, const int32_t *ids, const int32_t *expo_day, int pre_days, const uint8_t *ts_list,
+                   int n_ts, const double *asym_mult, const double *draws, int32_t *out, int32_t *status, cudaStream_t st)
+{
+    if (n <= 0) return 0;
+    const int grid = (int)((n + 127) / 128 < 1184 ? (n + 127) / 128 : 1184);
+    k9_seed_kernel<<<grid, 128, 0, st>>>(c, n, ids, expo_day, pre_days, ts_list, n_ts, asym_mult, draws, out, status);
     return 1;
 }

@@ -24,7 +24,7 @@ from .dynamicparams import DynamicParams, seir_states_from_occupancy
 
 
 class EpidemicRun:
-    def __init__(self, pop, epidemiologyparams, device=0, seed=0, max_rows=0):
+    def __init__(self, pop, epidemiologyparams, device=0, seed=0, max_rows=0, seed_initial_cases=True):
         self.pop, self.ep, self.seed = pop, epidemiologyparams, seed
         self.dev = torch.device("cuda", device)
         self.P = prm.build_params(None, epidemiologyparams)
@@ -39,8 +39,20 @@ class EpidemicRun:
         with torch.cuda.stream(self.stream):
             h.set_cells(pop.cell_type, pop.cell_indid, mem=D)
             h.set_static(pop.age_bracket, pop.epi_age_bracket, pop.soc_rate, pop.res_cellid, mem=D)
-            h.set_state(seir=pop.seir, inf_type=pop.inf_type, inf_sev=pop.inf_sev, sched=pop.sched, sched_cnt=pop.sched_cnt, mem=D)
+            if seed_initial_cases:      # schedules come from K9 below, not from the population's placeholder entries
+                h.set_state(seir=pop.seir, inf_type=pop.inf_type, inf_sev=pop.inf_sev, sched=torch.zeros_like(pop.sched),
+                            sched_cnt=torch.zeros_like(pop.sched_cnt), mem=D)
+            else:
+                h.set_state(seir=pop.seir, inf_type=pop.inf_type, inf_sev=pop.inf_sev, sched=pop.sched, sched_cnt=pop.sched_cnt, mem=D)
         h.sync()
+        self.n_seeded = 0
+        if seed_initial_cases:
+            # itinerary.py:373-395: on day 1 every agent that starts Infectious was exposed during the last
+            # pre_exposure_days days; its whole trajectory is sampled from that day and its states reset (K9)
+            ids = torch.nonzero(pop.seir == 3).flatten().to(torch.int32).cpu().numpy()
+            d1 = h.make_day(capi.MODE_PHILOX, 1, 0.0, False, False, seed=seed)
+            h.seed_exposures(d1, ids, pre_exposure_days=int(epidemiologyparams.get("pre_exposure_days", 7)))
+            self.n_seeded = len(ids)
         h.set_intervention_mask(True)
         # vaccination: ids that are not part of the population are never candidates
         h.enable_vaccination(pop.n_agents)

@@ -83,6 +83,72 @@ class Epidemiology:
             bridge.scatter(h.get_state(), exposed, self.agents_epi, vu)
         return exposed
 
+    # ------------------------------------------------------------------ trajectory of one exposure (K9)
+    def simulate_seir_state_transition(self, current_day, exposed_agent, exposed_agent_id, incremental_days,
+                                       overlapping_timesteps, agent_state_transition_by_day, agent_epi_age_bracket_index,
+                                       agent_quarantine_days, asymptomatic_multiplier=1.0):
+        """epidemiology.py:233-500 called on its own, as the itinerary stage does for the agents that start Infectious
+        (itinerary.py:373-395: `incremental_days` < 1 -> reset_states).  -> (agent_state_transition_by_day, seir_state,
+        infection_type, infection_severity, recovered); test and hospitalisation records are written into
+        `exposed_agent`, the quarantine record is left to the caller's overwrite (itinerary.py:390), as in the
+        reference.  Sampled on the device (mtd_seed_exposures); replay mode reads one EXPO_W row from `self.tape`.
+        For many agents use `seed_initial_cases`, one launch for the whole batch."""
+        from . import bridge, capi
+        from .epidemiologyclasses import InfectionType, SEIRState, SEIRStateTransition, Severity
+        a = int(exposed_agent_id)
+        n_agents = max(int(self.n_locals + self.n_tourists), a + 1)
+        st = bridge.DenseState(n_agents)
+        st.epi_age_bracket[a] = int(agent_epi_age_bracket_index)
+        bridge._rec(st.test_day, a, exposed_agent.get("test_day")); bridge._rec(st.test_result_day, a, exposed_agent.get("test_result_day"))
+        bridge._rec(st.hosp, a, exposed_agent.get("hospitalisation_days"))
+        h = bridge.get_handle(n_agents, 1, 16, self.params, self.device)
+        bridge.upload(h, st, np.zeros(1, np.int8), np.full(1, -1, np.int16))
+        replay = self.mode == "replay"
+        if replay and self.tape is None:
+            raise RuntimeError("replay mode needs the reference's draws of this call (one EXPO_W row)")
+        dp = self.dyn_params
+        d = h.make_day(capi.MODE_REPLAY if replay else capi.MODE_PHILOX, int(current_day), 0.0, bool(dp.testing_enabled),
+                       bool(dp.quarantine_enabled), seed=self.seed)
+        out = h.seed_exposures(d, [a], exposure_day=[int(incremental_days)], timesteps=np.asarray(overlapping_timesteps),
+                               asym_mult=[float(asymptomatic_multiplier)],
+                               draws=np.asarray(self.tape, np.float64).reshape(1, -1) if replay else None)[0]
+        dev = h.get_state()
+        if agent_state_transition_by_day is None:
+            agent_state_transition_by_day = []
+        for v in dev["sched"][a, :int(dev["sched_cnt"][a])]:
+            day, trans, ts = bridge.unpack_sched(v)
+            agent_state_transition_by_day.append([day, SEIRStateTransition(trans), ts])
+        if dev["test_day"][a, 0] != prm.NONE and st.test_day[a, 0] == prm.NONE:
+            exposed_agent["test_day"] = bridge._lst(dev["test_day"][a])
+            exposed_agent["test_result_day"] = bridge._lst(dev["test_result_day"][a])
+        if dev["hosp"][a, 0] != prm.NONE:
+            exposed_agent["hospitalisation_days"] = bridge._lst(dev["hosp"][a])
+        return (agent_state_transition_by_day, SEIRState(int(out[0])), InfectionType(int(out[1])), Severity(int(out[2])),
+                bool(out[3]))
+
+    def seed_initial_cases(self, simday, agent_ids, pre_exposure_days, potential_timesteps=None):
+        """The loop of itinerary.py:373-395 over all agents that start Infectious, as ONE device batch: exposure day drawn
+        from arange(simday - pre_exposure_days, simday), trajectory sampled, states reset, records written back into
+        agents_epi / vars_util.  -> the ids, in the order given."""
+        from . import bridge, capi
+        ids = np.ascontiguousarray([int(a) for a in agent_ids], np.int32)
+        if len(ids) == 0:
+            return []
+        n_agents = int(self.n_locals + self.n_tourists)
+        dense = bridge.flatten(n_agents, self.agents_static, self.agents_epi, self.vars_util, ids)
+        h = bridge.get_handle(n_agents, 1, 16, self.params, self.device)
+        bridge.upload(h, dense, np.zeros(1, np.int8), np.full(1, -1, np.int16))
+        dp = self.dyn_params
+        d = h.make_day(capi.MODE_PHILOX, int(simday), 0.0, bool(dp.testing_enabled), bool(dp.quarantine_enabled), seed=self.seed)
+        h.seed_exposures(d, ids, pre_exposure_days=int(pre_exposure_days),
+                         timesteps=np.arange(144) if potential_timesteps is None else np.asarray(potential_timesteps))
+        dev = h.get_state()
+        quar = {int(a): self.agents_epi[int(a)].get("quarantine_days") for a in ids}
+        bridge.scatter(dev, ids, self.agents_epi, self.vars_util)
+        for a, q in quar.items():                       # agent_epi["quarantine_days"] = agent_quarantine_days (:390)
+            self.agents_epi[a]["quarantine_days"] = q
+        return [int(a) for a in ids]
+
     # ------------------------------------------------------------------ small host-side helpers of the class
     def update_quarantine(self, agent, new_start_day, new_start_ts, new_end_day, new_end_ts):
         """epidemiology.py:627-630: overwrite the agent's quarantine record [start day, timestep, end day]"""

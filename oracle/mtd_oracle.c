@@ -517,16 +517,21 @@ static void sched_append(mtdo_agents *A, int32_t ag, int32_t day, int trans, int
     A->sched_cnt[ag] = c + 1;
 }
 
-/* simulate_seir_state_transition + schedule_* as reached from simulate_direct_contacts (epidemiology.py:233-660) */
-static void expose_agent(const mtdo_params *P, const mtdo_dayctx *D, mtdo_agents *A, int32_t ag, int n_ts,
-                         const uint8_t *ts_list, double asym_mult, mtdo_stats *S)
+/* incr0: the exposure day (today for a contact of the day step; a day before the start of the simulation for the
+ * itinerary's initial cases, itinerary.py:373-395 -> reset_states, epidemiology.py:243); row: the replay draws of this
+ * exposure (NULL: looked up in the day's tape); out8 (optional): [seir, infection type, severity, recovered, entries
+ * appended, exposure timestep, exposure day, symptomatic day] */
+static void expose_agent_ex(const mtdo_params *P, const mtdo_dayctx *D, mtdo_agents *A, int32_t ag, int n_ts,
+                            const uint8_t *ts_list, double asym_mult, mtdo_stats *S, int32_t incr0, const double *row,
+                            int32_t *out8)
 {
-    expodraws E = { D, ag, NULL, S };
-    if (D->mode == MTDO_MODE_REPLAY) {
+    expodraws E = { D, ag, row, S };
+    if (D->mode == MTDO_MODE_REPLAY && !row) {
         int64_t r = tape_find_expo(D->tape, ag);
         if (r >= 0) E.row = D->tape->expo_row + r * MTDO_EXPO_W; else S->tape_miss++;
     }
-    int32_t current_day = D->day, incr = D->day;
+    int32_t current_day = D->day, incr = incr0;
+    int first_T = -1, n_app = 0;
     int b = A->epi_age_bracket[ag];
     /* sampled_exposed_timestep = np.random.choice(overlapping_timesteps) (:246) */
     int ts;
@@ -539,7 +544,7 @@ static void expose_agent(const mtdo_params *P, const mtdo_dayctx *D, mtdo_agents
     int symptomatic_day = -1, recovered = 0, start_hosp = MTDO_NONE, end_hosp = MTDO_NONE;
     int inf_type;
 #define STEP(T) do { incr += ed_lognormal_days(&E, 1 + (T), P->ln_mu[T], P->ln_sigma[T]); \
-                     if (incr >= current_day) sched_append(A, ag, incr, (T), ts, S); } while (0)
+                     if (incr >= current_day) { if (n_app++ == 0) first_T = (T); sched_append(A, ag, incr, (T), ts, S); } } while (0)
     STEP(T_EXP_INF);                                                                   /* :248-256 */
     double u = ed_uniform(&E, 11);                                                    /* :268 */
     if (u < P->probs_by_age[1][b] * asym_mult) {
@@ -584,7 +589,57 @@ static void expose_agent(const mtdo_params *P, const mtdo_dayctx *D, mtdo_agents
             (void)ed_uniform(&E, 20);
         }
     }
-    A->seir[ag] = S_EXP; A->inf_type[ag] = (int8_t)inf_type; A->inf_sev[ag] = SV_UNDEF;   /* :219-225 */
+    int seir = S_EXP, it = inf_type, sv = SV_UNDEF;                                    /* :219-225, :238-240 */
+    if (incr0 < 1) {
+        /* reset_states (:243): the states that PRECEDE the first transition still ahead (:257-470, as written: while
+         * waiting for ExposedToInfectious the type is PreAsymptomatic whatever the branch, :262-263; nothing ahead ->
+         * the agent stays Exposed with an empty schedule) */
+        switch (first_T) {
+        case T_EXP_INF:  seir = S_EXP; it = IT_PREASYMP; sv = SV_UNDEF; break;
+        case T_INF_SYMP: seir = S_INF; it = IT_PRESYMP; sv = SV_UNDEF; break;
+        case T_SYMP_SEV: case T_MILD_REC: seir = S_INF; it = IT_SYMP; sv = SV_MILD; break;
+        case T_SEV_CRI:  case T_SEV_REC:  seir = S_INF; it = IT_SYMP; sv = SV_SEVERE; break;
+        case T_CRI_DEATH: case T_CRI_REC: seir = S_INF; it = IT_SYMP; sv = SV_CRITICAL; break;
+        case T_ASYMP_REC: seir = S_INF; it = IT_ASYMP; sv = SV_UNDEF; break;
+        case T_REC_SUS:  seir = S_REC; it = IT_UNDEF; sv = SV_UNDEF; break;
+        default: break;
+        }
+    }
+    A->seir[ag] = (int8_t)seir; A->inf_type[ag] = (int8_t)it; A->inf_sev[ag] = (int8_t)sv;
+    if (out8) {
+        out8[0] = seir; out8[1] = it; out8[2] = sv; out8[3] = recovered; out8[4] = n_app; out8[5] = ts; out8[6] = incr0;
+        out8[7] = symptomatic_day;
+    }
+}
+
+/* simulate_seir_state_transition + schedule_* as reached from simulate_direct_contacts (epidemiology.py:233-660) */
+static void expose_agent(const mtdo_params *P, const mtdo_dayctx *D, mtdo_agents *A, int32_t ag, int n_ts,
+                         const uint8_t *ts_list, double asym_mult, mtdo_stats *S)
+{
+    expose_agent_ex(P, D, A, ag, n_ts, ts_list, asym_mult, S, D->day, NULL, NULL);
+}
+
+/* the itinerary stage's initial cases (itinerary.py:373-395): Epidemiology.simulate_seir_state_transition called with an
+ * exposure day before day 1.  exposure_day NULL: drawn from [day - pre_days, day) with word 1 of the slot-0 Philox
+ * block (Philox mode).  draws: replay rows, n x MTDO_EXPO_W.  Returns 0, or -1 on a bad id. */
+int64_t mtdo_seed_exposures(const mtdo_params *P, const mtdo_dayctx *D, mtdo_agents *A, int64_t n, const int32_t *ids,
+                            const int32_t *exposure_day, int32_t pre_days, const uint8_t *ts_list, int32_t n_ts,
+                            const double *asym_mult, const double *draws, int32_t *out8, mtdo_stats *S)
+{
+    for (int64_t i = 0; i < n; i++) {
+        const int32_t ag = ids[i];
+        if (ag < 0 || ag >= A->n_agents) return -1;
+        int32_t incr0;
+        if (exposure_day) incr0 = exposure_day[i];
+        else {
+            uint32_t w[4];
+            philox_site(D, MTDO_SITE_EXPO, (uint32_t)ag, 0, 0, w);
+            incr0 = D->day - pre_days + (int32_t)(((uint64_t)w[1] * (uint64_t)(uint32_t)pre_days) >> 32);
+        }
+        expose_agent_ex(P, D, A, ag, n_ts, ts_list, asym_mult ? asym_mult[i] : 1.0, S, incr0,
+                        draws ? draws + i * MTDO_EXPO_W : NULL, out8 ? out8 + 8 * i : NULL);
+    }
+    return 0;
 }
 
 int64_t mtdo_transmission(const mtdo_params *P, const mtdo_dayctx *D, int64_t M, const int32_t *iv_cell,

@@ -262,6 +262,26 @@ def process_test_results(params, ctx, agents: AgentState, epi_present=None):
     return np.nonzero(pos)[0].astype(np.int32)
 
 
+def seed_exposures(params, ctx, agents: AgentState, agent_ids, exposure_day=None, pre_exposure_days=0, timesteps=None,
+                   asym_mult=None, draws=None):
+    """itinerary.py:373-395 -> epidemiology.py:233-500 with reset_states: mutates `agents`; -> (out [n, 8], Stats)"""
+    a = agents.struct()
+    ids = np.ascontiguousarray(agent_ids, np.int32)
+    ts = np.ascontiguousarray(np.arange(144) if timesteps is None else timesteps, np.uint8)
+    ed = None if exposure_day is None else np.ascontiguousarray(exposure_day, np.int32)
+    am = None if asym_mult is None else np.ascontiguousarray(asym_mult, np.float64)
+    dr = None if draws is None else np.ascontiguousarray(draws, np.float64)
+    out = np.zeros((len(ids), 8), np.int32)
+    st = Stats()
+    L = lib()
+    L.mtdo_seed_exposures.restype = C.c_int64
+    r = L.mtdo_seed_exposures(C.byref(params), C.byref(ctx), C.byref(a), C.c_int64(len(ids)), _p(ids), _p(ed),
+                              C.c_int32(pre_exposure_days), _p(ts), C.c_int32(len(ts)), _p(am), _p(dr), _p(out), C.byref(st))
+    if r != 0:
+        raise ValueError("seed_exposures: agent id out of range")
+    return out, st
+
+
 def mask_intervals(day, iv_agent, iv_cell, agents: AgentState):
     """keep flags of the day's intervals under the intervention mask (deceased / quarantined / hospitalised agents stay
     in their residence cell only)"""
