@@ -319,7 +319,7 @@ def run_b200(args):
     achieved = k1_bytes / (k1_ms * 1e-3) / 1e9 if k1_ms > 0 else 0.0
     roofline = {"bound": "hbm", "kernel": "k1_contacts (6 size-class launches per day)", "achieved": achieved,
                 "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum over the 6 K1 launches of one day (profiles/r01_k1_traffic.json)",
+                "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum over the K1 launches, mean per day over the 7 day streams (profiles/r01_k1_traffic.json)",
                 "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
                 "algorithmic_bytes_per_day": k1_bytes, "k1_ms": k1_ms, "stage_ms": st_ms,
                 "k1_pairs_per_s": P_mean / (k1_ms * 1e-3) if k1_ms > 0 else None,

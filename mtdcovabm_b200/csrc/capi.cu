@@ -25,6 +25,7 @@ int launch_k7_schedule(const DevCtx &c, int64_t n_locals, long long k, int32_t *
 int launch_k7_replay(const DevCtx &c, int64_t n, const int32_t *ids, const int32_t *ts, int32_t *vacc_day, uint8_t *selected,
                      void *scratch, cudaStream_t st);
 int launch_k7_dose(const DevCtx &c, int day, int64_t n_locals, int32_t *vacc_day, cudaStream_t st, int sm_count);
+int launch_pack_attr(const DevCtx &c, AgentAttr *out, cudaStream_t st, int sm_count);
 int launch_k9_seed(const DevCtx &c, int64_t n, const int32_t *ids, const int32_t *expo_day, int pre_days, const uint8_t *ts_list,
                    int n_ts, const double *asym_mult, const double *draws, int32_t *out, int32_t *status, cudaStream_t st);
 int launch_k8(int64_t n_itin, const int64_t *ent_off, const int16_t *ent_ts, const int32_t *ent_cell, const int64_t *grp_off,
@@ -202,16 +203,17 @@ static int create_impl(mtd_handle h)
     int8_t *ct; int16_t *ci; int8_t *ab, *eb; double *sr; int32_t *rc;
     DA(ct, C); DA(ci, C); DA(ab, N); DA(eb, N); DA(sr, N); DA(rc, N);
     c.cell_type = ct; c.cell_indid = ci; c.age_bracket = ab; c.epi_age_bracket = eb; c.soc_rate = sr; c.res_cellid = rc;
+    { AgentAttr *at; DA(at, N); c.k1_attr = at; }
     DA(c.seir, N); DA(c.inf_type, N); DA(c.inf_sev, N); DA(c.last_dose_day, N);
     DA(c.sched, N * MTD_MAXSCHED); DA(c.sched_cnt, N); DA(c.test_day, 2 * N); DA(c.test_result_day, 2 * N);
     DA(c.quarantine, 3 * N); DA(c.hosp, 3 * N);
     DA(c.cell_count, C); DA(c.cell_first, C); DA(c.cell_base, C); DA(c.iv_pos, M); DA(c.flag_scan, M + 64);
-    DA(c.slot_cell, S + 1); DA(c.slot_m, S + 1); DA(c.slot_first, S + 1);
+    DA(c.slot_cell, S + 1); DA(c.slot_m, S + 1); DA(c.slot_first, S + 1); DA(c.slot_act, S + 1);
     DA(c.slot_off, S + 2); DA(c.slot_rowoff, S + 2); DA(c.slot_rowbound, S + 1);
     DA(c.slot_nrows, S + 1); DA(c.slot_denseoff, S + 2);
     c.class_stride = S + 1;
     DA(c.class_list, MTD_NUM_CLASSES * (S + 1));
-    DA(c.csr, M); DA(c.csr_sorted, M);
+    DA(c.csr, M);
     DA(c.scratch_rows, c.cap_scratch_rows); DA(c.rows, c.cap_rows);
     c.k1_bits_words = k1_bits_words_needed(h->sm_count);
     DA(c.k1_bits, c.k1_bits_words);
@@ -344,7 +346,9 @@ extern "C" int mtd_set_static(mtd_handle h, int64_t n, const int8_t *age_bracket
     COPY_IN(h->c.epi_age_bracket, epi_age_bracket, (size_t)n);
     COPY_IN(h->c.soc_rate, soc_rate, sizeof(double) * (size_t)n);
     COPY_IN(h->c.res_cellid, res_cellid, sizeof(int32_t) * (size_t)n);
+    launch_pack_attr(h->c, const_cast<AgentAttr *>(h->c.k1_attr), h->stream, h->sm_count);
     if (mem == MTD_MEM_HOST) CK(cudaStreamSynchronize(h->stream));
+    CK(cudaGetLastError());
     h->have_static = true;
     return MTD_OK;
 }

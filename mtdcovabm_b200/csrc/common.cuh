@@ -79,6 +79,9 @@ struct DevTape {
 };
 
 // everything a kernel needs, passed by value
+// the two static attributes K1 reads per distinct agent of a cell (contactnetwork.py:237-252), packed by mtd_set_static
+struct __align__(16) AgentAttr { double soc_rate; int32_t age_bracket; int32_t pad; };
+
 struct DevCtx {
     // capacities
     int64_t n_agents, n_cells, cap_intervals, cap_rows, cap_scratch_rows, cap_expo;
@@ -88,6 +91,7 @@ struct DevCtx {
     // static
     const int8_t *cell_type; const int16_t *cell_indid;
     const int8_t *age_bracket; const int8_t *epi_age_bracket; const double *soc_rate; const int32_t *res_cellid;
+    const AgentAttr *k1_attr;  // {soc_rate, age_bracket} of every agent in ONE 16-byte record: K1's gather touches one sector
     // state
     int8_t *seir; int8_t *inf_type; int8_t *inf_sev; int32_t *last_dose_day;
     int32_t *sched; uint8_t *sched_cnt; int32_t *test_day; int32_t *test_result_day; int32_t *quarantine; int32_t *hosp;
@@ -104,6 +108,7 @@ struct DevCtx {
     int32_t *slot_cell;        // [slots]
     int32_t *slot_m;           // [slots]
     uint32_t *slot_first;      // [slots] order key of the cell
+    uint8_t *slot_act;         // [slots] activity column of the cell (contactnetwork.py:317-347), resolved once by K0
     int64_t *slot_off;         // [slots+1] CSR offsets
     int64_t *slot_rowoff;      // [slots+1] scratch-row offsets
     int32_t *slot_rowbound;    // [slots]
@@ -126,7 +131,6 @@ struct DevCtx {
     DevCounters *ctr;
     StateCounters *sctr;
     const mtd_params *P;       // device copy of the parameters
-    IvRec *csr_sorted;         // [M] CSR records in list (emission) order within each cell, written by K1
     // intervention mask (mtd_set_intervention_mask): per-agent "stays in the residence cell today" flag, or NULL = off
     uint8_t *agent_masked;
     // caller-supplied contacts (mtd_set_contacts): overlap lists per dense row instead of the cell's interval records

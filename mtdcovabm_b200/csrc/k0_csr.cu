@@ -93,7 +93,9 @@ __global__ void __launch_bounds__(256) k0_assign_kernel(DevCtx c, const uint32_t
                 if (m > MTD_MAX_CELL_INTERVALS) { c.ctr->error = MTD_E_CELL_TOO_LARGE; m = 0; }
                 int ct = c.cell_type[cell];
                 int indid = (ct == CT_WORKPLACE && c.cell_indid) ? c.cell_indid[cell] : -1;
-                long long k = c.P->k_by_act[activity_of_celltype(ct, indid)];
+                const int act = activity_of_celltype(ct, indid);
+                c.slot_act[slot] = (uint8_t)act;
+                long long k = c.P->k_by_act[act];
                 // rows <= sum(deg)/2, sum(deg) <= max(k*n, S) + n/2 with n <= m; and rows <= m(m-1)/2
                 long long b1 = (long long)m * (m - 1) / 2, b2 = (k * m + m / 2 + 2) / 2 + 1;
                 c.slot_rowbound[slot] = (int)(b1 < b2 ? b1 : b2);
@@ -217,6 +219,20 @@ __global__ void k0_scatter_kernel(DevCtx c)
         r.pad = 0;
         c.csr[c.cell_base[cell] + p] = r;
     }
+}
+
+__global__ void pack_attr_kernel(DevCtx c, AgentAttr *out)
+{
+    for (int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; a < c.n_agents; a += (int64_t)gridDim.x * blockDim.x) {
+        AgentAttr r; r.soc_rate = c.soc_rate[a]; r.age_bracket = c.age_bracket[a]; r.pad = 0;
+        out[a] = r;
+    }
+}
+
+int launch_pack_attr(const DevCtx &c, AgentAttr *out, cudaStream_t st, int sm_count)
+{
+    pack_attr_kernel<<<sm_count * 8, 256, 0, st>>>(c, out);
+    return 1;
 }
 
 int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count)

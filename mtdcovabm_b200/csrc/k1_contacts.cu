@@ -61,6 +61,15 @@ __device__ __forceinline__ double log_int(const DevCtx &g, int v)
     return (v >= 0 && v < MTD_LOGTAB_N) ? g.logtab[v] : log((double)v);
 }
 
+// one 16-byte gather per agent: {soc_rate, age_bracket}
+__device__ __forceinline__ AgentAttr load_attr(const DevCtx &g, int ag)
+{
+    const int4 v = __ldg((const int4 *)(g.k1_attr + ag));
+    AgentAttr a;
+    a.soc_rate = __hiloint2double(v.y, v.x); a.age_bracket = v.z; a.pad = 0;
+    return a;
+}
+
 // contactnetwork.py:225-252: float degree of one agent
 __device__ __forceinline__ double degree_f2(const DevCtx &g, const mtd_params *P, int ab, double soc, int act, int ts, int pc,
                                             double avg_ts, double avg_pc, double log_avg_ts, double log_avg_pc,
@@ -78,7 +87,8 @@ __device__ __forceinline__ double degree_f(const DevCtx &g, const mtd_params *P,
                                            double avg_ts, double avg_pc, double log_avg_ts, double log_avg_pc,
                                            double one_minus_mhd)
 {
-    return degree_f2(g, P, g.age_bracket[ag], g.soc_rate[ag], act, ts, pc, avg_ts, avg_pc, log_avg_ts, log_avg_pc, one_minus_mhd);
+    const AgentAttr at = load_attr(g, ag);
+    return degree_f2(g, P, at.age_bracket, at.soc_rate, act, ts, pc, avg_ts, avg_pc, log_avg_ts, log_avg_pc, one_minus_mhd);
 }
 
 __device__ __forceinline__ int degree_i(double d, long long deg_sum, long long max_degree, int pc)
@@ -153,10 +163,11 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
 
     // the next cell's descriptor and this lane's record are fetched while the current cell is processed
     int w = (blockIdx.x * K1S_THREADS + (int)threadIdx.x) / G;
-    int nx_slot = 0, nx2_slot = 0, nx_m = 0, nx_cell = 0; int64_t nx_base = 0;
+    int nx_slot = 0, nx2_slot = 0, nx_m = 0, nx_cell = 0, nx_act = 0; int64_t nx_base = 0;
     IvRec nx_rec; nx_rec.agent = 0; nx_rec.order = 0xffffffffu; nx_rec.se = 0; nx_rec.pad = 0;
     if (w < total) {
         nx_slot = list[w]; nx_m = g.slot_m[nx_slot]; nx_base = g.slot_off[nx_slot]; nx_cell = g.slot_cell[nx_slot];
+        nx_act = g.slot_act[nx_slot];
         if (gl < nx_m) nx_rec = g.csr[nx_base + gl];
         if (w + n_groups < total) nx2_slot = list[w + n_groups];       // the slot index runs two cells ahead
     }
@@ -166,15 +177,14 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
         const int64_t base = nx_base;
         const int cell = nx_cell;
         IvRec rec = nx_rec;
-        const int ctype = g.cell_type[cell];
+        const int act = nx_act;
         if (w + n_groups < total) {
             nx_slot = nx2_slot; nx_m = g.slot_m[nx_slot]; nx_base = g.slot_off[nx_slot]; nx_cell = g.slot_cell[nx_slot];
+            nx_act = g.slot_act[nx_slot];
             nx_rec.agent = 0; nx_rec.order = 0xffffffffu; nx_rec.se = 0;
             if (gl < nx_m) nx_rec = g.csr[nx_base + gl];
             if (w + 2 * n_groups < total) nx2_slot = list[w + 2 * n_groups];
         }
-        const int indid = (ctype == CT_WORKPLACE && g.cell_indid) ? g.cell_indid[cell] : -1;
-        const int act = activity_of_celltype(ctype, indid);
 
         // ---- 1. my interval; restore list (emission) order by ranking the emission indices ----
         const bool have = gl < m;
@@ -187,7 +197,6 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
         __syncwarp(gmask);                          // previous cell's readers of the shared slots are done
         if (have) {
             sh_agent[tb + rank] = rec.agent; sh_se[tb + rank] = (uint16_t)(rec.se & 0xffffu);
-            g.csr_sorted[base + rank] = rec;
         }
         __syncwarp(gmask);
         const int agent = have ? sh_agent[tb + gl] : (-1 - gl);
@@ -197,7 +206,7 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
         const uint32_t mm = (__match_any_sync(gmask, agent) >> gbase) & gbits;      // my agent's interval positions
         const bool isag = have && ((__ffs(mm) - 1) == gl);
         int ab_pre = 0; double soc_pre = 0.0;                                       // gathered early, used in step 4
-        if (isag) { ab_pre = g.age_bracket[agent]; soc_pre = g.soc_rate[agent]; }
+        if (isag) { const AgentAttr at = load_attr(g, agent); ab_pre = at.age_bracket; soc_pre = at.soc_rate; }
         const uint32_t agm = (__ballot_sync(gmask, isag) >> gbase) & gbits;         // agent lanes (group-relative)
         const int n = __popc(agm);
         {   // metric: unordered interval pairs of different agents = (m^2 - sum_a cnt_a^2) / 2
@@ -487,9 +496,7 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, uint32_t 
     const int m = g.slot_m[slot];
     const int64_t base = g.slot_off[slot];
     const int cell = g.slot_cell[slot];
-    const int ctype = g.cell_type[cell];
-    const int indid = (ctype == CT_WORKPLACE && g.cell_indid) ? g.cell_indid[cell] : -1;
-    const int act = activity_of_celltype(ctype, indid);
+    const int act = g.slot_act[slot];
     uint32_t *t32a = (uint32_t *)c.key;           // two u32[P2] temporaries aliasing the sort-key region
     uint32_t *t32b = t32a + L::P2;
     double *degf = (double *)c.key;
@@ -513,7 +520,6 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, uint32_t 
     for (int p = lane; p < m; p += 32) {
         IvRec r = g.csr[base + (uint32_t)c.key[p]];
         c.agent[p] = r.agent; c.se[p] = (uint16_t)(r.se & 0xffffu);
-        g.csr_sorted[base + p] = r;
     }
     __syncwarp();
 

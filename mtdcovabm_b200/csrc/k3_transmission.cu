@@ -202,6 +202,7 @@ __global__ void __launch_bounds__(K3T_WARPS * 32) k3_trajectory_kernel(DevCtx c,
 {
     __shared__ double s_row[K3T_WARPS][MTD_EXPO_W + 3];
     __shared__ uint16_t s_iv[K3T_WARPS][2][K3T_MAXIV];
+    __shared__ uint32_t s_ord[K3T_WARPS][2][K3T_MAXIV];
     const int n = c.ctr->n_succ;
     const mtd_params *P = c.P;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -238,18 +239,21 @@ __global__ void __launch_bounds__(K3T_WARPS * 32) k3_trajectory_kernel(DevCtx c,
             D.row = s_row[warp];
         } else {
             if (lane >= 1 && lane < MTD_EXPO_W) s_row[warp][lane] = philox_slot_draw(c, P, ex, lane);
-            // the two agents' intervals in list order: lanes scan the cell's records, ranks by ballot
+            // the two agents' intervals in list (emission) order: lanes scan the cell's records as K0 laid them out
+            // (arrival order of the scatter), gather the two agents' records and order those few by emission index
             const int64_t b = c.slot_off[r.slot];
             const int m = c.slot_m[r.slot];
             int na = 0, nb = 0;
             for (int p0 = 0; p0 < m; p0 += 32) {
                 const int p = p0 + lane;
-                IvRec rec; rec.agent = -1; rec.se = 0;
-                if (p < m) rec = c.csr_sorted[b + p];
+                IvRec rec; rec.agent = -1; rec.se = 0; rec.order = 0;
+                if (p < m) rec = c.csr[b + p];
                 const bool ia = p < m && rec.agent == r.a1, ib = p < m && rec.agent == r.a2;
                 const uint32_t ba = __ballot_sync(FULLMASK, ia), bb = __ballot_sync(FULLMASK, ib);
-                if (ia) { int k = na + __popc(ba & lanemask_lt()); if (k < K3T_MAXIV) s_iv[warp][0][k] = (uint16_t)(rec.se & 0xffffu); }
-                if (ib) { int k = nb + __popc(bb & lanemask_lt()); if (k < K3T_MAXIV) s_iv[warp][1][k] = (uint16_t)(rec.se & 0xffffu); }
+                if (ia) { int k = na + __popc(ba & lanemask_lt());
+                          if (k < K3T_MAXIV) { s_iv[warp][0][k] = (uint16_t)(rec.se & 0xffffu); s_ord[warp][0][k] = rec.order; } }
+                if (ib) { int k = nb + __popc(bb & lanemask_lt());
+                          if (k < K3T_MAXIV) { s_iv[warp][1][k] = (uint16_t)(rec.se & 0xffffu); s_ord[warp][1][k] = rec.order; } }
                 na += __popc(ba); nb += __popc(bb);
             }
             __syncwarp();
@@ -260,6 +264,17 @@ __global__ void __launch_bounds__(K3T_WARPS * 32) k3_trajectory_kernel(DevCtx c,
                 // flattened overlap list of key (a1, a2): a1's intervals (outer) x a2's (inner), list order
                 bool done = false;
                 if (na <= K3T_MAXIV && nb <= K3T_MAXIV) {
+                    for (int side = 0; side < 2; side++) {       // insertion sort by emission index (a handful of entries)
+                        const int cnt = side ? nb : na;
+                        for (int x = 1; x < cnt; x++) {
+                            const uint32_t o = s_ord[warp][side][x]; const uint16_t v = s_iv[warp][side][x];
+                            int y = x - 1;
+                            while (y >= 0 && s_ord[warp][side][y] > o) {
+                                s_ord[warp][side][y + 1] = s_ord[warp][side][y]; s_iv[warp][side][y + 1] = s_iv[warp][side][y]; y--;
+                            }
+                            s_ord[warp][side][y + 1] = o; s_iv[warp][side][y + 1] = v;
+                        }
+                    }
                     for (int p = 0; p < na && !done; p++) {
                         const int sa = s_iv[warp][0][p] & 0xff, ea = s_iv[warp][0][p] >> 8;
                         for (int q = 0; q < nb; q++) {
@@ -270,17 +285,27 @@ __global__ void __launch_bounds__(K3T_WARPS * 32) k3_trajectory_kernel(DevCtx c,
                             idx -= len;
                         }
                     }
-                } else {                                     // more intervals than the staging holds: walk the records
-                    for (int p = 0; p < m && !done; p++) {
-                        IvRec ra = c.csr_sorted[b + p];
-                        if (ra.agent != r.a1) continue;
-                        int sa = ra.se & 0xff, ea = (ra.se >> 8) & 0xff;
-                        for (int q = 0; q < m; q++) {
-                            IvRec rb = c.csr_sorted[b + q];
-                            if (rb.agent != r.a2) continue;
-                            int lo = max(sa, (int)(rb.se & 0xff)), hi = min(ea, (int)((rb.se >> 8) & 0xff));
+                } else {      // more intervals than the staging holds: walk the records in emission order by repeated
+                              // minimum search (emission indices are unique)
+                    long long la = -1;
+                    for (int p = 0; p < na && !done; p++) {
+                        uint32_t best = 0xffffffffu; int sa = 0, ea = -1;
+                        for (int x = 0; x < m; x++) {
+                            const IvRec ra = c.csr[b + x];
+                            if (ra.agent == r.a1 && (long long)ra.order > la && ra.order <= best) { best = ra.order; sa = ra.se & 0xff; ea = (ra.se >> 8) & 0xff; }
+                        }
+                        la = (long long)best;
+                        long long lb = -1;
+                        for (int q = 0; q < nb; q++) {
+                            uint32_t bestb = 0xffffffffu; int sb = 0, eb = -1;
+                            for (int x = 0; x < m; x++) {
+                                const IvRec rb = c.csr[b + x];
+                                if (rb.agent == r.a2 && (long long)rb.order > lb && rb.order <= bestb) { bestb = rb.order; sb = rb.se & 0xff; eb = (rb.se >> 8) & 0xff; }
+                            }
+                            lb = (long long)bestb;
+                            const int lo = max(sa, sb), hi = min(ea, eb);
                             if (lo > hi) continue;
-                            int len = hi - lo + 1;
+                            const int len = hi - lo + 1;
                             if (idx < len) { ts = lo + idx; done = true; break; }
                             idx -= len;
                         }

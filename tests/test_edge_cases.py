@@ -132,3 +132,31 @@ def test_invalid_cell_id_fails_loudly():
     with pytest.raises(RuntimeError):
         h.counters()
     h.close()
+
+
+@pytest.mark.parametrize("n_rep_iv", [5, 24])
+def test_exposure_timestep_with_many_intervals_per_agent(n_rep_iv):
+    """an infectious agent that comes back to the same cell n times (5: staged in shared memory; 24: more than the
+    staging holds -> record walk) beside susceptible partners with several visits each, arrival order shuffled: the
+    exposure timestep is drawn from the flattened overlap list in LIST order, so every schedule entry must match"""
+    rng = np.random.default_rng(n_rep_iv)
+    n_cells, per = 400, 6
+    n_agents = n_cells * per
+    st, ct, ci = population(n_agents, n_cells, seed=3, cell_type=np.zeros(n_cells))
+    st.seir[:] = 1; st.inf_type[:] = 0; st.inf_sev[:] = 0
+    cell, agent, start, end = [], [], [], []
+    for c_ in range(n_cells):
+        a0 = c_ * per
+        st.seir[a0] = 3; st.inf_type[a0] = 4; st.inf_sev[a0] = 1; st.res_cellid[a0:a0 + per] = c_
+        s0 = np.sort(rng.choice(140, n_rep_iv, replace=False))
+        for s in rng.permutation(s0):                                       # the reference keeps LIST order, not time order
+            cell.append(c_); agent.append(a0); start.append(s); end.append(min(143, s + rng.integers(0, 4)))
+        for k in range(1, per):
+            for _ in range(3):
+                s = int(rng.integers(0, 100))
+                cell.append(c_); agent.append(a0 + k); start.append(s); end.append(s + int(rng.integers(5, 43)))
+    o = rng.permutation(len(cell))
+    o = o[np.argsort(np.array(cell)[o] % 7, kind="stable")]               # cells interleaved, per-cell order scrambled
+    iv = [np.array(x)[o] for x in (cell, agent, start, end)]
+    rows, dur, c = run_both(st, ct, ci, iv, seed=n_rep_iv)
+    assert c.error == 0 and c.n_exposed > 20
