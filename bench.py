@@ -310,9 +310,11 @@ def run_b200(args):
     # measured DRAM traffic of the K1 launches of one day (ncu --set full capture, committed under profiles/), scaled to
     # this rank's share of the day's intervals
     traffic = None
+    warp_instr = None
     try:
         tr = json.load(open(os.path.join(ROOT, "profiles", "r01_k1_traffic.json")))
         traffic = tr["dram_bytes_total"] * M_mean / tr["intervals_of_day"]
+        warp_instr = tr["warp_instructions"] * M_mean / tr["intervals_of_day"]
     except Exception:
         pass
     k1_ms = st_ms["k1_contacts"]
@@ -324,6 +326,17 @@ def run_b200(args):
                 "algorithmic_bytes_per_day": k1_bytes, "k1_ms": k1_ms, "stage_ms": st_ms,
                 "k1_pairs_per_s": P_mean / (k1_ms * 1e-3) if k1_ms > 0 else None,
                 "note": "K1 is issue/latency-bound (sequential greedy sampling per cell), not HBM-bound: see DESIGN.md"}
+    # SM-side bound of K1: warp instructions issued per day (ncu smsp__inst_executed.sum, same capture as
+    # `traffic`) against the issue rate of the device, 4 schedulers x 148 SMs x the SM clock sampled during the loop
+    cs = clocks.summary()
+    if warp_instr and k1_ms > 0 and cs.get("sm_mhz"):
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        issue_peak = sms * 4 * cs["sm_mhz"] * 1e6
+        roofline["sm_side"] = {"bound": "issue", "warp_instructions_per_day": warp_instr,
+                               "achieved_warp_inst_per_s": warp_instr / (k1_ms * 1e-3), "peak_warp_inst_per_s": issue_peak,
+                               "frac": warp_instr / (k1_ms * 1e-3) / issue_peak,
+                               "warp_instructions_per_pair": warp_instr / P_mean if P_mean else None,
+                               "note": "k1_ms is the stage's wall time with its six launches on three concurrent streams"}
     h.set_profiling(False)
 
     # ---------------- end to end: host buffers in, host results out, every step

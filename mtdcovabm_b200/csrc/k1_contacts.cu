@@ -255,7 +255,9 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
         // ---- 4. degrees (contactnetwork.py:210-269) ----
         const long long max_degree = (long long)P->k_by_act[act] * n;
         const double avg_ts = (double)ts_sum / (double)n, avg_pc = (double)pc_sum / (double)n;
-        const double log_avg_ts = log(avg_ts), log_avg_pc = log(avg_pc);
+        // the two logarithms in ONE pass of the fp64 log sequence: even lanes take avg_ts, odd lanes avg_pc
+        const double lg = log((gl & 1) ? avg_pc : avg_ts);
+        const double log_avg_ts = __shfl_sync(gmask, lg, gbase), log_avg_pc = __shfl_sync(gmask, lg, gbase + 1);
         double degf = 0.0;
         if (isag && pc > 0) degf = degree_f2(g, P, ab_pre, soc_pre, act, ts, pc, avg_ts, avg_pc, log_avg_ts, log_avg_pc, one_minus_mhd);
         double dsum;
@@ -655,7 +657,8 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, uint32_t 
     const double avg_ts = (double)ts_sum / (double)n;
     const double avg_pc = (double)pc_sum / (double)n;     // every agent has an entry once n >= 2
     const double one_minus_mhd = 1 - g.day.mhd;
-    const double log_avg_ts = log(avg_ts), log_avg_pc = log(avg_pc);
+    const double lg = log((lane & 1) ? avg_pc : avg_ts);                  // both logarithms in one pass (even / odd lanes)
+    const double log_avg_ts = __shfl_sync(FULLMASK, lg, 0), log_avg_pc = __shfl_sync(FULLMASK, lg, 1);
     for (int l = lane; l < n; l += 32) {
         double d = 0.0;
         int pcv = c.pc[l];
