@@ -212,7 +212,8 @@ static int create_impl(mtd_handle h)
     DA(c.slot_off, S + 2); DA(c.slot_rowoff, S + 2); DA(c.slot_rowbound, S + 1);
     DA(c.slot_nrows, S + 1); DA(c.slot_denseoff, S + 2);
     c.class_stride = S + 1;
-    DA(c.class_list, MTD_NUM_CLASSES * (S + 1));
+    DA(c.class_list, (MTD_NUM_CLASSES + 5) * (S + 1));      // + five regions: every class but the last again, sorted by size
+    DA(c.k1_bins, 2 * 3 * 32);
     DA(c.csr, M);
     DA(c.scratch_rows, c.cap_scratch_rows); DA(c.rows, c.cap_rows);
     c.k1_bits_words = k1_bits_words_needed(h->sm_count);

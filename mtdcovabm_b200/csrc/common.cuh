@@ -114,12 +114,13 @@ struct DevCtx {
     int32_t *slot_rowbound;    // [slots]
     int32_t *slot_nrows;       // [slots] rows produced
     int64_t *slot_denseoff;    // [slots+1]
-    int32_t *class_list;       // [MTD_NUM_CLASSES][slots cap]
+    int32_t *class_list;       // [MTD_NUM_CLASSES + 5][slots cap]; the extra regions hold classes 4, 3, 0, 1, 2 sorted by cell size (K1)
     int64_t class_stride;
     IvRec *csr;                // [M]
     // K1 products
     RowRec *scratch_rows;      // [cap_scratch_rows]
     uint32_t *rows12;          // [3 * cap_rows] packed 12-byte rows of the day for the async export (NULL = off)
+    int32_t *k1_bins;          // [2][3][32] histogram and cursors of the small-class size sort (K1)
     uint32_t *k1_bits;         // [k1_bits_words] per-warp adjacency bit matrices of the large-cell K1 (L2-resident scratch)
     int64_t k1_bits_words;
     RowRec *rows;              // [cap_rows] dense

@@ -139,8 +139,70 @@ __device__ __forceinline__ void pair_row_bits(const uint16_t *se, uint32_t ivx, 
 // ------------------------------------------------------------------------------------------------ small cells
 #define K1S_THREADS 256
 
+// The sub-warp kernels step 32/G cells per warp in lock step: a warp iteration lasts as long as its slowest cell, so
+// cells of very different sizes side by side waste lanes (G = 8: four cells of 1..8 intervals per warp).  The class
+// lists of the three small classes are therefore counting-sorted by interval count (largest first) before the
+// kernels run: neighbours in a warp then hold cells of the same size.  Two passes over the lists (block-aggregated
+// histogram, then block-aggregated scatter); the order inside a size bin is arbitrary, every cell writes only its rows.
+#define K1B_THREADS 256
+__device__ __forceinline__ int small_bin(int cls, int m)
+{   // class 0: m in 1..8, class 1: 9..16, class 2: 17..32 -> bin 0 = largest
+    const int hi = cls == 0 ? 8 : (cls == 1 ? 16 : 32);
+    int b = hi - m;
+    return b < 0 ? 0 : (b > 31 ? 31 : b);
+}
+
+__global__ void __launch_bounds__(K1B_THREADS) k1_bin_hist_kernel(DevCtx g)
+{
+    __shared__ int hist[3][32];
+    for (int i = threadIdx.x; i < 96; i += K1B_THREADS) (&hist[0][0])[i] = 0;
+    __syncthreads();
+    for (int cls = 0; cls < 3; cls++) {
+        const int total = g.ctr->class_cells[cls];
+        const int32_t *list = g.class_list + (int64_t)cls * g.class_stride;
+        for (int i = blockIdx.x * K1B_THREADS + threadIdx.x; i < total; i += gridDim.x * K1B_THREADS)
+            atomicAdd(&hist[cls][small_bin(cls, g.slot_m[list[i]])], 1);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 96; i += K1B_THREADS) { const int v = (&hist[0][0])[i]; if (v) atomicAdd(&g.k1_bins[i], v); }
+}
+
+__global__ void __launch_bounds__(K1B_THREADS) k1_bin_scatter_kernel(DevCtx g, int first_region)
+{
+    __shared__ int cnt[3][32], base[3][32];
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 96; i += K1B_THREADS) (&cnt[0][0])[i] = 0;
+    __syncthreads();
+    // same chunks as the histogram pass: count, reserve one range per bin and block, then place
+    for (int cls = 0; cls < 3; cls++) {
+        const int total = g.ctr->class_cells[cls];
+        const int32_t *list = g.class_list + (int64_t)cls * g.class_stride;
+        for (int i = blockIdx.x * K1B_THREADS + tid; i < total; i += gridDim.x * K1B_THREADS)
+            atomicAdd(&cnt[cls][small_bin(cls, g.slot_m[list[i]])], 1);
+    }
+    __syncthreads();
+    if (tid < 96) {
+        const int cls = tid >> 5, b = tid & 31;
+        int off = 0;                                             // start of bin b = sum of the bins before it
+        for (int k = 0; k < b; k++) off += g.k1_bins[cls * 32 + k];
+        const int c = cnt[cls][b];
+        base[cls][b] = off + (c ? atomicAdd(&g.k1_bins[96 + tid], c) : 0);
+    }
+    __syncthreads();
+    for (int cls = 0; cls < 3; cls++) {
+        const int total = g.ctr->class_cells[cls];
+        const int32_t *list = g.class_list + (int64_t)cls * g.class_stride;
+        int32_t *out = g.class_list + (int64_t)(first_region + cls) * g.class_stride;
+        for (int i = blockIdx.x * K1B_THREADS + tid; i < total; i += gridDim.x * K1B_THREADS) {
+            const int slot = list[i];
+            out[atomicAdd(&base[cls][small_bin(cls, g.slot_m[slot])], 1)] = slot;
+        }
+    }
+}
+
+
 template <int G>
-__global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int cls)
+__global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int cls, int list_region)
 {
     // per-lane shared slots, indexed [group base + position]
     __shared__ int32_t sh_agent[K1S_THREADS];
@@ -155,7 +217,7 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
     const int tb = (int)threadIdx.x - gl;           // group base in the block-wide shared arrays
     if (g.ctr->error) return;
     const int total = g.ctr->class_cells[cls];
-    const int32_t *list = g.class_list + (int64_t)cls * g.class_stride;
+    const int32_t *list = g.class_list + (int64_t)list_region * g.class_stride;
     const int n_groups = (gridDim.x * K1S_THREADS) / G;
     const mtd_params *P = g.P;
     const double one_minus_mhd = 1 - g.day.mhd;
@@ -790,8 +852,36 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, uint32_t 
     __syncwarp();
 }
 
+// Longest-processing-time-first order of one large class: a 300-interval cell keeps one warp busy for ~0.6 ms, so it
+// must be among the first cells fetched, not the last (the tail decides the stage when a rank holds only a few
+// thousand such cells).  One block: counting sort of the class list by interval count, descending, into the extra
+// list region.  The order of cells inside a bin is arbitrary; every cell writes only its own rows.
+__global__ void __launch_bounds__(1024) k1_lpt_kernel(DevCtx g, int cls, int out_region, int m_hi, int n_bins)
+{
+    __shared__ int hist[512];
+    const int total = g.ctr->class_cells[cls];
+    const int32_t *list = g.class_list + (int64_t)cls * g.class_stride;
+    int32_t *out = g.class_list + (int64_t)out_region * g.class_stride;
+    for (int b = threadIdx.x; b < n_bins; b += blockDim.x) hist[b] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+        int b = m_hi - g.slot_m[list[i]];
+        b = b < 0 ? 0 : (b >= n_bins ? n_bins - 1 : b);
+        atomicAdd(&hist[b], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { int acc = 0; for (int b = 0; b < n_bins; b++) { const int h = hist[b]; hist[b] = acc; acc += h; } }
+    __syncthreads();
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+        const int slot = list[i];
+        int b = m_hi - g.slot_m[slot];
+        b = b < 0 ? 0 : (b >= n_bins ? n_bins - 1 : b);
+        out[atomicAdd(&hist[b], 1)] = slot;
+    }
+}
+
 template <int MM, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32, (MM == 128 ? 8 : 1)) k1_large_kernel(DevCtx g, int cls, int64_t bits_off)
+__global__ void __launch_bounds__(WARPS * 32, (MM == 128 ? 8 : 1)) k1_large_kernel(DevCtx g, int cls, int64_t bits_off, int list_cls)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -799,7 +889,7 @@ __global__ void __launch_bounds__(WARPS * 32, (MM == 128 ? 8 : 1)) k1_large_kern
     uint32_t *bits = g.k1_bits + bits_off + ((size_t)blockIdx.x * WARPS + warp) * Lay<MM>::bits_words;
     if (g.ctr->error) return;
     const int total = g.ctr->class_cells[cls];
-    const int32_t *list = g.class_list + (int64_t)cls * g.class_stride;
+    const int32_t *list = g.class_list + (int64_t)list_cls * g.class_stride;
     unsigned long long acc_pairs = 0, acc_pot = 0;
     while (true) {
         int w = 0;
@@ -829,25 +919,26 @@ int large_blocks_per_sm(int cap)
 }
 
 template <int MM, int WARPS>
-int launch_large(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int cap, int64_t bits_off)
+int launch_large(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int cap, int64_t bits_off, int lpt_region = 0)
 {
     int grid = sm_count * large_blocks_per_sm<MM, WARPS>(cap);
     const int64_t fit = (c.k1_bits_words - bits_off) / (int64_t)(Lay<MM>::bits_words * WARPS);
     if (grid > fit) grid = (int)fit;
     if (grid < 1) return 0;
-    k1_large_kernel<MM, WARPS><<<grid, WARPS * 32, Lay<MM>::bytes * WARPS, st>>>(c, cls, bits_off);
-    return 1;
+    if (lpt_region) k1_lpt_kernel<<<1, 1024, 0, st>>>(c, cls, lpt_region, MM, 512);
+    k1_large_kernel<MM, WARPS><<<grid, WARPS * 32, Lay<MM>::bytes * WARPS, st>>>(c, cls, bits_off, lpt_region ? lpt_region : cls);
+    return lpt_region ? 2 : 1;
 }
 
 template <int G>
-int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count)
+int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int list_region)
 {
     static int per_sm = 0;
     if (per_sm == 0) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_small_kernel<G>, K1S_THREADS, 0);
         if (per_sm < 1) per_sm = 1;
     }
-    k1_small_kernel<G><<<sm_count * per_sm, K1S_THREADS, 0, st>>>(c, cls);
+    k1_small_kernel<G><<<sm_count * per_sm, K1S_THREADS, 0, st>>>(c, cls, list_region);
     return 1;
 }
 
@@ -890,6 +981,7 @@ int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t a
 {
     static const int cap4 = env_int("MTD_K1_CAP320", K1_NOCAP), cap3 = env_int("MTD_K1_CAP128", K1_NOCAP);
     static const int overlap = env_int("MTD_K1_OVERLAP", 1);
+    static const int lpt = env_int("MTD_K1_LPT", 7);     // bit 0: class 4, bit 1: class 3 longest-first; bit 2: small classes by size
     int64_t o5, o4, o3;
     k1_bits_offsets(sm_count, o5, o4, o3);
     cudaStream_t sl = st, sl2 = st;
@@ -903,11 +995,18 @@ int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t a
     // big cells first: they are the long poles; the two big classes on streams of their own, so that the tail of one
     // (a handful of warps finishing 300-interval cells) overlaps the other
     n += launch_large<K1_C5>(c, 5, sl, sm_count, K1_C5_CAP, o5);
-    n += launch_large<K1_C4>(c, 4, sl, sm_count, cap4, o4);
-    n += launch_large<K1_C3>(c, 3, sl2, sm_count, cap3, o3);
-    n += launch_small<16>(c, 1, st, sm_count);
-    n += launch_small<8>(c, 0, st, sm_count);
-    n += launch_small<32>(c, 2, st, sm_count);
+    n += launch_large<K1_C4>(c, 4, sl, sm_count, cap4, o4, (lpt & 1) ? MTD_NUM_CLASSES : 0);
+    n += launch_large<K1_C3>(c, 3, sl2, sm_count, cap3, o3, (lpt & 2) ? MTD_NUM_CLASSES + 1 : 0);
+    const int sorted_small = (lpt & 4) ? MTD_NUM_CLASSES + 2 : 0;      // regions +2, +3, +4 = classes 0, 1, 2 by size
+    if (sorted_small) {
+        cudaMemsetAsync(c.k1_bins, 0, sizeof(int32_t) * 2 * 96, st);
+        k1_bin_hist_kernel<<<sm_count * 2, K1B_THREADS, 0, st>>>(c);
+        k1_bin_scatter_kernel<<<sm_count * 2, K1B_THREADS, 0, st>>>(c, sorted_small);
+        n += 2;
+    }
+    n += launch_small<16>(c, 1, st, sm_count, sorted_small ? sorted_small + 1 : 1);
+    n += launch_small<8>(c, 0, st, sm_count, sorted_small ? sorted_small : 0);
+    n += launch_small<32>(c, 2, st, sm_count, sorted_small ? sorted_small + 2 : 2);
     if (sl != st) {
         cudaEventRecord(ev_join, sl);
         cudaEventRecord(ev_join2, sl2);
