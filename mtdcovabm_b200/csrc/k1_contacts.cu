@@ -248,6 +248,8 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
             if (w + 2 * n_groups < total) nx2_slot = list[w + 2 * n_groups];
         }
 
+        if (m < 2) continue;                        // a lone interval: no pair, no row (K0 zeroed slot_nrows); with the
+                                                    //   size-sorted list these cells sit together at the end
         // ---- 1. my interval; restore list (emission) order by ranking the emission indices ----
         const bool have = gl < m;
         int rank = 0;

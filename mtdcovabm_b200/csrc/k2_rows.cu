@@ -2,7 +2,19 @@
 // rows of a cell in creation order.  K1 wrote each cell's rows into its own scratch segment; here they are packed.
 #include "common.cuh"
 
-__global__ void k2_compact_kernel(DevCtx c)
+__device__ __forceinline__ void k2_copy_row(const DevCtx &c, int64_t src, int64_t dst, uint32_t sc)
+{
+    if (dst < c.cap_rows) {
+        const RowRec rr = c.scratch_rows[src];
+        c.rows[dst] = rr;
+        if (c.rows12) {     // {a1, a2, start | end << 8 | simcelltype << 16}
+            uint32_t *o = c.rows12 + 3 * dst;
+            o[0] = (uint32_t)rr.a1; o[1] = (uint32_t)rr.a2; o[2] = (rr.sed & 0xffffu) | (sc << 16);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) k2_compact_kernel(DevCtx c)
 {
     const int lane = threadIdx.x & 31;
     const int n_slots = c.ctr->n_slots;
@@ -12,10 +24,38 @@ __global__ void k2_compact_kernel(DevCtx c)
         if (total > c.cap_rows) c.ctr->error = MTD_E_CAPACITY;
     }
     const int warps = (gridDim.x * blockDim.x) >> 5;
-    for (int s0 = (((int)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 32; s0 < n_slots; s0 += warps * 32) {
+    const int gwarp = ((int)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    // Cells of more than 32 intervals hold hundreds to thousands of rows: left to the slot loop below, one warp would
+    // copy such a cell alone while its 31 other slots wait (the tail of the stage when a rank holds few cells).  They
+    // are taken from their size-class lists instead: a warp per cell of class 3, a block per cell of classes 4 and 5.
+    {
+        const int n3 = c.ctr->class_cells[3];
+        const int32_t *list = c.class_list + 3 * c.class_stride;
+        for (int j = gwarp; j < n3; j += warps) {
+            const int s = list[j];
+            const int cnt = c.slot_nrows[s];
+            if (cnt <= 0) continue;
+            const int64_t src = c.slot_rowoff[s], dst = c.slot_denseoff[s];
+            const uint32_t sc = c.rows12 ? (uint32_t)simcelltype_of(c.cell_type[c.slot_cell[s]]) : 0u;
+            for (int r = lane; r < cnt; r += 32) k2_copy_row(c, src + r, dst + r, sc);
+        }
+    }
+    for (int cls = 4; cls < MTD_NUM_CLASSES; cls++) {
+        const int nl = c.ctr->class_cells[cls];
+        const int32_t *list = c.class_list + (int64_t)cls * c.class_stride;
+        for (int j = blockIdx.x; j < nl; j += gridDim.x) {
+            const int s = list[j];
+            const int cnt = c.slot_nrows[s];
+            if (cnt <= 0) continue;
+            const int64_t src = c.slot_rowoff[s], dst = c.slot_denseoff[s];
+            const uint32_t sc = c.rows12 ? (uint32_t)simcelltype_of(c.cell_type[c.slot_cell[s]]) : 0u;
+            for (int r = threadIdx.x; r < cnt; r += blockDim.x) k2_copy_row(c, src + r, dst + r, sc);
+        }
+    }
+    for (int s0 = gwarp * 32; s0 < n_slots; s0 += warps * 32) {
         int s = s0 + lane;
         int cnt = 0, sct = 0; int64_t src = 0, dst = 0;
-        if (s < n_slots) {
+        if (s < n_slots && c.slot_m[s] <= 32) {                 // size classes 0..2 (and the cells of a day in error)
             cnt = c.slot_nrows[s]; src = c.slot_rowoff[s]; dst = c.slot_denseoff[s];
             if (c.rows12 && cnt > 0) sct = simcelltype_of(c.cell_type[c.slot_cell[s]]);
         }
@@ -26,15 +66,7 @@ __global__ void k2_compact_kernel(DevCtx c)
             int n = __shfl_sync(FULLMASK, cnt, l);
             int64_t sb = __shfl_sync(FULLMASK, src, l), db = __shfl_sync(FULLMASK, dst, l);
             const uint32_t sc = (uint32_t)__shfl_sync(FULLMASK, sct, l);
-            for (int r = lane; r < n; r += 32)
-                if (db + r < c.cap_rows) {
-                    const RowRec rr = c.scratch_rows[sb + r];
-                    c.rows[db + r] = rr;
-                    if (c.rows12) {     // {a1, a2, start | end << 8 | simcelltype << 16}
-                        uint32_t *o = c.rows12 + 3 * (db + r);
-                        o[0] = (uint32_t)rr.a1; o[1] = (uint32_t)rr.a2; o[2] = (rr.sed & 0xffffu) | (sc << 16);
-                    }
-                }
+            for (int r = lane; r < n; r += 32) k2_copy_row(c, sb + r, db + r, sc);
         }
     }
 }
