@@ -832,16 +832,10 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, uint32_t 
             const int nd = (int)c.deg[y] - 1;
             c.deg[y] = (int16_t)nd;
             if (nd == 0) atomicAnd(&c.alive[y >> 5], ~(1u << (y & 31)));
-            bool x_first; int st, en, dur;
-            pair_row_lists(c, x, y, x_first, st, en, dur);
-            if (n_rows + t < row_cap) {
-                RowRec rr;
-                const int agy = c.agent[y];
-                rr.a1 = x_first ? agx : agy; rr.a2 = x_first ? agy : agx;
-                rr.sed = (uint32_t)st | ((uint32_t)en << 8) | ((uint32_t)dur << 16);
-                rr.slot = slot;
-                rows[n_rows + t] = rr;
-            } else g.ctr->error = MTD_E_CAPACITY;
+            // the row is only reserved here (local indices of the pair); its overlap scan runs after the greedy loop with
+            // all 32 lanes on rows, not `made` lanes inside the sequential chain
+            if (n_rows + t < row_cap) __stcg(&rows[n_rows + t].a1, (int32_t)((uint32_t)x | ((uint32_t)y << 16)));
+            else g.ctr->error = MTD_E_CAPACITY;
         }
         if (lane == 0) {                                     // the main agent's degree is spent
             c.deg[x] = (int16_t)(d - spent);
@@ -850,7 +844,22 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, uint32_t 
         n_rows += made;
         __syncwarp();
     }
-    if (lane == 0) g.slot_nrows[slot] = n_rows < row_cap ? n_rows : row_cap;
+    const int n_out = n_rows < row_cap ? n_rows : row_cap;
+    if (lane == 0) g.slot_nrows[slot] = n_out;
+    __syncwarp();
+    // ---- 7. contact rows of the reserved pairs (contactnetwork.py:98-105, 160-196) ----
+    for (int r = lane; r < n_out; r += 32) {
+        const uint32_t xy = (uint32_t)__ldcg(&rows[r].a1);
+        const int x = (int)(xy & 0xffffu), y = (int)(xy >> 16);
+        bool x_first; int st, en, dur;
+        pair_row_lists(c, x, y, x_first, st, en, dur);
+        RowRec rr;
+        const int agx = c.agent[x], agy = c.agent[y];
+        rr.a1 = x_first ? agx : agy; rr.a2 = x_first ? agy : agx;
+        rr.sed = (uint32_t)st | ((uint32_t)en << 8) | ((uint32_t)dur << 16);
+        rr.slot = slot;
+        rows[r] = rr;
+    }
     __syncwarp();
 }
 
