@@ -365,7 +365,6 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
             const uint32_t alive = (__ballot_sync(gmask, isag && deg > 0) >> gbase) & gbits;
             uint32_t cand = __shfl_sync(gmask, adj, x) & alive;     // util.get_all_contacts_ids_by_id
             const int agx = __shfl_sync(gmask, agent, x);
-            const uint32_t ivx = __shfl_sync(gmask, mm, x);
             if (dx <= 0) continue;
             const int nc = __popc(cand);
             if (nc == 0) continue;                                  // returned None (contactnetwork.py:294)
@@ -403,25 +402,37 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
                 if (gl < d) mypick = nth_set_bit(cand, q);
                 picked = __reduce_or_sync(gmask, gl < d ? (1u << mypick) : 0u);
             }
-            // rows: lane t builds the row of pick t
-            const uint32_t ivy = __shfl_sync(gmask, mm, gbase + (mypick >= 0 ? mypick : gl));
-            const int agy = __shfl_sync(gmask, agent, gbase + (mypick >= 0 ? mypick : gl));
+            // rows: lane t reserves the row of pick t (group-relative lanes of the pair); the rows are built after the
+            // greedy loop, a lane per row, instead of by d of the G lanes in every iteration
             if (mypick >= 0) {
-                bool x_first; int st, en, dur;
-                pair_row_bits(se, ivx, ivy, x_first, st, en, dur);
-                if (n_rows + gl < row_cap) {
-                    RowRec rr;
-                    rr.a1 = x_first ? agx : agy; rr.a2 = x_first ? agy : agx;
-                    rr.sed = (uint32_t)st | ((uint32_t)en << 8) | ((uint32_t)dur << 16);
-                    rr.slot = slot;
-                    rows[n_rows + gl] = rr;
-                } else g.ctr->error = MTD_E_CAPACITY;
+                if (n_rows + gl < row_cap) __stcg(&rows[n_rows + gl].a1, (int32_t)((uint32_t)(x - gbase) | ((uint32_t)mypick << 8)));
+                else g.ctr->error = MTD_E_CAPACITY;
             }
             if ((picked >> gl) & 1u) deg -= 1;                      // partner degree - 1 (dead at 0: alive mask)
             if (lane == x) deg = d - npick;                         // the main agent's degree is spent
             n_rows += npick;
         }
-        if (gl == 0) g.slot_nrows[slot] = n_rows < row_cap ? n_rows : row_cap;
+        const int n_out = n_rows < row_cap ? n_rows : row_cap;
+        if (gl == 0) g.slot_nrows[slot] = n_out;
+        __syncwarp(gmask);
+        // ---- 7. contact rows of the reserved pairs (contactnetwork.py:98-105, 160-196) ----
+        for (int r0 = 0; r0 < n_out; r0 += G) {
+            const int r = r0 + gl;
+            const bool v = r < n_out;
+            const uint32_t xy = v ? (uint32_t)__ldcg(&rows[r].a1) : 0u;
+            const int xl = gbase + (int)(xy & 0xffu), yl = gbase + (int)(xy >> 8);
+            const uint32_t ivx = __shfl_sync(gmask, mm, xl), ivy = __shfl_sync(gmask, mm, yl);
+            const int agx = __shfl_sync(gmask, agent, xl), agy = __shfl_sync(gmask, agent, yl);
+            if (v) {
+                bool x_first; int st, en, dur;
+                pair_row_bits(se, ivx, ivy, x_first, st, en, dur);
+                RowRec rr;
+                rr.a1 = x_first ? agx : agy; rr.a2 = x_first ? agy : agx;
+                rr.sed = (uint32_t)st | ((uint32_t)en << 8) | ((uint32_t)dur << 16);
+                rr.slot = slot;
+                rows[r] = rr;
+            }
+        }
     }
     if (gl == 0 && (acc_pairs | acc_pot)) {
         atomicAdd(&g.ctr->pairs_evaluated, acc_pairs);
