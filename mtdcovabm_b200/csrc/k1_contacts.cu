@@ -208,6 +208,7 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
     __shared__ int32_t sh_agent[K1S_THREADS];
     __shared__ uint16_t sh_se[K1S_THREADS];
     __shared__ __align__(16) uint32_t sh_mask[K1S_THREADS][6];     // agent occupancy masks (5 words used)
+    __shared__ uint16_t sh_pair[2 * K1S_THREADS];                  // reserved rows of the cell: 2 G pairs per group
 
     const int lane = threadIdx.x & 31;
     const int gl = lane & (G - 1);                  // lane in group
@@ -405,8 +406,11 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
             // rows: lane t reserves the row of pick t (group-relative lanes of the pair); the rows are built after the
             // greedy loop, a lane per row, instead of by d of the G lanes in every iteration
             if (mypick >= 0) {
-                if (n_rows + gl < row_cap) __stcg(&rows[n_rows + gl].a1, (int32_t)((uint32_t)(x - gbase) | ((uint32_t)mypick << 8)));
-                else g.ctr->error = MTD_E_CAPACITY;
+                const int ri = n_rows + gl;
+                const uint32_t xy = (uint32_t)(x - gbase) | ((uint32_t)mypick << 8);
+                if (ri >= row_cap) g.ctr->error = MTD_E_CAPACITY;
+                else if (ri < 2 * G) sh_pair[2 * tb + ri] = (uint16_t)xy;
+                else __stcg(&rows[ri].a1, (int32_t)xy);              // beyond the shared slots (rare): through the row itself
             }
             if ((picked >> gl) & 1u) deg -= 1;                      // partner degree - 1 (dead at 0: alive mask)
             if (lane == x) deg = d - npick;                         // the main agent's degree is spent
@@ -419,7 +423,7 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
         for (int r0 = 0; r0 < n_out; r0 += G) {
             const int r = r0 + gl;
             const bool v = r < n_out;
-            const uint32_t xy = v ? (uint32_t)__ldcg(&rows[r].a1) : 0u;
+            const uint32_t xy = !v ? 0u : (r < 2 * G ? (uint32_t)sh_pair[2 * tb + r] : (uint32_t)__ldcg(&rows[r].a1));
             const int xl = gbase + (int)(xy & 0xffu), yl = gbase + (int)(xy >> 8);
             const uint32_t ivx = __shfl_sync(gmask, mm, xl), ivy = __shfl_sync(gmask, mm, yl);
             const int agx = __shfl_sync(gmask, agent, xl), agy = __shfl_sync(gmask, agent, yl);
@@ -776,6 +780,8 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, uint32_t 
     // q += (q >= r_s) for s = t-1 .. 0, and selects that set bit -- all picks of the main agent in parallel.
     uint16_t *rarr = c.ts;                                 // draws r_t (ts is dead after phase 4)
     uint16_t *pickarr = c.pc;                              // replay: picked local agents (pc is dead after phase 4)
+    uint32_t *stage = (uint32_t *)(sm + L::o_u);           // reserved rows (pairs of local agents); U is dead from here on
+    constexpr int stage_cap = (int)(L::u_bytes / sizeof(uint32_t));
     RowRec *rows = g.scratch_rows + g.slot_rowoff[slot];
     const int row_cap = g.slot_rowbound[slot];
     const bool replay = g.day.mode == MTD_MODE_REPLAY;
@@ -845,8 +851,11 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, uint32_t 
             if (nd == 0) atomicAnd(&c.alive[y >> 5], ~(1u << (y & 31)));
             // the row is only reserved here (local indices of the pair); its overlap scan runs after the greedy loop with
             // all 32 lanes on rows, not `made` lanes inside the sequential chain
-            if (n_rows + t < row_cap) __stcg(&rows[n_rows + t].a1, (int32_t)((uint32_t)x | ((uint32_t)y << 16)));
-            else g.ctr->error = MTD_E_CAPACITY;
+            const int ri = n_rows + t;
+            const uint32_t xy = (uint32_t)x | ((uint32_t)y << 16);
+            if (ri >= row_cap) g.ctr->error = MTD_E_CAPACITY;
+            else if (ri < stage_cap) stage[ri] = xy;
+            else __stcg(&rows[ri].a1, (int32_t)xy);                // beyond the shared scratch (rare): through the row itself
         }
         if (lane == 0) {                                     // the main agent's degree is spent
             c.deg[x] = (int16_t)(d - spent);
@@ -860,7 +869,7 @@ __device__ void process_cell_large(const DevCtx &g, unsigned char *sm, uint32_t 
     __syncwarp();
     // ---- 7. contact rows of the reserved pairs (contactnetwork.py:98-105, 160-196) ----
     for (int r = lane; r < n_out; r += 32) {
-        const uint32_t xy = (uint32_t)__ldcg(&rows[r].a1);
+        const uint32_t xy = r < stage_cap ? stage[r] : (uint32_t)__ldcg(&rows[r].a1);
         const int x = (int)(xy & 0xffffu), y = (int)(xy >> 16);
         bool x_first; int st, en, dur;
         pair_row_lists(c, x, y, x_first, st, en, dur);
