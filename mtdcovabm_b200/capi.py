@@ -25,7 +25,7 @@ EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mt
            "mtd_get_contacts", "mtd_get_exposed", "mtd_get_infection_prob", "mtd_occupancy", "mtd_sync",
            "mtd_set_profiling", "mtd_get_stage_ms", "mtd_set_export", "mtd_prefetch_intervals",
            "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced",
-           "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts", "mtd_seed_exposures", "mtd_set_intervention_mask",
+           "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts", "mtd_seed_exposures", "mtd_set_intervention_mask", "mtd_set_k0_overlap",
            "mtd_process_test_results", "mtd_enable_vaccination", "mtd_schedule_vaccinations", "mtd_set_vaccination",
            "mtd_get_vaccination", "mtd_build_intervals", "mtd_get_intervals"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
@@ -283,6 +283,10 @@ class Handle:
     def set_intervention_mask(self, on=True):
         """K0 keeps deceased / quarantined / hospitalised agents in their residence cell only"""
         self._ck(self.lib.mtd_set_intervention_mask(self.h, int(on)), "mtd_set_intervention_mask")
+
+    def set_k0_overlap(self, on=True):
+        """MEM_DEVICE interval arrays are complete at call time: K0 of the next day may run beside this day's K1..K3"""
+        self._ck(self.lib.mtd_set_k0_overlap(self.h, int(on)), "mtd_set_k0_overlap")
 
     def advance_seir(self, day, mask=None, mem=MEM_HOST):
         self._ck(self.lib.mtd_advance_seir(self.h, C.c_int32(day), _ptr(mask), mem), "mtd_advance_seir")

@@ -49,6 +49,21 @@ struct mtd_handle_s {
     // own stream beside K0/K1/K2 of day d+1, which read no per-agent state; K3 of day d+1 joins the two.
     cudaStream_t state_stream = nullptr;
     cudaEvent_t ev_state = nullptr, ev_main = nullptr;
+    // K0 of day d+1 reads only the interval stream and static cell attributes, and it is bound by L2 atomics and a random
+    // scatter while K1 is bound by instruction issue: it runs on a stream of its own beside K1..K3 of day d.  Everything
+    // K0 produces (and the day's counters) is double-buffered by day parity; DevCtx is passed by value at launch, so
+    // swapping the pointers in h->c at the start of a day is all the later stages need.
+    struct K0Set { int32_t *cell_count; uint32_t *cell_first; int64_t *cell_base; uint16_t *iv_pos; int32_t *flag_scan;
+                   int32_t *slot_cell, *slot_m; uint32_t *slot_first; uint8_t *slot_act; int64_t *slot_off, *slot_rowoff;
+                   int32_t *slot_rowbound, *slot_nrows; int64_t *slot_denseoff; int32_t *class_list; IvRec *csr;
+                   DevCounters *ctr; } k0set[2] = {};
+    cudaStream_t k0_stream = nullptr;
+    cudaEvent_t ev_k0_ready = nullptr, ev_main_mark[2] = {}, ev_state_mark[2] = {};
+    long long *scan_tmp_k0 = nullptr;
+    bool k0_pipe = true;                         // MTD_K0_PIPE=0 keeps K0 on the main stream
+    bool k0_pipe_staged = false;
+    bool k0_device_ready = false;                // mtd_set_k0_overlap: MTD_MEM_DEVICE inputs are complete at call time
+    int64_t k0_seq = 0;
     bool state_dirty = false;                    // the state stream has work the main stream has not waited for
     bool main_dirty = false;                     // the main stream touched per-agent state since the state stream last waited
     // peer exchange (NVLink peer memory, one slice per source rank and day parity)
@@ -237,6 +252,33 @@ static int create_impl(mtd_handle h)
     DA(h->d_iv_agent, M); DA(h->d_iv_cell, M); DA(h->d_iv_start, M); DA(h->d_iv_end, M); DA(h->d_iv_order, M);
     DA(h->d_mask, N);
     DA(h->scan_tmp, 2 * ((std::max(M, S) + 2) / 2048 + 16));
+    DA(h->scan_tmp_k0, 2 * ((std::max(M, S) + 2) / 2048 + 16));
+    {   // the second parity of the K0 products
+        mtd_handle_s::K0Set &a = h->k0set[0], &b = h->k0set[1];
+        a = { c.cell_count, c.cell_first, c.cell_base, c.iv_pos, c.flag_scan, c.slot_cell, c.slot_m, c.slot_first, c.slot_act,
+              c.slot_off, c.slot_rowoff, c.slot_rowbound, c.slot_nrows, c.slot_denseoff, c.class_list, c.csr, c.ctr };
+        DA(b.cell_count, C); DA(b.cell_first, C); DA(b.cell_base, C); DA(b.iv_pos, M); DA(b.flag_scan, M + 64);
+        DA(b.slot_cell, S + 1); DA(b.slot_m, S + 1); DA(b.slot_first, S + 1); DA(b.slot_act, S + 1);
+        DA(b.slot_off, S + 2); DA(b.slot_rowoff, S + 2); DA(b.slot_rowbound, S + 1);
+        DA(b.slot_nrows, S + 1); DA(b.slot_denseoff, S + 2);
+        DA(b.class_list, (MTD_NUM_CLASSES + 5) * (S + 1));
+        DA(b.csr, M); DA(b.ctr, 1);
+        CK(cudaMemsetAsync(b.ctr, 0, sizeof(DevCounters), h->stream));
+        int lo = 0, hi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        const char *pe = getenv("MTD_K0_PRIO");
+        const int prio = (pe && *pe == '1') ? hi : ((pe && *pe == '2') ? 0 : lo);
+        CK(cudaStreamCreateWithPriority(&h->k0_stream, cudaStreamNonBlocking, prio));   // default: fills what K1 leaves free
+        CK(cudaEventCreateWithFlags(&h->ev_k0_ready, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&h->ev_main_mark[0], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&h->ev_main_mark[1], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&h->ev_state_mark[0], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&h->ev_state_mark[1], cudaEventDisableTiming));
+        const char *e = getenv("MTD_K0_PIPE");
+        h->k0_pipe = !(e && *e == '0');
+        const char *es = getenv("MTD_K0_PIPE_STAGED");
+        h->k0_pipe_staged = es && *es == '1';
+    }
     DA(h->expo_list, 2 * c.cap_expo);
     DA(h->occ, 8);
     // initial state: nobody present
@@ -279,6 +321,8 @@ extern "C" int mtd_destroy(mtd_handle h)
     cudaSetDevice(h->cfg.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->state_stream) { cudaStreamSynchronize(h->state_stream); cudaStreamDestroy(h->state_stream); }
+    if (h->k0_stream) { cudaStreamSynchronize(h->k0_stream); cudaStreamDestroy(h->k0_stream); }
+    for (cudaEvent_t e : { h->ev_k0_ready, h->ev_main_mark[0], h->ev_main_mark[1], h->ev_state_mark[0], h->ev_state_mark[1] }) if (e) cudaEventDestroy(e);
     if (h->ev_state) cudaEventDestroy(h->ev_state);
     if (h->ev_main) cudaEventDestroy(h->ev_main);
     for (void *p : { (void *)h->seed_buf, (void *)h->sc_a1, (void *)h->sc_a2, (void *)h->sc_off, (void *)h->sc_se, (void *)h->vacc_ids, (void *)h->vacc_ts,
@@ -443,10 +487,26 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     c.ov_off = nullptr; c.ov_se = nullptr;
     c.agent_masked = h->mask_on ? h->agent_masked : nullptr;
     if (h->mask_on) TOUCH();                 // K0 reads today's state (after K4 of today and the apply of yesterday)
+    // today's parity of the K0 products; K0 goes to its own stream when its inputs do not come through the main stream
+    const int kp = (int)(h->k0_seq++ & 1);
+    {
+        const mtd_handle_s::K0Set &k = h->k0set[kp];
+        c.cell_count = k.cell_count; c.cell_first = k.cell_first; c.cell_base = k.cell_base; c.iv_pos = k.iv_pos;
+        c.flag_scan = k.flag_scan; c.slot_cell = k.slot_cell; c.slot_m = k.slot_m; c.slot_first = k.slot_first;
+        c.slot_act = k.slot_act; c.slot_off = k.slot_off; c.slot_rowoff = k.slot_rowoff; c.slot_rowbound = k.slot_rowbound;
+        c.slot_nrows = k.slot_nrows; c.slot_denseoff = k.slot_denseoff; c.class_list = k.class_list; c.csr = k.csr; c.ctr = k.ctr;
+    }
+    const bool pipe = h->k0_pipe && !h->mask_on && M > 0 && ((mem == MTD_MEM_STAGED && h->k0_pipe_staged) || (mem == MTD_MEM_DEVICE && h->k0_device_ready));
+    cudaStream_t ks = pipe ? h->k0_stream : h->stream;
+    // this parity was last read by the day before yesterday's K1..K3 (main stream) and apply chain (state stream, which
+    // reads the day's counters): all of it had been enqueued when yesterday's call recorded its marks
+    if (pipe) { CK(cudaStreamWaitEvent(ks, h->ev_main_mark[kp ^ 1], 0)); CK(cudaStreamWaitEvent(ks, h->ev_state_mark[kp ^ 1], 0)); }
+    CK(cudaEventRecord(h->ev_main_mark[kp], h->stream));
+    CK(cudaEventRecord(h->ev_state_mark[kp], h->state_stream));
     if (mem == MTD_MEM_STAGED) {
         const int sl = h->st_ready;
         if (sl < 0 || h->st_n[sl] != M) { h->err = "MTD_MEM_STAGED without a matching mtd_prefetch_intervals"; return MTD_E_STATE; }
-        CK(cudaStreamWaitEvent(h->stream, h->ev_staged[sl], 0));
+        CK(cudaStreamWaitEvent(ks, h->ev_staged[sl], 0));
         c.iv_agent = h->st_agent[sl]; c.iv_cell = h->st_cell[sl]; c.iv_start = h->st_start[sl]; c.iv_end = h->st_end[sl];
         c.iv_order = h->st_has_order[sl] ? h->st_order[sl] : nullptr;
         h->st_ready = -1;
@@ -467,11 +527,12 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     } else {
         c.iv_agent = iv_agent; c.iv_cell = iv_cell; c.iv_start = iv_start; c.iv_end = iv_end; c.iv_order = iv_order;
     }
-    CK(cudaMemsetAsync(c.ctr, 0, sizeof(DevCounters), h->stream));
-    CK(cudaMemsetAsync(c.cell_count, 0, sizeof(int32_t) * (size_t)c.n_cells, h->stream));
-    CK(cudaMemsetAsync(c.cell_first, 0xff, sizeof(uint32_t) * (size_t)c.n_cells, h->stream));
-    { StageScope sc(h, MTD_STAGE_K0); sc.add(launch_k0(c, h->scan_tmp, h->stream, h->sm_count)); }
-    if (h->ev_k0_done) CK(cudaEventRecord(h->ev_k0_done, h->stream));      // the interval stream has been consumed
+    CK(cudaMemsetAsync(c.ctr, 0, sizeof(DevCounters), ks));
+    CK(cudaMemsetAsync(c.cell_count, 0, sizeof(int32_t) * (size_t)c.n_cells, ks));
+    CK(cudaMemsetAsync(c.cell_first, 0xff, sizeof(uint32_t) * (size_t)c.n_cells, ks));
+    { StageScope sc(h, MTD_STAGE_K0, ks); sc.add(launch_k0(c, pipe ? h->scan_tmp_k0 : h->scan_tmp, ks, h->sm_count)); }
+    if (h->ev_k0_done) CK(cudaEventRecord(h->ev_k0_done, ks));             // the interval stream has been consumed
+    if (pipe) { CK(cudaEventRecord(h->ev_k0_ready, ks)); CK(cudaStreamWaitEvent(h->stream, h->ev_k0_ready, 0)); }
     // an empty day (M == 0) has no cells: the zeroed counters are its result
     if (M > 0) { StageScope sc(h, MTD_STAGE_K1); sc.add(launch_k1(c, h->stream, h->aux_stream, h->aux2_stream, h->ev_fork, h->ev_join, h->ev_join2, h->sm_count)); }
     c.rows12 = nullptr;
@@ -773,6 +834,13 @@ extern "C" int mtd_set_intervention_mask(mtd_handle h, int on)
     return MTD_OK;
 }
 
+extern "C" int mtd_set_k0_overlap(mtd_handle h, int on)
+{
+    if (!h) return MTD_E_ARG;
+    h->k0_device_ready = on != 0;
+    return MTD_OK;
+}
+
 extern "C" int mtd_advance_seir(mtd_handle h, int32_t day, const uint8_t *mask, int mem)
 {
     if (!h) return MTD_E_ARG;
@@ -856,6 +924,7 @@ extern "C" int mtd_get_stage_ms(mtd_handle h, float ms[MTD_N_STAGES], int64_t la
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaStreamSynchronize(h->state_stream));
+    CK(cudaStreamSynchronize(h->k0_stream));
     for (int s = 0; s < MTD_N_STAGES; s++) {
         ms[s] = 0.f;
         double sum = 0.0;
@@ -878,6 +947,7 @@ extern "C" int mtd_sync(mtd_handle h)
     CK(cudaSetDevice(h->cfg.device));
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaStreamSynchronize(h->state_stream));
+    CK(cudaStreamSynchronize(h->k0_stream));
     return MTD_OK;
 }
 

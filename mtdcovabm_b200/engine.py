@@ -107,6 +107,12 @@ class DayEngine:
                              sched_cnt=pop.sched_cnt, mem=D)
         self.h.sync()
 
+    def set_inputs_ready(self, on=True):
+        """Promise that the device interval arrays given to step() are complete when step() is called (pre-built day
+        streams, nothing pending on any torch stream writes them): the library then runs K0 of day d+1 beside K1..K3 of
+        day d (mtd_set_k0_overlap).  step_host() needs no promise: the library owns its uploads."""
+        self.h.set_k0_overlap(on)
+
     # ---- one day
     def step(self, day, s, mhd=0.0, testing=False, quarantine=False, mem=capi.MEM_DEVICE, n=None):
         """s: dict(iv_agent, iv_cell, iv_start, iv_end, iv_order) -- device tensors (mem=MEM_DEVICE) or pinned host

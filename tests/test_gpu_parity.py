@@ -425,3 +425,61 @@ def test_checkpoint_resume_is_bit_exact(tmp_path):
     for k in st_a:
         assert np.array_equal(st_a[k], st_c[k]), k
     assert np.array_equal(vac_a[0], vac_c[0]) and np.array_equal(vac_a[1], vac_c[1]) and (vac_a[0] != prm.NONE).sum() > 0
+
+
+def test_k0_overlap_equals_serial_day_loop():
+    """mtd_set_k0_overlap: K0 of day d+1 on its own stream beside K1..K3 of day d (double-buffered K0 products) gives
+    the same rows, exposures and final state as the serial order, over more days than there are buffers"""
+    import torch
+    from mtdcovabm_b200 import engine
+    z = gio.load_run("ref_1k_seed6")
+    P = prm.build_params()
+    days = [gio.load_day(z, d) for d in (12, 16, 20)]
+    tiles = [H.tile_day(g, 6, agent_major=True, seed=4, infectious_frac=0.06) for g in days]
+    st = tiles[0]["state"]
+    N, C = st.n, len(tiles[0]["cell_type"])
+    M = max(len(t["iv_cell"]) for t in tiles)
+
+    class Pop:
+        pass
+    pop = Pop()
+    dev = torch.device("cuda", 0)
+    for name, arr in (("cell_type", np.asarray(tiles[0]["cell_type"], np.int8)), ("cell_indid", np.asarray(tiles[0]["cell_indid"], np.int16)),
+                      ("age_bracket", st.age_bracket), ("epi_age_bracket", st.epi_age_bracket), ("soc_rate", st.soc_rate),
+                      ("res_cellid", st.res_cellid), ("seir", st.seir), ("inf_type", st.inf_type), ("inf_sev", st.inf_sev),
+                      ("sched", st.sched), ("sched_cnt", st.sched_cnt)):
+        setattr(pop, name, torch.from_numpy(np.ascontiguousarray(arr)).to(dev))
+    ds = [{k: torch.from_numpy(np.ascontiguousarray(t[k])).to(dev) for k in ("iv_agent", "iv_cell", "iv_start", "iv_end")}
+          for t in tiles]
+    torch.cuda.synchronize()
+    n_days = 7
+
+    def run(overlap, read_every_day):
+        e = engine.DayEngine(N, C, M + 16, P, seed=11)
+        e.set_population(pop)
+        e.set_inputs_ready(overlap)
+        out = []
+        for k in range(n_days):
+            e.step(30 + k, ds[k % len(ds)], mhd=0.1, testing=True, quarantine=True)
+            if read_every_day:
+                rows, dur, cell = e.h.get_contacts()
+                out.append((rows, dur, e.h.get_exposed(), int(e.h.counters().pairs_evaluated)))
+        rows, dur, cell = e.h.get_contacts()
+        last = (rows, dur, e.h.get_exposed(), e.h.occupancy(), e.h.counters())
+        final = e.h.get_state()
+        e.close()
+        return out, last, final
+
+    want, wlast, wfinal = run(False, True)
+    got, glast, gfinal = run(True, True)
+    assert sum(len(w[2]) for w in want) > 0
+    for (r0, d0, e0, p0), (r1, d1, e1, p1) in zip(want, got):
+        assert np.array_equal(r0, r1) and np.array_equal(d0, d1) and np.array_equal(e0, e1) and p0 == p1
+    # without host reads between the days the host runs ahead and the stages really overlap
+    _, alast, afinal = run(True, False)
+    assert np.array_equal(wlast[0], alast[0]) and np.array_equal(wlast[1], alast[1]) and np.array_equal(wlast[2], alast[2])
+    assert np.array_equal(wlast[3], alast[3])
+    assert int(alast[4].error) == 0 and int(alast[4].n_rows) == int(wlast[4].n_rows)
+    for f in H.STATE_FIELDS:
+        assert np.array_equal(wfinal[f], gfinal[f]), f
+        assert np.array_equal(wfinal[f], afinal[f]), f
