@@ -321,7 +321,7 @@ def run_b200(args):
         pass
     k1_ms = st_ms["k1_contacts"]
     achieved = k1_bytes / (k1_ms * 1e-3) / 1e9 if k1_ms > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": "k1_contacts (6 size-class launches per day)", "achieved": achieved,
+    roofline = {"bound": "hbm", "kernel": "k1_contacts (6 size-class launches + 4 ordering helpers per day, three streams)", "achieved": achieved,
                 "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum over the K1 launches, mean per day over the 7 day streams (profiles/r01_k1_traffic.json)",
                 "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
@@ -338,7 +338,18 @@ def run_b200(args):
                                "achieved_warp_inst_per_s": warp_instr / (k1_ms * 1e-3), "peak_warp_inst_per_s": issue_peak,
                                "frac": warp_instr / (k1_ms * 1e-3) / issue_peak,
                                "warp_instructions_per_pair": warp_instr / P_mean if P_mean else None,
-                               "note": "k1_ms is the stage's wall time with its six launches on three concurrent streams"}
+                               "note": "k1_ms is the stage's wall time with its launches on three concurrent streams"}
+    # the timed loop runs K0 of day d+1 beside K1..K3 of day d, so its per-stage times include the sharing; a short
+    # untimed pass with the stages one after the other gives the stand-alone stage times next to them
+    eng.set_inputs_ready(False)
+    for step in range(args.warmup + args.steps, args.warmup + args.steps + 2 * nb):
+        eng.step(1 + step, streams[step % nb])
+    ser_ms, _ = h.stage_ms()
+    eng.set_inputs_ready(True)
+    roofline["stage_ms_serial"] = ser_ms
+    roofline["stage_note"] = ("stage_ms / k1_ms: CUDA events around each stage over the timed region, where K0 of day d+1 shares "
+                              "the SMs with K1..K3 of day d and the state chain (k3_apply, k4_advance) runs on its own stream; "
+                              "stage_ms_serial: the same events over %d untimed days with the stages one after the other" % (2 * nb))
     h.set_profiling(False)
 
     # ---------------- end to end: host buffers in, host results out, every step
