@@ -43,3 +43,9 @@ def test_two_gpus_equal_one_gpu_nccl_allgather():
 @needs2
 def test_two_gpus_equal_one_gpu_host_boundary():
     _run(["--host"], port=29543)
+
+
+@needs2
+def test_two_gpus_with_k0_overlap_equal_one_gpu_serial():
+    """the bench's N > 1 configuration: K0 of day d+1 beside K1..K3 of day d on every rank, peer exchange, host running ahead"""
+    _run(["--overlap"], port=29544)

@@ -24,7 +24,7 @@ from mtdcovabm_b200 import engine, params as prm, synth  # noqa: E402
 KEYS = ("seir", "inf_type", "inf_sev", "sched", "sched_cnt", "test_day", "test_result_day", "quarantine", "hosp")
 
 
-def run(eng, pop, streams, days, host):
+def run(eng, pop, streams, days, host, overlap=False):
     nb = len(streams)
     exposed = []
     if host:
@@ -35,6 +35,15 @@ def run(eng, pop, streams, days, host):
         # results of a day stay valid until day d+2 is submitted: only the last two can still be read
         rows = sum(r.n_rows for r in res)
         exposed = [r.n_exposed for r in res]
+    elif overlap:
+        # the bench's configuration: pre-built device streams, K0 of day d+1 beside K1..K3 of day d, no host read
+        # between the days (the host runs ahead, so the stages really overlap)
+        torch.cuda.synchronize()
+        eng.set_inputs_ready(True)
+        for d in range(days):
+            eng.step(1 + d, streams[d % nb], testing=True)
+        exposed = [int(eng.h.counters().n_exposed)]
+        rows = int(eng.h.counters().n_rows)
     else:
         for d in range(days):
             eng.step(1 + d, streams[d % nb], testing=True)
@@ -49,6 +58,7 @@ def main():
     ap.add_argument("--reps", type=int, default=40)
     ap.add_argument("--days", type=int, default=9)
     ap.add_argument("--host", action="store_true", help="drive both engines through the pipelined host boundary")
+    ap.add_argument("--overlap", action="store_true", help="the N-rank engine runs with mtd_set_k0_overlap on and no per-day host reads")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -69,7 +79,9 @@ def main():
 
     eN = engine.DayEngine(pop.n_agents, pop.n_cells, max_m, P, device=local, rank=rank, world=world, seed=5)
     eN.set_population(pop)
-    stN, exN, rowsN = run(eN, pop, mine, a.days, a.host)
+    stN, exN, rowsN = run(eN, pop, mine, a.days, a.host, a.overlap)
+    if a.overlap:
+        ex1 = ex1[-1:]
     kind = eN.exchange
     eN.close()
 
