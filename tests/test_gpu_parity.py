@@ -451,8 +451,11 @@ def test_k0_overlap_equals_serial_day_loop():
         setattr(pop, name, torch.from_numpy(np.ascontiguousarray(arr)).to(dev))
     ds = [{k: torch.from_numpy(np.ascontiguousarray(t[k])).to(dev) for k in ("iv_agent", "iv_cell", "iv_start", "iv_end")}
           for t in tiles]
+    # an empty day in the middle: it takes the serial path (nothing to overlap) between two overlapped days
+    ds.insert(2, {"iv_agent": torch.empty(0, dtype=torch.int32, device=dev), "iv_cell": torch.empty(0, dtype=torch.int32, device=dev),
+                  "iv_start": torch.empty(0, dtype=torch.uint8, device=dev), "iv_end": torch.empty(0, dtype=torch.uint8, device=dev)})
     torch.cuda.synchronize()
-    n_days = 7
+    n_days = 9
 
     def run(overlap, read_every_day):
         e = engine.DayEngine(N, C, M + 16, P, seed=11)
