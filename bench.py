@@ -250,7 +250,7 @@ def run_b200(args):
         pairs.append((int(c.pairs_evaluated), int(c.n_rows), int(c.n_slots)))
     eng.set_population(pop)          # reset the state
     torch.cuda.synchronize()
-    eng.set_inputs_ready(True)       # the day streams were built above and are complete: K0 of day d+1 may overlap day d
+    eng.set_inputs_ready(True)       # the day streams were built above and are complete: K0/K1 of the coming days may overlap the current one
 
     def barrier():
         if world > 1:
@@ -339,7 +339,7 @@ def run_b200(args):
                                "frac": warp_instr / (k1_ms * 1e-3) / issue_peak,
                                "warp_instructions_per_pair": warp_instr / P_mean if P_mean else None,
                                "note": "k1_ms is the stage's wall time with its launches on three concurrent streams"}
-    # the timed loop runs K0 of day d+1 beside K1..K3 of day d, so its per-stage times include the sharing; a short
+    # the timed loop runs K0 and K1 of the coming days beside K2/K3 of the current one, so its per-stage times include the sharing; a short
     # untimed pass with the stages one after the other gives the stand-alone stage times next to them
     eng.set_inputs_ready(False)
     for step in range(args.warmup + args.steps, args.warmup + args.steps + 2 * nb):
@@ -347,8 +347,9 @@ def run_b200(args):
     ser_ms, _ = h.stage_ms()
     eng.set_inputs_ready(True)
     roofline["stage_ms_serial"] = ser_ms
-    roofline["stage_note"] = ("stage_ms / k1_ms: CUDA events around each stage over the timed region, where K0 of day d+1 shares "
-                              "the SMs with K1..K3 of day d and the state chain (k3_apply, k4_advance) runs on its own stream; "
+    roofline["stage_note"] = ("stage_ms / k1_ms: CUDA events around each stage over the timed region, where the day runs as a "
+                              "three-stream pipeline (K0 of day d+2, K1 of day d+1 and K2/K3 of day d share the SMs; the state "
+                              "chain k3_apply / k4_advance has its own stream), so a stage's time includes waiting for SM slots; "
                               "stage_ms_serial: the same events over %d untimed days with the stages one after the other" % (2 * nb))
     h.set_profiling(False)
 

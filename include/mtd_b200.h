@@ -190,13 +190,13 @@ int mtd_advance_seir(mtd_handle h, int32_t day, const uint8_t *mask, int mem);
  * window, unless the interval is in the agent's residence cell. */
 int mtd_set_intervention_mask(mtd_handle h, int on);
 /* Day pipelining (no reference counterpart: the reference runs its stages one after the other, sim.py:1196-1365).
- * K0 of day d+1 depends on the day's interval stream and on static cell attributes only, so the library runs it on a
- * stream of its own beside K1..K3 of day d (its products are double-buffered by day parity).  That is automatic for
- * MTD_MEM_STAGED inputs (the library owns the upload and its event).  For MTD_MEM_DEVICE inputs the library cannot see
- * who wrote the arrays: with `on`, the caller promises that the interval arrays passed to
- * mtd_simulate_contact_network are complete when the call is made (no pending work of any stream still writes them)
- * and stay untouched until the call after the next one.  Off by default; results are identical either way.  Not used
- * while the intervention mask is on (K0 then reads the day's state). */
+ * K0 of a day depends on the day's interval stream and on static cell attributes only, K1 on K0's products and static
+ * agent attributes, so the library runs K0 and K1 of the coming days on streams of their own beside K2/K3 of the
+ * current day (K0's products, K1's scratch rows and the day's counters are double-buffered by day parity).  For
+ * MTD_MEM_DEVICE inputs the library cannot see who wrote the arrays: with `on`, the caller promises that the interval
+ * arrays passed to mtd_simulate_contact_network are complete when the call is made (no pending work of any stream
+ * still writes them) and stay untouched until the call after the next one.  Off by default; results are identical
+ * either way.  Not used while the intervention mask is on (K0 then reads the day's state). */
 int mtd_set_k0_overlap(mtd_handle h, int on);
 
 /* K7: vaccination.

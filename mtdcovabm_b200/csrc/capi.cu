@@ -56,9 +56,13 @@ struct mtd_handle_s {
     struct K0Set { int32_t *cell_count; uint32_t *cell_first; int64_t *cell_base; uint16_t *iv_pos; int32_t *flag_scan;
                    int32_t *slot_cell, *slot_m; uint32_t *slot_first; uint8_t *slot_act; int64_t *slot_off, *slot_rowoff;
                    int32_t *slot_rowbound, *slot_nrows; int64_t *slot_denseoff; int32_t *class_list; IvRec *csr;
-                   DevCounters *ctr; } k0set[2] = {};
-    cudaStream_t k0_stream = nullptr;
-    cudaEvent_t ev_k0_ready = nullptr, ev_main_mark[2] = {}, ev_state_mark[2] = {};
+                   DevCounters *ctr; RowRec *scratch_rows; } k0set[2] = {};
+    cudaStream_t k0_stream = nullptr, k1_stream = nullptr;   // K1 of day d+1 likewise runs beside K2/K3 of day d (its scratch rows are per parity too)
+    cudaEvent_t ev_k1_done = nullptr;
+    bool last_pipe = false;                      // the previous day ran pipelined
+    bool k1_pipe = true;                         // MTD_K1_PIPE=0 keeps K1 on the main stream
+    cudaEvent_t ev_k0_ready = nullptr, ev_main_mark[2] = {};
+    int32_t *n_succ_buf = nullptr;               // [2] by day parity (DevCtx::n_succ_pub)
     long long *scan_tmp_k0 = nullptr;
     bool k0_pipe = true;                         // MTD_K0_PIPE=0 keeps K0 on the main stream
     bool k0_pipe_staged = false;
@@ -256,13 +260,13 @@ static int create_impl(mtd_handle h)
     {   // the second parity of the K0 products
         mtd_handle_s::K0Set &a = h->k0set[0], &b = h->k0set[1];
         a = { c.cell_count, c.cell_first, c.cell_base, c.iv_pos, c.flag_scan, c.slot_cell, c.slot_m, c.slot_first, c.slot_act,
-              c.slot_off, c.slot_rowoff, c.slot_rowbound, c.slot_nrows, c.slot_denseoff, c.class_list, c.csr, c.ctr };
+              c.slot_off, c.slot_rowoff, c.slot_rowbound, c.slot_nrows, c.slot_denseoff, c.class_list, c.csr, c.ctr, c.scratch_rows };
         DA(b.cell_count, C); DA(b.cell_first, C); DA(b.cell_base, C); DA(b.iv_pos, M); DA(b.flag_scan, M + 64);
         DA(b.slot_cell, S + 1); DA(b.slot_m, S + 1); DA(b.slot_first, S + 1); DA(b.slot_act, S + 1);
         DA(b.slot_off, S + 2); DA(b.slot_rowoff, S + 2); DA(b.slot_rowbound, S + 1);
         DA(b.slot_nrows, S + 1); DA(b.slot_denseoff, S + 2);
         DA(b.class_list, (MTD_NUM_CLASSES + 5) * (S + 1));
-        DA(b.csr, M); DA(b.ctr, 1);
+        DA(b.csr, M); DA(b.ctr, 1); DA(b.scratch_rows, c.cap_scratch_rows);
         CK(cudaMemsetAsync(b.ctr, 0, sizeof(DevCounters), h->stream));
         int lo = 0, hi = 0;
         CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
@@ -270,10 +274,14 @@ static int create_impl(mtd_handle h)
         const int prio = (pe && *pe == '1') ? hi : ((pe && *pe == '2') ? 0 : lo);
         CK(cudaStreamCreateWithPriority(&h->k0_stream, cudaStreamNonBlocking, prio));   // default: fills what K1 leaves free
         CK(cudaEventCreateWithFlags(&h->ev_k0_ready, cudaEventDisableTiming));
+        CK(cudaStreamCreateWithFlags(&h->k1_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&h->ev_k1_done, cudaEventDisableTiming));
+        { const char *e1 = getenv("MTD_K1_PIPE"); h->k1_pipe = !(e1 && *e1 == '0'); }
         CK(cudaEventCreateWithFlags(&h->ev_main_mark[0], cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&h->ev_main_mark[1], cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&h->ev_state_mark[0], cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&h->ev_state_mark[1], cudaEventDisableTiming));
+        DA(h->n_succ_buf, 2);
+        CK(cudaMemsetAsync(h->n_succ_buf, 0, 2 * sizeof(int32_t), h->stream));
+        c.n_succ_pub = h->n_succ_buf;
         const char *e = getenv("MTD_K0_PIPE");
         h->k0_pipe = !(e && *e == '0');
         const char *es = getenv("MTD_K0_PIPE_STAGED");
@@ -322,7 +330,9 @@ extern "C" int mtd_destroy(mtd_handle h)
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->state_stream) { cudaStreamSynchronize(h->state_stream); cudaStreamDestroy(h->state_stream); }
     if (h->k0_stream) { cudaStreamSynchronize(h->k0_stream); cudaStreamDestroy(h->k0_stream); }
-    for (cudaEvent_t e : { h->ev_k0_ready, h->ev_main_mark[0], h->ev_main_mark[1], h->ev_state_mark[0], h->ev_state_mark[1] }) if (e) cudaEventDestroy(e);
+    if (h->k1_stream) { cudaStreamSynchronize(h->k1_stream); cudaStreamDestroy(h->k1_stream); }
+    if (h->ev_k1_done) cudaEventDestroy(h->ev_k1_done);
+    for (cudaEvent_t e : { h->ev_k0_ready, h->ev_main_mark[0], h->ev_main_mark[1] }) if (e) cudaEventDestroy(e);
     if (h->ev_state) cudaEventDestroy(h->ev_state);
     if (h->ev_main) cudaEventDestroy(h->ev_main);
     for (void *p : { (void *)h->seed_buf, (void *)h->sc_a1, (void *)h->sc_a2, (void *)h->sc_off, (void *)h->sc_se, (void *)h->vacc_ids, (void *)h->vacc_ts,
@@ -495,14 +505,19 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
         c.flag_scan = k.flag_scan; c.slot_cell = k.slot_cell; c.slot_m = k.slot_m; c.slot_first = k.slot_first;
         c.slot_act = k.slot_act; c.slot_off = k.slot_off; c.slot_rowoff = k.slot_rowoff; c.slot_rowbound = k.slot_rowbound;
         c.slot_nrows = k.slot_nrows; c.slot_denseoff = k.slot_denseoff; c.class_list = k.class_list; c.csr = k.csr; c.ctr = k.ctr;
+        c.scratch_rows = k.scratch_rows;
+        c.n_succ_pub = h->n_succ_buf + kp;
     }
     const bool pipe = h->k0_pipe && !h->mask_on && M > 0 && ((mem == MTD_MEM_STAGED && h->k0_pipe_staged) || (mem == MTD_MEM_DEVICE && h->k0_device_ready));
     cudaStream_t ks = pipe ? h->k0_stream : h->stream;
-    // this parity was last read by the day before yesterday's K1..K3 (main stream) and apply chain (state stream, which
-    // reads the day's counters): all of it had been enqueued when yesterday's call recorded its marks
-    if (pipe) { CK(cudaStreamWaitEvent(ks, h->ev_main_mark[kp ^ 1], 0)); CK(cudaStreamWaitEvent(ks, h->ev_state_mark[kp ^ 1], 0)); }
+    // this parity was last read by the day before yesterday's K1..K3 (main stream): all of it had been enqueued when
+    // yesterday's call recorded its mark.  (The apply chain on the state stream reads no K0 product: the one counter it
+    // needs, n_succ, is published by K3 into a slot of its own.)
+    if (pipe) CK(cudaStreamWaitEvent(ks, h->ev_main_mark[kp ^ 1], 0));
     CK(cudaEventRecord(h->ev_main_mark[kp], h->stream));
-    CK(cudaEventRecord(h->ev_state_mark[kp], h->state_stream));
+    // first pipelined day after a serial one: that day's K0/K1 ran on the main stream and own the K1 scratch until they end
+    if (pipe && !h->last_pipe) CK(cudaStreamWaitEvent(ks, h->ev_main_mark[kp], 0));
+    h->last_pipe = pipe;
     if (mem == MTD_MEM_STAGED) {
         const int sl = h->st_ready;
         if (sl < 0 || h->st_n[sl] != M) { h->err = "MTD_MEM_STAGED without a matching mtd_prefetch_intervals"; return MTD_E_STATE; }
@@ -532,9 +547,13 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     CK(cudaMemsetAsync(c.cell_first, 0xff, sizeof(uint32_t) * (size_t)c.n_cells, ks));
     { StageScope sc(h, MTD_STAGE_K0, ks); sc.add(launch_k0(c, pipe ? h->scan_tmp_k0 : h->scan_tmp, ks, h->sm_count)); }
     if (h->ev_k0_done) CK(cudaEventRecord(h->ev_k0_done, ks));             // the interval stream has been consumed
-    if (pipe) { CK(cudaEventRecord(h->ev_k0_ready, ks)); CK(cudaStreamWaitEvent(h->stream, h->ev_k0_ready, 0)); }
+    // K1 needs K0 of its own day only: in the pipelined mode it runs on a third stream, beside K2/K3 of the day before
+    // (main stream), and the main stream picks the day up again at K2
+    cudaStream_t k1s = (pipe && h->k1_pipe) ? h->k1_stream : h->stream;
+    if (pipe) { CK(cudaEventRecord(h->ev_k0_ready, ks)); CK(cudaStreamWaitEvent(k1s, h->ev_k0_ready, 0)); }
     // an empty day (M == 0) has no cells: the zeroed counters are its result
-    if (M > 0) { StageScope sc(h, MTD_STAGE_K1); sc.add(launch_k1(c, h->stream, h->aux_stream, h->aux2_stream, h->ev_fork, h->ev_join, h->ev_join2, h->sm_count)); }
+    if (M > 0) { StageScope sc(h, MTD_STAGE_K1, k1s); sc.add(launch_k1(c, k1s, h->aux_stream, h->aux2_stream, h->ev_fork, h->ev_join, h->ev_join2, h->sm_count)); }
+    if (k1s != h->stream) { CK(cudaEventRecord(h->ev_k1_done, k1s)); CK(cudaStreamWaitEvent(h->stream, h->ev_k1_done, 0)); }
     c.rows12 = nullptr;
     if (h->export_on) {     // K2 also packs the rows for the export; the slot's previous export must have drained
         const int sl = (int)(h->day_seq & 1);
@@ -543,6 +562,8 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
         c.rows12 = h->rows12_buf[sl];
     }
     h->day_seq++;
+    // K2 overwrites the dense rows the apply chain of the day before still reads when it clears its winners
+    { int r = main_after_state(h); if (r) return r; }
     if (M > 0) { StageScope sc(h, MTD_STAGE_K2); sc.add(launch_scan_nrows(c, h->scan_tmp, h->stream));
                  sc.add(launch_k2_compact(c, h->stream, h->sm_count)); }
     CK(cudaGetLastError());
@@ -925,6 +946,7 @@ extern "C" int mtd_get_stage_ms(mtd_handle h, float ms[MTD_N_STAGES], int64_t la
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaStreamSynchronize(h->state_stream));
     CK(cudaStreamSynchronize(h->k0_stream));
+    CK(cudaStreamSynchronize(h->k1_stream));
     for (int s = 0; s < MTD_N_STAGES; s++) {
         ms[s] = 0.f;
         double sum = 0.0;
@@ -948,6 +970,7 @@ extern "C" int mtd_sync(mtd_handle h)
     CK(cudaStreamSynchronize(h->stream));
     CK(cudaStreamSynchronize(h->state_stream));
     CK(cudaStreamSynchronize(h->k0_stream));
+    CK(cudaStreamSynchronize(h->k1_stream));
     return MTD_OK;
 }
 

@@ -130,6 +130,8 @@ struct DevCtx {
     double *row_p;             // [cap_rows] optional infection probability per row (NULL = off)
     int32_t *delta;            // [cap_expo][MTD_DELTA_WORDS]
     DevCounters *ctr;
+    int32_t *n_succ_pub;       // the day's n_succ, published by K3 for the apply chain (state stream), which must not
+                               //   read the day's counter block: the K0 of two days later clears it on another stream
     StateCounters *sctr;
     const mtd_params *P;       // device copy of the parameters
     // intervention mask (mtd_set_intervention_mask): per-agent "stays in the residence cell today" flag, or NULL = off

@@ -200,6 +200,7 @@ __device__ __forceinline__ void sample_trajectory(const mtd_params *P, Draws &D,
 // one WARP per successful draw; only the winner of each agent samples the trajectory
 __global__ void __launch_bounds__(K3T_WARPS * 32) k3_trajectory_kernel(DevCtx c, int32_t *dbuf, int64_t cap)
 {
+    if (blockIdx.x == 0 && threadIdx.x == 0) *c.n_succ_pub = c.ctr->n_succ;     // final: the eval kernel has finished
     __shared__ double s_row[K3T_WARPS][MTD_EXPO_W + 3];
     __shared__ uint16_t s_iv[K3T_WARPS][2][K3T_MAXIV];
     __shared__ uint32_t s_ord[K3T_WARPS][2][K3T_MAXIV];
@@ -463,7 +464,7 @@ __global__ void k3_apply_kernel(DevCtx c, const int32_t *bufs, int n_bufs, int64
 // successful rows and the agents of every gathered record) instead of refilling all N entries every day.
 __global__ void k3_reset_win_kernel(DevCtx c, const int32_t *bufs, int n_bufs, int64_t cap)
 {
-    const int n = c.ctr->n_succ;
+    const int n = *c.n_succ_pub;
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
         const RowRec r = c.rows[c.succ[t]];
         c.win[r.a1] = ~0ull; c.win[r.a2] = ~0ull;

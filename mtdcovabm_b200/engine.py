@@ -109,8 +109,8 @@ class DayEngine:
 
     def set_inputs_ready(self, on=True):
         """Promise that the device interval arrays given to step() are complete when step() is called (pre-built day
-        streams, nothing pending on any torch stream writes them): the library then runs K0 of day d+1 beside K1..K3 of
-        day d (mtd_set_k0_overlap).  step_host() needs no promise: the library owns its uploads."""
+        streams, nothing pending on any torch stream writes them): the library then runs K0 and K1 of the coming days
+        beside K2/K3 of the current one (mtd_set_k0_overlap).  step_host() needs no promise: the library owns its uploads."""
         self.h.set_k0_overlap(on)
 
     # ---- one day
