@@ -206,7 +206,12 @@ static int create_impl(mtd_handle h)
     CK(cudaStreamCreateWithFlags(&h->aux_stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&h->aux2_stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&h->ev_join2, cudaEventDisableTiming));
-    CK(cudaStreamCreateWithFlags(&h->state_stream, cudaStreamNonBlocking));
+    {   // the state chain (apply, K4) is short and on the path to the next K3: highest priority, like the caller's main stream
+        int plo = 0, phi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&plo, &phi));
+        const char *pe = getenv("MTD_MAIN_PRIO");
+        CK(cudaStreamCreateWithPriority(&h->state_stream, cudaStreamNonBlocking, (pe && *pe == '0') ? plo : phi));
+    }
     CK(cudaEventCreateWithFlags(&h->ev_state, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&h->ev_main, cudaEventDisableTiming));
     memset(&h->x, 0, sizeof(h->x));
     CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));

@@ -14,6 +14,8 @@ torch is used for device memory, streams and torch.distributed only; every compu
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import capi
@@ -33,7 +35,9 @@ class DayEngine:
         self.device = torch.device("cuda", device) if isinstance(device, int) else torch.device(device)
         self.rank, self.world, self.group = rank, world, group
         self.mode, self.seed = mode, seed
-        self.stream = torch.cuda.Stream(self.device)
+        # high priority: in the day pipeline the short K2/K3 kernels of the current day (this stream) get the SM slots that
+        # free up before the next persistent K1 kernel of the coming day does (MTD_MAIN_PRIO=0: default priority)
+        self.stream = torch.cuda.Stream(self.device, priority=0 if os.environ.get("MTD_MAIN_PRIO") == "0" else -1)
         self.delta_cap = int(delta_cap) if delta_cap else max(4096, n_agents // 64)
         self.h = capi.Handle(n_agents, n_cells, max_intervals, device=self.device.index or 0,
                              stream=self.stream.cuda_stream, max_rows=max_rows, max_exposures=self.delta_cap)
