@@ -347,6 +347,10 @@ def run_b200(args):
     ser_ms, _ = h.stage_ms()
     eng.set_inputs_ready(True)
     roofline["stage_ms_serial"] = ser_ms
+    if ser_ms.get("k1_contacts", 0) > 0:      # the same algorithmic bytes over K1's stand-alone time, next to the pipelined one
+        roofline["k1_ms_serial"] = ser_ms["k1_contacts"]
+        roofline["achieved_serial"] = k1_bytes / (ser_ms["k1_contacts"] * 1e-3) / 1e9
+        roofline["frac_serial"] = roofline["achieved_serial"] / peak
     roofline["stage_note"] = ("stage_ms / k1_ms: CUDA events around each stage over the timed region, where the day runs as a "
                               "three-stream pipeline (K0 of day d+2, K1 of day d+1 and K2/K3 of day d share the SMs; the state "
                               "chain k3_apply / k4_advance has its own stream), so a stage's time includes waiting for SM slots; "
