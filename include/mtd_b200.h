@@ -35,7 +35,8 @@ extern "C" {
 #define MTD_NONE (-32768)        /* "None" for day-valued record fields */
 #define MTD_EXPO_W 21            /* doubles per replay-tape exposure record (tests/golden/ref_harness.py) */
 #define MTD_DELTA_WORDS 20       /* int32 words per exposure delta record */
-#define MTD_MAX_CELL_INTERVALS 1024  /* largest cell (intervals) the on-chip path handles */
+#define MTD_MAX_CELL_INTERVALS 16384 /* largest cell (intervals of one cell on one day); cells up to 1024 intervals are processed
+                                      * in shared memory, larger ones in a global workspace sized from max_intervals */
 
 enum { MTD_OK = 0, MTD_E_ARG = 1, MTD_E_CUDA = 2, MTD_E_CAPACITY = 3, MTD_E_CELL_TOO_LARGE = 4, MTD_E_STATE = 5, MTD_E_TIMEOUT = 6 };
 enum { MTD_MEM_HOST = 0, MTD_MEM_DEVICE = 1, MTD_MEM_STAGED = 2 /* the stream given to mtd_prefetch_intervals */,
@@ -98,7 +99,8 @@ typedef struct {
     int64_t n_si_rows;           /* rows with exactly one Susceptible and one Infectious endpoint */
     int64_t sched_overflow;      /* schedule entries dropped (MTD_MAXSCHED reached) */
     int64_t tape_miss;           /* replay lookups without a record */
-    int64_t class_cells[6];      /* cells per size class (<=8, <=16, <=32, <=128, <=320, <=1024 intervals) */
+    int64_t class_cells[9];      /* cells per size class (<=8, <=16, <=32, <=64, <=128, <=192, <=320, <=1024 intervals, above) */
+    int64_t n_incidences;        /* sum over cells of distinct agents (cell, agent incidences) */
     int64_t error;               /* MTD_E_* raised on the device (capacity, cell too large) */
 } mtd_counters;
 

@@ -15,6 +15,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 SO = os.path.join(PKG, "libmtd_b200.so")
 MEM_HOST, MEM_DEVICE, MEM_STAGED, MEM_BUILT = 0, 1, 2, 3
 MODE_REPLAY, MODE_PHILOX = 0, 1
+MAX_CELL_INTERVALS = 16384     # include/mtd_b200.h MTD_MAX_CELL_INTERVALS
 DELTA_WORDS = 20
 APPLY_NONE, APPLY_LOCAL, APPLY_EXCHANGE = 0, 1, 2
 IPC_HANDLE_BYTES = 64
@@ -50,7 +51,7 @@ class Tape(C.Structure):
 class Counters(C.Structure):
     _fields_ = [("n_slots", C.c_int64), ("n_rows", C.c_int64), ("n_exposed", C.c_int64), ("pairs_evaluated", C.c_int64),
                 ("n_potential", C.c_int64), ("n_si_rows", C.c_int64), ("sched_overflow", C.c_int64),
-                ("tape_miss", C.c_int64), ("class_cells", C.c_int64 * 6), ("error", C.c_int64)]
+                ("tape_miss", C.c_int64), ("class_cells", C.c_int64 * 9), ("n_incidences", C.c_int64), ("error", C.c_int64)]
 
 
 class DayResult(C.Structure):

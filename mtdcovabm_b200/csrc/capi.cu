@@ -11,8 +11,8 @@
 // every launcher returns the number of kernels it launched
 int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count);
 int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t aux2, cudaEvent_t ev_fork, cudaEvent_t ev_join,
-              cudaEvent_t ev_join2, int sm_count);
-int64_t k1_bits_words_needed(int sm_count);
+              cudaEvent_t ev_join2, int sm_count, unsigned char *big_ws, int mm_big);
+int64_t k1_big_ws_bytes(int mm_big);
 int launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count);
 int launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap, cudaStream_t st);
 int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, bool win_clean, cudaStream_t st, int sm_count);
@@ -44,6 +44,7 @@ struct mtd_handle_s {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     cudaStream_t aux_stream = nullptr, aux2_stream = nullptr;   // large-cell K1 kernels run beside the small-cell ones
+    unsigned char *k1_big_ws = nullptr; int k1_mm_big = 0;      // global workspace of the cells above 1024 intervals
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr;
     // The state chain -- apply of day d's exposure records (after the peer exchange), then K4 of day d+1 -- runs on its
     // own stream beside K0/K1/K2 of day d+1, which read no per-agent state; K3 of day d+1 joins the two.
@@ -190,7 +191,7 @@ static int touch_state_on_main(mtd_handle h)
 }
 #define TOUCH() do { int r_ = touch_state_on_main(h); if (r_) return r_; } while (0)
 
-extern "C" int mtd_abi_version(void) { return 2; }
+extern "C" int mtd_abi_version(void) { return 3; }
 
 extern "C" const char *mtd_last_error(mtd_handle h) { return h ? h->err.c_str() : "null handle"; }
 
@@ -240,8 +241,10 @@ static int create_impl(mtd_handle h)
     DA(c.k1_bins, 2 * 3 * 32);
     DA(c.csr, M);
     DA(c.scratch_rows, c.cap_scratch_rows); DA(c.rows, c.cap_rows);
-    c.k1_bits_words = k1_bits_words_needed(h->sm_count);
-    DA(c.k1_bits, c.k1_bits_words);
+    // cells above 1024 intervals are processed in a global workspace: as large as a cell of this handle can get
+    c.max_cell_m = (int32_t)std::min<int64_t>(MTD_MAX_CELL_INTERVALS, M);
+    h->k1_mm_big = c.max_cell_m > 1024 ? ((c.max_cell_m + 31) & ~31) : 0;
+    if (h->k1_mm_big) DA(h->k1_big_ws, k1_big_ws_bytes(h->k1_mm_big));
     DA(c.win, N); DA(c.succ, c.cap_rows);
     c.row_p = nullptr;
     DA(h->delta_own, (c.cap_expo + 1) * MTD_DELTA_WORDS);
@@ -557,7 +560,7 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     cudaStream_t k1s = (pipe && h->k1_pipe) ? h->k1_stream : h->stream;
     if (pipe) { CK(cudaEventRecord(h->ev_k0_ready, ks)); CK(cudaStreamWaitEvent(k1s, h->ev_k0_ready, 0)); }
     // an empty day (M == 0) has no cells: the zeroed counters are its result
-    if (M > 0) { StageScope sc(h, MTD_STAGE_K1, k1s); sc.add(launch_k1(c, k1s, h->aux_stream, h->aux2_stream, h->ev_fork, h->ev_join, h->ev_join2, h->sm_count)); }
+    if (M > 0) { StageScope sc(h, MTD_STAGE_K1, k1s); sc.add(launch_k1(c, k1s, h->aux_stream, h->aux2_stream, h->ev_fork, h->ev_join, h->ev_join2, h->sm_count, h->k1_big_ws, h->k1_mm_big)); }
     if (k1s != h->stream) { CK(cudaEventRecord(h->ev_k1_done, k1s)); CK(cudaStreamWaitEvent(h->stream, h->ev_k1_done, 0)); }
     c.rows12 = nullptr;
     if (h->export_on) {     // K2 also packs the rows for the export; the slot's previous export must have drained
@@ -992,7 +995,7 @@ extern "C" int mtd_get_counters(mtd_handle h, mtd_counters *out)
     if (!d.error && sc.error) d.error = sc.error;
     out->n_slots = d.n_slots; out->n_rows = d.n_rows; out->n_exposed = sc.n_applied;
     out->pairs_evaluated = (int64_t)d.pairs_evaluated; out->n_potential = (int64_t)d.n_potential;
-    out->n_si_rows = d.n_si_rows; out->sched_overflow = sc.sched_overflow; out->tape_miss = d.tape_miss;
+    out->n_incidences = (int64_t)d.n_incidences; out->n_si_rows = d.n_si_rows; out->sched_overflow = sc.sched_overflow; out->tape_miss = d.tape_miss;
     for (int k = 0; k < MTD_NUM_CLASSES; k++) out->class_cells[k] = d.class_cells[k];
     out->error = d.error;
     if (d.error) {

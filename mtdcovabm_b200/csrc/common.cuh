@@ -4,7 +4,8 @@
 #include <stdint.h>
 #include "../../include/mtd_b200.h"
 
-#define MTD_NUM_CLASSES 6      // cells by interval count: <=8, <=16, <=32 (sub-warp groups), <=128, <=320, <=1024 (warp)
+#define MTD_NUM_CLASSES 9      // cells by interval count: <=8, <=16, <=32 (sub-warp groups); <=64, <=128, <=192, <=320, <=1024
+                               //   (block per cell, shared memory), above (block per cell, global workspace)
 #define MTD_LOGTAB_N 4096      // host-computed math.log(i) for small integers
 #define FULLMASK 0xffffffffu
 
@@ -23,7 +24,7 @@ enum { SITE_SELECT = 1, SITE_PAIR = 2, SITE_EXPO = 3, SITE_TRACE = 4 };
 struct DevCounters {
     unsigned long long pairs_evaluated;
     unsigned long long n_potential;
-    unsigned long long unused0;
+    unsigned long long n_incidences;    // sum over cells of distinct agents (the U of the algorithmic-bytes formula)
     unsigned long long row_bound_total; // total scratch rows requested
     int n_slots;
     int n_rows;
@@ -114,15 +115,14 @@ struct DevCtx {
     int32_t *slot_rowbound;    // [slots]
     int32_t *slot_nrows;       // [slots] rows produced
     int64_t *slot_denseoff;    // [slots+1]
-    int32_t *class_list;       // [MTD_NUM_CLASSES + 5][slots cap]; the extra regions hold classes 4, 3, 0, 1, 2 sorted by cell size (K1)
+    int32_t *class_list;       // [MTD_NUM_CLASSES + 5][slots cap]; the extra regions hold classes 6, 5, 0, 1, 2 sorted by cell size (K1)
     int64_t class_stride;
     IvRec *csr;                // [M]
     // K1 products
     RowRec *scratch_rows;      // [cap_scratch_rows]
     uint32_t *rows12;          // [3 * cap_rows] packed 12-byte rows of the day for the async export (NULL = off)
     int32_t *k1_bins;          // [2][3][32] histogram and cursors of the small-class size sort (K1)
-    uint32_t *k1_bits;         // [k1_bits_words] per-warp adjacency bit matrices of the large-cell K1 (L2-resident scratch)
-    int64_t k1_bits_words;
+    int32_t max_cell_m;        // largest cell (intervals) this handle takes: min(MTD_MAX_CELL_INTERVALS, max_intervals)
     RowRec *rows;              // [cap_rows] dense
     // K3
     unsigned long long *win;   // [n_agents] winner key per agent

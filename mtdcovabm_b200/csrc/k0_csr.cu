@@ -40,7 +40,7 @@ __global__ void k0_hist_kernel(DevCtx c)
             if (c.agent_masked[ag] && cell != c.res_cellid[ag]) { c.iv_pos[i] = 0xffffu; continue; }     // dropped
         }
         const int pos = atomicAdd(&c.cell_count[cell], 1);
-        c.iv_pos[i] = (uint16_t)(pos < 0xffff ? pos : 0xffff);         // cells beyond MTD_MAX_CELL_INTERVALS are rejected in assign
+        c.iv_pos[i] = (uint16_t)(pos < 0xffff ? pos : 0xffff);         // cells beyond the handle's largest cell are rejected in assign
         atomicMin(&c.cell_first[cell], order_of(c, i));
     }
 }
@@ -62,7 +62,7 @@ __global__ void k0_flags_kernel(DevCtx c, uint32_t *words, int32_t *cnt)
 
 __device__ __forceinline__ int size_class(int m)
 {
-    return m <= 8 ? 0 : (m <= 16 ? 1 : (m <= 32 ? 2 : (m <= 128 ? 3 : (m <= 320 ? 4 : 5))));
+    return m <= 8 ? 0 : (m <= 16 ? 1 : (m <= 32 ? 2 : (m <= 64 ? 3 : (m <= 128 ? 4 : (m <= 192 ? 5 : (m <= 320 ? 6 : (m <= 1024 ? 7 : 8)))))));
 }
 
 __global__ void __launch_bounds__(256) k0_assign_kernel(DevCtx c, const uint32_t *words, const int32_t *word_excl)
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(256) k0_assign_kernel(DevCtx c, const uint32_t
                 c.slot_first[slot] = order_of(c, i);
                 c.slot_nrows[slot] = 0;
                 c.slot_m[slot] = m;                   // the CSR segment keeps its true length; the day is in error
-                if (m > MTD_MAX_CELL_INTERVALS) { c.ctr->error = MTD_E_CELL_TOO_LARGE; m = 0; }
+                if (m > c.max_cell_m) { c.ctr->error = MTD_E_CELL_TOO_LARGE; m = 0; }
                 int ct = c.cell_type[cell];
                 int indid = (ct == CT_WORKPLACE && c.cell_indid) ? c.cell_indid[cell] : -1;
                 const int act = activity_of_celltype(ct, indid);
@@ -211,7 +211,7 @@ __global__ void k0_scatter_kernel(DevCtx c)
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < c.M; i += (int64_t)gridDim.x * blockDim.x) {
         const int cell = c.iv_cell[i];
         const uint32_t p = c.iv_pos[i];
-        if (cell < 0 || cell >= c.n_cells || p >= (uint32_t)MTD_MAX_CELL_INTERVALS) continue;
+        if (cell < 0 || cell >= c.n_cells || p >= (uint32_t)c.max_cell_m) continue;
         IvRec r;
         r.agent = c.iv_agent[i];
         r.order = order_of(c, i);

@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(256) k2_compact_kernel(DevCtx c)
     const int gwarp = ((int)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     // Cells of more than 32 intervals hold hundreds to thousands of rows: left to the slot loop below, one warp would
     // copy such a cell alone while its 31 other slots wait (the tail of the stage when a rank holds few cells).  They
-    // are taken from their size-class lists instead: a warp per cell of class 3, a block per cell of classes 4 and 5.
+    // are taken from their size-class lists instead: a warp per cell of class 3 (<= 64 intervals), a block per cell above.
     {
         const int n3 = c.ctr->class_cells[3];
         const int32_t *list = c.class_list + 3 * c.class_stride;

@@ -13,7 +13,9 @@ if ROOT not in sys.path:
 
 from oracle import mtd_oracle as mo  # noqa: E402
 
-RUNS = {"ref_1k_seed6": "epidemiology.json", "ref_1k_strict_seed7": "epidemiology_strict_days.json"}
+RUNS = {"ref_1k_seed6": "epidemiology.json", "ref_1k_strict_seed7": "epidemiology_strict_days.json",
+        # hand-made cells through the reference's ContactNetwork (make_cells_kat.py): edge cases + one cell per K1 size class
+        "ref_cells_kat": "epidemiology.json"}
 NONE = -32768
 
 

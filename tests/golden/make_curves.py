@@ -3,6 +3,8 @@ data/epidemiology.json) together with what is needed to re-run the contact-netwo
 the same itineraries in Philox mode (north_star: per-day two-sample KS on incidence and state occupancy).
 
     python tests/golden/make_curves.py [--seeds 32] [--jobs 8]      # build container only (/root/reference)
+    python tests/golden/make_curves.py --name curves_10k_normal --pop 10k --variant epidemiology_normal_days.json \
+           --days 30 --seeds 8 --jobs 4                              # configs 2 / 5 on the tiled 10k population
 
 Writes tests/golden/curves_1k.npz:
   run-level : seeds, n_agents
@@ -33,9 +35,22 @@ sys.path.insert(0, HERE)
 DAYS = 20
 
 
-def one(seed, out_path):
+def one(seed, out_path, pop="1k", variant=None, days=None):
+    """pop: "1k" (the reference's own population) or "10k" (make_pop10k.py tiling, configs 2 and 5)"""
+    global DAYS
     import ref_harness as rh
-    wd = rh.prepare_workdir("/tmp/refcurves_%d" % seed)
+    if days is not None:
+        DAYS = days
+    if pop == "10k":
+        import make_pop10k
+        if not os.path.exists("/tmp/pop10k/agents.json"):
+            make_pop10k.tile("/tmp/pop10k", 10)
+        wd = rh.prepare_workdir("/tmp/refcurves_%s_%s_%d" % (pop, (variant or "base")[:20], seed), popsubfolder="tiled10k",
+                                pop_src="/tmp/pop10k", epidemiology_variant=variant)
+        kw = {"popsubfolder": "tiled10k"}
+    else:
+        wd = rh.prepare_workdir("/tmp/refcurves_%d" % seed, epidemiology_variant=variant)
+        kw = {}
     comp = {"days": []}
 
     def on_day(d):
@@ -56,7 +71,12 @@ def one(seed, out_path):
         # drop the heavy tape of this day: only the curves are wanted here
         d["tape_sel"] = d["tape_pair_u"] = d["tape_expo"] = None
 
-    rec = rh.run_reference(wd, seed=seed, days=DAYS, on_day=on_day)
+    def on_day_drop(d):      # keep memory flat over long runs: the recorder's own copy of the day is not needed
+        on_day(d)
+        for k in ("pre", "post", "pre_epi", "post_epi", "ext_epi", "contacts", "iv_cell", "iv_agent"):
+            d[k] = None
+
+    rec = rh.run_reference(wd, seed=seed, days=DAYS, on_day=on_day_drop, **kw)
     rec.days.clear()
     days = comp["days"]
     assert len(days) == DAYS
@@ -73,10 +93,10 @@ def one(seed, out_path):
     for i, d in enumerate(days):
         off[i + 1] = off[i] + len(d["iv_cell"])
     out["iv_off"] = off
-    out["iv_cell"] = np.concatenate([d["iv_cell"] for d in days]).astype(np.int16)
-    out["iv_agent"] = np.concatenate([d["iv_agent"] for d in days]).astype(np.int16)
+    small = nc < 32768 and N < 32768
+    out["iv_cell"] = np.concatenate([d["iv_cell"] for d in days]).astype(np.int16 if small else np.int32)
+    out["iv_agent"] = np.concatenate([d["iv_agent"] for d in days]).astype(np.int16 if small else np.int32)
     out["iv_start"] = np.concatenate([d["iv_start"] for d in days]); out["iv_end"] = np.concatenate([d["iv_end"] for d in days])
-    assert nc < 32768 and N < 32768
     age = np.zeros(N, np.int8); epi = np.zeros(N, np.int8); soc = np.ones(N, np.float64); res = np.full(N, -1, np.int32)
     for d in days:
         ids, a, e, s, r = d["static"]
@@ -105,6 +125,7 @@ def one(seed, out_path):
     out["arr_sched"] = np.array(arr_sched, np.int32).reshape(-1, 5)
     out["last_dose"] = np.array(dose, np.int32).reshape(-1, 3)
     out["dyn"] = np.array([d["dyn"] for d in days], np.float64)
+    out["days"] = np.array([DAYS], np.int64)
     out["ref_incidence"] = np.array([d["incidence"] for d in days], np.int32)
     out["ref_occupancy"] = np.stack([d["occupancy"] for d in days]).astype(np.int32)
     out["n_agents"] = np.array([N], np.int64)
@@ -112,21 +133,28 @@ def one(seed, out_path):
 
 
 def main():
+    def opt(name, default=None):
+        return sys.argv[sys.argv.index(name) + 1] if name in sys.argv else default
+
+    pop, variant, days = opt("--pop", "1k"), opt("--variant"), opt("--days")
+    days = None if days is None else int(days)
     if len(sys.argv) > 1 and sys.argv[1] == "--one":
-        one(int(sys.argv[2]), sys.argv[3])
+        one(int(sys.argv[2]), sys.argv[3], pop, variant, days)
         return
-    n_seeds = int(sys.argv[sys.argv.index("--seeds") + 1]) if "--seeds" in sys.argv else 32
-    jobs = int(sys.argv[sys.argv.index("--jobs") + 1]) if "--jobs" in sys.argv else 8
+    n_seeds = int(opt("--seeds", 32))
+    jobs = int(opt("--jobs", 8))
     seeds = list(range(100, 100 + n_seeds))
-    tmp = "/tmp/refcurves_out"
+    name = opt("--name", "curves_1k")
+    tmp = "/tmp/refcurves_out_" + name
     os.makedirs(tmp, exist_ok=True)
     procs = []
     pending = list(seeds)
     while pending or procs:
         while pending and len(procs) < jobs:
             s = pending.pop(0)
+            extra = ["--pop", pop] + (["--variant", variant] if variant else []) + (["--days", str(days)] if days else [])
             procs.append((s, subprocess.Popen([sys.executable, os.path.abspath(__file__), "--one", str(s),
-                                               os.path.join(tmp, "s%d.npz" % s)], stdout=subprocess.DEVNULL)))
+                                               os.path.join(tmp, "s%d.npz" % s)] + extra, stdout=subprocess.DEVNULL)))
         s, p = procs.pop(0)
         if p.wait() != 0:
             raise SystemExit("seed %d failed" % s)
@@ -134,13 +162,13 @@ def main():
     for s in seeds:
         z = np.load(os.path.join(tmp, "s%d.npz" % s))
         for k in z.files:
-            if k in ("n_agents",):
+            if k in ("n_agents", "days"):
                 if k in merged:
                     assert np.array_equal(merged[k], z[k])
                 merged[k] = z[k]
             else:
                 merged["s%d_%s" % (s, k)] = z[k]
-    path = os.path.join(HERE, "curves_1k.npz")
+    path = os.path.join(HERE, name + ".npz")
     np.savez_compressed(path, **merged)
     print(path, os.path.getsize(path))
 

@@ -132,6 +132,9 @@ def encode_run(rec, keep_days):
         encode_day(d, out, "d%02d_" % d["day"])
     # update_agent_state KAT
     adv = rec.advance_calls
+    if len(adv) > 20000:        # long runs: the KAT keeps the calls of the kept days only
+        ks = set(keep_days)
+        adv = [a for a in adv if a[0] in ks]
     A = len(adv)
     out["adv_day_agent"] = np.array([[a[0], a[1]] for a in adv], dtype=np.int32).reshape(-1, 2)
     out["adv_pre"] = np.array([a[3] for a in adv], dtype=np.int8).reshape(-1, 3)
@@ -235,9 +238,13 @@ def encode_traces(rec, out, days_back=2):
 
 
 RUNS = [
-    # name, epidemiology variant (None = data/epidemiology.json), seed, days, days kept in the fixture
+    # name, epidemiology variant (None = data/epidemiology.json), seed, days, days kept in the fixture[, population]
     ("ref_1k_seed6", None, 6, 20, [1, 2, 5, 9, 12, 16, 20]),
     ("ref_1k_strict_seed7", "epidemiology_strict_days.json", 7, 25, [3, 10, 18, 21, 25]),
+    # BASELINE.json configs 2 and 5 at their own size and parameter file: the 1k population tiled x10
+    # (make_pop10k.py; the upstream 10k agents.json is missing), 90 days each, about 25 min per run on one core
+    ("ref_10k_normal_seed11", "epidemiology_normal_days.json", 11, 90, [2, 15, 30, 45, 60, 75, 90], "10k"),
+    ("ref_10k_strict_seed12", "epidemiology_strict_days.json", 12, 90, [3, 10, 20, 35, 50, 70, 90], "10k"),
 ]
 
 
@@ -246,16 +253,31 @@ def main():
     if len(sys.argv) > 1 and sys.argv[1] == "--one":
         name, variant, seed, days = sys.argv[2], sys.argv[3], int(sys.argv[4]), int(sys.argv[5])
         keep = [int(x) for x in sys.argv[6].split(",")]
-        wd = rh.prepare_workdir("/tmp/refwork_" + name, epidemiology_variant=None if variant == "-" else variant)
-        rec = rh.run_reference(wd, seed=seed, days=days)
+        pop = sys.argv[7] if len(sys.argv) > 7 else "1k"
+        variant = None if variant == "-" else variant
+        if pop == "10k":
+            import make_pop10k
+            if not os.path.exists("/tmp/pop10k/agents.json"):
+                make_pop10k.tile("/tmp/pop10k", 10)
+            wd = rh.prepare_workdir("/tmp/refwork_" + name, popsubfolder="tiled10k", pop_src="/tmp/pop10k",
+                                    epidemiology_variant=variant)
+            # only the kept days are recorded (a 90-day record of every day would not fit the fixture budget)
+            rec = rh.run_reference(wd, seed=seed, days=days, popsubfolder="tiled10k", record_days=set(keep))
+        else:
+            wd = rh.prepare_workdir("/tmp/refwork_" + name, epidemiology_variant=variant)
+            rec = rh.run_reference(wd, seed=seed, days=days)
         out = encode_run(rec, keep)
         np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
         sys.stderr.write("%s: %d days recorded, %d kept, %d advance KATs\n" % (name, len(rec.days), len(keep),
                                                                                len(rec.advance_calls)))
         return
-    for name, variant, seed, days, keep in RUNS:  # one interpreter per run: sim.py keeps module-level state
+    only = sys.argv[2:] if len(sys.argv) > 2 and sys.argv[1] == "--runs" else None
+    for run in RUNS:  # one interpreter per run: sim.py keeps module-level state
+        name, variant, seed, days, keep = run[:5]
+        if only is not None and name not in only:
+            continue
         subprocess.check_call([sys.executable, os.path.abspath(__file__), "--one", name, variant or "-", str(seed),
-                               str(days), ",".join(map(str, keep))])
+                               str(days), ",".join(map(str, keep))] + list(run[5:]))
 
 
 if __name__ == "__main__":

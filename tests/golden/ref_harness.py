@@ -94,8 +94,9 @@ def _install_stubs():
     sys.modules["distributed"].diagnostics = sys.modules["distributed.diagnostics"]
 
 
-def prepare_workdir(workdir, popsubfolder="1kagents2ktourists2019", epidemiology_variant=None):
-    """Writable copy of the files sim.py opens relative to the CWD (Appendix F step 1)."""
+def prepare_workdir(workdir, popsubfolder="1kagents2ktourists2019", epidemiology_variant=None, pop_src=None):
+    """Writable copy of the files sim.py opens relative to the CWD (Appendix F step 1).  pop_src: a population
+    directory outside the reference tree (the tiled 10k population of make_pop10k.py)."""
     if os.path.exists(workdir):
         shutil.rmtree(workdir)
     os.makedirs(workdir)
@@ -103,7 +104,7 @@ def prepare_workdir(workdir, popsubfolder="1kagents2ktourists2019", epidemiology
     shutil.copytree(os.path.join(REF_ROOT, "data"), os.path.join(workdir, "data"))
     shutil.copy(os.path.join(REF_ROOT, "config.json"), os.path.join(workdir, "config.json"))
     os.makedirs(os.path.join(workdir, "population"))
-    shutil.copytree(os.path.join(REF_ROOT, "population", popsubfolder),
+    shutil.copytree(pop_src if pop_src is not None else os.path.join(REF_ROOT, "population", popsubfolder),
                     os.path.join(workdir, "population", popsubfolder))
     if epidemiology_variant is not None:  # sim.py:443 hard-codes data/epidemiology.json
         shutil.copy(os.path.join(REF_ROOT, "data", epidemiology_variant),
@@ -144,13 +145,30 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
     np.random.seed(seed)
 
     import sim  # noqa: E402  (reference module)
-    import contactnetwork as cn  # noqa: E402
-    import epidemiology as epi  # noqa: E402
-    import util as rutil  # noqa: E402
 
     sim.params.update({"popsubfolder": popsubfolder, "simulationdays": days, "numprocesses": 1, "use_mp": True,
                        "logmemoryinfo": False, "logfilename": "golden_%d.txt" % seed})
     rec = Recorder()
+    install_recorder(rec, record_days, on_day)
+    stdout = sys.stdout
+    try:
+        sim.main()
+    finally:
+        try:
+            if sys.stdout is not stdout and hasattr(sys.stdout, "close"):
+                sys.stdout.close()
+        except Exception:
+            pass
+        sys.stdout = stdout
+    return rec
+
+
+def install_recorder(rec, record_days=None, on_day=None):
+    """Monkey-patch the imported reference modules (simulator/ must be on sys.path) so that every call of
+    ContactNetwork.simulate_contact_network fills `rec` with the boundary snapshot and the keyed draw tape."""
+    import contactnetwork as cn  # noqa: E402
+    import epidemiology as epi  # noqa: E402
+    import util as rutil  # noqa: E402
 
     # ---------------- boundary snapshot ----------------
     orig_sim_cn = cn.ContactNetwork.simulate_contact_network
@@ -487,6 +505,8 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
         traced = sorted(int(x) for x in vu.contact_tracing_agent_ids)
         if not (self.dyn_params.contact_tracing_enabled and len(traced) > 0):
             return orig_ct(self, day, distributed, f)
+        if record_days is not None and day not in record_days:     # long runs: only the kept days carry a trace record
+            return orig_ct(self, day, distributed, f)
         if rec.residences is None:
             rec.residences = {}
             rec._hh_inst = set()
@@ -533,15 +553,3 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
         return out
 
     epi.Epidemiology.contact_tracing = patched_ct
-
-    stdout = sys.stdout
-    try:
-        sim.main()
-    finally:
-        try:
-            if sys.stdout is not stdout and hasattr(sys.stdout, "close"):
-                sys.stdout.close()
-        except Exception:
-            pass
-        sys.stdout = stdout
-    return rec

@@ -1,6 +1,6 @@
 """Edge cases of the day step on the GPU, checked against the oracle (which is pinned on the reference's golden days):
 empty day, cells of one interval / one agent, inclusive touching intervals, zero overlap, every size-class boundary up
-to the largest on-chip cell (1024 intervals), shuffled arrival order, indid == 9 and Classroom cells, and the loud
+to the largest shared-memory cell (1024 intervals) and beyond (global-workspace class, up to 16384 intervals), shuffled arrival order, indid == 9 and Classroom cells, and the loud
 failures (oversized cell, row capacity, invalid cell id)."""
 import numpy as np
 import pytest
@@ -79,7 +79,8 @@ def test_hand_made_cells():
         assert (s0, e0, du) == (30, 100, 11 + 11)
 
 
-@pytest.mark.parametrize("m", [1, 2, 8, 9, 16, 17, 32, 33, 128, 129, 320, 321, 700, 1024])
+@pytest.mark.parametrize("m", [1, 2, 8, 9, 16, 17, 32, 33, 50, 64, 65, 128, 129, 192, 193, 320, 321, 700, 1024, 1025, 2048, 5000,
+                               16384])
 def test_size_class_boundaries(m):
     """one cell of exactly m intervals (+ a few small neighbours), arrival order shuffled by the scatter"""
     rng = np.random.default_rng(m)
@@ -87,7 +88,8 @@ def test_size_class_boundaries(m):
     st, ct, ci = population(n_agents, 6, seed=m, cell_type=[1, 0, 5, 8, 4, 0])
     agents = rng.permutation(n_agents)[:m]
     if m > 4:
-        agents[rng.integers(0, m, m // 8)] = agents[0]                           # some agents come back several times
+        agents[rng.integers(0, m, m // 8 if m <= 1024 else m // 64)] = agents[0]  # some agents come back several times
+        agents[rng.integers(0, m, m // 8)] = agents[rng.integers(0, m, m // 8)]  # ... and others once or twice more
     start = rng.integers(0, 120, m); end = np.minimum(143, start + rng.integers(0, 60, m))
     cell = np.zeros(m, np.int64)
     extra_c = rng.integers(1, 6, 30); extra_a = rng.integers(0, n_agents, 30)
@@ -101,7 +103,7 @@ def test_size_class_boundaries(m):
 
 
 def test_oversized_cell_fails_loudly():
-    m = capi.MAX_CELL_INTERVALS + 1 if hasattr(capi, "MAX_CELL_INTERVALS") else 1025
+    m = capi.MAX_CELL_INTERVALS + 1                # the reference has no limit; this library's is 16384 intervals per cell
     st, ct, ci = population(m, 2)
     h = H.make_handle(P, st, ct, ci, m + 16)
     d = h.make_day(capi.MODE_PHILOX, 1, 0.0, seed=1)

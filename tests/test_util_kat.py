@@ -105,3 +105,20 @@ def test_epidemiology_table_helpers():
     agent = {"quarantine_days": None}
     e.update_quarantine(agent, 3, 50, 17, 60)
     assert agent["quarantine_days"] == [3, 50, 17]
+
+
+def test_initialize_agent_states_kat():
+    """seirstateutil.initialize_agent_states (seirstateutil.py:5-32) on the reference's legacy RNG streams
+    (tests/golden/make_cells_kat.py -> init_states_kat.npz): the host mirror assigns exactly the same state to every id"""
+    import random
+    from mtdcovabm_b200 import seirstateutil as ssu
+    from mtdcovabm_b200.epidemiologyclasses import SEIRState
+    K = np.load(os.path.join(os.path.dirname(__file__), "golden", "init_states_kat.npz"))
+    k = 0
+    while "c%d_n" % k in K.files:
+        n, s1, s2 = (int(x) for x in K["c%d_n" % k])
+        np.random.seed(s1); random.seed(s2)
+        st = ssu.initialize_agent_states(n, [float(x) for x in K["c%d_dist" % k]], {i: SEIRState.Undefined for i in range(n)})
+        assert [int(st[i]) for i in range(n)] == [int(x) for x in K["c%d_out" % k]]
+        k += 1
+    assert k == 4
