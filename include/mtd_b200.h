@@ -248,11 +248,19 @@ int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_trace_tape *
                         const int32_t *traced, int64_t n_slices, const int64_t *slice_off, const int32_t *rows3,
                         const uint8_t *epi_present, int mem);
 int mtd_get_traced(mtd_handle h, uint8_t *primary, uint8_t *secondary, mtd_trace_stats *stats, int mem);
-/* K6: test-result processing of the itinerary stage (itinerary.py:2301-2332) over all
- * agents (epi_present: optional u8[N], agents without an epi record are skipped): results due today flag the agent
- * positive (false-negative / false-positive rates of epidemiology.py:59-60), positive agents get a Positive quarantine
- * (epidemiology.py:568-625) and are returned, ascending, as the day's contact_tracing_agent_ids -- the `traced` input
- * of mtd_contact_tracing; result days in the past are cleared.  Philox draws keyed (day, agent). */
+/* K6: the record bookkeeping of Itinerary.sample_intervention_activities (itinerary.py:2283-2528; SURVEY.md section 8f
+ * rank 4), once per day over all agents (epi_present: optional u8[N], agents without an epi record are skipped), in the
+ * reference's order: (A) :2301-2332 results due today flag the agent positive (false-negative / false-positive rates of
+ * epidemiology.py:59-60), positive agents get a Positive quarantine (epidemiology.py:568-625) and are returned,
+ * ascending, as the day's contact_tracing_agent_ids -- the `traced` input of mtd_contact_tracing; result days in the past
+ * are cleared; (B) :2396 hospitalisation_days cleared on their end day; (C) :2456 quarantine_days cleared on their end
+ * day (not when the window starts today, nor when the hospitalisation ended today inside it); (D) :2486-2487 test_day
+ * cleared six days after the test.  Call it AFTER mtd_advance_seir of the day: the reference advances the agent's state
+ * first (itinerary.py:399,1587) and judges the result on the new state.  The stage's re-timing of records on arrival /
+ * departure days belongs to the itinerary and is not done here.
+ * Draws: Philox keyed (day, agent); replay mode: the tape of mtd_set_k6_tape (HOST pointers: strictly ascending agent
+ * ids, two doubles per agent = the result draw of :2310/:2322 and the quarantine draw of epidemiology.py:580). */
+int mtd_set_k6_tape(mtd_handle h, int64_t n, const int32_t *agent_ids, const double *draws2);
 int mtd_process_test_results(mtd_handle h, const mtd_day *day, const uint8_t *epi_present, int32_t *traced_ids,
                              int64_t cap, int64_t *n, int mem);
 

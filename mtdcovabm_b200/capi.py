@@ -27,7 +27,7 @@ EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mt
            "mtd_set_profiling", "mtd_get_stage_ms", "mtd_set_export", "mtd_prefetch_intervals",
            "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced",
            "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts", "mtd_seed_exposures", "mtd_set_intervention_mask", "mtd_set_k0_overlap",
-           "mtd_process_test_results", "mtd_enable_vaccination", "mtd_schedule_vaccinations", "mtd_set_vaccination",
+           "mtd_process_test_results", "mtd_set_k6_tape", "mtd_enable_vaccination", "mtd_schedule_vaccinations", "mtd_set_vaccination",
            "mtd_get_vaccination", "mtd_build_intervals", "mtd_get_intervals"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
 
@@ -337,8 +337,14 @@ class Handle:
                                               _ptr(slice_off), _ptr(rows3), _ptr(epi_present), mem),
                  "mtd_contact_tracing")
 
+    def set_k6_tape(self, agent_ids, draws2):
+        """replay tape of K6: strictly ascending agent ids, [n, 2] doubles (result draw, quarantine draw)"""
+        agent_ids = np.ascontiguousarray(agent_ids, np.int32); draws2 = np.ascontiguousarray(draws2, np.float64)
+        assert draws2.shape == (len(agent_ids), 2)
+        self._ck(self.lib.mtd_set_k6_tape(self.h, C.c_int64(len(agent_ids)), _ptr(agent_ids), _ptr(draws2)), "mtd_set_k6_tape")
+
     def process_test_results(self, day: Day, epi_present=None):
-        """K6 (itinerary.py:2301-2332) -> ascending ids of the agents added to contact_tracing_agent_ids today"""
+        """K6 (itinerary.py:2283-2528, records) -> ascending ids of the agents added to contact_tracing_agent_ids today"""
         ids = np.zeros(self.n_agents, np.int32)
         n = C.c_int64(0)
         if epi_present is not None:

@@ -81,6 +81,7 @@ struct mtd_handle_s {
     int32_t *sc_a1 = nullptr, *sc_a2 = nullptr; int64_t sc_cap_rows = 0; int64_t *sc_off = nullptr; int64_t sc_cap_off = 0;
     uint8_t *sc_se = nullptr; int64_t sc_cap_se = 0;
     uint8_t *agent_masked = nullptr; bool mask_on = false;
+    int32_t *k6_agent = nullptr; double *k6_u = nullptr; int64_t k6_n = 0;   // replay tape of K6 (mtd_set_k6_tape)
     uint8_t *seed_buf = nullptr; int64_t seed_cap = 0;        // staging of mtd_seed_exposures
     // K8 interval builder: device copies of the itinerary CSR + scratch; the built stream lives in d_iv_*
     int64_t *k8_ent_off = nullptr, *k8_grp_off = nullptr, *k8_out_off = nullptr; int16_t *k8_ent_ts = nullptr;
@@ -343,6 +344,7 @@ extern "C" int mtd_destroy(mtd_handle h)
     for (cudaEvent_t e : { h->ev_k0_ready, h->ev_main_mark[0], h->ev_main_mark[1] }) if (e) cudaEventDestroy(e);
     if (h->ev_state) cudaEventDestroy(h->ev_state);
     if (h->ev_main) cudaEventDestroy(h->ev_main);
+    for (void *p : { (void *)h->k6_agent, (void *)h->k6_u }) if (p) cudaFree(p);
     for (void *p : { (void *)h->seed_buf, (void *)h->sc_a1, (void *)h->sc_a2, (void *)h->sc_off, (void *)h->sc_se, (void *)h->vacc_ids, (void *)h->vacc_ts,
                      (void *)h->k8_ent_off, (void *)h->k8_grp_off, (void *)h->k8_out_off, (void *)h->k8_ent_ts, (void *)h->k8_ent_cell,
                      (void *)h->k8_grp_agent, (void *)h->k8_grp_res, (void *)h->k8_count, (void *)h->k8_scan }) if (p) cudaFree(p);
@@ -1210,7 +1212,26 @@ extern "C" int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_t
 }
 
 int launch_k6(const DevCtx &c, const uint8_t *epi_present, uint8_t *positive, int32_t *flag_scan, long long *scan_tmp,
-              int32_t *ids, int64_t cap, int32_t *n_out, cudaStream_t st, int sm_count);
+              int32_t *ids, int64_t cap, int32_t *n_out, int64_t rp_n, const int32_t *rp_agent, const double *rp_u,
+              cudaStream_t st, int sm_count);
+
+extern "C" int mtd_set_k6_tape(mtd_handle h, int64_t n, const int32_t *agent_ids, const double *draws2)
+{
+    if (!h || n < 0 || (n && (!agent_ids || !draws2))) { if (h) h->err = "mtd_set_k6_tape: bad arguments"; return MTD_E_ARG; }
+    CK(cudaSetDevice(h->cfg.device));
+    CK(cudaStreamSynchronize(h->stream));
+    if (h->k6_agent) { cudaFree(h->k6_agent); h->k6_agent = nullptr; }
+    if (h->k6_u) { cudaFree(h->k6_u); h->k6_u = nullptr; }
+    h->k6_n = 0;
+    if (n == 0) return MTD_OK;
+    for (int64_t i = 1; i < n; i++) if (agent_ids[i] <= agent_ids[i - 1]) { h->err = "mtd_set_k6_tape: agent ids must be strictly ascending"; return MTD_E_ARG; }
+    CK(cudaMalloc((void **)&h->k6_agent, 4 * (size_t)n)); CK(cudaMalloc((void **)&h->k6_u, 16 * (size_t)n));
+    CK(cudaMemcpyAsync(h->k6_agent, agent_ids, 4 * (size_t)n, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->k6_u, draws2, 16 * (size_t)n, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    h->k6_n = n;
+    return MTD_OK;
+}
 
 extern "C" int mtd_process_test_results(mtd_handle h, const mtd_day *day, const uint8_t *epi_present, int32_t *traced_ids,
                                         int64_t cap, int64_t *n, int mem)
@@ -1228,8 +1249,9 @@ extern "C" int mtd_process_test_results(mtd_handle h, const mtd_day *day, const 
         present = h->d_epi_present;
     }
     { int r = regrow(h, &h->d_traced, &h->cap_traced, (int64_t)N); if (r) return r; }
+    if (day->mode == MTD_MODE_REPLAY && h->k6_n == 0) { h->err = "mtd_process_test_results: replay mode without mtd_set_k6_tape"; return MTD_E_STATE; }
     launch_k6(h->c, present, h->is_traced, h->trace_flagscan, h->trace_scan_tmp, h->d_traced, (int64_t)N, h->trace_scalars + 12,
-              h->stream, h->sm_count);
+              h->k6_n, h->k6_agent, h->k6_u, h->stream, h->sm_count);
     int32_t cnt = 0;
     CK(cudaMemcpyAsync(&cnt, h->trace_scalars + 12, sizeof(cnt), cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));

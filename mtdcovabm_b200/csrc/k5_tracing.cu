@@ -257,11 +257,18 @@ __global__ void k5_count_kernel(TraceCtx c)
     if ((threadIdx.x & 31) == 0 && (np | ns)) { atomicAdd(&c.stats[ST_PRIM], np); atomicAdd(&c.stats[ST_SEC], ns); }
 }
 
-// K6 -- test-result processing of the itinerary stage (itinerary.py:2301-2332), one thread per agent: a result due
-// today flags the agent positive unless a false negative (Exposed / Infectious) or only on a false positive (everybody
-// else); a positive agent joins contact_tracing_agent_ids and gets a Positive quarantine (schedule_quarantine,
-// epidemiology.py:568-625); a result day in the past is cleared.  Draws: Philox keyed (day, agent), site 6.
-__global__ void k6_test_results_kernel(DevCtx c, const uint8_t *epi_present, uint8_t *positive)
+// K6 -- intervention bookkeeping of the itinerary stage, one thread per agent (Itinerary.sample_intervention_activities,
+// itinerary.py:2283-2528), in the reference's order:
+//   (A) :2301-2332  a test result due today flags the agent positive unless a false negative (Exposed / Infectious) or
+//       only on a false positive (everybody else); a positive agent joins contact_tracing_agent_ids and gets a Positive
+//       quarantine (schedule_quarantine, epidemiology.py:568-625); a result day in the past is cleared;
+//   (B) :2334-2397  hospitalisation_days are cleared on their end day (not on a day that is also their start day);
+//   (C) :2399-2457  quarantine_days are cleared on their end day, unless the window starts today or the hospitalisation
+//       ended today inside the window;
+//   (D) :2459-2487  test_day is cleared six days after the test.
+// Draws: replay tape keyed by agent (two doubles: result draw, quarantine draw) or Philox keyed (day, agent), site 6.
+__global__ void k6_test_results_kernel(DevCtx c, const uint8_t *epi_present, uint8_t *positive, int64_t rp_n,
+                                       const int32_t *rp_agent, const double *rp_u)
 {
     const mtd_params *P = c.P;
     const int day = c.day.day;
@@ -270,24 +277,46 @@ __global__ void k6_test_results_kernel(DevCtx c, const uint8_t *epi_present, uin
         if (epi_present && !epi_present[a]) continue;
         int32_t *tr = c.test_result_day + 2 * a;
         const int trd = tr[0];
-        if (trd == MTD_NONE) continue;
-        if (day == trd) {
-            const int ts = tr[1];
-            uint32_t w[4];
-            philox4x32((uint32_t)day, (uint32_t)a, 0u, 0u, c.day.seed, 6u, w);
-            const double u = u53(w[0], w[1]), u2 = u53(w[2], w[3]);
-            const int st = c.seir[a];
-            const bool pos = (st == S_EXP || st == S_INF) ? !(u < P->testing_false_negative_rate)
-                                                           : (u < P->testing_false_positive_rate);
-            if (!pos) continue;
-            positive[a] = 1;
-            if (!c.day.quarantine_enabled) continue;
-            if (u2 < P->ignore_quarantine_rules_probability) continue;
-            int32_t *q = c.quarantine + 3 * a;
-            const int start = day, end = day + P->quarantine_positive_duration;
-            if (q[0] != MTD_NONE && start >= q[0]) continue;            // epidemiology.py:606-611
-            q[0] = start; q[1] = ts; q[2] = end;
-        } else if (day > trd) { tr[0] = MTD_NONE; tr[1] = MTD_NONE; }
+        if (trd != MTD_NONE) {                                              // (A)
+            if (day == trd) {
+                const int ts = tr[1];
+                double u, u2;
+                if (c.day.mode == MTD_MODE_REPLAY) {
+                    int64_t lo = 0, hi = rp_n;
+                    while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (rp_agent[mid] < (int32_t)a) lo = mid + 1; else hi = mid; }
+                    if (lo < rp_n && rp_agent[lo] == (int32_t)a) { u = rp_u[2 * lo]; u2 = rp_u[2 * lo + 1]; }
+                    else { u = 2.0; u2 = 2.0; atomicAdd(&c.ctr->tape_miss, 1); }
+                } else {
+                    uint32_t w[4];
+                    philox4x32((uint32_t)day, (uint32_t)a, 0u, 0u, c.day.seed, 6u, w);
+                    u = u53(w[0], w[1]); u2 = u53(w[2], w[3]);
+                }
+                const int st = c.seir[a];
+                const bool pos = (st == S_EXP || st == S_INF) ? !(u < P->testing_false_negative_rate)
+                                                               : (u < P->testing_false_positive_rate);
+                if (pos) {
+                    positive[a] = 1;
+                    if (c.day.quarantine_enabled && !(u2 < P->ignore_quarantine_rules_probability)) {
+                        int32_t *q = c.quarantine + 3 * a;
+                        const int start = day, end = day + P->quarantine_positive_duration;
+                        if (!(q[0] != MTD_NONE && start >= q[0])) { q[0] = start; q[1] = ts; q[2] = end; }   // epidemiology.py:606-611
+                    }
+                }
+            } else if (day > trd) { tr[0] = MTD_NONE; tr[1] = MTD_NONE; }
+        }
+        bool hosp_end_today = false;
+        int32_t *hp = c.hosp + 3 * a;
+        const int h0 = hp[0];
+        if (h0 != MTD_NONE && h0 != day && hp[2] == day) { hosp_end_today = true; hp[0] = MTD_NONE; hp[1] = MTD_NONE; hp[2] = MTD_NONE; }   // (B)
+        int32_t *q = c.quarantine + 3 * a;
+        const int q0 = q[0];
+        if (q0 != MTD_NONE) {                                               // (C)
+            const int q2 = q[2];
+            if (!(q0 == day || (hosp_end_today && day <= q2)) && q2 == day) { q[0] = MTD_NONE; q[1] = MTD_NONE; q[2] = MTD_NONE; }
+        }
+        int32_t *td = c.test_day + 2 * a;
+        const int t0 = td[0];
+        if (t0 != MTD_NONE && day != t0 && day - t0 == 6) { td[0] = MTD_NONE; td[1] = MTD_NONE; }   // (D)
     }
 }
 
@@ -303,9 +332,10 @@ __global__ void k6_compact_kernel(int64_t n_agents, const uint8_t *positive, con
 }  // namespace
 
 int launch_k6(const DevCtx &c, const uint8_t *epi_present, uint8_t *positive, int32_t *flag_scan, long long *scan_tmp,
-              int32_t *ids, int64_t cap, int32_t *n_out, cudaStream_t st, int sm_count)
+              int32_t *ids, int64_t cap, int32_t *n_out, int64_t rp_n, const int32_t *rp_agent, const double *rp_u,
+              cudaStream_t st, int sm_count)
 {
-    k6_test_results_kernel<<<sm_count * 8, 256, 0, st>>>(c, epi_present, positive);
+    k6_test_results_kernel<<<sm_count * 8, 256, 0, st>>>(c, epi_present, positive, rp_n, rp_agent, rp_u);
     int n = 1 + device_scan<uint8_t, int32_t>(positive, flag_scan, c.n_agents, nullptr, scan_tmp, st);
     k6_compact_kernel<<<sm_count * 8, 256, 0, st>>>(c.n_agents, positive, flag_scan, ids, cap, n_out);
     return n + 1;

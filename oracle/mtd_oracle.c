@@ -790,39 +790,79 @@ void mtdo_vaccination_day(int32_t day, int64_t n_locals, int32_t *last_dose_day,
     }
 }
 
-/* Test-result processing of the itinerary stage (itinerary.py:2301-2332): an agent whose test result is due today is
- * flagged positive unless a false negative (Exposed / Infectious) or only on a false positive (everybody else); a
- * positive agent enters contact_tracing_agent_ids and gets a Positive quarantine (schedule_quarantine,
- * epidemiology.py:568-625); a result day in the past is cleared.  Philox draws keyed (day, agent, slot), site 6.
+/* Intervention bookkeeping of the itinerary stage, once per agent and day (Itinerary.sample_intervention_activities,
+ * itinerary.py:2283-2528), in the reference's order:
+ *   (A) :2301-2332  a test result due today flags the agent positive unless a false negative (Exposed / Infectious) or
+ *       only on a false positive (everybody else); a positive agent enters contact_tracing_agent_ids and gets a Positive
+ *       quarantine (schedule_quarantine, epidemiology.py:568-625); a result day in the past is cleared;
+ *   (B) :2334-2397  hospitalisation_days are cleared on their end day (not on a day that is also their start day);
+ *   (C) :2399-2457  quarantine_days are cleared on their end day, unless the window starts today or the hospitalisation
+ *       ended today inside the window (the agent is then sent home for the rest of it);
+ *   (D) :2459-2487  test_day is cleared six days after the test.
+ * The stage's re-timing of records on arrival / departure days (:2342-2383, :2412-2425, :2467-2481) belongs to the
+ * itinerary and is not part of this path.  Draws: replay (rp_agent ascending, two doubles per record: the result draw and
+ * the quarantine draw, NaN = not consumed) or Philox keyed (day, agent), site 6.
  * positive[a] = 1 for the agents added to contact_tracing_agent_ids.  Returns their number. */
-int64_t mtdo_process_test_results(const mtdo_params *P, const mtdo_dayctx *D, mtdo_agents *A, const uint8_t *epi_present,
-                                  uint8_t *positive)
+int64_t mtdo_process_interventions(const mtdo_params *P, const mtdo_dayctx *D, mtdo_agents *A, const uint8_t *epi_present,
+                                   int64_t rp_n, const int32_t *rp_agent, const double *rp_u, uint8_t *positive,
+                                   int64_t *tape_miss)
 {
     int64_t n = 0;
     for (int64_t a = 0; a < A->n_agents; a++) {
         positive[a] = 0;
         if (epi_present && !epi_present[a]) continue;
         int32_t *tr = A->test_result_day + 2 * a;
-        if (tr[0] == MTDO_NONE) continue;
-        if (D->day == tr[0]) {
-            const int ts = tr[1];
-            uint32_t ctr[4] = { (uint32_t)D->day, (uint32_t)a, 0u, 0u }, key[2] = { D->seed, 6u }, w[4];
-            mtdo_philox4x32(ctr, key, w);
-            const double u = mtdo_u53(w[0], w[1]), u2 = mtdo_u53(w[2], w[3]);
-            int pos;
-            if (A->seir[a] == S_EXP || A->seir[a] == S_INF) pos = !(u < P->testing_false_negative_rate);
-            else pos = (u < P->testing_false_positive_rate);
-            if (!pos) continue;
-            positive[a] = 1; n++;
-            if (!D->quarantine_enabled) continue;
-            if (u2 < P->ignore_quarantine_rules_probability) continue;
-            int32_t *q = A->quarantine + 3 * a;
-            const int start = D->day, end = D->day + P->quarantine_positive_duration;
-            if (q[0] != MTDO_NONE && start >= q[0]) continue;       /* epidemiology.py:606-611 */
-            q[0] = start; q[1] = ts; q[2] = end;
-        } else if (D->day > tr[0]) { tr[0] = MTDO_NONE; tr[1] = MTDO_NONE; }
+        if (tr[0] != MTDO_NONE) {                                       /* (A) */
+            if (D->day == tr[0]) {
+                const int ts = tr[1];
+                double u, u2;
+                if (D->mode == MTDO_MODE_REPLAY) {
+                    int64_t lo = 0, hi = rp_n;
+                    while (lo < hi) { int64_t mid = (lo + hi) >> 1; if (rp_agent[mid] < (int32_t)a) lo = mid + 1; else hi = mid; }
+                    if (lo < rp_n && rp_agent[lo] == (int32_t)a) { u = rp_u[2 * lo]; u2 = rp_u[2 * lo + 1]; }
+                    else { u = 2.0; u2 = 2.0; if (tape_miss) (*tape_miss)++; }
+                } else {
+                    uint32_t ctr[4] = { (uint32_t)D->day, (uint32_t)a, 0u, 0u }, key[2] = { D->seed, 6u }, w[4];
+                    mtdo_philox4x32(ctr, key, w);
+                    u = mtdo_u53(w[0], w[1]); u2 = mtdo_u53(w[2], w[3]);
+                }
+                int pos;
+                if (A->seir[a] == S_EXP || A->seir[a] == S_INF) pos = !(u < P->testing_false_negative_rate);
+                else pos = (u < P->testing_false_positive_rate);
+                if (pos) {
+                    positive[a] = 1; n++;
+                    if (D->quarantine_enabled && !(u2 < P->ignore_quarantine_rules_probability)) {
+                        int32_t *q = A->quarantine + 3 * a;
+                        const int start = D->day, end = D->day + P->quarantine_positive_duration;
+                        if (!(q[0] != MTDO_NONE && start >= q[0])) { q[0] = start; q[1] = ts; q[2] = end; }   /* epidemiology.py:606-611 */
+                    }
+                }
+            } else if (D->day > tr[0]) { tr[0] = MTDO_NONE; tr[1] = MTDO_NONE; }
+        }
+        int hosp_end_today = 0;
+        int32_t *hp = A->hosp + 3 * a;
+        if (hp[0] != MTDO_NONE) {                                       /* (B) */
+            if (hp[0] == D->day) { /* the itinerary sends the agent to a hospital cell */ }
+            else if (hp[2] == D->day) { hosp_end_today = 1; hp[0] = hp[1] = hp[2] = MTDO_NONE; }
+        }
+        int32_t *q = A->quarantine + 3 * a;
+        if (q[0] != MTDO_NONE) {                                        /* (C) */
+            if (q[0] == D->day || (hosp_end_today && D->day <= q[2])) { /* the itinerary sends the agent home */ }
+            else if (q[2] == D->day) { q[0] = q[1] = q[2] = MTDO_NONE; }
+        }
+        int32_t *td = A->test_day + 2 * a;
+        if (td[0] != MTDO_NONE) {                                       /* (D) */
+            if (D->day == td[0]) { /* the itinerary adds the visit to a testing hub */ }
+            else if (D->day - td[0] == 6) { td[0] = td[1] = MTDO_NONE; }
+        }
     }
     return n;
+}
+
+int64_t mtdo_process_test_results(const mtdo_params *P, const mtdo_dayctx *D, mtdo_agents *A, const uint8_t *epi_present,
+                                  uint8_t *positive)
+{
+    return mtdo_process_interventions(P, D, A, epi_present, 0, NULL, NULL, positive, NULL);
 }
 
 /* Intervention coupling of the tiled configurations: the itinerary stage keeps agents

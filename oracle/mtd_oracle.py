@@ -250,15 +250,21 @@ def vaccination_day(day, n_locals, last_dose_day, vacc_day):
     L.mtdo_vaccination_day(C.c_int32(day), C.c_int64(n_locals), _p(last_dose_day), _p(vacc_day))
 
 
-def process_test_results(params, ctx, agents: AgentState, epi_present=None):
-    """itinerary.py:2301-2332 over all agents -> ids added to contact_tracing_agent_ids (ascending)"""
+def process_test_results(params, ctx, agents: AgentState, epi_present=None, replay_agents=None, replay_u=None):
+    """itinerary.py:2283-2528 (record bookkeeping) over all agents -> ids added to contact_tracing_agent_ids (ascending).
+    Replay mode: replay_agents ascending ids, replay_u [n, 2] the result draw and the quarantine draw of each."""
     a = agents.struct()
     pos = np.zeros(agents.n, np.uint8)
     if epi_present is not None:
         epi_present = np.ascontiguousarray(epi_present, np.uint8)
+    ra = None if replay_agents is None else np.ascontiguousarray(replay_agents, np.int32)
+    ru = None if replay_u is None else np.ascontiguousarray(replay_u, np.float64)
+    miss = C.c_int64(0)
     L = lib()
-    L.mtdo_process_test_results.restype = C.c_int64
-    L.mtdo_process_test_results(C.byref(params), C.byref(ctx), C.byref(a), _p(epi_present), _p(pos))
+    L.mtdo_process_interventions.restype = C.c_int64
+    L.mtdo_process_interventions(C.byref(params), C.byref(ctx), C.byref(a), _p(epi_present), C.c_int64(0 if ra is None else len(ra)),
+                                 _p(ra), _p(ru), _p(pos), C.byref(miss))
+    process_test_results.tape_miss = miss.value
     return np.nonzero(pos)[0].astype(np.int32)
 
 

@@ -15,7 +15,10 @@ from oracle import mtd_oracle as mo  # noqa: E402
 
 RUNS = {"ref_1k_seed6": "epidemiology.json", "ref_1k_strict_seed7": "epidemiology_strict_days.json",
         # hand-made cells through the reference's ContactNetwork (make_cells_kat.py): edge cases + one cell per K1 size class
-        "ref_cells_kat": "epidemiology.json"}
+        "ref_cells_kat": "epidemiology.json",
+        # BASELINE.json configs 2 / 5 at their own size and parameter file: the 1k population tiled x10 (make_pop10k.py),
+        # 90-day runs of the unmodified reference, seven kept days each
+        "ref_10k_strict_seed12": "epidemiology_strict_days.json"}
 NONE = -32768
 
 

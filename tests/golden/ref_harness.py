@@ -134,7 +134,7 @@ class Recorder:
 
 
 def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", record_days=None, quiet=True,
-                  on_day=None):
+                  on_day=None, extra_install=None):
     """Run sim.main() of the unmodified reference and return the Recorder."""
     _install_stubs()
     simdir = os.path.join(workdir, "simulator")
@@ -150,6 +150,8 @@ def run_reference(workdir, seed, days, popsubfolder="1kagents2ktourists2019", re
                        "logmemoryinfo": False, "logfilename": "golden_%d.txt" % seed})
     rec = Recorder()
     install_recorder(rec, record_days, on_day)
+    if extra_install is not None:          # further patches of a fixture script (make_k6_kat.py)
+        extra_install(rec)
     stdout = sys.stdout
     try:
         sim.main()

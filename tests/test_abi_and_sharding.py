@@ -39,7 +39,8 @@ def test_struct_layouts_match_header_constants():
     src = open(os.path.join(ROOT, "include", "mtd_b200.h")).read()
     assert int(re.search(r"#define MTD_DELTA_WORDS (\d+)", src).group(1)) == capi.DELTA_WORDS
     assert int(re.search(r"#define MTD_MAXSCHED (\d+)", src).group(1)) == capi.MAXSCHED
-    assert ctypes.sizeof(capi.Counters) == 8 * (8 + 6 + 1)
+    assert ctypes.sizeof(capi.Counters) == 8 * (8 + 9 + 1 + 1)       # 8 scalars, class_cells[9], n_incidences, error
+    assert int(re.search(r"#define MTD_MAX_CELL_INTERVALS (\d+)", src).group(1)) == capi.MAX_CELL_INTERVALS
     assert ctypes.sizeof(capi.Day) == 32
 
 
