@@ -248,6 +248,18 @@ int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_trace_tape *
                         const int32_t *traced, int64_t n_slices, const int64_t *slice_off, const int32_t *rows3,
                         const uint8_t *epi_present, int mem);
 int mtd_get_traced(mtd_handle h, uint8_t *primary, uint8_t *secondary, mtd_trace_stats *stats, int mem);
+/* Cell-sharded contact tracing (the reference's stateful strategy syncs the traced agents between the partitions at the
+ * end of the day, sim.py:2034-2063, actor_dist.py:432-569).  The contact rows stay on the rank that produced them:
+ *   mtd_contact_tracing_scan    marks the traced positives and scans THIS rank's look-back slices; primary_out (device
+ *                               u8[N]) receives the primary-contact flags found in them.  Philox mode only: the scan draw
+ *                               is keyed by (day, look-back distance, a1, a2), so it does not depend on the sharding;
+ *   (caller)                    OR / MAX all-reduce of the flags over the ranks -- the path's second exchange step;
+ *   mtd_contact_tracing_finish  takes the merged flags (device u8[N]) and runs the scheduling phases on this rank's
+ *                               replica of the per-agent records: identical on every rank, identical to one GPU. */
+int mtd_contact_tracing_scan(mtd_handle h, const mtd_day *day, int64_t n_traced, const int32_t *traced, int64_t n_slices,
+                             const int64_t *slice_off, const int32_t *rows3, const uint8_t *epi_present,
+                             uint8_t *primary_out, int mem);
+int mtd_contact_tracing_finish(mtd_handle h, const uint8_t *primary_in);
 /* K6: the record bookkeeping of Itinerary.sample_intervention_activities (itinerary.py:2283-2528; SURVEY.md section 8f
  * rank 4), once per day over all agents (epi_present: optional u8[N], agents without an epi record are skipped), in the
  * reference's order: (A) :2301-2332 results due today flag the agent positive (false-negative / false-positive rates of

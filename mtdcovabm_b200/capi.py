@@ -27,7 +27,7 @@ EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mt
            "mtd_set_profiling", "mtd_get_stage_ms", "mtd_set_export", "mtd_prefetch_intervals",
            "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced",
            "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts", "mtd_seed_exposures", "mtd_set_intervention_mask", "mtd_set_k0_overlap",
-           "mtd_process_test_results", "mtd_set_k6_tape", "mtd_enable_vaccination", "mtd_schedule_vaccinations", "mtd_set_vaccination",
+           "mtd_process_test_results", "mtd_set_k6_tape", "mtd_contact_tracing_scan", "mtd_contact_tracing_finish", "mtd_enable_vaccination", "mtd_schedule_vaccinations", "mtd_set_vaccination",
            "mtd_get_vaccination", "mtd_build_intervals", "mtd_get_intervals"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
 
@@ -336,6 +336,17 @@ class Handle:
                                               C.c_int64(len(traced)), _ptr(traced), C.c_int64(len(slice_off) - 1),
                                               _ptr(slice_off), _ptr(rows3), _ptr(epi_present), mem),
                  "mtd_contact_tracing")
+
+    def contact_tracing_scan(self, day: Day, traced, slice_off, rows3, primary_out, epi_present=None):
+        """cell-sharded K5, phase 1 (DEVICE tensors): this rank's rows -> primary flags into primary_out (u8[N])"""
+        slice_off = np.ascontiguousarray(slice_off, np.int64)
+        self._ck(self.lib.mtd_contact_tracing_scan(self.h, C.byref(day), C.c_int64(len(traced)), _ptr(traced),
+                                                   C.c_int64(len(slice_off) - 1), _ptr(slice_off), _ptr(rows3),
+                                                   _ptr(epi_present), _ptr(primary_out), MEM_DEVICE), "mtd_contact_tracing_scan")
+
+    def contact_tracing_finish(self, primary_in):
+        """cell-sharded K5, phase 2: the flags merged over the ranks (device u8[N]) -> scheduling on the replicated records"""
+        self._ck(self.lib.mtd_contact_tracing_finish(self.h, _ptr(primary_in)), "mtd_contact_tracing_finish")
 
     def set_k6_tape(self, agent_ids, draws2):
         """replay tape of K6: strictly ascending agent ids, [n, 2] doubles (result draw, quarantine draw)"""

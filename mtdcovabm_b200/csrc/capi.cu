@@ -7,6 +7,7 @@
 #include <string>
 #include <vector>
 #include "common.cuh"
+#include "k5_ctx.h"
 
 // every launcher returns the number of kernels it launched
 int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count);
@@ -82,6 +83,7 @@ struct mtd_handle_s {
     uint8_t *sc_se = nullptr; int64_t sc_cap_se = 0;
     uint8_t *agent_masked = nullptr; bool mask_on = false;
     int32_t *k6_agent = nullptr; double *k6_u = nullptr; int64_t k6_n = 0;   // replay tape of K6 (mtd_set_k6_tape)
+    TraceCtx *trace_ctx = nullptr; bool trace_scan_pending = false;   // cell-sharded K5: context between scan and finish
     uint8_t *seed_buf = nullptr; int64_t seed_cap = 0;        // staging of mtd_seed_exposures
     // K8 interval builder: device copies of the itinerary CSR + scratch; the built stream lives in d_iv_*
     int64_t *k8_ent_off = nullptr, *k8_grp_off = nullptr, *k8_out_off = nullptr; int16_t *k8_ent_ts = nullptr;
@@ -345,6 +347,7 @@ extern "C" int mtd_destroy(mtd_handle h)
     if (h->ev_state) cudaEventDestroy(h->ev_state);
     if (h->ev_main) cudaEventDestroy(h->ev_main);
     for (void *p : { (void *)h->k6_agent, (void *)h->k6_u }) if (p) cudaFree(p);
+    delete h->trace_ctx;
     for (void *p : { (void *)h->seed_buf, (void *)h->sc_a1, (void *)h->sc_a2, (void *)h->sc_off, (void *)h->sc_se, (void *)h->vacc_ids, (void *)h->vacc_ts,
                      (void *)h->k8_ent_off, (void *)h->k8_grp_off, (void *)h->k8_out_off, (void *)h->k8_ent_ts, (void *)h->k8_ent_cell,
                      (void *)h->k8_grp_agent, (void *)h->k8_grp_res, (void *)h->k8_count, (void *)h->k8_scan }) if (p) cudaFree(p);
@@ -1096,6 +1099,8 @@ extern "C" int mtd_occupancy(mtd_handle h, int64_t out[6])
 // ------------------------------------------------------------------------------------------------ K5
 #include "k5_ctx.h"
 int launch_k5(const TraceCtx &c, int32_t *flag_scan, long long *scan_tmp, cudaStream_t st, int sm_count);
+int launch_k5_scan(const TraceCtx &c, cudaStream_t st, int sm_count);
+int launch_k5_finish(const TraceCtx &c, int32_t *flag_scan, long long *scan_tmp, cudaStream_t st, int sm_count);
 
 template <typename T>
 static int regrow(mtd_handle h, T **p, int64_t *cap, int64_t need)
@@ -1161,9 +1166,9 @@ static int trace_up(mtd_handle h, const T **dst, const T *src, size_t n)
     return 0;
 }
 
-extern "C" int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_trace_tape *tape, int64_t n_traced,
-                                   const int32_t *traced, int64_t n_slices, const int64_t *slice_off,
-                                   const int32_t *rows3, const uint8_t *epi_present, int mem)
+static int trace_prepare(mtd_handle h, const mtd_day *day, const mtd_trace_tape *tape, int64_t n_traced,
+                         const int32_t *traced, int64_t n_slices, const int64_t *slice_off,
+                         const int32_t *rows3, const uint8_t *epi_present, int mem, TraceCtx &t)
 {
     if (!h || !day || n_traced < 0 || n_slices < 0 || n_slices > 8 || (n_slices && !slice_off)) {
         if (h) h->err = "mtd_contact_tracing: bad arguments"; return MTD_E_ARG; }
@@ -1176,7 +1181,6 @@ extern "C" int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_t
     CK(cudaStreamSynchronize(h->stream));
     for (void *p : h->trace_tape_allocs) cudaFree(p);
     h->trace_tape_allocs.clear();
-    TraceCtx t;
     memset(&t, 0, sizeof(t));
     t.n_agents = h->c.n_agents; t.n_res_cells = h->n_res_cells; t.day = *day; t.P = h->d_params;
     if (tape && day->mode == MTD_MODE_REPLAY) {
@@ -1206,8 +1210,50 @@ extern "C" int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_t
     t.order = h->trace_order; t.n_order = h->trace_scalars + 8; t.cursor = h->trace_cursor;
     t.res_first = h->res_first; t.res_k = h->res_k; t.sel = h->trace_sel; t.sec_owner = h->sec_owner;
     t.stats = h->trace_scalars;
+    return MTD_OK;
+}
+
+extern "C" int mtd_contact_tracing(mtd_handle h, const mtd_day *day, const mtd_trace_tape *tape, int64_t n_traced,
+                                   const int32_t *traced, int64_t n_slices, const int64_t *slice_off,
+                                   const int32_t *rows3, const uint8_t *epi_present, int mem)
+{
+    TraceCtx t;
+    { int r = trace_prepare(h, day, tape, n_traced, traced, n_slices, slice_off, rows3, epi_present, mem, t); if (r) return r; }
     launch_k5(t, h->trace_flagscan, h->trace_scan_tmp, h->stream, h->sm_count);
     CK(cudaGetLastError());
+    return MTD_OK;
+}
+
+// Cell-sharded contact tracing ("after K5: allgather of primary-contact ids; contact rows stay
+// sharded"): every rank scans the contact rows of its own cells, the primary-contact flags are OR-ed over the ranks by
+// the caller (one all-reduce of N bytes), and every rank then runs the scheduling phases on its replica of the records.
+extern "C" int mtd_contact_tracing_scan(mtd_handle h, const mtd_day *day, int64_t n_traced, const int32_t *traced,
+                                        int64_t n_slices, const int64_t *slice_off, const int32_t *rows3,
+                                        const uint8_t *epi_present, uint8_t *primary_out, int mem)
+{
+    if (!h || !primary_out) { if (h) h->err = "mtd_contact_tracing_scan: bad arguments"; return MTD_E_ARG; }
+    if (day && day->mode == MTD_MODE_REPLAY) { h->err = "mtd_contact_tracing_scan: Philox mode only (the replay tape is keyed by global row index)"; return MTD_E_ARG; }
+    if (!h->trace_ctx) h->trace_ctx = new (std::nothrow) TraceCtx();
+    if (!h->trace_ctx) return MTD_E_ARG;
+    TraceCtx &t = *h->trace_ctx;
+    { int r = trace_prepare(h, day, nullptr, n_traced, traced, n_slices, slice_off, rows3, epi_present, mem, t); if (r) return r; }
+    launch_k5_scan(t, h->stream, h->sm_count);
+    CK(cudaMemcpyAsync(primary_out, h->primary, (size_t)h->c.n_agents, cudaMemcpyDeviceToDevice, h->stream));
+    CK(cudaGetLastError());
+    h->trace_scan_pending = true;
+    return MTD_OK;
+}
+
+extern "C" int mtd_contact_tracing_finish(mtd_handle h, const uint8_t *primary_in)
+{
+    if (!h || !primary_in) { if (h) h->err = "mtd_contact_tracing_finish: bad arguments"; return MTD_E_ARG; }
+    if (!h->trace_scan_pending) { h->err = "mtd_contact_tracing_finish before mtd_contact_tracing_scan"; return MTD_E_STATE; }
+    CK(cudaSetDevice(h->cfg.device));
+    TOUCH();
+    CK(cudaMemcpyAsync(h->primary, primary_in, (size_t)h->c.n_agents, cudaMemcpyDeviceToDevice, h->stream));
+    launch_k5_finish(*h->trace_ctx, h->trace_flagscan, h->trace_scan_tmp, h->stream, h->sm_count);
+    CK(cudaGetLastError());
+    h->trace_scan_pending = false;
     return MTD_OK;
 }
 

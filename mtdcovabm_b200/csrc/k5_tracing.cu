@@ -46,7 +46,8 @@ __global__ void k5_scan_kernel(TraceCtx c)
             u = c.scan_u[lo];
         } else {
             uint32_t w[4];
-            philox4x32((uint32_t)c.day.day, (uint32_t)back, (uint32_t)idx, 0u, c.day.seed, SITE_TRACE, w);
+            philox4x32((uint32_t)c.day.day, (uint32_t)back, (uint32_t)a1, (uint32_t)a2, c.day.seed, SITE_TRACE, w);   // keyed by the pair,
+                                        // not by the row index: the same draw however the contact rows are sharded over ranks
             u = u53(w[0], w[1]);
         }
         local++;
@@ -341,21 +342,33 @@ int launch_k6(const DevCtx &c, const uint8_t *epi_present, uint8_t *positive, in
     return n + 1;
 }
 
-int launch_k5(const TraceCtx &c, int32_t *flag_scan, long long *scan_tmp, cudaStream_t st, int sm_count)
+// phase 1: traced marks + scan of the look-back slices -> primary-contact flags (c.primary).  Under cell sharding every rank
+// scans the rows of its own cells; the flags are OR-ed over the ranks before phase 2.
+int launch_k5_scan(const TraceCtx &c, cudaStream_t st, int sm_count)
 {
     const int T = 256;
     const size_t N = (size_t)c.n_agents;
     cudaMemsetAsync(c.is_traced, 0, N, st); cudaMemsetAsync(c.primary, 0, N, st); cudaMemsetAsync(c.secondary, 0, N, st);
     cudaMemsetAsync(c.stats, 0, 4 * sizeof(int32_t), st); cudaMemsetAsync(c.n_order, 0, sizeof(int32_t), st);
+    auto grid = [&](int64_t n) { int64_t g = (n + T - 1) / T; int64_t cap = (int64_t)sm_count * 16; return (unsigned)(g < 1 ? 1 : (g < cap ? g : cap)); };
+    int launches = 0;
+    if (c.n_traced > 0) { k5_mark_kernel<<<grid(c.n_traced), T, 0, st>>>(c); launches++; }
+    const int64_t n_rows = c.slice_off[c.n_slices];
+    if (n_rows > 0) { k5_scan_kernel<<<grid(n_rows), T, 0, st>>>(c); launches++; }
+    return launches;
+}
+
+// phase 2: processing order, primary / secondary scheduling on the (replicated) per-agent records
+int launch_k5_finish(const TraceCtx &c, int32_t *flag_scan, long long *scan_tmp, cudaStream_t st, int sm_count)
+{
+    const int T = 256;
+    const size_t N = (size_t)c.n_agents;
     cudaMemsetAsync(c.cursor, 0, sizeof(int32_t) * N, st);
     cudaMemsetAsync(c.sec_owner, 0x7f, sizeof(int32_t) * N, st);
     cudaMemsetAsync(c.res_first, 0x7f, sizeof(int32_t) * (size_t)c.n_res_cells, st);
     cudaMemsetAsync(c.res_k, 0, sizeof(int32_t) * (size_t)c.n_res_cells, st);
     auto grid = [&](int64_t n) { int64_t g = (n + T - 1) / T; int64_t cap = (int64_t)sm_count * 16; return (unsigned)(g < 1 ? 1 : (g < cap ? g : cap)); };
     int launches = 0;
-    if (c.n_traced > 0) { k5_mark_kernel<<<grid(c.n_traced), T, 0, st>>>(c); launches++; }
-    const int64_t n_rows = c.slice_off[c.n_slices];
-    if (n_rows > 0) { k5_scan_kernel<<<grid(n_rows), T, 0, st>>>(c); launches++; }
     if (c.day.mode == MTD_MODE_REPLAY) {
         if (c.n_prim > 0) { k5_order_replay_kernel<<<grid(c.n_prim), T, 0, st>>>(c); launches++; }
     } else {
@@ -369,4 +382,9 @@ int launch_k5(const TraceCtx &c, int32_t *flag_scan, long long *scan_tmp, cudaSt
     k5_secondary_kernel<<<g, T, 0, st>>>(c);
     k5_count_kernel<<<grid(c.n_agents), T, 0, st>>>(c);
     return launches + 4;
+}
+
+int launch_k5(const TraceCtx &c, int32_t *flag_scan, long long *scan_tmp, cudaStream_t st, int sm_count)
+{
+    return launch_k5_scan(c, st, sm_count) + launch_k5_finish(c, flag_scan, scan_tmp, st, sm_count);
 }

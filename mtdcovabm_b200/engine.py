@@ -27,6 +27,40 @@ def exchange_deltas(gather: torch.Tensor, rank: int, group=None):
     torch.distributed.all_gather_into_tensor(gather.view(-1), gather[rank].reshape(-1).clone(), group=group)
 
 
+def setup_peer_exchange(h, rank, world, delta_cap, group=None):
+    """map every peer's exchange buffer (CUDA IPC) -> "p2p"; "nccl" if that is not possible on this box"""
+    import sys
+    dist = torch.distributed
+    ok, mine, why = 1, b"", ""
+    if os.environ.get("MTD_EXCHANGE", "p2p") == "nccl":
+        ok, why = 0, "MTD_EXCHANGE=nccl"
+    else:
+        try:
+            mine = h.exchange_init(rank, world, delta_cap)
+        except RuntimeError as e:
+            ok, why = 0, str(e)
+    handles = [None] * world
+    dist.all_gather_object(handles, (ok, mine, why), group=group)
+    if all(o for o, _, _ in handles):
+        try:
+            for r, (_, hb, _) in enumerate(handles):
+                if r != rank:
+                    h.exchange_open(r, hb)
+            h.exchange_ready()
+        except RuntimeError as e:
+            ok, why = 0, str(e)
+    else:
+        ok = 0
+        why = why or next(w for o, _, w in handles if not o)
+    flags = [None] * world
+    dist.all_gather_object(flags, ok, group=group)        # also the barrier after the mappings
+    if all(flags):
+        return "p2p"
+    if rank == 0:
+        sys.stderr.write("mtdcovabm_b200: peer exchange unavailable (%s); using the NCCL all-gather\n" % why)
+    return "nccl"
+
+
 class DayEngine:
     def __init__(self, n_agents, n_cells, max_intervals, params, device=0, rank=0, world=1, delta_cap=0,
                  max_rows=0, mode=capi.MODE_PHILOX, seed=0, group=None):
@@ -54,38 +88,7 @@ class DayEngine:
         self._vaccination = False
 
     def _setup_peer_exchange(self):
-        """map every peer's exchange buffer (CUDA IPC) -> "p2p"; "nccl" if that is not possible on this box"""
-        import os
-        import sys
-        dist = torch.distributed
-        ok, mine, why = 1, b"", ""
-        if os.environ.get("MTD_EXCHANGE", "p2p") == "nccl":
-            ok, why = 0, "MTD_EXCHANGE=nccl"
-        else:
-            try:
-                mine = self.h.exchange_init(self.rank, self.world, self.delta_cap)
-            except RuntimeError as e:
-                ok, why = 0, str(e)
-        handles = [None] * self.world
-        dist.all_gather_object(handles, (ok, mine, why), group=self.group)
-        if all(o for o, _, _ in handles):
-            try:
-                for r, (_, hb, _) in enumerate(handles):
-                    if r != self.rank:
-                        self.h.exchange_open(r, hb)
-                self.h.exchange_ready()
-            except RuntimeError as e:
-                ok, why = 0, str(e)
-        else:
-            ok = 0
-            why = why or next(w for o, _, w in handles if not o)
-        flags = [None] * self.world
-        dist.all_gather_object(flags, ok, group=self.group)        # also the barrier after the mappings
-        if all(flags):
-            return "p2p"
-        if self.rank == 0:
-            sys.stderr.write("mtdcovabm_b200: peer exchange unavailable (%s); using the NCCL all-gather\n" % why)
-        return "nccl"
+        return setup_peer_exchange(self.h, self.rank, self.world, self.delta_cap, self.group)
 
     def _transmission(self, d):
         """K3 of the day + the exchange and application of the exposure records"""

@@ -999,7 +999,8 @@ int64_t mtdo_contact_tracing(const mtdo_params *P, const mtdo_dayctx *D, const m
                 u = T->scan_u[t];
             } else {
                 uint32_t w[4];
-                philox_site(D, MTDO_SITE_TRACE, (uint32_t)back, (uint32_t)idx, 0, w);
+                philox_site(D, MTDO_SITE_TRACE, (uint32_t)back, (uint32_t)a1, (uint32_t)a2, w);   /* keyed by the row's pair, not by its
+                                                                                       * index: the same draw however the rows are sharded */
                 u = mtdo_u53(w[0], w[1]);
             }
             S->n_scan_draws++;

@@ -38,6 +38,13 @@ def test_full_state_step_day_loop():
     dosed = (last != prm.NONE) & (st["seir"] != 0)
     assert 0 < dosed.sum() <= sum(r["vaccinations"] for r in log)
     assert (st["quarantine"][:, 0] != prm.NONE).sum() > 0 and (st["test_day"][:, 0] != prm.NONE).sum() > 0
+    # records expire as in the itinerary stage (itinerary.py:2396, 2456, 2486): nothing stale is left behind, so agents
+    # can be tested and quarantined again later in the run
+    q, hp, td, tr = st["quarantine"], st["hosp"], st["test_day"], st["test_result_day"]
+    assert ((hp[:, 0] != prm.NONE) & (hp[:, 2] < 40) & (hp[:, 0] != hp[:, 2])).sum() == 0
+    assert ((q[:, 0] != prm.NONE) & (q[:, 2] < 40) & (q[:, 0] != q[:, 2])).sum() <= 5      # (hospital discharge on the end day keeps it)
+    assert ((td[:, 0] != prm.NONE) & (td[:, 0] < 40 - 6)).sum() == 0
+    assert ((tr[:, 0] != prm.NONE) & (tr[:, 0] < 40)).sum() == 0
     log2, st2, last2, _ = _run(3)
     assert [r["occupancy"] for r in log] == [r["occupancy"] for r in log2]
     assert [r["primary"] for r in log] == [r["primary"] for r in log2]

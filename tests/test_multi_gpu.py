@@ -49,3 +49,16 @@ def test_two_gpus_equal_one_gpu_host_boundary():
 def test_two_gpus_with_k0_overlap_equal_one_gpu_serial():
     """the bench's N > 1 configuration: K0 of day d+1 beside K1..K3 of day d on every rank, peer exchange, host running ahead"""
     _run(["--overlap"], port=29544)
+
+
+@needs2
+def test_two_gpu_whole_state_step_equals_one_gpu():
+    """40 days of dayloop.EpidemicRun (K4, K6, K0 with the intervention mask, K1-K3, K5 over the sharded row ring, K7) on
+    2 GPUs == on 1 GPU: every per-agent record, the vaccination records and the per-day log, bit for bit"""
+    env = dict(os.environ)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+           "127.0.0.1", "--master-port", "29545", os.path.join(ROOT, "tools", "check_multi_gpu_dayloop.py"), "--reps", "20",
+           "--days", "40"]
+    p = subprocess.run(cmd, cwd=ROOT, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=1200)
+    assert p.returncode == 0, p.stdout[-4000:]
+    assert "EQUAL" in p.stdout, p.stdout[-4000:]
