@@ -177,6 +177,66 @@ def cpu_oracle_run(args, steps, warmup, sample_agents):
                 agents=n_present1 * reps)
 
 
+def parity_on_sample(args, sample_agents):
+    """The oracle (one thread, the reference's cell order) and the CUDA path on the SAME shard of the bench workload: day
+    stream 0 of a `sample_agents` tiling from the same initial state, Philox mode.  Contact rows must be equal element for
+    element and in order, exposed ids likewise.  -> dict for the JSON line; raises on a mismatch."""
+    from mtdcovabm_b200 import capi, params as prm, synth
+    from oracle import mtd_oracle as mo
+    bank = synth.load_bank()
+    P = prm.build_params()
+    N1 = int(bank["n_agents"][0]); n_present1 = int(bank["present"].sum())
+    reps = max(1, sample_agents // n_present1)
+    agent, cell, start, end, perm = cpu_day_numpy(bank, reps, 0, args.seed)
+    N = N1 * reps
+    st = mo.AgentState(N)
+    for name in ("age_bracket", "epi_age_bracket", "soc_rate"):
+        getattr(st, name)[perm] = np.tile(bank[name], reps)
+    rc = np.tile(bank["res_cellid"].astype(np.int64), reps)
+    rc = np.where(rc >= 0, rc + np.repeat(np.arange(reps, dtype=np.int64), N1) * len(bank["cell_type"]), rc)
+    st.res_cellid[perm] = rc.astype(np.int32)
+    present = np.zeros(N, bool); present[perm] = np.tile(bank["present"], reps)
+    rng = np.random.default_rng(99 + args.seed)
+    st.seir[:] = np.where(present, 1, 0)
+    inf = present & (rng.random(N) < 0.02)
+    st.seir[inf] = 3; st.inf_type[inf] = 3; st.inf_sev[inf] = 1
+    cell_type = np.ascontiguousarray(np.tile(bank["cell_type"], reps), np.int8)
+    cell_indid = np.ascontiguousarray(np.tile(bank["cell_indid"], reps), np.int16)
+    h = capi.Handle(N, len(cell_type), len(agent) + 16)
+    h.set_params(P)
+    h.set_cells(cell_type, cell_indid)
+    h.set_static(st.age_bracket, st.epi_age_bracket, st.soc_rate, st.res_cellid)
+    h.set_state(seir=st.seir, inf_type=st.inf_type, inf_sev=st.inf_sev)
+    d = h.make_day(capi.MODE_PHILOX, 1, 0.0, False, False, seed=args.seed)
+    h.simulate_contact_network(d, agent, cell, start, end)
+    h.simulate_direct_contacts(d)
+    c = h.counters()
+    grow, gdur, gcell = h.get_contacts()
+    gexp = h.get_exposed()
+    h.close()
+    ctx = mo.make_ctx(mo.MODE_PHILOX, 1, 0.0, False, False, seed=args.seed)
+    orow, odur, orc, s1 = mo.contact_network(P, ctx, cell, agent, start, end, cell_type, cell_indid, st)
+    oexp, _, _ = mo.transmission(P, ctx, cell, agent, start, end, cell_type, orow, odur, orc, st)
+    ok_rows = bool(np.array_equal(grow, orow) and np.array_equal(gdur, odur) and np.array_equal(gcell, orc))
+    ok_exp = bool(np.array_equal(gexp, oexp))
+    ok_cnt = bool(int(c.pairs_evaluated) == int(s1.pairs_evaluated) and int(c.n_potential) == int(s1.n_potential))
+    out = {"sample": "%d active agents (day stream 0 of the bench workload, %d replicas)" % (n_present1 * reps, reps),
+           "rows": int(len(orow)), "exposed": int(len(oexp)), "pairs": int(s1.pairs_evaluated), "rows_equal": ok_rows,
+           "exposed_equal": ok_exp, "counters_equal": ok_cnt}
+    if not (ok_rows and ok_exp and ok_cnt):
+        raise SystemExit("bench.py: the CUDA path and the oracle disagree on the bench workload sample: %s" % json.dumps(out))
+    return out
+
+
+def reference_python_timing():
+    """the UNMODIFIED reference's own contactnetwork_mp.contactnetwork_parallel, timed by tools/time_reference.py in the
+    build container (its sources do not travel to the GPU box): carried here next to the C port's number"""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "r02_reference_python_timing.json")))
+    except Exception:
+        return None
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -195,16 +255,14 @@ def run_reference(args):
             "config": workload_config(args, n1 * reps_full, int(len(bank["d0_iv_agent"])) * reps_full,
                                       int(len(bank["cell_type"])) * reps_full),
             "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port",
-                             "sample": r["sample"]},
+                             "sample": r["sample"], "reference_python": reference_python_timing()},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
 
 
-def workload_config(args, agents, intervals, cells, exchange=None):
+def workload_config(args, agents, intervals, cells):
     par = "cells sharded x%d, state replicated" % args.gpus
-    if exchange and args.gpus > 1:
-        par += ", exposure records exchanged by " + ("stores into NVLink peer memory" if exchange == "p2p" else "NCCL all-gather")
     return {"workload": "synthetic %d-agent population: reference 1k-agent itinerary bank tiled, ids shuffled, "
                         "agent-major emission order (BASELINE.json configs[3])" % agents,
             "agents": agents, "intervals_per_day": intervals, "cells": cells, "parallelism": par,
@@ -247,7 +305,7 @@ def run_b200(args):
             h.simulate_contact_network(d, s["iv_agent"], s["iv_cell"], s["iv_start"], s["iv_end"], iv_order=s["iv_order"],
                                        mem=capi.MEM_DEVICE)
         c = h.counters()
-        pairs.append((int(c.pairs_evaluated), int(c.n_rows), int(c.n_slots)))
+        pairs.append((int(c.pairs_evaluated), int(c.n_rows), int(c.n_slots), int(c.n_incidences)))
     eng.set_population(pop)          # reset the state
     torch.cuda.synchronize()
     eng.set_inputs_ready(True)       # the day streams were built above and are complete: K0/K1 of the coming days may overlap the current one
@@ -301,7 +359,7 @@ def run_b200(args):
     M_mean = sum(len(streams[t % nb]["iv_agent"]) for t in timed) / args.steps
     D_mean = sum(pairs[t % nb][1] for t in timed) / args.steps
     P_mean = sum(pairs[t % nb][0] for t in timed) / args.steps
-    U_mean = 0.73 * M_mean
+    U_mean = sum(pairs[t % nb][3] for t in timed) / args.steps        # (cell, agent) incidences, counted by K1
     k1_bytes = 10 * M_mean + 13 * U_mean + 12 * D_mean
     peaks = {}
     try:
@@ -314,18 +372,19 @@ def run_b200(args):
     traffic = None
     warp_instr = None
     try:
-        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_k1_traffic.json")))
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r02_k1_traffic.json")))
         traffic = tr["dram_bytes_total"] * M_mean / tr["intervals_of_day"]
         warp_instr = tr["warp_instructions"] * M_mean / tr["intervals_of_day"]
     except Exception:
         pass
     k1_ms = st_ms["k1_contacts"]
     achieved = k1_bytes / (k1_ms * 1e-3) / 1e9 if k1_ms > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": "k1_contacts (6 size-class launches + 4 ordering helpers per day, three streams)", "achieved": achieved,
+    roofline = {"bound": "hbm", "kernel": "k1_contacts (3 sub-warp kernels for cells <= 32 intervals, 5 block-per-cell kernels above, 4 ordering helpers; three streams)", "achieved": achieved,
                 "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum over the K1 launches, mean per day over the 7 day streams (profiles/r01_k1_traffic.json)",
+                "traffic_source": "ncu dram__bytes_read.sum + dram__bytes_write.sum over the K1 launches, mean per day over the 7 day streams (profiles/r02_k1_traffic.json; null until this round's kernels have been captured)",
                 "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
-                "algorithmic_bytes_per_day": k1_bytes, "k1_ms": k1_ms, "stage_ms": st_ms,
+                "algorithmic_bytes_per_day": k1_bytes, "algorithmic_units": {"M_intervals": M_mean, "U_incidences": U_mean, "D_rows": D_mean},
+                "k1_ms": k1_ms, "stage_ms": st_ms,
                 "k1_pairs_per_s": P_mean / (k1_ms * 1e-3) if k1_ms > 0 else None,
                 "note": "K1 is issue/latency-bound (sequential greedy sampling per cell), not HBM-bound: see DESIGN.md"}
     # SM-side bound of K1: warp instructions issued per day (ncu smsp__inst_executed.sum, same capture as
@@ -398,12 +457,42 @@ def run_b200(args):
         e_ms = allmax((time.perf_counter() - t0) * 1e3)
         assert last_res.n_rows > 0 and int(last_res.occupancy.sum()) > 0
         e2e = {"value": total_pairs / (e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(allsum(h2d)) // args.steps,
-               "d2h_bytes_per_step": int(allsum(d2h)) // args.steps, "ms_per_step": e_ms / args.steps, "api": api}
+               "d2h_bytes_per_step": int(allsum(d2h)) // args.steps, "ms_per_step": e_ms / args.steps, "api": api,
+               "mode": "pipelined: day d+1's intervals are uploaded while day d computes (needs tomorrow's itinerary today: "
+                       "legal for recorded / tiled streams, not behind sim.py's loop)"}
+        # the dependency sim.py's day loop really has (the itinerary of day d+1 reads the state after day d,
+        # itinerary.py:2283-2528): no prefetch, the result of day d is waited for before day d+1 is submitted
+        ser_steps = max(2, min(args.steps, 2 * nb))
+
+        def run_serial(first, count):
+            for step in range(first, first + count):
+                r = eng.step_host(1 + step, host[step % nb], next_s=None)
+                r.wait()
+            return r
+
+        run_serial(args.warmup + args.steps, 2)
+        barrier()
+        t0 = time.perf_counter()
+        run_serial(args.warmup + args.steps + 2, ser_steps)
+        barrier()
+        s_ms = allmax((time.perf_counter() - t0) * 1e3)
+        ser_pairs = allsum(sum(pairs[st_ % nb][0] for st_ in range(args.warmup + args.steps + 2, args.warmup + args.steps + 2 + ser_steps)))
+        e2e["serial"] = {"value": ser_pairs / (s_ms * 1e-3), "unit": UNIT, "ms_per_step": s_ms / ser_steps, "steps": ser_steps,
+                         "mode": "dependency-honouring: upload, compute and export of day d complete before day d+1 is submitted"}
 
     cpu = None
+    parity = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         r = cpu_oracle_run(args, 20, 2, args.cpu_sample_agents or 1_000_000)     # ~10 s of CPU work
-        cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
+        cpu = {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"],
+               "reference_python": reference_python_timing()}
+        parity = parity_on_sample(args, min(args.cpu_sample_agents or 1_000_000, 1_000_000))
+    # per-rank stage times of the timed region: load balance of K1 and the wait for the slowest peer inside k3_apply
+    per_rank = None
+    if world > 1:
+        allst = [None] * world
+        dist.all_gather_object(allst, {k: st_ms.get(k) for k in ("k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")})
+        per_rank = {k: [a.get(k) for a in allst] for k in allst[0]}
 
     contacts_per_day = allsum(allsum_rows(pairs, args, nb))
     if rank == 0:
@@ -411,11 +500,14 @@ def run_b200(args):
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
                 "vs_baseline": None, "dtype": "int32+f64", "data": "synthetic",
-                "config": workload_config(args, agents, int(streams[0]["n_total"]), pop.n_cells, eng.exchange),
+                "config": workload_config(args, agents, int(streams[0]["n_total"]), pop.n_cells),
+                "exchange": {"none": "single GPU", "p2p": "exposure records pushed with stores into NVLink peer memory (CUDA IPC), arrival flags",
+                             "nccl": "NCCL all-gather of fixed-capacity record buffers"}[eng.exchange],
                 "agent_days_per_s": agents * args.steps / (ms * 1e-3),
                 "pairs_per_day": total_pairs / args.steps, "contacts_per_day": contacts_per_day,
                 "exposed_last_day": int(c.n_exposed),
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
+                "roofline": roofline, "cpu_baseline": cpu, "parity": parity, "per_rank_stage_ms": per_rank, "e2e": e2e,
+                "gpu_launches": launches,
                 "clocks": clocks.summary()}
         print(json.dumps(line), flush=True)
     eng.close()
