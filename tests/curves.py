@@ -17,18 +17,23 @@ from oracle import mtd_oracle as mo
 HERE = os.path.dirname(os.path.abspath(__file__))
 DAYS = 20
 _cache = {}
+# fixture -> the epidemiology parameter file its reference runs used (sim.py:443)
+FIXTURES = {"curves_1k": "epidemiology.json",                       # config 1: 32 seeds x 20 days
+            "curves_10k_normal": "epidemiology_normal_days.json",   # config 2: 1k population tiled x10, 8 seeds x 30 days
+            "curves_10k_strict": "epidemiology_strict_days.json"}   # config 5
 
 
-def load():
-    if "z" not in _cache:
-        _cache["z"] = np.load(os.path.join(HERE, "golden", "curves_1k.npz"))
-    return _cache["z"]
+def load(name="curves_1k"):
+    if name not in _cache:
+        _cache[name] = np.load(os.path.join(HERE, "golden", name + ".npz"))
+    return _cache[name]
 
 
 class SeedData:
     def __init__(self, z, seed):
         p = "s%d_" % seed
         self.N = int(z["n_agents"][0])
+        self.days = int(z["days"][0]) if "days" in z.files else DAYS
         self.cell_type = z[p + "cell_type"]; self.cell_indid = z[p + "cell_indid"]
         self.iv_off = z[p + "iv_off"]
         self.iv_cell = z[p + "iv_cell"].astype(np.int32); self.iv_agent = z[p + "iv_agent"].astype(np.int32)
@@ -69,8 +74,8 @@ class SeedData:
 def run_seed_oracle(sd: SeedData, P, philox_seed):
     """-> (incidence[20], occupancy[20, 6]) of the CPU oracle in Philox mode"""
     st = sd.initial_state()
-    inc = np.zeros(DAYS, np.int32); occ = np.zeros((DAYS, 6), np.int32)
-    for i in range(DAYS):
+    inc = np.zeros(sd.days, np.int32); occ = np.zeros((sd.days, 6), np.int32)
+    for i in range(sd.days):
         day = i + 1
         mo.advance(day, st, None)
         sd.apply_arrivals(st, i)
@@ -90,8 +95,8 @@ def run_seed_gpu(sd: SeedData, P, philox_seed):
     from tests import helpers as H
     st = sd.initial_state()
     h = H.make_handle(P, st, sd.cell_type, sd.cell_indid, int(np.diff(sd.iv_off).max()) + 16)
-    inc = np.zeros(DAYS, np.int32); occ = np.zeros((DAYS, 6), np.int32)
-    for i in range(DAYS):
+    inc = np.zeros(sd.days, np.int32); occ = np.zeros((sd.days, 6), np.int32)
+    for i in range(sd.days):
         day = i + 1
         h.advance_seir(day, None)
         dev = h.get_state()
@@ -114,11 +119,16 @@ def run_seed_gpu(sd: SeedData, P, philox_seed):
 def ks_table(ours_inc, ours_occ, ref_inc, ref_occ):
     """two-sample KS p-value per day for incidence and each occupied SEIR state -> dict name -> p[20]"""
     from scipy.stats import ks_2samp
-    out = {"incidence": np.array([ks_2samp(ours_inc[:, d], ref_inc[:, d]).pvalue for d in range(DAYS)])}
+    days = ours_inc.shape[1]
+    out = {"incidence": np.array([ks_2samp(ours_inc[:, d], ref_inc[:, d]).pvalue for d in range(days)])}
     for k, name in ((1, "S"), (2, "E"), (3, "I"), (4, "R"), (5, "D")):
-        out[name] = np.array([ks_2samp(ours_occ[:, d, k], ref_occ[:, d, k]).pvalue for d in range(DAYS)])
+        out[name] = np.array([ks_2samp(ours_occ[:, d, k], ref_occ[:, d, k]).pvalue for d in range(days)])
     return out
 
 
 def params_config1():
     return prm.build_params(None, prm.load_json("epidemiology.json"))
+
+
+def params_for(name):
+    return prm.build_params(None, prm.load_json(FIXTURES[name]))

@@ -18,6 +18,7 @@ RUNS = {"ref_1k_seed6": "epidemiology.json", "ref_1k_strict_seed7": "epidemiolog
         "ref_cells_kat": "epidemiology.json",
         # BASELINE.json configs 2 / 5 at their own size and parameter file: the 1k population tiled x10 (make_pop10k.py),
         # 90-day runs of the unmodified reference, seven kept days each
+        "ref_10k_normal_seed11": "epidemiology_normal_days.json",
         "ref_10k_strict_seed12": "epidemiology_strict_days.json"}
 NONE = -32768
 

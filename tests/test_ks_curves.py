@@ -10,8 +10,8 @@ from tests import curves as C
 ALPHA = 0.05
 
 
-def _run_all(runner, n=None):
-    z = C.load(); P = C.params_config1()
+def _run_all(runner, n=None, name="curves_1k"):
+    z = C.load(name); P = C.params_for(name)
     seeds = [int(s) for s in z["seeds"]][:n]
     oi, oo, ri, ro = [], [], [], []
     for s in seeds:
@@ -39,3 +39,25 @@ def test_gpu_philox_curves_match_reference_ks():
     # and the CUDA path reproduces the oracle's Philox curves exactly (same draws, same arithmetic)
     ci, co, _, _ = _run_all(C.run_seed_oracle, n=4)
     assert np.array_equal(oi[:4], ci) and np.array_equal(oo[:4], co)
+
+
+# ---- BASELINE.json configs 2 and 5 at their own size and parameter file: the 1k population tiled x10 so that the
+# UNMODIFIED reference can run it (tests/golden/make_pop10k.py), 8 seeds x 30 days each (tests/golden/make_curves.py)
+@pytest.mark.parametrize("name", ["curves_10k_normal", "curves_10k_strict"])
+def test_oracle_philox_curves_match_reference_ks_10k(name):
+    oi, oo, ri, ro = _run_all(C.run_seed_oracle, name=name)
+    assert ri.sum() > 5000 and oi.sum() > 5000
+    ks = C.ks_table(oi, oo, ri, ro)
+    for k, p in ks.items():
+        assert p.min() > ALPHA, (name, k, p.round(3))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["curves_10k_normal", "curves_10k_strict"])
+def test_gpu_philox_curves_match_reference_ks_10k(name):
+    oi, oo, ri, ro = _run_all(C.run_seed_gpu, name=name)
+    ks = C.ks_table(oi, oo, ri, ro)
+    for k, p in ks.items():
+        assert p.min() > ALPHA, (name, k, p.round(3))
+    ci, co, _, _ = _run_all(C.run_seed_oracle, n=2, name=name)
+    assert np.array_equal(oi[:2], ci) and np.array_equal(oo[:2], co)
