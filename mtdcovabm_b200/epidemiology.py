@@ -150,6 +150,76 @@ class Epidemiology:
         return [int(a) for a in ids]
 
     # ------------------------------------------------------------------ small host-side helpers of the class
+    # The itinerary stage calls the three schedulers below once per agent on ITS side of the boundary (itinerary.py:2319,
+    # 2330, 2383; SURVEY.md section 8b "Who calls it") with the legacy global RNG streams, so they are host methods on the
+    # agent's dict that consume random.random() / np.random.lognormal exactly like the reference's.  The day step's own
+    # uses of the same rules (exposures of K3, traced contacts of K5, positive results of K6) run on the device.
+    def schedule_test(self, agent, agent_id, incremental_days, start_timestep, quarantine_type):
+        """epidemiology.py:502-565 -> (scheduled, test_day, test_result_day)"""
+        import random
+        from . import util
+        from .epidemiologyclasses import QuarantineType
+        ep = self.epidemiologyparams
+        test_day = result_day = None
+        if not self.dyn_params.testing_enabled:
+            return False, test_day, result_day
+        test_day = agent["test_day"]
+        if test_day is not None and len(test_day) > 0:                  # one pending test at a time (:519-521)
+            return False, test_day, result_day
+        if quarantine_type == QuarantineType.Symptomatic and not (random.random() < ep["testing_after_symptoms_probability"]):
+            return False, test_day, result_day
+        wait = {QuarantineType.PositiveContact: self.contact_tracing_positive_delay_days,
+                QuarantineType.SecondaryContact: self.contact_tracing_secondary_delay_days}.get(quarantine_type, 0)
+        wait += util.sample_log_normal(*ep["testing_days_distribution_parameters"][:2], 1, True)
+        day_of_test = incremental_days + wait
+        until_result = util.sample_log_normal(*ep["testing_results_days_distribution_parameters"][:2], 1, True)
+        agent["test_day"] = [day_of_test, start_timestep]
+        agent["test_result_day"] = [day_of_test + until_result, start_timestep]
+        return True, agent["test_day"], agent["test_result_day"]
+
+    def schedule_quarantine(self, agent_id, start_day, start_timestep, quarantine_type, end_day=None, quarantine_days=None,
+                            agent=None):
+        """epidemiology.py:568-625 -> (scheduled, quarantine_days)"""
+        import random
+        from .epidemiologyclasses import QuarantineType
+        ep = self.epidemiologyparams
+        if not self.dyn_params.quarantine_enabled:
+            return False, quarantine_days
+        u = random.random()
+        if quarantine_type == QuarantineType.Symptomatic:
+            comply = u < ep["quarantine_after_symptoms_probability"]
+        else:
+            comply = not (u < ep["ignore_quarantine_rules_probability"])
+        if not comply:
+            return False, quarantine_days
+        record = agent if agent is not None else self.agents_epi[agent_id]
+        if quarantine_days is None:
+            quarantine_days = record["quarantine_days"]
+        if end_day is None:
+            d_pos, d_contact, d_secondary = ep["quarantine_duration_parameters"][:3]
+            if quarantine_type in (QuarantineType.Symptomatic, QuarantineType.Positive):
+                end_day = start_day + d_pos
+            elif quarantine_type == QuarantineType.PositiveContact:
+                start_day += self.contact_tracing_positive_delay_days
+                end_day = start_day + d_contact
+            elif quarantine_type == QuarantineType.SecondaryContact:
+                start_day += self.contact_tracing_secondary_delay_days
+                end_day = start_day + d_secondary
+        if quarantine_days is not None and len(quarantine_days) > 0 and start_day >= quarantine_days[0]:
+            return False, quarantine_days                               # never moved to the same or a later start (:606-611)
+        quarantine_days = [start_day, start_timestep, end_day]
+        record["quarantine_days"] = quarantine_days
+        return True, quarantine_days
+
+    def schedule_hospitalisation(self, agent, agent_id, hospitalisation_days):
+        """epidemiology.py:647-660: an existing window keeps its start day and takes the new end"""
+        cur = agent["hospitalisation_days"]
+        if cur is not None and len(cur) > 0:
+            agent["hospitalisation_days"] = [cur[0], hospitalisation_days[1], hospitalisation_days[2]]
+        else:
+            agent["hospitalisation_days"] = hospitalisation_days
+        # (returns None, like the reference's)
+
     def update_quarantine(self, agent, new_start_day, new_start_ts, new_end_day, new_end_ts):
         """epidemiology.py:627-630: overwrite the agent's quarantine record [start day, timestep, end day]"""
         agent["quarantine_days"] = [new_start_day, new_start_ts, new_end_day]

@@ -218,3 +218,4 @@ def test_schedule_vaccinations_dropin_replays_reference_calls():
                            42 <= agents_epi[a]["vaccination_days"][-1][1] <= 120 for a in upd)
             for a in upd:                                       # the next day's itinerary stage administers the doses
                 vu.agents_vaccination_doses.setdefault(a, []).append(row["day"] + 1)
+

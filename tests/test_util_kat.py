@@ -122,3 +122,26 @@ def test_initialize_agent_states_kat():
         assert [int(st[i]) for i in range(n)] == [int(x) for x in K["c%d_out" % k]]
         k += 1
     assert k == 4
+
+
+def test_schedule_helpers_match_reference_kat():
+    """Epidemiology.schedule_test / schedule_quarantine / schedule_hospitalisation (epidemiology.py:502-660): the host
+    mirrors return the same values, leave the same records and consume the same draws as the reference on 480 seeded
+    calls each (tests/golden/make_schedule_kat.py -> schedule_kat.json).  CPU-only: these are host-side helpers."""
+    import json
+    import os
+    from types import SimpleNamespace
+    from mtdcovabm_b200 import epidemiology as E, params as prm
+    from mtdcovabm_b200.epidemiologyclasses import QuarantineType
+    from tests.golden import make_schedule_kat as MK
+
+    def make(variant, dp):
+        agents_epi = {}
+        vu = SimpleNamespace(agents_vaccination_doses={}, agents_seir_state={}, agents_infection_type={}, agents_infection_severity={})
+        return E.Epidemiology(prm.load_json(variant), 100, 0, 1.0, None, agents_epi, vu, {}, {}, {}, dp), agents_epi
+
+    want = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "schedule_kat.json")))
+    got = MK.battery(make, QuarantineType)
+    assert len(got) == len(want) and sum(1 for k in want if k[0] == "test" and k[1][0]) > 50
+    for g, w in zip(got, want):
+        assert g == w
