@@ -312,6 +312,9 @@ int mtd_export_wait(mtd_handle h, int64_t ticket);
 enum { MTD_STAGE_H2D = 0, MTD_STAGE_K0 = 1, MTD_STAGE_K1 = 2, MTD_STAGE_K2 = 3, MTD_STAGE_K3_EVAL = 4,
        MTD_STAGE_K3_APPLY = 5, MTD_STAGE_K4 = 6, MTD_N_STAGES = 7 };
 int mtd_set_profiling(mtd_handle h, int on);
+/* test hook: out[i] = CUDA's fp64 log(x[i]) (HOST pointers), the function K1 uses for its two per-cell logarithms
+ * log(avg_ts), log(avg_pc) (contactnetwork.py:240-245 uses glibc's through math.log); tests/test_device_log.py */
+int mtd_debug_log(mtd_handle h, int64_t n, const double *x, double *out);
 int mtd_get_stage_ms(mtd_handle h, float ms[MTD_N_STAGES], int64_t launches[MTD_N_STAGES]);
 
 #ifdef __cplusplus

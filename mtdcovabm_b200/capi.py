@@ -27,7 +27,7 @@ EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mt
            "mtd_set_profiling", "mtd_get_stage_ms", "mtd_set_export", "mtd_prefetch_intervals",
            "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced",
            "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts", "mtd_seed_exposures", "mtd_set_intervention_mask", "mtd_set_k0_overlap",
-           "mtd_process_test_results", "mtd_set_k6_tape", "mtd_contact_tracing_scan", "mtd_contact_tracing_finish", "mtd_enable_vaccination", "mtd_schedule_vaccinations", "mtd_set_vaccination",
+           "mtd_process_test_results", "mtd_debug_log", "mtd_set_k6_tape", "mtd_contact_tracing_scan", "mtd_contact_tracing_finish", "mtd_enable_vaccination", "mtd_schedule_vaccinations", "mtd_set_vaccination",
            "mtd_get_vaccination", "mtd_build_intervals", "mtd_get_intervals"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
 
@@ -394,6 +394,13 @@ class Handle:
     # ---- measurement hooks
     def set_profiling(self, on=True):
         self._ck(self.lib.mtd_set_profiling(self.h, int(on)), "mtd_set_profiling")
+
+    def debug_log(self, x):
+        """CUDA's fp64 log of every element (test hook)"""
+        x = np.ascontiguousarray(x, np.float64)
+        out = np.empty_like(x)
+        self._ck(self.lib.mtd_debug_log(self.h, C.c_int64(len(x)), _ptr(x), _ptr(out)), "mtd_debug_log")
+        return out
 
     def stage_ms(self):
         """-> ({stage: mean ms over its executions since the previous call}, {stage: kernels launched since then})"""

@@ -196,6 +196,29 @@ static int touch_state_on_main(mtd_handle h)
 
 extern "C" int mtd_abi_version(void) { return 3; }
 
+__global__ void debug_log_kernel(int64_t n, const double *x, double *out)
+{
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = log(x[i]);
+}
+
+// test hook (tests/test_device_log.py): CUDA's fp64 log on the caller's values, as K1 computes log(avg_ts), log(avg_pc)
+extern "C" int mtd_debug_log(mtd_handle h, int64_t n, const double *x, double *out)
+{
+    if (!h || n < 0 || (n && (!x || !out))) return MTD_E_ARG;
+    CK(cudaSetDevice(h->cfg.device));
+    if (n == 0) return MTD_OK;
+    double *dx = nullptr, *dout = nullptr;
+    CK(cudaMalloc((void **)&dx, 8 * (size_t)n)); 
+    if (cudaMalloc((void **)&dout, 8 * (size_t)n) != cudaSuccess) { cudaFree(dx); h->err = "mtd_debug_log: cudaMalloc"; return MTD_E_CUDA; }
+    cudaMemcpyAsync(dx, x, 8 * (size_t)n, cudaMemcpyHostToDevice, h->stream);
+    debug_log_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(n, dx, dout);
+    cudaMemcpyAsync(out, dout, 8 * (size_t)n, cudaMemcpyDeviceToHost, h->stream);
+    cudaError_t e = cudaStreamSynchronize(h->stream);
+    cudaFree(dx); cudaFree(dout);
+    if (e != cudaSuccess) { h->err = std::string("mtd_debug_log: ") + cudaGetErrorString(e); return MTD_E_CUDA; }
+    return MTD_OK;
+}
+
 extern "C" const char *mtd_last_error(mtd_handle h) { return h ? h->err.c_str() : "null handle"; }
 
 static int create_impl(mtd_handle h)

@@ -70,7 +70,7 @@ __global__ void k3_eval_kernel(DevCtx c)
         else if (sct == SCT_WORKPLACE) base = (cell == c.res_cellid[ex]) ? P->p_workplace : P->p_community;
         else if (sct == SCT_SCHOOL) base = P->p_school;
         else base = P->p_community;
-        double lg = log((double)dur);
+        double lg = (dur >= 0 && dur < MTD_LOGTAB_N) ? c.logtab[dur] : log((double)dur);   // math.log of an integer: glibc table
         double mult = lg > 1.0 ? lg : 1.0;                                              // max(1, math.log(duration))
         double imm, asym;
         vacc_multipliers(P, c.last_dose_day[ex], c.day.day, imm, asym);

@@ -276,6 +276,19 @@ static int cmp_desc_deg_id(const void *x, const void *y, void *arg)
     return W->ids[i] > W->ids[j] ? -1 : (W->ids[i] < W->ids[j] ? 1 : 0);
 }
 
+/* Test knob (tests/test_device_log.py): the two per-cell logarithms log(avg_ts), log(avg_pc) moved by this many ulps.  The
+ * CUDA path computes them with CUDA's log (<= 1 ulp), the reference with glibc's: a degree can only differ if it sits
+ * within such a perturbation of a rounding boundary, which the test shows does not happen on any recorded cell. */
+int mtdo_log_ulp_shift = 0;
+static double log_avg(double x)
+{
+    double l = log(x);
+    for (int i = 0; i < mtdo_log_ulp_shift; i++) l = nextafter(l, INFINITY);
+    for (int i = 0; i > mtdo_log_ulp_shift; i--) l = nextafter(l, -INFINITY);
+    return l;
+}
+void mtdo_log_array(int64_t n, const double *x, double *out) { for (int64_t i = 0; i < n; i++) out[i] = log(x[i]); }
+
 /* One cell.  iv = emission indices of the cell's intervals in list order.  Appends rows; returns number appended,
  * or -1 on output overflow. */
 static int64_t run_cell(const mtdo_params *P, const mtdo_dayctx *D, cellws *W, int32_t cellid, int64_t m,
@@ -353,8 +366,8 @@ static int64_t run_cell(const mtdo_params *P, const mtdo_dayctx *D, cellws *W, i
             if (ab < 0) ab += 16;                                        /* numpy negative index */
             double cmv = P->cm[ab][act];
             double tsm = 1.0, pcm = 1.0;
-            if ((double)W->ts[a] != avg_ts && avg_ts > 1) tsm = log((double)W->ts[a]) / log(avg_ts);   /* math.log(x, base) */
-            if ((double)W->pc[a] != avg_pc && avg_pc > 1) pcm = log((double)W->pc[a]) / log(avg_pc);
+            if ((double)W->ts[a] != avg_ts && avg_ts > 1) tsm = log((double)W->ts[a]) / log_avg(avg_ts);   /* math.log(x, base) */
+            if ((double)W->pc[a] != avg_pc && avg_pc > 1) pcm = log((double)W->pc[a]) / log_avg(avg_pc);
             double soc = A->soc_rate[W->ids[a]];
             W->degf[a] = cmv * tsm * pcm * soc * one_minus_mhd;
         }

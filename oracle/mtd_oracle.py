@@ -250,6 +250,18 @@ def vaccination_day(day, n_locals, last_dose_day, vacc_day):
     L.mtdo_vaccination_day(C.c_int32(day), C.c_int64(n_locals), _p(last_dose_day), _p(vacc_day))
 
 
+def set_log_ulp_shift(k):
+    """test knob: move the oracle's two per-cell logarithms by k ulps (0 = glibc's value)"""
+    C.c_int.in_dll(lib(), "mtdo_log_ulp_shift").value = int(k)
+
+
+def glibc_log(x):
+    x = np.ascontiguousarray(x, np.float64)
+    out = np.empty_like(x)
+    lib().mtdo_log_array(C.c_int64(len(x)), _p(x), _p(out))
+    return out
+
+
 def process_test_results(params, ctx, agents: AgentState, epi_present=None, replay_agents=None, replay_u=None):
     """itinerary.py:2283-2528 (record bookkeeping) over all agents -> ids added to contact_tracing_agent_ids (ascending).
     Replay mode: replay_agents ascending ids, replay_u [n, 2] the result draw and the quarantine draw of each."""
