@@ -37,6 +37,34 @@ def cell_owner(cell: torch.Tensor, world: int) -> torch.Tensor:
     return ((h >> 7) % world).to(cell.dtype)
 
 
+def balanced_cell_owner(weight: np.ndarray, world: int, exact: int = 200_000) -> np.ndarray:
+    """Static owner map cell -> rank that balances the expected K1 cost of the ranks (the reference
+    balances its partitions the same way, greedily on a min-heap, with the member count as the weight, util.py:675-707).
+    weight[c] = expected cost of cell c (sum over the day streams of m^2 + 16 m, m = intervals of the cell that day).
+    Longest-processing-time-first: the `exact` heaviest cells go, heaviest first, to the currently lightest rank (heap);
+    the long tail of light cells is dealt out in snake order of weight.  Deterministic; every rank computes the same map."""
+    import heapq
+    C = len(weight)
+    owner = np.zeros(C, np.int32)
+    if world == 1:
+        return owner
+    order = np.argsort(-weight, kind="stable")
+    k = int(min(exact, C))
+    heap = [(0.0, r) for r in range(world)]
+    w = weight.astype(np.float64)
+    for c in order[:k]:
+        load, r = heapq.heappop(heap)
+        owner[c] = r
+        heapq.heappush(heap, (load + w[c], r))
+    if k < C:
+        rest = order[k:]
+        pos = np.arange(len(rest)) % (2 * world)
+        snake = np.where(pos < world, pos, 2 * world - 1 - pos)
+        by_load = np.array([r for _, r in sorted(heap)], np.int32)      # lightest rank first
+        owner[rest] = by_load[snake]
+    return owner
+
+
 class SynthPopulation:
     """`reps` replicas of the bank population on `device` (all ranks build the identical population)."""
 
@@ -80,6 +108,23 @@ class SynthPopulation:
         self.sched[:, 0] = torch.where(inf, (rec_day << 16) | (T_ASYMP_REC << 8) | 60, 0)
         self.sched_cnt = inf.to(torch.uint8)
 
+    def owner_map(self, world):
+        """cell -> rank, balanced on the cells' expected cost over the bank's day streams (balanced_cell_owner);
+        MTD_OWNER=hash switches back to the multiplicative hash"""
+        key = ("owner", world)
+        if key not in self.__dict__:
+            if os.environ.get("MTD_OWNER", "balanced") == "hash":
+                self.__dict__[key] = cell_owner(torch.arange(self.n_cells, device=self.device, dtype=torch.int32), world)
+            else:
+                b = self.bank
+                w1 = np.zeros(self.C1, np.float64)
+                for k in range(self.n_days):
+                    m = np.bincount(b["d%d_iv_cell" % k].astype(np.int64), minlength=self.C1).astype(np.float64)
+                    w1 += m * m + 16.0 * m
+                owner = balanced_cell_owner(np.tile(w1, self.reps), world)
+                self.__dict__[key] = torch.from_numpy(owner).to(self.device)
+        return self.__dict__[key]
+
     def stream(self, k, rank=0, world=1):
         """bank day k tiled -> dict(iv_agent, iv_cell, iv_start, iv_end, iv_order, n_total) of this rank's shard"""
         b, dev = self.bank, self.device
@@ -102,7 +147,7 @@ class SynthPopulation:
         M = agent.numel()
         order = None
         if world > 1:
-            sel = cell_owner(cell, world) == rank
+            sel = self.owner_map(world)[cell.long()] == rank
             order = torch.nonzero(sel).flatten().to(torch.int32)   # read as uint32 by the C ABI
             agent, cell, start, end = agent[sel], cell[sel], start[sel], end[sel]
         return dict(iv_agent=agent.contiguous(), iv_cell=cell.contiguous(), iv_start=start.contiguous(),
