@@ -14,6 +14,8 @@ int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_coun
 int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t aux2, cudaEvent_t ev_fork, cudaEvent_t ev_join,
               cudaEvent_t ev_join2, int sm_count, unsigned char *big_ws, int mm_big);
 int64_t k1_big_ws_bytes(int mm_big);
+int64_t k1_legacy_bits_words(int sm_count);
+bool k1_use_legacy();
 int launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count);
 int launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap, cudaStream_t st);
 int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, bool win_clean, cudaStream_t st, int sm_count);
@@ -271,6 +273,7 @@ static int create_impl(mtd_handle h)
     c.max_cell_m = (int32_t)std::min<int64_t>(MTD_MAX_CELL_INTERVALS, M);
     h->k1_mm_big = c.max_cell_m > 1024 ? ((c.max_cell_m + 31) & ~31) : 0;
     if (h->k1_mm_big) DA(h->k1_big_ws, k1_big_ws_bytes(h->k1_mm_big));
+    if (k1_use_legacy()) { c.k1_bits_words = k1_legacy_bits_words(h->sm_count); DA(c.k1_bits, c.k1_bits_words); }
     DA(c.win, N); DA(c.succ, c.cap_rows);
     c.row_p = nullptr;
     DA(h->delta_own, (c.cap_expo + 1) * MTD_DELTA_WORDS);

@@ -122,6 +122,8 @@ struct DevCtx {
     RowRec *scratch_rows;      // [cap_scratch_rows]
     uint32_t *rows12;          // [3 * cap_rows] packed 12-byte rows of the day for the async export (NULL = off)
     int32_t *k1_bins;          // [2][3][32] histogram and cursors of the small-class size sort (K1)
+    uint32_t *k1_bits;         // [k1_bits_words] per-warp adjacency bit matrices of the legacy warp-per-cell K1 (k1_legacy.cu)
+    int64_t k1_bits_words;
     int32_t max_cell_m;        // largest cell (intervals) this handle takes: min(MTD_MAX_CELL_INTERVALS, max_intervals)
     RowRec *rows;              // [cap_rows] dense
     // K3

@@ -779,7 +779,7 @@ int64_t k1_big_ws_bytes(int mm_big) { const Lay L(mm_big); return (int64_t)K1_BI
 
 // size classes 3..8 (33-64, -128, -192, -320, -1024, above): see size_class() in k0_csr.cu
 int launch_k1_blocks(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_count, unsigned char *big_ws, int mm_big,
-                     int lpt_region_a, int lpt_region_b)
+                     int lpt_region_a, int lpt_region_b, bool only_big)
 {
     int n = 0;
     // the classes with the longest cells first; two streams so that the tail of one class overlaps the next
@@ -788,6 +788,7 @@ int launch_k1_blocks(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_c
         k1_block_kernel<1024, K1_BIG_CW, 1, true><<<K1_BIG_BLOCKS, K1_BIG_CW * 32, 0, sa>>>(c, 8, 8, big_ws, (int64_t)al16(L.bytes), mm_big);
         n++;
     }
+    if (only_big) return n;
     n += launch_block_class<1024, 8, 1>(c, 7, sa, sm_count, 0);
     n += launch_block_class<320, 4, 6>(c, 6, sa, sm_count, lpt_region_a);
     n += launch_block_class<192, 4, 8>(c, 5, sb, sm_count, lpt_region_b);

@@ -460,7 +460,16 @@ int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int li
 }  // namespace
 
 int launch_k1_blocks(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_count, unsigned char *big_ws, int mm_big,
-                     int lpt_region_a, int lpt_region_b);
+                     int lpt_region_a, int lpt_region_b, bool only_big);
+int launch_k1_legacy(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_count);
+
+// MTD_K1_IMPL = block (block per cell, k1_block.cu) | legacy (round 1's warp per cell, k1_legacy.cu; cells above 1024
+// intervals still go through the block kernel's global-workspace class).  Both produce the same rows, bit for bit.
+bool k1_use_legacy()
+{
+    static const int v = [] { const char *e = getenv("MTD_K1_IMPL"); return (e && e[0] == 'b') ? 0 : 1; }();
+    return v != 0;
+}
 
 static int env_int(const char *name, int dflt)
 {
@@ -483,7 +492,11 @@ int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t a
         cudaStreamWaitEvent(aux2, ev_fork, 0);
         sl = aux; sl2 = aux2;
     }
-    int n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, (lpt & 1) ? MTD_NUM_CLASSES : 0, (lpt & 2) ? MTD_NUM_CLASSES + 1 : 0);
+    int n;
+    if (k1_use_legacy() && c.k1_bits) {
+        n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, 0, 0, true);
+        n += launch_k1_legacy(c, sl, sl2, sm_count);
+    } else n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, (lpt & 1) ? MTD_NUM_CLASSES : 0, (lpt & 2) ? MTD_NUM_CLASSES + 1 : 0, false);
     const int sorted_small = (lpt & 4) ? MTD_NUM_CLASSES + 2 : 0;      // regions +2, +3, +4 = classes 0, 1, 2 by size
     if (sorted_small) {
         cudaMemsetAsync(c.k1_bins, 0, sizeof(int32_t) * 2 * 96, st);

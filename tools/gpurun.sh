@@ -14,8 +14,13 @@ set -u
 R=${1:-quick}; T=${2:-$R}; O=gpurun_out; mkdir -p $O
 case $R in
 quick)
-  timeout 1500 python -m pytest tests/test_edge_cases.py tests/test_gpu_parity.py tests/test_dropin_api.py -m gpu -x -q > $O/${T}_tests.log 2>&1; echo "tests=$?"; tail -n 15 $O/${T}_tests.log
-  timeout 600 python bench.py --steps 14 --warmup 7 --no-cpu-baseline > $O/${T}_bench.json 2> $O/${T}_bench.err; echo "bench=$?"; tail -n 3 $O/${T}_bench.err; cat $O/${T}_bench.json
+  # both K1 implementations (MTD_K1_IMPL=block | legacy): parity tests, then a short bench each
+  for impl in block legacy; do
+    MTD_K1_IMPL=$impl timeout 1500 python -m pytest tests/test_edge_cases.py tests/test_gpu_parity.py tests/test_dropin_api.py tests/test_k6_kat.py -m gpu -q > $O/${T}_tests_$impl.log 2>&1; echo "tests[$impl]=$?"; tail -n 12 $O/${T}_tests_$impl.log
+    MTD_K1_IMPL=$impl timeout 600 python bench.py --steps 14 --warmup 7 --no-cpu-baseline --no-e2e > $O/${T}_bench_$impl.json 2> $O/${T}_bench_$impl.err; echo "bench[$impl]=$?"; tail -n 3 $O/${T}_bench_$impl.err
+    python -c "
+import json; j=json.load(open('$O/${T}_bench_$impl.json')); r=j['roofline']; print('$impl', j['ms_per_step'], r['stage_ms'], r['stage_ms_serial'])"
+  done
   ;;
 tests)
   python -c "import __graft_entry__ as g; g.smoke()" > $O/${T}_smoke.log 2>&1; echo "smoke=$?"; tail -n 2 $O/${T}_smoke.log
