@@ -477,6 +477,20 @@ def run_b200(args):
         barrier()
         s_ms = allmax((time.perf_counter() - t0) * 1e3)
         ser_pairs = allsum(sum(pairs[st_ % nb][0] for st_ in range(args.warmup + args.steps + 2, args.warmup + args.steps + 2 + ser_steps)))
+        # the same pipelined loop for a caller that keeps the contact rows in HBM (contact tracing on the device):
+        # counts, occupancy and exposed ids only
+        eng.enable_host_pipeline(cap_rows, export_rows=False)
+        d2h_keep = d2h
+        run(args.warmup + args.steps + 2 + ser_steps, 2, False)
+        barrier()
+        t0 = time.perf_counter()
+        run(args.warmup + args.steps + 4 + ser_steps, ser_steps, False)
+        barrier()
+        n_ms = allmax((time.perf_counter() - t0) * 1e3)
+        d2h = d2h_keep
+        nr_pairs = allsum(sum(pairs[st_ % nb][0] for st_ in range(args.warmup + args.steps + 4 + ser_steps, args.warmup + args.steps + 4 + 2 * ser_steps)))
+        e2e["rows_on_device"] = {"value": nr_pairs / (n_ms * 1e-3), "unit": UNIT, "ms_per_step": n_ms / ser_steps, "steps": ser_steps,
+                                 "mode": "pipelined, contact rows stay in HBM for device-side contact tracing: intervals in; counts, occupancy, exposed ids out"}
         e2e["serial"] = {"value": ser_pairs / (s_ms * 1e-3), "unit": UNIT, "ms_per_step": s_ms / ser_steps, "steps": ser_steps,
                          "mode": "dependency-honouring: upload, compute and export of day d complete before day d+1 is submitted"}
 

@@ -72,7 +72,9 @@ class DayEngine:
         # high priority: in the day pipeline the short K2/K3 kernels of the current day (this stream) get the SM slots that
         # free up before the next persistent K1 kernel of the coming day does (MTD_MAIN_PRIO=0: default priority)
         self.stream = torch.cuda.Stream(self.device, priority=0 if os.environ.get("MTD_MAIN_PRIO") == "0" else -1)
-        self.delta_cap = int(delta_cap) if delta_cap else max(4096, n_agents // 64)
+        # exposure records of one day (80 B each): sized for an epidemic peak of ~6 % of all ids in one day; only the
+        # records actually produced are exchanged, so a generous capacity costs memory, not bandwidth
+        self.delta_cap = int(delta_cap) if delta_cap else max(4096, n_agents // 16)
         self.h = capi.Handle(n_agents, n_cells, max_intervals, device=self.device.index or 0,
                              stream=self.stream.cuda_stream, max_rows=max_rows, max_exposures=self.delta_cap)
         self.h.set_params(params)
@@ -134,14 +136,17 @@ class DayEngine:
             self._transmission(d)
 
     # ---- host boundary, pipelined: pinned host buffers in, pinned host buffers out, copies beside the kernels
-    def enable_host_pipeline(self, cap_rows, cap_exposed=None):
-        """two sets of pinned result buffers (day d's results stay valid until day d+2 is submitted)"""
+    def enable_host_pipeline(self, cap_rows, cap_exposed=None, export_rows=True):
+        """two sets of pinned result buffers (day d's results stay valid until day d+2 is submitted).  export_rows=False:
+        the day's contact rows stay in HBM (a caller that runs contact tracing on the device, mtd_contact_tracing, never
+        needs them on the host) and only the counts, the occupancy and the exposed ids are exported."""
         import numpy as np
         cap_exposed = int(cap_exposed or self.delta_cap)
         self.h.set_export(True)
         self._res = []
+        self._export_rows = bool(export_rows)
         for _ in range(2):
-            rows = torch.empty((int(cap_rows), 3), dtype=torch.int32).pin_memory()
+            rows = torch.empty((int(cap_rows) if export_rows else 1, 3), dtype=torch.int32).pin_memory()
             kv = torch.empty((cap_exposed, 2), dtype=torch.int64).pin_memory()
             res = torch.zeros(capi.RESULT_WORDS, dtype=torch.int64).pin_memory()
             self._res.append((rows, kv, res))
@@ -171,8 +176,9 @@ class DayEngine:
             self._transmission(d)
             rows, kv, res = self._res[self._k]
             self._k ^= 1
-            ticket = h.export_day_async(rows, self._cap_rows, kv, self._cap_exposed, res, mem=capi.MEM_HOST)
-        return HostDayResult(h, ticket, rows, kv, res)
+            ticket = h.export_day_async(rows if self._export_rows else None, self._cap_rows if self._export_rows else 0, kv,
+                                        self._cap_exposed, res, mem=capi.MEM_HOST)
+        return HostDayResult(h, ticket, rows if self._export_rows else None, kv, res)
 
     # ---- checkpoint / resume (the reference has none; the whole dynamic state of the path is a
     # handful of dense per-agent arrays, so a checkpoint is their copy plus the day and the Philox seed)
@@ -252,6 +258,8 @@ class HostDayResult:
     def rows(self):
         """structured view (capi.ROW12) of the contact rows, in the reference's row order"""
         n = self.n_rows
+        if self._rows is None:
+            raise RuntimeError("this host pipeline keeps the contact rows on the device (export_rows=False)")
         return self._rows.numpy()[:n].view(capi.ROW12).reshape(n)
 
     def exposed(self, reference_order=True):
@@ -264,4 +272,4 @@ class HostDayResult:
 
     @property
     def nbytes(self):
-        return 12 * self.n_rows + 16 * self.n_exposed + 8 * capi.RESULT_WORDS
+        return (12 * self.n_rows if self._rows is not None else 0) + 16 * self.n_exposed + 8 * capi.RESULT_WORDS

@@ -9,6 +9,7 @@
 #   launches  ncu launch list (gpu__time_duration) of a short bench
 #   ncu_k1    ncu --set full of the K1 kernels of one day (+ metrics csv over the seven day streams)
 #   perday    per-day-stream stage times (tools/k1_per_day.py)
+#   dictapi   cost of the reference-shaped dict API on the golden days (tools/time_dict_api.py)
 #   configs   the BASELINE.json configuration shapes through the whole day loop (tools/run_config.py)
 set -u
 R=${1:-quick}; T=${2:-$R}; O=gpurun_out; mkdir -p $O
@@ -51,6 +52,9 @@ ncu_k1)
   ;;
 perday)
   python tools/k1_per_day.py 2>&1 | tail -n 16 | tee $O/${T}_perday.txt
+  ;;
+dictapi)
+  timeout 900 python tools/time_dict_api.py > $O/${T}_dict_api_cost.json 2> $O/${T}_dict_api.err; echo "dictapi=$?"; tail -n 25 $O/${T}_dict_api.err
   ;;
 configs)
   timeout 1500 python tools/run_config.py 2>&1 | tee $O/${T}_runs.txt | tail -n 30
