@@ -35,7 +35,8 @@ struct DevCounters {
     int sched_overflow;
     int tape_miss;
     int class_cells[MTD_NUM_CLASSES];
-    int class_cursor[MTD_NUM_CLASSES];   // work-fetch cursors of the persistent K1 warps
+    int class_cursor[MTD_NUM_CLASSES];   // work-fetch cursors of the K1 blocks
+    int class_started[MTD_NUM_CLASSES];  // K1 blocks of the class that have started (slot turnover, k1_block.cu)
     int error;
     int pad;
 };

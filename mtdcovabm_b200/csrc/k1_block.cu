@@ -20,6 +20,8 @@
 
 namespace {
 
+#define K1_CELLS_PER_BLOCK 2    // cells a block takes before it gives its SM slot back (while blocks of its grid still wait)
+#define K1_GRID_ROUNDS 8        // grid = resident blocks x this
 #define K1_TS_ROWS 160          // timestep domain of the S/E tables (the small-cell kernel's 5 x 32-bit masks)
 
 __host__ __device__ constexpr int pow2_ge(int x) { int p = 1; while (p < x) p <<= 1; return p; }
@@ -738,13 +740,26 @@ __global__ void __launch_bounds__(CW * 32, MINB) k1_block_kernel(DevCtx g, int c
     if (CW > 1) __syncthreads(); else __syncwarp();
     uint32_t mbar_phase = 0;
     unsigned long long acc_pairs = 0, acc_pot = 0, acc_inc = 0;
+    // Slot turnover: the grid holds several times the resident blocks; a block leaves after K1_CELLS_PER_BLOCK cells as long
+    // as blocks of its grid are still waiting to start, so the SM slot it held goes to whatever the hardware schedules
+    // next -- the short high-priority kernels of the day's other stages (K2/K3, the state chain) included -- instead of
+    // staying with one persistent block until the class is exhausted.  Once every block of the grid has started, the
+    // blocks that are left drain the class.
+    if (threadIdx.x == 0) atomicAdd(&g.ctr->class_started[cls], 1);
+    int done = 0;
     while (true) {
-        if (threadIdx.x == 0) bs.w = atomicAdd(&g.ctr->class_cursor[cls], 1);
+        if (threadIdx.x == 0) {
+            int w = -1;
+            if (done < K1_CELLS_PER_BLOCK || *(volatile int *)&g.ctr->class_started[cls] >= (int)gridDim.x)
+                w = atomicAdd(&g.ctr->class_cursor[cls], 1);
+            bs.w = w;
+        }
         bsync<CW>();
         const int w = bs.w;
         bsync<CW>();                                        // bs.w is reused by the cell
-        if (w >= total) break;
+        if (w < 0 || w >= total) break;
         process_cell<CW, GWS>(g, L, sm, bs, mbar_phase, list[w], w + 1 < total ? list[w + 1] : -1, acc_pairs, acc_pot, acc_inc);
+        done++;
     }
     if (threadIdx.x == 0 && (acc_pairs | acc_pot | acc_inc)) {
         atomicAdd(&g.ctr->pairs_evaluated, acc_pairs);
@@ -765,7 +780,7 @@ int launch_block_class(const DevCtx &c, int cls, cudaStream_t st, int sm_count, 
     }
     int n = 0;
     if (lpt_region) { k1_lpt_kernel<<<1, 1024, 0, st>>>(c, cls, lpt_region, MM, 512); n++; }
-    k1_block_kernel<MM, CW, MINB, false><<<sm_count * per_sm, CW * 32, L.bytes, st>>>(c, cls, lpt_region ? lpt_region : cls, nullptr, 0, MM);
+    k1_block_kernel<MM, CW, MINB, false><<<sm_count * per_sm * K1_GRID_ROUNDS, CW * 32, L.bytes, st>>>(c, cls, lpt_region ? lpt_region : cls, nullptr, 0, MM);
     return n + 1;
 }
 
