@@ -16,6 +16,7 @@ int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t a
 int64_t k1_big_ws_bytes(int mm_big);
 int64_t k1_legacy_bits_words(int sm_count);
 bool k1_use_legacy();
+bool k1_use_split();
 int launch_k2_compact(const DevCtx &c, cudaStream_t st, int sm_count);
 int launch_export_rows(const DevCtx &c, int32_t *rows5, int32_t *row_dur, int32_t *row_cell, int64_t cap, cudaStream_t st);
 int launch_k3_eval(const DevCtx &c, int32_t *dbuf, int64_t cap, bool win_clean, cudaStream_t st, int sm_count);
@@ -48,6 +49,8 @@ struct mtd_handle_s {
     bool own_stream = false;
     cudaStream_t aux_stream = nullptr, aux2_stream = nullptr;   // large-cell K1 kernels run beside the small-cell ones
     unsigned char *k1_big_ws = nullptr; int k1_mm_big = 0;      // global workspace of the cells above 1024 intervals
+    unsigned char *k1_rec[2] = {};                              // split K1: per-cell chain records, by day parity (K2 of day d reads
+                                                                //   them while the K1 of day d+1 already writes)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr;
     // The state chain -- apply of day d's exposure records (after the peer exchange), then K4 of day d+1 -- runs on its
     // own stream beside K0/K1/K2 of day d+1, which read no per-agent state; K3 of day d+1 joins the two.
@@ -265,7 +268,7 @@ static int create_impl(mtd_handle h)
     DA(c.slot_off, S + 2); DA(c.slot_rowoff, S + 2); DA(c.slot_rowbound, S + 1);
     DA(c.slot_nrows, S + 1); DA(c.slot_denseoff, S + 2);
     c.class_stride = S + 1;
-    DA(c.class_list, (MTD_NUM_CLASSES + 5) * (S + 1));      // + five regions: every class but the last again, sorted by size
+    DA(c.class_list, (MTD_NUM_CLASSES + 7) * (S + 1));      // + five regions: every class but the last again, sorted by size
     DA(c.k1_bins, 2 * 3 * 32);
     DA(c.csr, M);
     DA(c.scratch_rows, c.cap_scratch_rows); DA(c.rows, c.cap_rows);
@@ -274,6 +277,7 @@ static int create_impl(mtd_handle h)
     h->k1_mm_big = c.max_cell_m > 1024 ? ((c.max_cell_m + 31) & ~31) : 0;
     if (h->k1_mm_big) DA(h->k1_big_ws, k1_big_ws_bytes(h->k1_mm_big));
     if (k1_use_legacy()) { c.k1_bits_words = k1_legacy_bits_words(h->sm_count); DA(c.k1_bits, c.k1_bits_words); }
+    if (k1_use_split()) { c.k1_split = 1; DA(h->k1_rec[0], 64 * (size_t)M + 64); DA(h->k1_rec[1], 64 * (size_t)M + 64); c.k1_rec = h->k1_rec[0]; }
     DA(c.win, N); DA(c.succ, c.cap_rows);
     c.row_p = nullptr;
     DA(h->delta_own, (c.cap_expo + 1) * MTD_DELTA_WORDS);
@@ -302,7 +306,7 @@ static int create_impl(mtd_handle h)
         DA(b.slot_cell, S + 1); DA(b.slot_m, S + 1); DA(b.slot_first, S + 1); DA(b.slot_act, S + 1);
         DA(b.slot_off, S + 2); DA(b.slot_rowoff, S + 2); DA(b.slot_rowbound, S + 1);
         DA(b.slot_nrows, S + 1); DA(b.slot_denseoff, S + 2);
-        DA(b.class_list, (MTD_NUM_CLASSES + 5) * (S + 1));
+        DA(b.class_list, (MTD_NUM_CLASSES + 7) * (S + 1));
         DA(b.csr, M); DA(b.ctr, 1); DA(b.scratch_rows, c.cap_scratch_rows);
         CK(cudaMemsetAsync(b.ctr, 0, sizeof(DevCounters), h->stream));
         int lo = 0, hi = 0;
@@ -546,6 +550,7 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
         c.slot_nrows = k.slot_nrows; c.slot_denseoff = k.slot_denseoff; c.class_list = k.class_list; c.csr = k.csr; c.ctr = k.ctr;
         c.scratch_rows = k.scratch_rows;
         c.n_succ_pub = h->n_succ_buf + kp;
+        if (c.k1_split) c.k1_rec = h->k1_rec[kp];
     }
     const bool pipe = h->k0_pipe && !h->mask_on && M > 0 && ((mem == MTD_MEM_STAGED && h->k0_pipe_staged) || (mem == MTD_MEM_DEVICE && h->k0_device_ready));
     cudaStream_t ks = pipe ? h->k0_stream : h->stream;

@@ -265,7 +265,8 @@ struct BlockShared {
 // GWS: the working set lives in a global workspace (cells above the shared-memory classes); plain loads instead of TMA
 template <int CW, bool GWS>
 __device__ void process_cell(const DevCtx &g, const Lay &L, unsigned char *sm, BlockShared &bs, uint32_t &mbar_phase, int slot,
-                             int next_slot, unsigned long long &acc_pairs, unsigned long long &acc_pot, unsigned long long &acc_inc)
+                             int next_slot, unsigned long long &acc_pairs, unsigned long long &acc_pot, unsigned long long &acc_inc,
+                             bool skip_chain, bool split)
 {
     constexpr int T = CW * 32;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
@@ -517,7 +518,10 @@ __device__ void process_cell(const DevCtx &g, const Lay &L, unsigned char *sm, B
     pc_sum = block_sum<CW>(pc_sum, bs.red, lane, wid);
     if (tid == 0) acc_pot += (unsigned)pc_sum / 2;
     if (pc_sum == 0) {                                    // contactnetwork.py:198
-        if (tid == 0) g.slot_nrows[slot] = 0;
+        if (tid == 0) {
+            g.slot_nrows[slot] = 0;
+            if (split) *(int4 *)(g.k1_rec + (size_t)64 * (size_t)base) = make_int4(0, n, m, bwm);    // nothing for the chain kernel to do
+        }
         bsync<CW>();
         return;
     }
@@ -537,7 +541,7 @@ __device__ void process_cell(const DevCtx &g, const Lay &L, unsigned char *sm, B
         const int pcv = c.pc[l];
         if (pcv > 0) {
             d = degree_f(g, P, c.agent[l], act, c.ts[l], pcv, avg_ts, avg_pc, log_avg_ts, log_avg_pc, one_minus_mhd);
-            if (!replay) {                                // the first four draws of the agent, should it become a main agent
+            if (!replay && !split) {                      // the first four draws of the agent, should it become a main agent
                 uint32_t w4[4];
                 philox4x32((uint32_t)g.day.day, (uint32_t)cell, (uint32_t)c.agent[l], 0u, g.day.seed, SITE_SELECT, w4);
                 draws4[l] = make_uint4(w4[0], w4[1], w4[2], w4[3]);
@@ -574,6 +578,40 @@ __device__ void process_cell(const DevCtx &g, const Lay &L, unsigned char *sm, B
     for (int l = tid; l < n_act; l += T) c.ord[l] = (uint16_t)((~okey[l]) & 0xffff);
     bsync<CW>();
 
+    if (split) {
+        // ---- 5b. split path: leave the cell's record in HBM for the thread-per-cell chain kernel (k1_chain.cu) and for
+        //          K2's row builder (K1Rec, common.cuh); the sequential sampling does not run in this kernel
+        unsigned char *rec = g.k1_rec + (size_t)64 * (size_t)base;
+        const K1Rec R(m, n, bwm);
+        uint32_t *mains = (uint32_t *)(rec + R.o_main);
+        const uint32_t mw = R.main_words;
+        if (tid == 0) *(int4 *)rec = make_int4(skip_chain ? 0 : n_act, n, m, bwm);
+        for (int w = tid; w < (int)R.bw2; w += T) ((uint32_t *)(rec + R.o_alive))[w] = w < bwm ? c.alive[w] : 0u;
+        for (uint32_t i = tid; i < (uint32_t)n_act * mw; i += T) {
+            const uint32_t oi = i / mw, k = i - oi * mw;
+            const int x = c.ord[oi];
+            uint32_t v;
+            if (k == 0) v = (uint32_t)x | ((uint32_t)c.first[x] << 16);
+            else if (k == 1) v = (uint32_t)c.agent[x];
+            else v = (int)(k - 2) < bwm ? c.bits[x * bwm + (k - 2)] : 0u;
+            mains[i] = v;
+        }
+        int32_t *r_agent = (int32_t *)(rec + R.o_agent);
+        uint16_t *r_deg = (uint16_t *)(rec + R.o_deg), *r_se = (uint16_t *)(rec + R.o_se), *r_la = (uint16_t *)(rec + R.o_la),
+                 *r_apos = (uint16_t *)(rec + R.o_apos), *r_aoff = (uint16_t *)(rec + R.o_aoff);
+        for (int l = tid; l < n; l += T) { r_agent[l] = c.agent[l]; r_aoff[l] = c.aoff[l]; }
+        if (tid == 0) r_aoff[n] = c.aoff[n];
+        for (int p = tid; p < m; p += T) {
+            const int l = c.la[p];
+            const int dg = c.deg[l];
+            r_deg[p] = (uint16_t)((c.first[l] == p && dg > 0) ? dg : 0);
+            r_se[p] = c.se[p]; r_la[p] = (uint16_t)l; r_apos[p] = c.apos[p];
+        }
+        if (tid == 0) g.slot_nrows[slot] = 0;            // the chain kernel sets the count
+        bsync<CW>();
+        return;
+    }
+
     // ---- 6. greedy sampling + create_contacts (contactnetwork.py:287-301, 386-424), warp 0 ----
     // Per main agent x: candidates = adjacency row of x AND alive (util.get_all_contacts_ids_by_id).  Philox mode: draw t
     // takes the r_t-th REMAINING candidate in canonical order, r_t = floor(u_t * (nc - t)).  That sequence is a Lehmer
@@ -582,6 +620,7 @@ __device__ void process_cell(const DevCtx &g, const Lay &L, unsigned char *sm, B
     RowRec *rows = g.scratch_rows + g.slot_rowoff[slot];
     const int row_cap = g.slot_rowbound[slot];
     int n_rows = 0;
+    if (skip_chain) n_act = 0;                              // timing experiment (MTD_K1_SKIPCHAIN=1): phases 1-5 only, no rows
     if (wid == 0) {
         uint16_t *rarr = c.ts;                             // draws r_t (ts is dead after phase 4)
         uint16_t *pickarr = c.pc;                          // replay: picked local agents (pc is dead after phase 5)
@@ -758,7 +797,8 @@ __global__ void __launch_bounds__(CW * 32, MINB) k1_block_kernel(DevCtx g, int c
         const int w = bs.w;
         bsync<CW>();                                        // bs.w is reused by the cell
         if (w < 0 || w >= total) break;
-        process_cell<CW, GWS>(g, L, sm, bs, mbar_phase, list[w], w + 1 < total ? list[w + 1] : -1, acc_pairs, acc_pot, acc_inc);
+        process_cell<CW, GWS>(g, L, sm, bs, mbar_phase, list[w], w + 1 < total ? list[w + 1] : -1, acc_pairs, acc_pot, acc_inc,
+                               !GWS && mm_rt < 0, !GWS && g.k1_split && MM <= MTD_K1_SPLIT_MAX_M);
         done++;
     }
     if (threadIdx.x == 0 && (acc_pairs | acc_pot | acc_inc)) {
@@ -780,7 +820,9 @@ int launch_block_class(const DevCtx &c, int cls, cudaStream_t st, int sm_count, 
     }
     int n = 0;
     if (lpt_region) { k1_lpt_kernel<<<1, 1024, 0, st>>>(c, cls, lpt_region, MM, 512); n++; }
-    k1_block_kernel<MM, CW, MINB, false><<<sm_count * per_sm * K1_GRID_ROUNDS, CW * 32, L.bytes, st>>>(c, cls, lpt_region ? lpt_region : cls, nullptr, 0, MM);
+    static const bool skip = [] { const char *e = getenv("MTD_K1_SKIPCHAIN"); return e && *e == '1'; }();
+    k1_block_kernel<MM, CW, MINB, false><<<sm_count * per_sm * K1_GRID_ROUNDS, CW * 32, L.bytes, st>>>(c, cls, lpt_region ? lpt_region : cls, nullptr, 0,
+                                                                                                    skip ? -MM : MM);
     return n + 1;
 }
 
@@ -792,9 +834,13 @@ int launch_block_class(const DevCtx &c, int cls, cudaStream_t st, int sm_count, 
 // bytes of the global workspace the class of cells above 1024 intervals needs (mm_big: its capacity in intervals)
 int64_t k1_big_ws_bytes(int mm_big) { const Lay L(mm_big); return (int64_t)K1_BIG_BLOCKS * (int64_t)al16(L.bytes); }
 
-// size classes 3..8 (33-64, -128, -192, -320, -1024, above): see size_class() in k0_csr.cu
+int launch_k1_chain(const DevCtx &c, int cls, int list_region, cudaStream_t st, int sm_count);
+
+// size classes 3..8 (33-64, -128, -192, -320, -1024, above): see size_class() in k0_csr.cu.  lpt[k]: list region holding
+// class 3 + k sorted by cell size, largest first (0 = unsorted class list).  With c.k1_split the kernels of classes 3..6
+// only prepare their cells and a thread-per-cell chain kernel follows each of them on the same stream (k1_chain.cu).
 int launch_k1_blocks(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_count, unsigned char *big_ws, int mm_big,
-                     int lpt_region_a, int lpt_region_b, bool only_big)
+                     const int lpt[4], bool only_big)
 {
     int n = 0;
     // the classes with the longest cells first; two streams so that the tail of one class overlaps the next
@@ -805,9 +851,13 @@ int launch_k1_blocks(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_c
     }
     if (only_big) return n;
     n += launch_block_class<1024, 8, 1>(c, 7, sa, sm_count, 0);
-    n += launch_block_class<320, 4, 6>(c, 6, sa, sm_count, lpt_region_a);
-    n += launch_block_class<192, 4, 8>(c, 5, sb, sm_count, lpt_region_b);
-    n += launch_block_class<128, 2, 16>(c, 4, sb, sm_count, 0);
-    n += launch_block_class<64, 2, 16>(c, 3, sb, sm_count, 0);
+    n += launch_block_class<320, 4, 6>(c, 6, sa, sm_count, lpt[3]);
+    if (c.k1_split) n += launch_k1_chain(c, 6, lpt[3] ? lpt[3] : 6, sa, sm_count);
+    n += launch_block_class<192, 4, 8>(c, 5, sb, sm_count, lpt[2]);
+    if (c.k1_split) n += launch_k1_chain(c, 5, lpt[2] ? lpt[2] : 5, sb, sm_count);
+    n += launch_block_class<128, 2, 16>(c, 4, sb, sm_count, lpt[1]);
+    if (c.k1_split) n += launch_k1_chain(c, 4, lpt[1] ? lpt[1] : 4, sb, sm_count);
+    n += launch_block_class<64, 2, 16>(c, 3, sb, sm_count, lpt[0]);
+    if (c.k1_split) n += launch_k1_chain(c, 3, lpt[0] ? lpt[0] : 3, sb, sm_count);
     return n;
 }

@@ -23,6 +23,8 @@
 #include "common.cuh"
 #include <stdlib.h>
 
+#define K1_IMPL_DEFAULT 0      // 0 legacy, 1 block, 2 split (see k1_impl below)
+
 namespace {
 
 __host__ __device__ constexpr int pow2_ge(int x) { int p = 1; while (p < x) p <<= 1; return p; }
@@ -460,16 +462,21 @@ int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int li
 }  // namespace
 
 int launch_k1_blocks(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_count, unsigned char *big_ws, int mm_big,
-                     int lpt_region_a, int lpt_region_b, bool only_big);
+                     const int lpt[4], bool only_big);
 int launch_k1_legacy(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_count);
 
-// MTD_K1_IMPL = block (block per cell, k1_block.cu) | legacy (round 1's warp per cell, k1_legacy.cu; cells above 1024
-// intervals still go through the block kernel's global-workspace class).  Both produce the same rows, bit for bit.
-bool k1_use_legacy()
+// MTD_K1_IMPL = split  (cells of 33..320 intervals: block per cell prepares, thread per cell samples, K2 builds the rows;
+//                        k1_block.cu + k1_chain.cu + k2_rows.cu)
+//             | block  (block per cell does everything, k1_block.cu)
+//             | legacy (round 1's warp per cell, k1_legacy.cu)
+// Cells above 320 (split) resp. 1024 (legacy) intervals go through the block kernels.  All produce the same rows, bit for bit.
+int k1_impl()
 {
-    static const int v = [] { const char *e = getenv("MTD_K1_IMPL"); return (e && e[0] == 'b') ? 0 : 1; }();
-    return v != 0;
+    static const int v = [] { const char *e = getenv("MTD_K1_IMPL"); return !e ? K1_IMPL_DEFAULT : (e[0] == 's' ? 2 : (e[0] == 'b' ? 1 : 0)); }();
+    return v;
 }
+bool k1_use_legacy() { return k1_impl() == 0; }
+bool k1_use_split() { return k1_impl() == 2; }
 
 static int env_int(const char *name, int dflt)
 {
@@ -493,10 +500,14 @@ int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t a
         sl = aux; sl2 = aux2;
     }
     int n;
+    const int none[4] = { 0, 0, 0, 0 };
+    // list regions of the size-sorted classes: 6 -> +0, 5 -> +1, (small classes +2..+4), 4 -> +5, 3 -> +6
+    const int regs[4] = { c.k1_split ? MTD_NUM_CLASSES + 6 : 0, c.k1_split ? MTD_NUM_CLASSES + 5 : 0,
+                          (lpt & 2) ? MTD_NUM_CLASSES + 1 : 0, (lpt & 1) ? MTD_NUM_CLASSES : 0 };
     if (k1_use_legacy() && c.k1_bits) {
-        n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, 0, 0, true);
+        n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, none, true);
         n += launch_k1_legacy(c, sl, sl2, sm_count);
-    } else n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, (lpt & 1) ? MTD_NUM_CLASSES : 0, (lpt & 2) ? MTD_NUM_CLASSES + 1 : 0, false);
+    } else n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, regs, false);
     const int sorted_small = (lpt & 4) ? MTD_NUM_CLASSES + 2 : 0;      // regions +2, +3, +4 = classes 0, 1, 2 by size
     if (sorted_small) {
         cudaMemsetAsync(c.k1_bins, 0, sizeof(int32_t) * 2 * 96, st);

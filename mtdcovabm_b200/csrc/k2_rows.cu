@@ -14,6 +14,59 @@ __device__ __forceinline__ void k2_copy_row(const DevCtx &c, int64_t src, int64_
     }
 }
 
+// Split K1 (cells of 33..320 intervals): the chain kernel left (first position of x) | (first position of y) << 16 in the
+// scratch row; the contact row is built here from the cell's record (K1Rec, common.cuh).  Key orientation = the agent
+// whose interval is reached first by the reference's ordered double loop (contactnetwork.py:160-196); start = first
+// overlap's start, end = last overlap's end in that orientation (contactnetwork.py:101); dur = summed overlap length
+// (epidemiology.py:170).  Same rule as pair_row_lists in k1_block.cu.
+__device__ __forceinline__ void k2_build_row(const DevCtx &c, const unsigned char *rec, const K1Rec &R, int slot, int64_t src,
+                                             int64_t dst, uint32_t sc)
+{
+    if (dst >= c.cap_rows) return;
+    const uint32_t xy = (uint32_t)__ldcg(&c.scratch_rows[src].a1);
+    const uint16_t *la = (const uint16_t *)(rec + R.o_la), *se = (const uint16_t *)(rec + R.o_se),
+                   *apos = (const uint16_t *)(rec + R.o_apos), *aoff = (const uint16_t *)(rec + R.o_aoff);
+    const int32_t *agent = (const int32_t *)(rec + R.o_agent);
+    const int x = la[xy & 0xffffu], y = la[xy >> 16];
+    const int xa = aoff[x], xb = aoff[x + 1], ya = aoff[y], yb = aoff[y + 1];
+    bool x_first; int start, end, dur = 0;
+    if (xb - xa == 1 && yb - ya == 1) {                             // one interval each (the common case): one overlap
+        const int pa = apos[xa], pb = apos[ya];
+        start = max((int)(se[pa] & 0xff), (int)(se[pb] & 0xff)); end = min((int)(se[pa] >> 8), (int)(se[pb] >> 8));
+        dur = end - start + 1; x_first = pa < pb;
+    } else {
+        int fx = 1 << 30, fy = 1 << 30, a_start = 0, a_end = 0, b_min = 0x7fffffff, b_max = -1, b_start = 0, b_end = 0;
+        bool a_none = true;
+        for (int qa = xa; qa < xb; qa++) {
+            const int pa = apos[qa]; const int sa = se[pa] & 0xff, ea = se[pa] >> 8;
+            for (int qb = ya; qb < yb; qb++) {
+                const int pb = apos[qb]; const int sb = se[pb] & 0xff, eb = se[pb] >> 8;
+                const int lo = max(sa, sb), hi = min(ea, eb);
+                if (lo <= hi) {
+                    fx = min(fx, pa); fy = min(fy, pb); dur += hi - lo + 1;
+                    if (a_none) { a_start = lo; a_none = false; }
+                    a_end = hi;
+                    const int kb = (pb << 15) | pa;
+                    if (kb < b_min) { b_min = kb; b_start = lo; }
+                    if (kb > b_max) { b_max = kb; b_end = hi; }
+                }
+            }
+        }
+        x_first = fx < fy;
+        start = x_first ? a_start : b_start; end = x_first ? a_end : b_end;
+    }
+    RowRec rr;
+    const int agx = agent[x], agy = agent[y];
+    rr.a1 = x_first ? agx : agy; rr.a2 = x_first ? agy : agx;
+    rr.sed = (uint32_t)start | ((uint32_t)end << 8) | ((uint32_t)dur << 16);
+    rr.slot = slot;
+    c.rows[dst] = rr;
+    if (c.rows12) {
+        uint32_t *o = c.rows12 + 3 * dst;
+        o[0] = (uint32_t)rr.a1; o[1] = (uint32_t)rr.a2; o[2] = (rr.sed & 0xffffu) | (sc << 16);
+    }
+}
+
 __global__ void __launch_bounds__(256) k2_compact_kernel(DevCtx c)
 {
     const int lane = threadIdx.x & 31;
@@ -37,7 +90,13 @@ __global__ void __launch_bounds__(256) k2_compact_kernel(DevCtx c)
             if (cnt <= 0) continue;
             const int64_t src = c.slot_rowoff[s], dst = c.slot_denseoff[s];
             const uint32_t sc = c.rows12 ? (uint32_t)simcelltype_of(c.cell_type[c.slot_cell[s]]) : 0u;
-            for (int r = lane; r < cnt; r += 32) k2_copy_row(c, src + r, dst + r, sc);
+            if (c.k1_split) {
+                const unsigned char *rec = c.k1_rec + (size_t)64 * (size_t)c.slot_off[s];
+                const int4 hdr = *(const int4 *)rec;
+                const K1Rec R(hdr.z, hdr.y, hdr.w);
+                for (int r = lane; r < cnt; r += 32) k2_build_row(c, rec, R, s, src + r, dst + r, sc);
+            } else
+                for (int r = lane; r < cnt; r += 32) k2_copy_row(c, src + r, dst + r, sc);
         }
     }
     for (int cls = 4; cls < MTD_NUM_CLASSES; cls++) {
@@ -49,7 +108,13 @@ __global__ void __launch_bounds__(256) k2_compact_kernel(DevCtx c)
             if (cnt <= 0) continue;
             const int64_t src = c.slot_rowoff[s], dst = c.slot_denseoff[s];
             const uint32_t sc = c.rows12 ? (uint32_t)simcelltype_of(c.cell_type[c.slot_cell[s]]) : 0u;
-            for (int r = threadIdx.x; r < cnt; r += blockDim.x) k2_copy_row(c, src + r, dst + r, sc);
+            if (c.k1_split && cls <= 6) {
+                const unsigned char *rec = c.k1_rec + (size_t)64 * (size_t)c.slot_off[s];
+                const int4 hdr = *(const int4 *)rec;
+                const K1Rec R(hdr.z, hdr.y, hdr.w);
+                for (int r = threadIdx.x; r < cnt; r += blockDim.x) k2_build_row(c, rec, R, s, src + r, dst + r, sc);
+            } else
+                for (int r = threadIdx.x; r < cnt; r += blockDim.x) k2_copy_row(c, src + r, dst + r, sc);
         }
     }
     for (int s0 = gwarp * 32; s0 < n_slots; s0 += warps * 32) {

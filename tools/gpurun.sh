@@ -16,7 +16,7 @@ R=${1:-quick}; T=${2:-$R}; O=gpurun_out; mkdir -p $O
 case $R in
 quick)
   # both K1 implementations (MTD_K1_IMPL=block | legacy): parity tests, then a short bench each
-  for impl in block legacy; do
+  for impl in ${IMPLS:-split block legacy}; do
     MTD_K1_IMPL=$impl timeout 1500 python -m pytest tests/test_edge_cases.py tests/test_gpu_parity.py tests/test_dropin_api.py tests/test_k6_kat.py -m gpu -q > $O/${T}_tests_$impl.log 2>&1; echo "tests[$impl]=$?"; tail -n 12 $O/${T}_tests_$impl.log
     MTD_K1_IMPL=$impl timeout 600 python bench.py --steps 14 --warmup 7 --no-cpu-baseline --no-e2e > $O/${T}_bench_$impl.json 2> $O/${T}_bench_$impl.err; echo "bench[$impl]=$?"; tail -n 3 $O/${T}_bench_$impl.err
     python -c "
@@ -46,7 +46,7 @@ ncu_k1)
   M="dram__bytes_read.sum,dram__bytes_write.sum,smsp__inst_executed.sum,gpu__time_duration.sum,lts__t_sectors_srcunit_tex_op_read.sum,lts__t_sectors_srcunit_tex_op_read_lookup_hit.sum,smsp__issue_active.avg.pct_of_peak_sustained_active,sm__warps_active.avg.pct_of_peak_sustained_active"
   timeout 900 ncu --metrics $M --clock-control none -k regex:k1_ -c 120 --csv --log-file $O/${T}_traffic.csv \
       python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-e2e > $O/${T}_ncu.log 2>&1; echo "ncu=$?"
-  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k1_ -s 16 -c 16 -o $O/${T}_full -f \
+  timeout 1200 ncu --set full --clock-control none --import-source on -k regex:k1_ -s 24 -c 12 -o $O/${T}_full -f \
       python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e > $O/${T}_full.log 2>&1; echo "ncu2=$?"
   ls -la $O/ | tail -n 5
   ;;
