@@ -12,7 +12,7 @@
 // every launcher returns the number of kernels it launched
 int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count);
 int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t aux2, cudaEvent_t ev_fork, cudaEvent_t ev_join,
-              cudaEvent_t ev_join2, int sm_count, unsigned char *big_ws, int mm_big);
+              cudaEvent_t ev_join2, int sm_count, unsigned char *big_ws, int mm_big, const K1ChainStreams *cs);
 int64_t k1_big_ws_bytes(int mm_big);
 int64_t k1_legacy_bits_words(int sm_count);
 bool k1_use_legacy();
@@ -49,6 +49,7 @@ struct mtd_handle_s {
     bool own_stream = false;
     cudaStream_t aux_stream = nullptr, aux2_stream = nullptr;   // large-cell K1 kernels run beside the small-cell ones
     unsigned char *k1_big_ws = nullptr; int k1_mm_big = 0;      // global workspace of the cells above 1024 intervals
+    K1ChainStreams k1cs = {}; bool have_k1cs = false;
     unsigned char *k1_rec[2] = {};                              // split K1: per-cell chain records, by day parity (K2 of day d reads
                                                                 //   them while the K1 of day d+1 already writes)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr;
@@ -277,7 +278,14 @@ static int create_impl(mtd_handle h)
     h->k1_mm_big = c.max_cell_m > 1024 ? ((c.max_cell_m + 31) & ~31) : 0;
     if (h->k1_mm_big) DA(h->k1_big_ws, k1_big_ws_bytes(h->k1_mm_big));
     if (k1_use_legacy()) { c.k1_bits_words = k1_legacy_bits_words(h->sm_count); DA(c.k1_bits, c.k1_bits_words); }
-    if (k1_use_split()) { c.k1_split = 1; DA(h->k1_rec[0], 64 * (size_t)M + 64); DA(h->k1_rec[1], 64 * (size_t)M + 64); c.k1_rec = h->k1_rec[0]; }
+    if (k1_use_split()) {
+        for (int k = 0; k < 4; k++) {
+            CK(cudaStreamCreateWithFlags(&h->k1cs.st[k], cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&h->k1cs.prep[k], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&h->k1cs.done[k], cudaEventDisableTiming));
+        }
+        h->have_k1cs = true;
+    }
+    if (k1_use_split()) { c.k1_split = 1; DA(h->k1_rec[0], MTD_K1_REC_STRIDE * (size_t)M + 64); DA(h->k1_rec[1], MTD_K1_REC_STRIDE * (size_t)M + 64); c.k1_rec = h->k1_rec[0]; }
     DA(c.win, N); DA(c.succ, c.cap_rows);
     c.row_p = nullptr;
     DA(h->delta_own, (c.cap_expo + 1) * MTD_DELTA_WORDS);
@@ -391,6 +399,7 @@ extern "C" int mtd_destroy(mtd_handle h)
                      (void *)h->trace_flagscan, (void *)h->trace_scan_tmp, (void *)h->d_traced, (void *)h->d_rows3 })
         if (p) cudaFree(p);
     for (int s = 0; s < MTD_N_STAGES; s++) for (cudaEvent_t e : h->ev[s]) cudaEventDestroy(e);
+    if (h->have_k1cs) for (int k = 0; k < 4; k++) { cudaStreamSynchronize(h->k1cs.st[k]); cudaStreamDestroy(h->k1cs.st[k]); cudaEventDestroy(h->k1cs.prep[k]); cudaEventDestroy(h->k1cs.done[k]); }
     if (h->aux_stream) { cudaStreamSynchronize(h->aux_stream); cudaStreamDestroy(h->aux_stream); }
     if (h->aux2_stream) { cudaStreamSynchronize(h->aux2_stream); cudaStreamDestroy(h->aux2_stream); }
     if (h->ev_join2) cudaEventDestroy(h->ev_join2);
@@ -596,7 +605,7 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     cudaStream_t k1s = (pipe && h->k1_pipe) ? h->k1_stream : h->stream;
     if (pipe) { CK(cudaEventRecord(h->ev_k0_ready, ks)); CK(cudaStreamWaitEvent(k1s, h->ev_k0_ready, 0)); }
     // an empty day (M == 0) has no cells: the zeroed counters are its result
-    if (M > 0) { StageScope sc(h, MTD_STAGE_K1, k1s); sc.add(launch_k1(c, k1s, h->aux_stream, h->aux2_stream, h->ev_fork, h->ev_join, h->ev_join2, h->sm_count, h->k1_big_ws, h->k1_mm_big)); }
+    if (M > 0) { StageScope sc(h, MTD_STAGE_K1, k1s); sc.add(launch_k1(c, k1s, h->aux_stream, h->aux2_stream, h->ev_fork, h->ev_join, h->ev_join2, h->sm_count, h->k1_big_ws, h->k1_mm_big, h->have_k1cs ? &h->k1cs : nullptr)); }
     if (k1s != h->stream) { CK(cudaEventRecord(h->ev_k1_done, k1s)); CK(cudaStreamWaitEvent(h->stream, h->ev_k1_done, 0)); }
     c.rows12 = nullptr;
     if (h->export_on) {     // K2 also packs the rows for the export; the slot's previous export must have drained

@@ -126,7 +126,7 @@ struct DevCtx {
     int32_t *k1_bins;          // [2][3][32] histogram and cursors of the small-class size sort (K1)
     uint32_t *k1_bits;         // [k1_bits_words] per-warp adjacency bit matrices of the legacy warp-per-cell K1 (k1_legacy.cu)
     int64_t k1_bits_words;
-    unsigned char *k1_rec;     // [64 * cap_intervals] per-cell chain records of the split K1 (K1Rec below), at 64 * slot_off[slot]
+    unsigned char *k1_rec;     // [80 * cap_intervals] per-cell chain records of the split K1 (K1Rec below), at 80 * slot_off[slot]
     int32_t k1_split;          // the day's cells of 33..320 intervals go through prepare / chain / row-build kernels
     int32_t max_cell_m;        // largest cell (intervals) this handle takes: min(MTD_MAX_CELL_INTERVALS, max_intervals)
     RowRec *rows;              // [cap_rows] dense
@@ -151,18 +151,19 @@ struct DevCtx {
 
 // ---------------------------------------------------------------- split K1: the per-cell record between its three kernels
 // Cells of 33..320 intervals: k1_block.cu (a block per cell) prepares the cell -- agents, adjacency rows, degrees, greedy
-// order -- and leaves this record in HBM at k1_rec + 64 * slot_off[slot] (64 bytes per interval of the cell: enough for
+// order -- and leaves this record in HBM at k1_rec + 80 * slot_off[slot] (80 bytes per interval of the cell: enough for
 // every cell of up to 336 intervals); k1_chain.cu runs the sequential greedy sampling with ONE THREAD per cell on it (32
 // cells per warp); K2 builds the contact rows of the selected pairs from it.
 //   header  int4 {n_act, n, m, bwm}; alive0 u32[bw2] (first positions of the agents with degree > 0)
-//   mains   n_act records in greedy order, (2 + bw2) words each: {x | first position << 16, agent id, adjacency row[bw2]}
+//   mains   n_act records in greedy order, (6 + bw2) words each: {x | first position << 16, agent id, the agent's first
+//           Philox block (4 draws), adjacency row[bw2]}
 //   agent   i32[n] agent id per local agent;  deg u16[m] initial degree at an agent's first position (0 elsewhere)
 //   se u16[m] start | end << 8;  la u16[m] local agent of a position;  apos u16[m], aoff u16[n + 1] interval lists
 struct K1Rec {
     uint32_t bw2, main_words, o_alive, o_main, o_agent, o_deg, o_se, o_la, o_apos, o_aoff;
     __host__ __device__ K1Rec(int m, int n, int bwm)
     {
-        bw2 = (uint32_t)((bwm + 1) & ~1); main_words = 2 + bw2;
+        bw2 = (uint32_t)((bwm + 1) & ~1); main_words = 6 + bw2;
         uint32_t o = 16;
         o_alive = o; o += 48;
         o_main = o;  o += (uint32_t)n * main_words * 4; o = (o + 15u) & ~15u;
@@ -174,7 +175,12 @@ struct K1Rec {
         o_aoff = o;
     }
 };
-#define MTD_K1_SPLIT_MAX_M 320     // largest cell the split path takes (record: 64 bytes per interval)
+#define MTD_K1_REC_STRIDE 80       // bytes of record space per interval
+#define MTD_K1_SPLIT_MAX_M 320     // largest cell the split path takes
+
+// streams / events of the split K1's chain kernels (owned by the handle): the chain kernel of a class waits for the class's
+// prepare kernel and runs beside the prepare kernels of the next classes; the stage joins on `done`
+struct K1ChainStreams { cudaStream_t st[4]; cudaEvent_t prep[4], done[4]; };
 
 // ---------------------------------------------------------------- Philox4x32-10
 __host__ __device__ __forceinline__ void philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,

@@ -520,7 +520,7 @@ __device__ void process_cell(const DevCtx &g, const Lay &L, unsigned char *sm, B
     if (pc_sum == 0) {                                    // contactnetwork.py:198
         if (tid == 0) {
             g.slot_nrows[slot] = 0;
-            if (split) *(int4 *)(g.k1_rec + (size_t)64 * (size_t)base) = make_int4(0, n, m, bwm);    // nothing for the chain kernel to do
+            if (split) *(int4 *)(g.k1_rec + (size_t)MTD_K1_REC_STRIDE * (size_t)base) = make_int4(0, n, m, bwm);    // nothing for the chain kernel to do
         }
         bsync<CW>();
         return;
@@ -581,7 +581,7 @@ __device__ void process_cell(const DevCtx &g, const Lay &L, unsigned char *sm, B
     if (split) {
         // ---- 5b. split path: leave the cell's record in HBM for the thread-per-cell chain kernel (k1_chain.cu) and for
         //          K2's row builder (K1Rec, common.cuh); the sequential sampling does not run in this kernel
-        unsigned char *rec = g.k1_rec + (size_t)64 * (size_t)base;
+        unsigned char *rec = g.k1_rec + (size_t)MTD_K1_REC_STRIDE * (size_t)base;
         const K1Rec R(m, n, bwm);
         uint32_t *mains = (uint32_t *)(rec + R.o_main);
         const uint32_t mw = R.main_words;
@@ -593,9 +593,17 @@ __device__ void process_cell(const DevCtx &g, const Lay &L, unsigned char *sm, B
             uint32_t v;
             if (k == 0) v = (uint32_t)x | ((uint32_t)c.first[x] << 16);
             else if (k == 1) v = (uint32_t)c.agent[x];
-            else v = (int)(k - 2) < bwm ? c.bits[x * bwm + (k - 2)] : 0u;
+            else if (k < 6) continue;                      // the Philox block is written below
+            else v = (int)(k - 6) < bwm ? c.bits[x * bwm + (k - 6)] : 0u;
             mains[i] = v;
         }
+        if (!replay)                                       // the first four draws of every main agent (one Philox block)
+            for (int oi = tid; oi < n_act; oi += T) {
+                uint32_t w4[4];
+                philox4x32((uint32_t)g.day.day, (uint32_t)cell, (uint32_t)c.agent[c.ord[oi]], 0u, g.day.seed, SITE_SELECT, w4);
+                uint32_t *d4 = mains + (size_t)oi * mw + 2;
+                d4[0] = w4[0]; d4[1] = w4[1]; d4[2] = w4[2]; d4[3] = w4[3];
+            }
         int32_t *r_agent = (int32_t *)(rec + R.o_agent);
         uint16_t *r_deg = (uint16_t *)(rec + R.o_deg), *r_se = (uint16_t *)(rec + R.o_se), *r_la = (uint16_t *)(rec + R.o_la),
                  *r_apos = (uint16_t *)(rec + R.o_apos), *r_aoff = (uint16_t *)(rec + R.o_aoff);
@@ -840,7 +848,7 @@ int launch_k1_chain(const DevCtx &c, int cls, int list_region, cudaStream_t st, 
 // class 3 + k sorted by cell size, largest first (0 = unsorted class list).  With c.k1_split the kernels of classes 3..6
 // only prepare their cells and a thread-per-cell chain kernel follows each of them on the same stream (k1_chain.cu).
 int launch_k1_blocks(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_count, unsigned char *big_ws, int mm_big,
-                     const int lpt[4], bool only_big)
+                     const int lpt[4], bool only_big, const K1ChainStreams *cs)
 {
     int n = 0;
     // the classes with the longest cells first; two streams so that the tail of one class overlaps the next
@@ -850,14 +858,23 @@ int launch_k1_blocks(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_c
         n++;
     }
     if (only_big) return n;
+    // the chain kernel of class 3 + k: on its own stream behind the class's prepare kernel (cs), else right behind it
+    auto chain = [&](int k, cudaStream_t prep_stream) {
+        if (!c.k1_split) return 0;
+        cudaStream_t st = prep_stream;
+        if (cs) { cudaEventRecord(cs->prep[k], prep_stream); cudaStreamWaitEvent(cs->st[k], cs->prep[k], 0); st = cs->st[k]; }
+        const int r = launch_k1_chain(c, 3 + k, lpt[k] ? lpt[k] : 3 + k, st, sm_count);
+        if (cs) cudaEventRecord(cs->done[k], st);
+        return r;
+    };
     n += launch_block_class<1024, 8, 1>(c, 7, sa, sm_count, 0);
     n += launch_block_class<320, 4, 6>(c, 6, sa, sm_count, lpt[3]);
-    if (c.k1_split) n += launch_k1_chain(c, 6, lpt[3] ? lpt[3] : 6, sa, sm_count);
+    n += chain(3, sa);
     n += launch_block_class<192, 4, 8>(c, 5, sb, sm_count, lpt[2]);
-    if (c.k1_split) n += launch_k1_chain(c, 5, lpt[2] ? lpt[2] : 5, sb, sm_count);
-    n += launch_block_class<128, 2, 16>(c, 4, sb, sm_count, lpt[1]);
-    if (c.k1_split) n += launch_k1_chain(c, 4, lpt[1] ? lpt[1] : 4, sb, sm_count);
+    n += chain(2, sb);
+    n += launch_block_class<128, 2, 16>(c, 4, sa, sm_count, lpt[1]);
+    n += chain(1, sa);
     n += launch_block_class<64, 2, 16>(c, 3, sb, sm_count, lpt[0]);
-    if (c.k1_split) n += launch_k1_chain(c, 3, lpt[0] ? lpt[0] : 3, sb, sm_count);
+    n += chain(0, sb);
     return n;
 }

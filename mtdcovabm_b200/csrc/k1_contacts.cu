@@ -462,7 +462,7 @@ int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int li
 }  // namespace
 
 int launch_k1_blocks(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_count, unsigned char *big_ws, int mm_big,
-                     const int lpt[4], bool only_big);
+                     const int lpt[4], bool only_big, const K1ChainStreams *cs);
 int launch_k1_legacy(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_count);
 
 // MTD_K1_IMPL = split  (cells of 33..320 intervals: block per cell prepares, thread per cell samples, K2 builds the rows;
@@ -488,7 +488,7 @@ static int env_int(const char *name, int dflt)
 // greedy chain of their cells, the sub-warp kernels of the small classes by instruction issue: the two families run side
 // by side -- large classes on two auxiliary streams, small classes on the main stream -- and join before K2.
 int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t aux2, cudaEvent_t ev_fork, cudaEvent_t ev_join,
-              cudaEvent_t ev_join2, int sm_count, unsigned char *big_ws, int mm_big)
+              cudaEvent_t ev_join2, int sm_count, unsigned char *big_ws, int mm_big, const K1ChainStreams *cs)
 {
     static const int overlap = env_int("MTD_K1_OVERLAP", 1);
     static const int lpt = env_int("MTD_K1_LPT", 7);     // bit 0: class 6, bit 1: class 5 longest-first; bit 2: small classes by size
@@ -505,9 +505,9 @@ int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t a
     const int regs[4] = { c.k1_split ? MTD_NUM_CLASSES + 6 : 0, c.k1_split ? MTD_NUM_CLASSES + 5 : 0,
                           (lpt & 2) ? MTD_NUM_CLASSES + 1 : 0, (lpt & 1) ? MTD_NUM_CLASSES : 0 };
     if (k1_use_legacy() && c.k1_bits) {
-        n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, none, true);
+        n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, none, true, nullptr);
         n += launch_k1_legacy(c, sl, sl2, sm_count);
-    } else n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, regs, false);
+    } else n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, regs, false, (sl != st) ? cs : nullptr);
     const int sorted_small = (lpt & 4) ? MTD_NUM_CLASSES + 2 : 0;      // regions +2, +3, +4 = classes 0, 1, 2 by size
     if (sorted_small) {
         cudaMemsetAsync(c.k1_bins, 0, sizeof(int32_t) * 2 * 96, st);
@@ -523,6 +523,7 @@ int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t a
         cudaEventRecord(ev_join2, sl2);
         cudaStreamWaitEvent(st, ev_join, 0);
         cudaStreamWaitEvent(st, ev_join2, 0);
+        if (cs && c.k1_split && !(k1_use_legacy() && c.k1_bits)) for (int k = 0; k < 4; k++) cudaStreamWaitEvent(st, cs->done[k], 0);
     }
     return n;
 }

@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(256) k2_compact_kernel(DevCtx c)
             const int64_t src = c.slot_rowoff[s], dst = c.slot_denseoff[s];
             const uint32_t sc = c.rows12 ? (uint32_t)simcelltype_of(c.cell_type[c.slot_cell[s]]) : 0u;
             if (c.k1_split) {
-                const unsigned char *rec = c.k1_rec + (size_t)64 * (size_t)c.slot_off[s];
+                const unsigned char *rec = c.k1_rec + (size_t)MTD_K1_REC_STRIDE * (size_t)c.slot_off[s];
                 const int4 hdr = *(const int4 *)rec;
                 const K1Rec R(hdr.z, hdr.y, hdr.w);
                 for (int r = lane; r < cnt; r += 32) k2_build_row(c, rec, R, s, src + r, dst + r, sc);
@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(256) k2_compact_kernel(DevCtx c)
             const int64_t src = c.slot_rowoff[s], dst = c.slot_denseoff[s];
             const uint32_t sc = c.rows12 ? (uint32_t)simcelltype_of(c.cell_type[c.slot_cell[s]]) : 0u;
             if (c.k1_split && cls <= 6) {
-                const unsigned char *rec = c.k1_rec + (size_t)64 * (size_t)c.slot_off[s];
+                const unsigned char *rec = c.k1_rec + (size_t)MTD_K1_REC_STRIDE * (size_t)c.slot_off[s];
                 const int4 hdr = *(const int4 *)rec;
                 const K1Rec R(hdr.z, hdr.y, hdr.w);
                 for (int r = threadIdx.x; r < cnt; r += blockDim.x) k2_build_row(c, rec, R, s, src + r, dst + r, sc);
