@@ -317,6 +317,21 @@ int mtd_set_profiling(mtd_handle h, int on);
 int mtd_debug_log(mtd_handle h, int64_t n, const double *x, double *out);
 int mtd_get_stage_ms(mtd_handle h, float ms[MTD_N_STAGES], int64_t launches[MTD_N_STAGES]);
 
+/* Occupancy count without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same result as mtd_occupancy (agents per SEIR state 0..5), but handle-free: the caller passes the input
+ * (seir: DEVICE int8[n_agents]) and the output (out6: DEVICE int64[6]) and the stream to run on (NULL = the default
+ * stream); the call is asynchronous on that stream.  The kernel's scratch (per-block partial counts + an arrival
+ * ticket) is a file-scope __device__ array of MTD_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until
+ * exit; the entry point calls no cudaMalloc / cudaFree / allocating library routine.  The array's device address is
+ * resolved once per device on the first call for that device (make that call outside a graph capture).
+ * n_agents > MTD_NOALLOC_MAX_AGENTS -> MTD_E_CAPACITY with the text in err (err / err_cap: optional caller buffer for
+ * the error message).  All calls on a device share the array: calls that overlap on one GPU race -- serialise them. */
+#define MTD_NOALLOC_MAX_AGENTS (1LL << 26)         /* 67 108 864 agent ids: 1024 blocks of 65536 */
+#define MTD_NOALLOC_SCRATCH_BYTES 65792            /* 1024 rows x 8 x u64 + 256 bytes (ticket) */
+int mtd_occupancy_noalloc(int32_t device, const int8_t *seir, int64_t n_agents, int64_t *out6, void *stream,
+                          char *err, int64_t err_cap);
+
 #ifdef __cplusplus
 }
 #endif

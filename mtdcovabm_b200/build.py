@@ -8,7 +8,7 @@ import sys
 PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 SO = os.path.join(PKG, "libmtd_b200.so")
-SOURCES = ["capi.cu", "k0_csr.cu", "k1_contacts.cu", "k1_block.cu", "k1_legacy.cu", "k1_chain.cu", "k2_rows.cu", "k3_transmission.cu", "k5_tracing.cu", "k7_vaccination.cu", "k8_intervals.cu"]
+SOURCES = ["capi.cu", "k0_csr.cu", "k1_contacts.cu", "k1_block.cu", "k1_legacy.cu", "k1_chain.cu", "k2_rows.cu", "k3_transmission.cu", "k5_tracing.cu", "k7_vaccination.cu", "k8_intervals.cu", "noalloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",
          "-Xcompiler", "-fPIC", "-Xcompiler", "-O2"]

@@ -16,6 +16,7 @@ SO = os.path.join(PKG, "libmtd_b200.so")
 MEM_HOST, MEM_DEVICE, MEM_STAGED, MEM_BUILT = 0, 1, 2, 3
 MODE_REPLAY, MODE_PHILOX = 0, 1
 MAX_CELL_INTERVALS = 16384     # include/mtd_b200.h MTD_MAX_CELL_INTERVALS
+NOALLOC_MAX_AGENTS = 1 << 26   # include/mtd_b200.h MTD_NOALLOC_MAX_AGENTS
 DELTA_WORDS = 20
 APPLY_NONE, APPLY_LOCAL, APPLY_EXCHANGE = 0, 1, 2
 IPC_HANDLE_BYTES = 64
@@ -28,7 +29,7 @@ EXPORTS = ["mtd_create", "mtd_destroy", "mtd_last_error", "mtd_abi_version", "mt
            "mtd_export_day_async", "mtd_export_wait", "mtd_set_residences", "mtd_contact_tracing", "mtd_get_traced",
            "mtd_exchange_init", "mtd_exchange_open", "mtd_exchange_ready", "mtd_set_contacts", "mtd_seed_exposures", "mtd_set_intervention_mask", "mtd_set_k0_overlap",
            "mtd_process_test_results", "mtd_debug_log", "mtd_set_k6_tape", "mtd_contact_tracing_scan", "mtd_contact_tracing_finish", "mtd_enable_vaccination", "mtd_schedule_vaccinations", "mtd_set_vaccination",
-           "mtd_get_vaccination", "mtd_build_intervals", "mtd_get_intervals"]
+           "mtd_get_vaccination", "mtd_build_intervals", "mtd_get_intervals", "mtd_occupancy_noalloc"]
 STAGES = ("h2d", "k0_csr", "k1_contacts", "k2_rows", "k3_eval", "k3_apply", "k4_advance")
 
 
