@@ -28,6 +28,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+import mtdcovabm_b200  # noqa: E402,F401  (sets CUDA_DEVICE_MAX_CONNECTIONS for multi-rank runs before CUDA is initialised)
 
 METRIC = "agent_contact_pairs_per_s"
 UNIT = "pairs/s"
@@ -44,6 +45,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--shard-of", type=int, default=0,
+                    help="development aid: run rank 0's shard of a W-rank job on ONE GPU (no exchange); the line is not a bench value")
     return ap.parse_args()
 
 
@@ -288,7 +291,7 @@ def run_b200(args):
     reps = max(1, round(args.agents / n_present1))
     pop = synth.SynthPopulation(bank, reps, dev, seed=args.seed)
     nb = pop.n_days
-    streams = [pop.stream(k, rank, world) for k in range(nb)]
+    streams = [pop.stream(k, rank, world) if not (args.shard_of and world == 1) else pop.stream(k, 0, args.shard_of) for k in range(nb)]
     max_m = max(len(s["iv_agent"]) for s in streams)
     P = prm.build_params()
     eng = engine.DayEngine(pop.n_agents, pop.n_cells, max_m + 16, P, device=local, rank=rank, world=world,
@@ -339,8 +342,10 @@ def run_b200(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clocks:
         ev0.record(eng.stream)
+        t_sub0 = time.perf_counter()
         for step in range(args.warmup, args.warmup + args.steps):
             eng.step(1 + step, streams[step % nb])
+        host_submit_ms = (time.perf_counter() - t_sub0) * 1e3 / args.steps   # host time to enqueue one day (no waiting in it unless a queue is full)
         ev1.record(eng.stream)
         barrier()
     ms = allmax(ev0.elapsed_time(ev1))
@@ -521,7 +526,7 @@ def run_b200(args):
                 "pairs_per_day": total_pairs / args.steps, "contacts_per_day": contacts_per_day,
                 "exposed_last_day": int(c.n_exposed),
                 "roofline": roofline, "cpu_baseline": cpu, "parity": parity, "per_rank_stage_ms": per_rank, "e2e": e2e,
-                "gpu_launches": launches,
+                "gpu_launches": launches, "host_submit_ms_per_step": host_submit_ms,
                 "clocks": clocks.summary()}
         print(json.dumps(line), flush=True)
     eng.close()

@@ -11,8 +11,9 @@
 
 // every launcher returns the number of kernels it launched
 int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_count);
+#define MTD_MAX_PARITIES 3
 int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t aux2, cudaEvent_t ev_fork, cudaEvent_t ev_join,
-              cudaEvent_t ev_join2, int sm_count, unsigned char *big_ws, int mm_big, const K1ChainStreams *cs);
+              cudaEvent_t ev_join2, int sm_count, unsigned char *big_ws, int mm_big, const K1ChainStreams *cs, bool *joined);
 int64_t k1_big_ws_bytes(int mm_big);
 int64_t k1_legacy_bits_words(int sm_count);
 bool k1_use_legacy();
@@ -50,7 +51,7 @@ struct mtd_handle_s {
     cudaStream_t aux_stream = nullptr, aux2_stream = nullptr;   // large-cell K1 kernels run beside the small-cell ones
     unsigned char *k1_big_ws = nullptr; int k1_mm_big = 0;      // global workspace of the cells above 1024 intervals
     K1ChainStreams k1cs = {}; bool have_k1cs = false;
-    unsigned char *k1_rec[2] = {};                              // split K1: per-cell chain records, by day parity (K2 of day d reads
+    unsigned char *k1_rec[MTD_MAX_PARITIES] = {};                              // split K1: per-cell chain records, by day parity (K2 of day d reads
                                                                 //   them while the K1 of day d+1 already writes)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr;
     // The state chain -- apply of day d's exposure records (after the peer exchange), then K4 of day d+1 -- runs on its
@@ -64,12 +65,15 @@ struct mtd_handle_s {
     struct K0Set { int32_t *cell_count; uint32_t *cell_first; int64_t *cell_base; uint16_t *iv_pos; int32_t *flag_scan;
                    int32_t *slot_cell, *slot_m; uint32_t *slot_first; uint8_t *slot_act; int64_t *slot_off, *slot_rowoff;
                    int32_t *slot_rowbound, *slot_nrows; int64_t *slot_denseoff; int32_t *class_list; IvRec *csr;
-                   DevCounters *ctr; RowRec *scratch_rows; } k0set[2] = {};
+                   DevCounters *ctr; RowRec *scratch_rows; } k0set[MTD_MAX_PARITIES] = {};
+    int n_par = 2;                               // sets of the K0 / K1 products in flight (MTD_PARITIES = 2 | 3)
+    cudaStream_t k1_join_stream = nullptr; cudaEvent_t ev_k1_small = nullptr; bool k1_days_overlap = false;   // see the day overlap of K1 in mtd_simulate_contact_network
+    cudaStream_t k1_stream2 = nullptr; int32_t *k1_bins_base = nullptr;   // K1 stages of consecutive days alternate between k1_stream and k1_stream2 (day overlap)
     cudaStream_t k0_stream = nullptr, k1_stream = nullptr;   // K1 of day d+1 likewise runs beside K2/K3 of day d (its scratch rows are per parity too)
     cudaEvent_t ev_k1_done = nullptr;
     bool last_pipe = false;                      // the previous day ran pipelined
     bool k1_pipe = true;                         // MTD_K1_PIPE=0 keeps K1 on the main stream
-    cudaEvent_t ev_k0_ready = nullptr, ev_main_mark[2] = {};
+    cudaEvent_t ev_k0_ready = nullptr, ev_main_mark[MTD_MAX_PARITIES] = {};
     int32_t *n_succ_buf = nullptr;               // [2] by day parity (DevCtx::n_succ_pub)
     long long *scan_tmp_k0 = nullptr;
     bool k0_pipe = true;                         // MTD_K0_PIPE=0 keeps K0 on the main stream
@@ -270,7 +274,7 @@ static int create_impl(mtd_handle h)
     DA(c.slot_nrows, S + 1); DA(c.slot_denseoff, S + 2);
     c.class_stride = S + 1;
     DA(c.class_list, (MTD_NUM_CLASSES + 7) * (S + 1));      // + five regions: every class but the last again, sorted by size
-    DA(c.k1_bins, 2 * 3 * 32);
+    DA(c.k1_bins, 2 * 2 * 3 * 32); h->k1_bins_base = c.k1_bins;       // two sets: the small-cell ordering of two days may be in flight
     DA(c.csr, M);
     DA(c.scratch_rows, c.cap_scratch_rows); DA(c.rows, c.cap_rows);
     // cells above 1024 intervals are processed in a global workspace: as large as a cell of this handle can get
@@ -280,12 +284,25 @@ static int create_impl(mtd_handle h)
     if (k1_use_legacy()) { c.k1_bits_words = k1_legacy_bits_words(h->sm_count); DA(c.k1_bits, c.k1_bits_words); }
     if (k1_use_split()) {
         for (int k = 0; k < 4; k++) {
-            CK(cudaStreamCreateWithFlags(&h->k1cs.st[k], cudaStreamNonBlocking));
+            // the class streams carry the latency-bound chain kernels: above the throughput-bound small-cell kernels
+            // (default priority), below the main / state streams
+            int plo = 0, phi = 0;
+            CK(cudaDeviceGetStreamPriorityRange(&plo, &phi));
+            const char *pe = getenv("MTD_K1_CHAIN_PRIO");
+            const int want = (pe && *pe) ? atoi(pe) : -1;
+            const int cprio = want < phi ? phi : (want > plo ? plo : want);
+            CK(cudaStreamCreateWithPriority(&h->k1cs.st[k], cudaStreamNonBlocking, cprio));
+            const char *e3 = getenv("MTD_K1_CHAIN_PARITY");
+            if (!(e3 && *e3 == '0')) {
+                CK(cudaStreamCreateWithPriority(&h->k1cs.st2[k], cudaStreamNonBlocking, cprio));
+                CK(cudaStreamCreateWithFlags(&h->k1cs.pst[k], cudaStreamNonBlocking));
+            }
             CK(cudaEventCreateWithFlags(&h->k1cs.prep[k], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&h->k1cs.done[k], cudaEventDisableTiming));
         }
         h->have_k1cs = true;
     }
-    if (k1_use_split()) { c.k1_split = 1; DA(h->k1_rec[0], MTD_K1_REC_STRIDE * (size_t)M + 64); DA(h->k1_rec[1], MTD_K1_REC_STRIDE * (size_t)M + 64); c.k1_rec = h->k1_rec[0]; }
+    { const char *e = getenv("MTD_PARITIES"); h->n_par = (e && *e == '2') ? 2 : 3; }
+    if (k1_use_split()) { c.k1_split = 1; for (int q = 0; q < h->n_par; q++) DA(h->k1_rec[q], MTD_K1_REC_STRIDE * (size_t)M + 64); c.k1_rec = h->k1_rec[0]; }
     DA(c.win, N); DA(c.succ, c.cap_rows);
     c.row_p = nullptr;
     DA(h->delta_own, (c.cap_expo + 1) * MTD_DELTA_WORDS);
@@ -306,17 +323,20 @@ static int create_impl(mtd_handle h)
     DA(h->d_mask, N);
     DA(h->scan_tmp, 2 * ((std::max(M, S) + 2) / 2048 + 16));
     DA(h->scan_tmp_k0, 2 * ((std::max(M, S) + 2) / 2048 + 16));
-    {   // the second parity of the K0 products
-        mtd_handle_s::K0Set &a = h->k0set[0], &b = h->k0set[1];
+    {   // the further sets of the K0 products (a day's set is reused n_par days later)
+        mtd_handle_s::K0Set &a = h->k0set[0];
         a = { c.cell_count, c.cell_first, c.cell_base, c.iv_pos, c.flag_scan, c.slot_cell, c.slot_m, c.slot_first, c.slot_act,
               c.slot_off, c.slot_rowoff, c.slot_rowbound, c.slot_nrows, c.slot_denseoff, c.class_list, c.csr, c.ctr, c.scratch_rows };
-        DA(b.cell_count, C); DA(b.cell_first, C); DA(b.cell_base, C); DA(b.iv_pos, M); DA(b.flag_scan, M + 64);
-        DA(b.slot_cell, S + 1); DA(b.slot_m, S + 1); DA(b.slot_first, S + 1); DA(b.slot_act, S + 1);
-        DA(b.slot_off, S + 2); DA(b.slot_rowoff, S + 2); DA(b.slot_rowbound, S + 1);
-        DA(b.slot_nrows, S + 1); DA(b.slot_denseoff, S + 2);
-        DA(b.class_list, (MTD_NUM_CLASSES + 7) * (S + 1));
-        DA(b.csr, M); DA(b.ctr, 1); DA(b.scratch_rows, c.cap_scratch_rows);
-        CK(cudaMemsetAsync(b.ctr, 0, sizeof(DevCounters), h->stream));
+        for (int q = 1; q < h->n_par; q++) {
+            mtd_handle_s::K0Set &b = h->k0set[q];
+            DA(b.cell_count, C); DA(b.cell_first, C); DA(b.cell_base, C); DA(b.iv_pos, M); DA(b.flag_scan, M + 64);
+            DA(b.slot_cell, S + 1); DA(b.slot_m, S + 1); DA(b.slot_first, S + 1); DA(b.slot_act, S + 1);
+            DA(b.slot_off, S + 2); DA(b.slot_rowoff, S + 2); DA(b.slot_rowbound, S + 1);
+            DA(b.slot_nrows, S + 1); DA(b.slot_denseoff, S + 2);
+            DA(b.class_list, (MTD_NUM_CLASSES + 7) * (S + 1));
+            DA(b.csr, M); DA(b.ctr, 1); DA(b.scratch_rows, c.cap_scratch_rows);
+            CK(cudaMemsetAsync(b.ctr, 0, sizeof(DevCounters), h->stream));
+        }
         int lo = 0, hi = 0;
         CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
         const char *pe = getenv("MTD_K0_PRIO");
@@ -324,12 +344,17 @@ static int create_impl(mtd_handle h)
         CK(cudaStreamCreateWithPriority(&h->k0_stream, cudaStreamNonBlocking, prio));   // default: fills what K1 leaves free
         CK(cudaEventCreateWithFlags(&h->ev_k0_ready, cudaEventDisableTiming));
         CK(cudaStreamCreateWithFlags(&h->k1_stream, cudaStreamNonBlocking));
+        { const char *e4 = getenv("MTD_K1_STREAMS"); if (!(e4 && *e4 == '1')) CK(cudaStreamCreateWithFlags(&h->k1_stream2, cudaStreamNonBlocking)); }
         CK(cudaEventCreateWithFlags(&h->ev_k1_done, cudaEventDisableTiming));
         { const char *e1 = getenv("MTD_K1_PIPE"); h->k1_pipe = !(e1 && *e1 == '0'); }
-        CK(cudaEventCreateWithFlags(&h->ev_main_mark[0], cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&h->ev_main_mark[1], cudaEventDisableTiming));
-        DA(h->n_succ_buf, 2);
-        CK(cudaMemsetAsync(h->n_succ_buf, 0, 2 * sizeof(int32_t), h->stream));
+        if (h->have_k1cs) {
+            CK(cudaStreamCreateWithFlags(&h->k1_join_stream, cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&h->ev_k1_small, cudaEventDisableTiming));
+            const char *e2 = getenv("MTD_K1_DAYS_OVERLAP"); h->k1_days_overlap = !(e2 && *e2 == '0');
+        }
+        for (int q = 0; q < MTD_MAX_PARITIES; q++) CK(cudaEventCreateWithFlags(&h->ev_main_mark[q], cudaEventDisableTiming));
+        DA(h->n_succ_buf, MTD_MAX_PARITIES);
+        CK(cudaMemsetAsync(h->n_succ_buf, 0, MTD_MAX_PARITIES * sizeof(int32_t), h->stream));
         c.n_succ_pub = h->n_succ_buf;
         const char *e = getenv("MTD_K0_PIPE");
         h->k0_pipe = !(e && *e == '0');
@@ -380,8 +405,11 @@ extern "C" int mtd_destroy(mtd_handle h)
     if (h->state_stream) { cudaStreamSynchronize(h->state_stream); cudaStreamDestroy(h->state_stream); }
     if (h->k0_stream) { cudaStreamSynchronize(h->k0_stream); cudaStreamDestroy(h->k0_stream); }
     if (h->k1_stream) { cudaStreamSynchronize(h->k1_stream); cudaStreamDestroy(h->k1_stream); }
+    if (h->k1_stream2) { cudaStreamSynchronize(h->k1_stream2); cudaStreamDestroy(h->k1_stream2); }
+    if (h->k1_join_stream) { cudaStreamSynchronize(h->k1_join_stream); cudaStreamDestroy(h->k1_join_stream); }
+    if (h->ev_k1_small) cudaEventDestroy(h->ev_k1_small);
     if (h->ev_k1_done) cudaEventDestroy(h->ev_k1_done);
-    for (cudaEvent_t e : { h->ev_k0_ready, h->ev_main_mark[0], h->ev_main_mark[1] }) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : { h->ev_k0_ready, h->ev_main_mark[0], h->ev_main_mark[1], h->ev_main_mark[2] }) if (e) cudaEventDestroy(e);
     if (h->ev_state) cudaEventDestroy(h->ev_state);
     if (h->ev_main) cudaEventDestroy(h->ev_main);
     for (void *p : { (void *)h->k6_agent, (void *)h->k6_u }) if (p) cudaFree(p);
@@ -399,7 +427,10 @@ extern "C" int mtd_destroy(mtd_handle h)
                      (void *)h->trace_flagscan, (void *)h->trace_scan_tmp, (void *)h->d_traced, (void *)h->d_rows3 })
         if (p) cudaFree(p);
     for (int s = 0; s < MTD_N_STAGES; s++) for (cudaEvent_t e : h->ev[s]) cudaEventDestroy(e);
-    if (h->have_k1cs) for (int k = 0; k < 4; k++) { cudaStreamSynchronize(h->k1cs.st[k]); cudaStreamDestroy(h->k1cs.st[k]); cudaEventDestroy(h->k1cs.prep[k]); cudaEventDestroy(h->k1cs.done[k]); }
+    if (h->have_k1cs) for (int k = 0; k < 4; k++) { cudaStreamSynchronize(h->k1cs.st[k]); cudaStreamDestroy(h->k1cs.st[k]);
+        if (h->k1cs.st2[k]) { cudaStreamSynchronize(h->k1cs.st2[k]); cudaStreamDestroy(h->k1cs.st2[k]); }
+        if (h->k1cs.pst[k]) { cudaStreamSynchronize(h->k1cs.pst[k]); cudaStreamDestroy(h->k1cs.pst[k]); }
+        cudaEventDestroy(h->k1cs.prep[k]); cudaEventDestroy(h->k1cs.done[k]); }
     if (h->aux_stream) { cudaStreamSynchronize(h->aux_stream); cudaStreamDestroy(h->aux_stream); }
     if (h->aux2_stream) { cudaStreamSynchronize(h->aux2_stream); cudaStreamDestroy(h->aux2_stream); }
     if (h->ev_join2) cudaEventDestroy(h->ev_join2);
@@ -550,7 +581,7 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     c.agent_masked = h->mask_on ? h->agent_masked : nullptr;
     if (h->mask_on) TOUCH();                 // K0 reads today's state (after K4 of today and the apply of yesterday)
     // today's parity of the K0 products; K0 goes to its own stream when its inputs do not come through the main stream
-    const int kp = (int)(h->k0_seq++ & 1);
+    const int kp = (int)(h->k0_seq++ % h->n_par);
     {
         const mtd_handle_s::K0Set &k = h->k0set[kp];
         c.cell_count = k.cell_count; c.cell_first = k.cell_first; c.cell_base = k.cell_base; c.iv_pos = k.iv_pos;
@@ -566,7 +597,7 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     // this parity was last read by the day before yesterday's K1..K3 (main stream): all of it had been enqueued when
     // yesterday's call recorded its mark.  (The apply chain on the state stream reads no K0 product: the one counter it
     // needs, n_succ, is published by K3 into a slot of its own.)
-    if (pipe) CK(cudaStreamWaitEvent(ks, h->ev_main_mark[kp ^ 1], 0));
+    if (pipe) CK(cudaStreamWaitEvent(ks, h->ev_main_mark[(kp + 1) % h->n_par], 0));
     CK(cudaEventRecord(h->ev_main_mark[kp], h->stream));
     // first pipelined day after a serial one: that day's K0/K1 ran on the main stream and own the K1 scratch until they end
     if (pipe && !h->last_pipe) CK(cudaStreamWaitEvent(ks, h->ev_main_mark[kp], 0));
@@ -602,11 +633,33 @@ extern "C" int mtd_simulate_contact_network(mtd_handle h, const mtd_day *day, in
     if (h->ev_k0_done) CK(cudaEventRecord(h->ev_k0_done, ks));             // the interval stream has been consumed
     // K1 needs K0 of its own day only: in the pipelined mode it runs on a third stream, beside K2/K3 of the day before
     // (main stream), and the main stream picks the day up again at K2
-    cudaStream_t k1s = (pipe && h->k1_pipe) ? h->k1_stream : h->stream;
+    const bool k1_alt = h->k1_stream2 && h->k1_join_stream && h->k1_days_overlap && ((h->k0_seq - 1) & 1);
+    cudaStream_t k1s = (pipe && h->k1_pipe) ? (k1_alt ? h->k1_stream2 : h->k1_stream) : h->stream;
+    c.k1_bins = h->k1_bins_base + (((h->k0_seq - 1) & 1) ? 2 * 3 * 32 : 0);
     if (pipe) { CK(cudaEventRecord(h->ev_k0_ready, ks)); CK(cudaStreamWaitEvent(k1s, h->ev_k0_ready, 0)); }
     // an empty day (M == 0) has no cells: the zeroed counters are its result
-    if (M > 0) { StageScope sc(h, MTD_STAGE_K1, k1s); sc.add(launch_k1(c, k1s, h->aux_stream, h->aux2_stream, h->ev_fork, h->ev_join, h->ev_join2, h->sm_count, h->k1_big_ws, h->k1_mm_big, h->have_k1cs ? &h->k1cs : nullptr)); }
-    if (k1s != h->stream) { CK(cudaEventRecord(h->ev_k1_done, k1s)); CK(cudaStreamWaitEvent(h->stream, h->ev_k1_done, 0)); }
+    // Day overlap of K1 (pipelined mode, class streams): the K1 stream does not wait for the stage's side streams -- the
+    // chain kernels of the large classes are bound by the latency of their longest cell, and the next day's small-cell
+    // and prepare kernels fill the machine beside them (every product of the stage is double-buffered by day parity, and
+    // each class stream takes the days in order).  The stage is joined on a stream of its own, which the main stream waits
+    // for before K2 and which carries the stage's end event.
+    if (M > 0) {
+        StageScope sc(h, MTD_STAGE_K1, k1s);
+        bool joined = true;
+        const bool overlap_days = k1s != h->stream && h->k1_join_stream && h->k1_days_overlap;
+        h->k1cs.par = (int)((h->k0_seq - 1) & 1);      // chain streams alternate day by day, whatever the number of product sets
+        sc.add(launch_k1(c, k1s, h->aux_stream, h->aux2_stream, h->ev_fork, h->ev_join, h->ev_join2, h->sm_count, h->k1_big_ws, h->k1_mm_big,
+                         h->have_k1cs ? &h->k1cs : nullptr, overlap_days ? &joined : nullptr));
+        if (!joined) {
+            cudaStream_t js = h->k1_join_stream;
+            CK(cudaEventRecord(h->ev_k1_small, k1s)); CK(cudaStreamWaitEvent(js, h->ev_k1_small, 0));
+            CK(cudaStreamWaitEvent(js, h->ev_join, 0)); CK(cudaStreamWaitEvent(js, h->ev_join2, 0));
+            for (int k = 0; k < 4; k++) CK(cudaStreamWaitEvent(js, h->k1cs.done[k], 0));
+            sc.st = js;                                  // the stage ends when its last stream does
+            CK(cudaEventRecord(h->ev_k1_done, js));
+            CK(cudaStreamWaitEvent(h->stream, h->ev_k1_done, 0));
+        } else if (k1s != h->stream) { CK(cudaEventRecord(h->ev_k1_done, k1s)); CK(cudaStreamWaitEvent(h->stream, h->ev_k1_done, 0)); }
+    } else if (k1s != h->stream) { CK(cudaEventRecord(h->ev_k1_done, k1s)); CK(cudaStreamWaitEvent(h->stream, h->ev_k1_done, 0)); }
     c.rows12 = nullptr;
     if (h->export_on) {     // K2 also packs the rows for the export; the slot's previous export must have drained
         const int sl = (int)(h->day_seq & 1);
@@ -1000,6 +1053,7 @@ extern "C" int mtd_get_stage_ms(mtd_handle h, float ms[MTD_N_STAGES], int64_t la
     CK(cudaStreamSynchronize(h->state_stream));
     CK(cudaStreamSynchronize(h->k0_stream));
     CK(cudaStreamSynchronize(h->k1_stream));
+    if (h->k1_stream2) CK(cudaStreamSynchronize(h->k1_stream2));
     for (int s = 0; s < MTD_N_STAGES; s++) {
         ms[s] = 0.f;
         double sum = 0.0;
@@ -1024,6 +1078,7 @@ extern "C" int mtd_sync(mtd_handle h)
     CK(cudaStreamSynchronize(h->state_stream));
     CK(cudaStreamSynchronize(h->k0_stream));
     CK(cudaStreamSynchronize(h->k1_stream));
+    if (h->k1_stream2) CK(cudaStreamSynchronize(h->k1_stream2));
     return MTD_OK;
 }
 

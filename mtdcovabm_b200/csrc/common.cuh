@@ -180,7 +180,12 @@ struct K1Rec {
 
 // streams / events of the split K1's chain kernels (owned by the handle): the chain kernel of a class waits for the class's
 // prepare kernel and runs beside the prepare kernels of the next classes; the stage joins on `done`
-struct K1ChainStreams { cudaStream_t st[4]; cudaEvent_t prep[4], done[4]; };
+// Development aid (MTD_K1_TIMELINE=<n>): the n-th K1 stage of the process records an event behind every launch on the
+// launch's stream; the next K1 stage prints, per mark, when the work ahead of it on its stream had ended (k1_contacts.cu).
+void k1_tl_mark(const char *name, cudaStream_t st);
+// st[k] / st2[k]: chain stream of class 3 + k for days of even / odd parity; pst[k]: the class's prepare stream; par: parity
+// of the day being launched
+struct K1ChainStreams { cudaStream_t st[4]; cudaEvent_t prep[4], done[4]; cudaEvent_t fork; cudaStream_t st2[4], pst[4]; int par; };
 
 // ---------------------------------------------------------------- Philox4x32-10
 __host__ __device__ __forceinline__ void philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,

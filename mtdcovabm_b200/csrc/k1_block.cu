@@ -867,6 +867,38 @@ int launch_k1_blocks(const DevCtx &c, cudaStream_t sa, cudaStream_t sb, int sm_c
         if (cs) cudaEventRecord(cs->done[k], st);
         return r;
     };
+    static const int sched = [] { const char *e = getenv("MTD_K1_SCHED"); return (e && *e) ? atoi(e) : 1; }();
+    if (sched == 1 && cs && c.k1_split) {
+        // One stream per size class: ordering helper, prepare kernel and chain kernel of a class follow each other on the
+        // class's own stream, and the four classes start together.  A rank of a sharded run holds too few cells to fill the
+        // machine, and its K1 stage then lasts as long as the longest dependency chain: lining the classes up two by two on
+        // the auxiliary streams put prepare(320) + prepare(128) + chain(128) on one path.
+        n += launch_block_class<1024, 8, 1>(c, 7, sa, sm_count, 0);
+        for (int k = 3; k >= 0; k--) {
+            // prepare kernels of a class follow each other day by day on the class's prepare stream; the chain kernel goes
+            // to the chain stream of the day's parity, so that the chains of two consecutive days -- latency-bound, a few
+            // resident warps each -- run side by side with the next day's prepare and small-cell kernels
+            cudaStream_t st = cs->pst[k] ? cs->pst[k] : cs->st[k];
+            cudaStream_t cst = cs->pst[k] ? ((cs->par & 1) ? cs->st2[k] : cs->st[k]) : st;
+            cudaStreamWaitEvent(st, cs->fork, 0);
+            static const char *nm[4][3] = { { "class 64: fork seen", "class 64: prepared", "class 64: chain done" }, { "class 128: fork seen", "class 128: prepared", "class 128: chain done" },
+                                            { "class 192: fork seen", "class 192: prepared", "class 192: chain done" }, { "class 320: fork seen", "class 320: prepared", "class 320: chain done" } };
+            k1_tl_mark(nm[k][0], st);
+            switch (k) {
+            case 3: n += launch_block_class<320, 4, 6>(c, 6, st, sm_count, lpt[3]); break;
+            case 2: n += launch_block_class<192, 4, 8>(c, 5, st, sm_count, lpt[2]); break;
+            case 1: n += launch_block_class<128, 2, 16>(c, 4, st, sm_count, lpt[1]); break;
+            default: n += launch_block_class<64, 2, 16>(c, 3, st, sm_count, lpt[0]); break;
+            }
+            cudaEventRecord(cs->prep[k], st);             // the class is prepared: its chain kernel is next on this stream
+            k1_tl_mark(nm[k][1], st);
+            if (cst != st) cudaStreamWaitEvent(cst, cs->prep[k], 0);
+            n += launch_k1_chain(c, 3 + k, lpt[k] ? lpt[k] : 3 + k, cst, sm_count);
+            cudaEventRecord(cs->done[k], cst);
+            k1_tl_mark(nm[k][2], cst);
+        }
+        return n;
+    }
     n += launch_block_class<1024, 8, 1>(c, 7, sa, sm_count, 0);
     n += launch_block_class<320, 4, 6>(c, 6, sa, sm_count, lpt[3]);
     n += chain(3, sa);

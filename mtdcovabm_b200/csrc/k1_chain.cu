@@ -44,7 +44,7 @@ __device__ __forceinline__ long long tape_find_sel(const DevTape &T, int cell, i
 // Per group in shared memory: remaining degrees DEG[MMAX], draws u16[MMAX], alive / candidate / prefix words u32[BW] each,
 // the current main record u32[16].
 template <int G, int BW, int MMAX, typename DEG>
-__global__ void __launch_bounds__(K1C_WARPS * 32) k1_chain_kernel(DevCtx g, int cls, int list_region)
+__global__ void __launch_bounds__(K1C_WARPS * 32) k1_chain_kernel(DevCtx g, int cls, int list_region, int sparse_ok)
 {
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int GPW = 32 / G;
@@ -61,6 +61,10 @@ __global__ void __launch_bounds__(K1C_WARPS * 32) k1_chain_kernel(DevCtx g, int 
              *recw = (uint32_t *)(gs + o_rec);
     if (g.ctr->error) return;
     const int total = g.ctr->class_cells[cls];
+    // Few cells (a rank of a sharded run): one group per warp.  The groups of a warp follow their own control flow, so they
+    // take turns at the warp's issue slot, and a cell's chain -- bound by latency -- runs faster alone; with no more cells
+    // than warps in the grid every cell still has its group at once.
+    if (GPW > 1 && sparse_ok && total <= (int)gridDim.x * K1C_WARPS && lane >= G) return;
     const int32_t *list = g.class_list + (int64_t)list_region * g.class_stride;
     const bool replay = g.day.mode == MTD_MODE_REPLAY;
     int n_miss = 0;
@@ -204,7 +208,8 @@ int launch_chain(const DevCtx &c, int cls, int list_region, cudaStream_t st, int
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_chain_kernel<G, BW, MMAX, DEG>, K1C_WARPS * 32, smem);
         if (per_sm < 1) per_sm = 1;
     }
-    k1_chain_kernel<G, BW, MMAX, DEG><<<sm_count * per_sm, K1C_WARPS * 32, smem, st>>>(c, cls, list_region);
+    static const int sparse_ok = [] { const char *e = getenv("MTD_K1_CHAIN_SPARSE"); return (e && *e == '1') ? 1 : 0; }();      // off by default: faster stand-alone, slower inside the day pipeline (profiles/r02_k1_schedule_ab.txt)
+    k1_chain_kernel<G, BW, MMAX, DEG><<<sm_count * per_sm, K1C_WARPS * 32, smem, st>>>(c, cls, list_region, sparse_ok);
     return 1;
 }
 

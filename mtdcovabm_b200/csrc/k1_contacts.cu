@@ -455,7 +455,15 @@ int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int li
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_small_kernel<G>, K1S_THREADS, 0);
         if (per_sm < 1) per_sm = 1;
     }
-    k1_small_kernel<G><<<sm_count * per_sm, K1S_THREADS, 0, st>>>(c, cls, list_region);
+    // Grid of several rounds of the resident blocks: the cells are dealt out grid-stride, so a block of a larger grid
+    // simply takes fewer of them and gives its SM slot back sooner -- to the chain kernels of the large classes and the
+    // short kernels of the day's other stages, which wait on streams of higher priority.
+    // Measured (profiles/r02_k1_schedule_ab.txt): four rounds pay on a full-size day (14M intervals: the state chain gets
+    // its SM slots sooner, 4.85 against 5.0 ms per day), one round on the 1.8M-interval shard of an 8-rank run (0.80 against
+    // 0.94: with few cells per group the software pipeline of the kernel never fills).
+    static const int rounds_env = [] { const char *e = getenv("MTD_K1_SMALL_ROUNDS"); return (e && *e) ? atoi(e) : 0; }();
+    const int rounds = rounds_env > 0 ? rounds_env : (c.M >= 8000000 ? 4 : (c.M >= 4000000 ? 2 : 1));
+    k1_small_kernel<G><<<sm_count * per_sm * rounds, K1S_THREADS, 0, st>>>(c, cls, list_region);
     return 1;
 }
 
@@ -475,6 +483,34 @@ int k1_impl()
     static const int v = [] { const char *e = getenv("MTD_K1_IMPL"); return !e ? K1_IMPL_DEFAULT : (e[0] == 's' ? 2 : (e[0] == 'b' ? 1 : 0)); }();
     return v;
 }
+// ---- timeline of one K1 stage (development aid, see common.cuh)
+#include <vector>
+#include <string>
+#include <stdio.h>
+static int g_tl_target = [] { const char *e = getenv("MTD_K1_TIMELINE"); return (e && *e) ? atoi(e) : -1; }();
+static int g_tl_count = 0;
+static bool g_tl_on = false;
+static std::vector<std::pair<std::string, cudaEvent_t>> g_tl;
+void k1_tl_mark(const char *name, cudaStream_t st)
+{
+    if (!g_tl_on) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, st);
+    g_tl.emplace_back(name, e);
+}
+static void k1_tl_begin(cudaStream_t st)
+{
+    if (g_tl_target < 0) return;
+    if (g_tl_on) {                                     // the stage after the recorded one: print and stop
+        cudaDeviceSynchronize();
+        for (auto &m : g_tl) { float ms = 0; cudaEventElapsedTime(&ms, g_tl[0].second, m.second); fprintf(stderr, "k1_timeline %8.1f us  %s\n", ms * 1e3, m.first.c_str()); }
+        g_tl_on = false; g_tl_target = -1;
+        return;
+    }
+    if (g_tl_count++ == g_tl_target) { g_tl_on = true; k1_tl_mark("stage begins (main)", st); }
+}
+
 bool k1_use_legacy() { return k1_impl() == 0; }
 bool k1_use_split() { return k1_impl() == 2; }
 
@@ -487,9 +523,12 @@ static int env_int(const char *name, int dflt)
 // The block-per-cell kernels of the classes above 32 intervals (k1_block.cu) are bound by the latency of the sequential
 // greedy chain of their cells, the sub-warp kernels of the small classes by instruction issue: the two families run side
 // by side -- large classes on two auxiliary streams, small classes on the main stream -- and join before K2.
+// joined (optional): receives false when the stage's side streams were NOT joined into st -- the caller then makes the
+// consumer of the stage wait for ev_join, ev_join2 and cs->done[0..3] itself (see the day overlap in capi.cu).
 int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t aux2, cudaEvent_t ev_fork, cudaEvent_t ev_join,
-              cudaEvent_t ev_join2, int sm_count, unsigned char *big_ws, int mm_big, const K1ChainStreams *cs)
+              cudaEvent_t ev_join2, int sm_count, unsigned char *big_ws, int mm_big, const K1ChainStreams *cs, bool *joined)
 {
+    k1_tl_begin(st);
     static const int overlap = env_int("MTD_K1_OVERLAP", 1);
     static const int lpt = env_int("MTD_K1_LPT", 7);     // bit 0: class 6, bit 1: class 5 longest-first; bit 2: small classes by size
     cudaStream_t sl = st, sl2 = st;
@@ -507,7 +546,17 @@ int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t a
     if (k1_use_legacy() && c.k1_bits) {
         n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, none, true, nullptr);
         n += launch_k1_legacy(c, sl, sl2, sm_count);
-    } else n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, regs, false, (sl != st) ? cs : nullptr);
+    } else {
+        K1ChainStreams csf;
+        if (cs) { csf = *cs; csf.fork = ev_fork; }
+        n = launch_k1_blocks(c, sl, sl2, sm_count, big_ws, mm_big, regs, false, (sl != st && cs) ? &csf : nullptr);
+    }
+    // MTD_K1_SMALL_AFTER_PREP=1: the small-cell kernels start when the large classes are prepared, i.e. together with the
+    // chain kernels (which sit on streams of higher priority and take the few SM slots they need first) instead of
+    // filling the machine ahead of them and holding it until they end.
+    static const int small_after_prep = env_int("MTD_K1_SMALL_AFTER_PREP", 0);
+    static const int sched = env_int("MTD_K1_SCHED", 1);
+    const bool class_streams = sched == 1 && sl != st && cs && c.k1_split && !(k1_use_legacy() && c.k1_bits);
     const int sorted_small = (lpt & 4) ? MTD_NUM_CLASSES + 2 : 0;      // regions +2, +3, +4 = classes 0, 1, 2 by size
     if (sorted_small) {
         cudaMemsetAsync(c.k1_bins, 0, sizeof(int32_t) * 2 * 96, st);
@@ -515,15 +564,27 @@ int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t a
         k1_bin_scatter_kernel<<<sm_count * 2, K1B_THREADS, 0, st>>>(c, sorted_small);
         n += 2;
     }
+    if (small_after_prep && class_streams) for (int k = 0; k < 4; k++) cudaStreamWaitEvent(st, cs->prep[k], 0);
+    k1_tl_mark("main: before small<16> (bin sort done, prep waits)", st);
     n += launch_small<16>(c, 1, st, sm_count, sorted_small ? sorted_small + 1 : 1);
+    k1_tl_mark("main: small<16> done", st);
     n += launch_small<8>(c, 0, st, sm_count, sorted_small ? sorted_small : 0);
+    k1_tl_mark("main: small<8> done", st);
     n += launch_small<32>(c, 2, st, sm_count, sorted_small ? sorted_small + 2 : 2);
-    if (sl != st) {
+    k1_tl_mark("main: small<32> done", st);
+    if (joined) *joined = true;
+    if (sl != st && joined && class_streams) {
+        // the caller joins: st carries on with the next day's small cells while this day's chains still run
+        cudaEventRecord(ev_join, sl);
+        cudaEventRecord(ev_join2, sl2);
+        *joined = false;
+    } else if (sl != st) {
         cudaEventRecord(ev_join, sl);
         cudaEventRecord(ev_join2, sl2);
         cudaStreamWaitEvent(st, ev_join, 0);
         cudaStreamWaitEvent(st, ev_join2, 0);
         if (cs && c.k1_split && !(k1_use_legacy() && c.k1_bits)) for (int k = 0; k < 4; k++) cudaStreamWaitEvent(st, cs->done[k], 0);
     }
+    k1_tl_mark("main: joined", st);
     return n;
 }
