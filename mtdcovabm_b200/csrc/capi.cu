@@ -340,8 +340,11 @@ static int create_impl(mtd_handle h)
         int lo = 0, hi = 0;
         CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
         const char *pe = getenv("MTD_K0_PRIO");
-        const int prio = (pe && *pe == '1') ? hi : ((pe && *pe == '2') ? 0 : lo);
-        CK(cudaStreamCreateWithPriority(&h->k0_stream, cudaStreamNonBlocking, prio));   // default: fills what K1 leaves free
+        // K0 of day d+1 gates K1 of day d+1, and K1 stages hold the machine back to back: at the default priority K0 only got
+        // its SM slots when K1 of day d drained, which put K1(d) -> K0(d+1) -> K1(d+1) in a row (8-rank shard: 0.755 -> 0.721
+        // ms/day with K0 above the K1 kernels, profiles/r02_k1_schedule_ab.txt).  MTD_K0_PRIO=0: lowest priority.
+        const int prio = (pe && *pe == '0') ? lo : hi;
+        CK(cudaStreamCreateWithPriority(&h->k0_stream, cudaStreamNonBlocking, prio));
         CK(cudaEventCreateWithFlags(&h->ev_k0_ready, cudaEventDisableTiming));
         CK(cudaStreamCreateWithFlags(&h->k1_stream, cudaStreamNonBlocking));
         { const char *e4 = getenv("MTD_K1_STREAMS"); if (!(e4 && *e4 == '1')) CK(cudaStreamCreateWithFlags(&h->k1_stream2, cudaStreamNonBlocking)); }

@@ -463,7 +463,11 @@ int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int li
     // 0.94: with few cells per group the software pipeline of the kernel never fills).
     static const int rounds_env = [] { const char *e = getenv("MTD_K1_SMALL_ROUNDS"); return (e && *e) ? atoi(e) : 0; }();
     const int rounds = rounds_env > 0 ? rounds_env : (c.M >= 8000000 ? 4 : (c.M >= 4000000 ? 2 : 1));
-    k1_small_kernel<G><<<sm_count * per_sm * rounds, K1S_THREADS, 0, st>>>(c, cls, list_region);
+    // MTD_K1_SMALL_PER_SM=n: at most n blocks per SM's worth of grid (4 fill the register file; 3 leave a quarter of it to the
+    // short kernels of the state chain, which otherwise wait for a persistent block to end)
+    static const int per_sm_cap = [] { const char *e = getenv("MTD_K1_SMALL_PER_SM"); return (e && *e) ? atoi(e) : 0; }();
+    const int psm = (per_sm_cap > 0 && per_sm_cap < per_sm) ? per_sm_cap : per_sm;
+    k1_small_kernel<G><<<sm_count * psm * rounds, K1S_THREADS, 0, st>>>(c, cls, list_region);
     return 1;
 }
 
@@ -502,7 +506,8 @@ void k1_tl_mark(const char *name, cudaStream_t st)
 static void k1_tl_begin(cudaStream_t st)
 {
     if (g_tl_target < 0) return;
-    if (g_tl_on) {                                     // the stage after the recorded one: print and stop
+    if (g_tl_on && g_tl_count++ == g_tl_target + 1) { k1_tl_mark("NEXT stage begins (main)", st); return; }   // two consecutive stages, one origin
+    if (g_tl_on) {                                     // the stage after the recorded ones: print and stop
         cudaDeviceSynchronize();
         for (auto &m : g_tl) { float ms = 0; cudaEventElapsedTime(&ms, g_tl[0].second, m.second); fprintf(stderr, "k1_timeline %8.1f us  %s\n", ms * 1e3, m.first.c_str()); }
         g_tl_on = false; g_tl_target = -1;
