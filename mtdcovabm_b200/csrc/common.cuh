@@ -152,7 +152,7 @@ struct DevCtx {
 // ---------------------------------------------------------------- split K1: the per-cell record between its three kernels
 // Cells of 33..320 intervals: k1_block.cu (a block per cell) prepares the cell -- agents, adjacency rows, degrees, greedy
 // order -- and leaves this record in HBM at k1_rec + 80 * slot_off[slot] (80 bytes per interval of the cell: enough for
-// every cell of up to 336 intervals); k1_chain.cu runs the sequential greedy sampling with ONE THREAD per cell on it (32
+// every cell of up to 336 intervals); k1_chain.cu runs the sequential greedy sampling with a GROUP OF 8 LANES per cell on it (4
 // cells per warp); K2 builds the contact rows of the selected pairs from it.
 //   header  int4 {n_act, n, m, bwm}; alive0 u32[bw2] (first positions of the agents with degree > 0)
 //   mains   n_act records in greedy order, (6 + bw2) words each: {x | first position << 16, agent id, the agent's first
