@@ -37,6 +37,8 @@ def close_handles():
 
 
 def pack_sched(day, trans, ts):
+    if not -32768 <= int(day) <= 32767:      # 16-bit day field of the packed schedule entry (MTD_NONE = -32768 is "None")
+        raise ValueError("schedule day %d does not fit the 16-bit field of the packed entry" % int(day))
     return np.int32(np.uint32((int(day) & 0xFFFF) << 16 | (int(trans) & 0xFF) << 8 | (int(ts) & 0xFF)))
 
 

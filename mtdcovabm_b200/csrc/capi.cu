@@ -40,6 +40,7 @@ int launch_k8(int64_t n_itin, const int64_t *ent_off, const int16_t *ent_ts, con
 int launch_xchg_push(const DevExchange &x, int par, unsigned long long seq, cudaStream_t st);
 int launch_xchg_wait(const DevExchange &x, int par, unsigned long long seq, StateCounters *sctr, cudaStream_t st);
 int launch_occupancy(const DevCtx &c, unsigned long long *out6, cudaStream_t st, int sm_count);
+int launch_k4_rebuild_next(const DevCtx &c, cudaStream_t st, int sm_count);
 int launch_scan_nrows(const DevCtx &c, long long *scan_tmp, cudaStream_t st);
 int launch_stream_out(void *dst, const void *src, const int64_t *n_items, int64_t item_bytes, int64_t cap_items,
                       int blocks, cudaStream_t st);
@@ -266,7 +267,7 @@ static int create_impl(mtd_handle h)
     c.cell_type = ct; c.cell_indid = ci; c.age_bracket = ab; c.epi_age_bracket = eb; c.soc_rate = sr; c.res_cellid = rc;
     { AgentAttr *at; DA(at, N); c.k1_attr = at; }
     DA(c.seir, N); DA(c.inf_type, N); DA(c.inf_sev, N); DA(c.last_dose_day, N);
-    DA(c.sched, N * MTD_MAXSCHED); DA(c.sched_cnt, N); DA(c.test_day, 2 * N); DA(c.test_result_day, 2 * N);
+    DA(c.sched, N * MTD_MAXSCHED); DA(c.sched_cnt, N); DA(c.sched_next, N + 8); DA(c.test_day, 2 * N); DA(c.test_result_day, 2 * N);
     DA(c.quarantine, 3 * N); DA(c.hosp, 3 * N);
     DA(c.cell_count, C); DA(c.cell_first, C); DA(c.cell_base, C); DA(c.iv_pos, M); DA(c.flag_scan, M + 64);
     DA(c.slot_cell, S + 1); DA(c.slot_m, S + 1); DA(c.slot_first, S + 1); DA(c.slot_act, S + 1);
@@ -370,6 +371,7 @@ static int create_impl(mtd_handle h)
     CK(cudaMemsetAsync(c.seir, 0, N, h->stream)); CK(cudaMemsetAsync(c.inf_type, 0, N, h->stream));
     CK(cudaMemsetAsync(c.inf_sev, 0, N, h->stream)); CK(cudaMemsetAsync(c.sched_cnt, 0, N, h->stream));
     CK(cudaMemsetAsync(c.sched, 0, sizeof(int32_t) * N * MTD_MAXSCHED, h->stream));
+    CK(cudaMemsetAsync(c.sched_next, 0x7f, sizeof(int16_t) * (N + 8), h->stream));      // MTD_SCHED_NEXT_NONE
     CK(cudaMemsetAsync(c.ctr, 0, sizeof(DevCounters), h->stream));
     CK(cudaMemsetAsync(c.sctr, 0, sizeof(StateCounters), h->stream));
     CK(cudaMemsetAsync(ci, 0xff, sizeof(int16_t) * C, h->stream));
@@ -508,6 +510,7 @@ extern "C" int mtd_set_state(mtd_handle h, int64_t n, const int8_t *seir, const 
     COPY_IN(h->c.sched, sched, 4 * N * MTD_MAXSCHED); COPY_IN(h->c.sched_cnt, sched_cnt, N);
     COPY_IN(h->c.test_day, test_day, 8 * N); COPY_IN(h->c.test_result_day, test_result_day, 8 * N);
     COPY_IN(h->c.quarantine, quarantine, 12 * N); COPY_IN(h->c.hosp, hosp, 12 * N);
+    if (sched || sched_cnt) launch_k4_rebuild_next(h->c, h->stream, h->sm_count);      // K4's per-agent "earliest entry day"
     if (mem == MTD_MEM_HOST) CK(cudaStreamSynchronize(h->stream));
     return MTD_OK;
 }

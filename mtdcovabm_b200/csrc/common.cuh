@@ -97,6 +97,7 @@ struct DevCtx {
     const AgentAttr *k1_attr;  // {soc_rate, age_bracket} of every agent in ONE 16-byte record: K1's gather touches one sector
     // state
     int8_t *seir; int8_t *inf_type; int8_t *inf_sev; int32_t *last_dose_day;
+    int16_t *sched_next;       // [n_agents] earliest day among the agent's schedule entries (MTD_SCHED_NEXT_NONE = none): K4's filter
     int32_t *sched; uint8_t *sched_cnt; int32_t *test_day; int32_t *test_result_day; int32_t *quarantine; int32_t *hosp;
     // day inputs
     int64_t M;
@@ -175,6 +176,7 @@ struct K1Rec {
         o_aoff = o;
     }
 };
+#define MTD_SCHED_NEXT_NONE 0x7f7f   // "no entry" of DevCtx::sched_next (what a byte-wise memset of 0x7f leaves; above every day)
 #define MTD_K1_REC_STRIDE 80       // bytes of record space per interval
 #define MTD_K1_SPLIT_MAX_M 320     // largest cell the split path takes
 

@@ -9,6 +9,7 @@
 //   finish   : per-cell CSR base (so that the scatter needs one gather), capacity check
 //   scatter  : records into their cell segment (arrival order; K1 restores list order by emission index)
 #include "common.cuh"
+#include <stdlib.h>
 
 #include "scan.cuh"
 
@@ -240,7 +241,10 @@ int launch_k0(const DevCtx &c, long long *scan_tmp, cudaStream_t st, int sm_coun
     if (c.M <= 0) return 0;
     const int threads = 256;
     const int64_t want = (c.M + threads - 1) / threads;
-    const unsigned grid = (unsigned)(want < (int64_t)sm_count * 16 ? want : (int64_t)sm_count * 16);
+    // blocks per SM's worth of grid: the kernels are grid-stride, so a larger grid means shorter blocks and SM slots that turn
+    // over faster for the short kernels of the state chain that run beside K0 (MTD_K0_BLOCKS_PER_SM, default 16)
+    static const int bps = [] { const char *e = getenv("MTD_K0_BLOCKS_PER_SM"); const int v = (e && *e) ? atoi(e) : 16; return v < 1 ? 1 : v; }();
+    const unsigned grid = (unsigned)(want < (int64_t)sm_count * bps ? want : (int64_t)sm_count * bps);
     const int64_t n_words = (c.M + 31) >> 5;
     int32_t *word_cnt = c.flag_scan;                                  // [n_words + 1], scanned in place
     uint32_t *words = (uint32_t *)(c.flag_scan + n_words + 2);        // [n_words]

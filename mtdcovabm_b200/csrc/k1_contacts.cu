@@ -211,6 +211,7 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
     __shared__ uint16_t sh_se[K1S_THREADS];
     __shared__ __align__(16) uint32_t sh_mask[K1S_THREADS][6];     // agent occupancy masks (5 words used)
     __shared__ uint16_t sh_pair[2 * K1S_THREADS];                  // reserved rows of the cell: 2 G pairs per group
+    __shared__ __align__(16) uint32_t sh_draw[K1S_THREADS][4];     // first Philox block of the agent on this lane (its first four draws as a main agent)
 
     const int lane = threadIdx.x & 31;
     const int gl = lane & (G - 1);                  // lane in group
@@ -357,6 +358,15 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
             ord += (dq > deg) || (dq == deg && aq > agent);
         }
 
+        // the first Philox block of every agent that can become a main agent, all agents of the warp's cells in ONE pass of the
+        // generator instead of one pass per main agent inside the sequential loop below
+        const bool philox_mode = g.day.mode != MTD_MODE_REPLAY;
+        if (philox_mode && isag && deg > 0) {
+            uint32_t w4[4];
+            philox4x32((uint32_t)g.day.day, (uint32_t)cell, (uint32_t)agent, 0u, g.day.seed, SITE_SELECT, w4);
+            *(uint4 *)sh_draw[threadIdx.x] = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+        }
+        __syncwarp(gmask);
         // ---- 6. greedy sampling + create_contacts (contactnetwork.py:287-301, 386-424) ----
         RowRec *rows = g.scratch_rows + g.slot_rowoff[slot];
         const int row_cap = g.slot_rowbound[slot];
@@ -393,9 +403,14 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
                 // its own pick's rank among the ORIGINAL candidates, q += (q >= r_s) for s = t-1 .. 0, all picks at once.
                 int rq = 0;
                 if (gl < d) {
-                    uint32_t w4[4];
-                    philox4x32((uint32_t)g.day.day, (uint32_t)cell, (uint32_t)agx, (uint32_t)(gl >> 2), g.day.seed, SITE_SELECT, w4);
-                    rq = (int)__umulhi(pick4(w4, gl & 3), (uint32_t)(nc - gl));
+                    uint32_t word;
+                    if (gl < 4) word = sh_draw[tb + (x - gbase)][gl];
+                    else {
+                        uint32_t w4[4];
+                        philox4x32((uint32_t)g.day.day, (uint32_t)cell, (uint32_t)agx, (uint32_t)(gl >> 2), g.day.seed, SITE_SELECT, w4);
+                        word = pick4(w4, gl & 3);
+                    }
+                    rq = (int)__umulhi(word, (uint32_t)(nc - gl));
                 }
                 int q = rq;
                 for (int s = d - 2; s >= 0; s--) {
@@ -466,7 +481,10 @@ int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int li
     // MTD_K1_SMALL_PER_SM=n: at most n blocks per SM's worth of grid (4 fill the register file; 3 leave a quarter of it to the
     // short kernels of the state chain, which otherwise wait for a persistent block to end)
     static const int per_sm_cap = [] { const char *e = getenv("MTD_K1_SMALL_PER_SM"); return (e && *e) ? atoi(e) : 0; }();
-    const int psm = (per_sm_cap > 0 && per_sm_cap < per_sm) ? per_sm_cap : per_sm;
+    // default: on a rank's shard (one round, the blocks stay until the class is done) half of the resident blocks -- the
+    // shard's K1 loses nothing (0.715 -> 0.715 ms/day, K1 alone 0.69 -> 0.60: the prepare and chain kernels get the room)
+    const int want = per_sm_cap > 0 ? per_sm_cap : (c.M >= 8000000 ? per_sm : (c.M >= 4000000 ? 3 : 2));
+    const int psm = want < per_sm ? want : per_sm;
     k1_small_kernel<G><<<sm_count * psm * rounds, K1S_THREADS, 0, st>>>(c, cls, list_region);
     return 1;
 }

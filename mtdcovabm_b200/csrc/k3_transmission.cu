@@ -378,11 +378,13 @@ __global__ void k9_seed_kernel(DevCtx c, int64_t n, const int32_t *ids, const in
                           c.day.testing_enabled != 0, c.day.quarantine_enabled != 0, c.test_day[2 * (int64_t)ag] != MTD_NONE, T);
         if (D.miss) atomicAdd(&status[2], D.miss);
         int cnt = c.sched_cnt[ag];
+        int nx = c.sched_next[ag];
         for (int k = 0; k < T.ns; k++) {
-            if (cnt < MTD_MAXSCHED) c.sched[(int64_t)ag * MTD_MAXSCHED + cnt++] = T.sched[k];
+            if (cnt < MTD_MAXSCHED) { c.sched[(int64_t)ag * MTD_MAXSCHED + cnt++] = T.sched[k]; nx = min(nx, T.sched[k] >> 16); }
             else atomicAdd(&status[1], 1);
         }
         c.sched_cnt[ag] = (uint8_t)cnt;
+        c.sched_next[ag] = (int16_t)nx;
         int seir = S_EXP, it = T.inf_type, sv = SV_UNDEF;
         if (incr0 < 1) {
             switch (T.first_T) {
@@ -439,11 +441,13 @@ __global__ void k3_apply_kernel(DevCtx c, const int32_t *bufs, int n_bufs, int64
             if (c.win[ag] != key) continue;
             int ns = (rec[3] >> 8) & 0xff;
             int cnt = c.sched_cnt[ag];
+            int nx = c.sched_next[ag];
             for (int k = 0; k < ns; k++) {            // agent_state_transition_by_day.append(...)
-                if (cnt < MTD_MAXSCHED) c.sched[(int64_t)ag * MTD_MAXSCHED + cnt++] = rec[4 + k];
+                if (cnt < MTD_MAXSCHED) { c.sched[(int64_t)ag * MTD_MAXSCHED + cnt++] = rec[4 + k]; nx = min(nx, rec[4 + k] >> 16); }
                 else atomicAdd(&c.sctr->sched_overflow, 1);
             }
             c.sched_cnt[ag] = (uint8_t)cnt;
+            c.sched_next[ag] = (int16_t)nx;
             c.seir[ag] = S_EXP; c.inf_type[ag] = (int8_t)(rec[3] & 0xff); c.inf_sev[ag] = SV_UNDEF;   // :219-225
             if (rec[10] != MTD_NONE) {
                 c.test_day[2 * (int64_t)ag] = rec[10]; c.test_day[2 * (int64_t)ag + 1] = rec[11];
@@ -493,41 +497,85 @@ __device__ __forceinline__ void transition(int seir, int it, int sv, int trans, 
     }
 }
 
-__device__ __forceinline__ void k4_advance_agent(const DevCtx &c, int64_t ag, int cnt, int day)
+// fire: false = the agent is masked out today (its entry dated today stays, unfired); either way the agent's earliest
+// entry day is recomputed over whatever its list holds afterwards
+__device__ __forceinline__ void k4_advance_agent(const DevCtx &c, int64_t ag, int day, bool fire)
 {
     int32_t *sc = c.sched + ag * MTD_MAXSCHED;
+    int cnt = c.sched_cnt[ag];
     int today = -1;
-    for (int i = 0; i < cnt; i++) if ((sc[i] >> 16) == day) { today = i; break; }   // first entry dated today only
-    if (today < 0) return;
-    int trans = (sc[today] >> 8) & 0xff;
-    int ns, nt, nv;
-    transition(c.seir[ag], c.inf_type[ag], c.inf_sev[ag], trans, ns, nt, nv);
-    c.seir[ag] = (int8_t)ns; c.inf_type[ag] = (int8_t)nt; c.inf_sev[ag] = (int8_t)nv;
-    for (int i = today; i + 1 < cnt; i++) sc[i] = sc[i + 1];                          // del list[today_index]
-    c.sched_cnt[ag] = (uint8_t)(cnt - 1);
+    if (fire) for (int i = 0; i < cnt; i++) if ((sc[i] >> 16) == day) { today = i; break; }   // first entry dated today only
+    if (today >= 0) {
+        int trans = (sc[today] >> 8) & 0xff;
+        int ns, nt, nv;
+        transition(c.seir[ag], c.inf_type[ag], c.inf_sev[ag], trans, ns, nt, nv);
+        c.seir[ag] = (int8_t)ns; c.inf_type[ag] = (int8_t)nt; c.inf_sev[ag] = (int8_t)nv;
+        for (int i = today; i + 1 < cnt; i++) sc[i] = sc[i + 1];                          // del list[today_index]
+        cnt--;
+        c.sched_cnt[ag] = (uint8_t)cnt;
+    }
+    // earliest day over what is left: entries of today or earlier that did not fire (a second entry of the same day, a masked
+    // agent's entry) keep it at or below today, so the agent is simply looked at again tomorrow
+    int nx = MTD_SCHED_NEXT_NONE;
+    for (int i = 0; i < cnt; i++) nx = min(nx, sc[i] >> 16);
+    c.sched_next[ag] = (int16_t)nx;
 }
 
-// sched_cnt is read 16 agents per load; almost every agent has an empty schedule
-__global__ void k4_advance_kernel(DevCtx c, int day, const uint8_t *mask)
+// K4 reads one 16-bit "earliest entry day" per agent, 8 agents per load: an agent is touched on the day one of its entries
+// is due, not on every day it has a pending schedule.  The due agents of a warp's 256 agents are first collected in a
+// shared queue and then advanced a lane per agent: at the height of a wave several percent of the population change state
+// every day, and advancing them where they are found would leave 31 lanes idle behind each of them.
+#define K4_THREADS 256
+__global__ void __launch_bounds__(K4_THREADS) k4_advance_kernel(DevCtx c, int day, const uint8_t *mask)
 {
-    const int64_t n16 = c.n_agents >> 4;
-    const uint4 *cnt16 = (const uint4 *)c.sched_cnt;
-    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n16; q += (int64_t)gridDim.x * blockDim.x) {
-        const uint4 v = cnt16[q];
-        if ((v.x | v.y | v.z | v.w) == 0u) continue;
-        const uint32_t w[4] = { v.x, v.y, v.z, v.w };
+    __shared__ int32_t queue[K4_THREADS / 32][256];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int32_t *qw = queue[wid];
+    const int64_t n8 = c.n_agents >> 3;
+    const uint4 *nx8 = (const uint4 *)c.sched_next;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    // the trip count is the same for every lane of a warp (the loop body holds warp-wide primitives)
+    for (int64_t q0 = (int64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31); q0 < n8; q0 += stride) {
+        const int64_t q = q0 + lane;
+        uint32_t due = 0;                                                     // bit k: agent 8 q + k has an entry due
+        if (q < n8) {
+            const uint4 v = nx8[q];
+            const uint32_t w[4] = { v.x, v.y, v.z, v.w };
 #pragma unroll
-        for (int k = 0; k < 16; k++) {
-            const int cnt = (int)((w[k >> 2] >> (8 * (k & 3))) & 0xffu);
-            const int64_t ag = (q << 4) + k;
-            if (cnt == 0 || (mask && !mask[ag])) continue;
-            k4_advance_agent(c, ag, cnt, day);
+            for (int k = 0; k < 8; k++) {
+                const int nx = (int)(int16_t)((w[k >> 1] >> (16 * (k & 1))) & 0xffffu);
+                due |= (nx <= day ? 1u : 0u) << k;
+            }
         }
+        if (__ballot_sync(FULLMASK, due != 0) == 0) continue;
+        const int cnt = __popc(due);
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULLMASK, incl, o); if (lane >= o) incl += t; }
+        const int total = __shfl_sync(FULLMASK, incl, 31);
+        int pos = incl - cnt;
+        for (uint32_t b = due; b; b &= b - 1) qw[pos++] = (int32_t)((q << 3) + __ffs(b) - 1);
+        __syncwarp();
+        for (int i = lane; i < total; i += 32) {
+            const int64_t ag = qw[i];
+            k4_advance_agent(c, ag, day, !(mask && !mask[ag]));
+        }
+        __syncwarp();
     }
-    if (blockIdx.x == 0 && threadIdx.x < (int)(c.n_agents & 15)) {          // tail
-        const int64_t ag = (n16 << 4) + threadIdx.x;
+    if (blockIdx.x == 0 && threadIdx.x < (int)(c.n_agents & 7)) {          // tail
+        const int64_t ag = (n8 << 3) + threadIdx.x;
+        if ((int)c.sched_next[ag] <= day) k4_advance_agent(c, ag, day, !(mask && !mask[ag]));
+    }
+}
+
+// sched_next from scratch (after the schedules were uploaded: mtd_set_state, checkpoints)
+__global__ void k4_rebuild_next_kernel(DevCtx c)
+{
+    for (int64_t ag = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; ag < c.n_agents; ag += (int64_t)gridDim.x * blockDim.x) {
         const int cnt = c.sched_cnt[ag];
-        if (cnt != 0 && !(mask && !mask[ag])) k4_advance_agent(c, ag, cnt, day);
+        int nx = MTD_SCHED_NEXT_NONE;
+        for (int i = 0; i < cnt && i < MTD_MAXSCHED; i++) nx = min(nx, c.sched[ag * MTD_MAXSCHED + i] >> 16);
+        c.sched_next[ag] = (int16_t)nx;
     }
 }
 
@@ -658,9 +706,15 @@ int launch_k3_apply(const DevCtx &c, const int32_t *bufs, int n_bufs, int64_t ca
     return resolve ? 3 : 2;
 }
 
+int launch_k4_rebuild_next(const DevCtx &c, cudaStream_t st, int sm_count)
+{
+    k4_rebuild_next_kernel<<<sm_count * 8, 256, 0, st>>>(c);
+    return 1;
+}
+
 int launch_k4(const DevCtx &c, int32_t day, const uint8_t *mask, cudaStream_t st, int sm_count)
 {
-    k4_advance_kernel<<<sm_count * 4, 256, 0, st>>>(c, day, mask);
+    k4_advance_kernel<<<sm_count * 4, K4_THREADS, 0, st>>>(c, day, mask);
     return 1;
 }
 
