@@ -117,6 +117,13 @@ __global__ void __launch_bounds__(256) k2_compact_kernel(DevCtx c)
                 for (int r = threadIdx.x; r < cnt; r += blockDim.x) k2_copy_row(c, src + r, dst + r, sc);
         }
     }
+    // Cells of up to 32 intervals hold a handful of rows each (5 on average): the rows of a warp's 32 slots are numbered
+    // through (inclusive prefix of the counts in shared memory) and copied 32 at a time, each lane finding its row's slot by
+    // a binary search over the prefix -- instead of one slot after the other with a few lanes busy.
+    __shared__ int32_t sh_incl[8][32];
+    __shared__ int64_t sh_src[8][32], sh_dst[8][32];
+    __shared__ uint8_t sh_sct[8][32];
+    const int wid = threadIdx.x >> 5;
     for (int s0 = gwarp * 32; s0 < n_slots; s0 += warps * 32) {
         int s = s0 + lane;
         int cnt = 0, sct = 0; int64_t src = 0, dst = 0;
@@ -124,14 +131,20 @@ __global__ void __launch_bounds__(256) k2_compact_kernel(DevCtx c)
             cnt = c.slot_nrows[s]; src = c.slot_rowoff[s]; dst = c.slot_denseoff[s];
             if (c.rows12 && cnt > 0) sct = simcelltype_of(c.cell_type[c.slot_cell[s]]);
         }
-        uint32_t have = __ballot_sync(FULLMASK, cnt > 0);
-        while (have) {
-            int l = __ffs(have) - 1;
-            have &= have - 1;
-            int n = __shfl_sync(FULLMASK, cnt, l);
-            int64_t sb = __shfl_sync(FULLMASK, src, l), db = __shfl_sync(FULLMASK, dst, l);
-            const uint32_t sc = (uint32_t)__shfl_sync(FULLMASK, sct, l);
-            for (int r = lane; r < n; r += 32) k2_copy_row(c, sb + r, db + r, sc);
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(FULLMASK, incl, o); if (lane >= o) incl += t; }
+        const int total_w = __shfl_sync(FULLMASK, incl, 31);
+        if (total_w == 0) continue;
+        __syncwarp();                                           // the previous iteration's readers are done
+        sh_incl[wid][lane] = incl; sh_src[wid][lane] = src - (incl - cnt); sh_dst[wid][lane] = dst - (incl - cnt);
+        sh_sct[wid][lane] = (uint8_t)sct;
+        __syncwarp();
+        for (int t = lane; t < total_w; t += 32) {
+            int j = 0;                                          // first slot whose inclusive count exceeds t
+#pragma unroll
+            for (int step = 16; step > 0; step >>= 1) if (sh_incl[wid][j + step - 1] <= t) j += step;
+            k2_copy_row(c, sh_src[wid][j] + t, sh_dst[wid][j] + t, (uint32_t)sh_sct[wid][j]);
         }
     }
 }
