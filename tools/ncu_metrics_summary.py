@@ -26,9 +26,9 @@ def main():
     L = load(sys.argv[1])
     marker = sys.argv[sys.argv.index("--day-marker") + 1] if "--day-marker" in sys.argv else "k1_block_kernel<1024, 16"
     starts = [i for i, x in enumerate(L) if marker in x["kernel"]]
-    per_day = starts[1] - starts[0]
-    n_days = len(starts) if len(L) - starts[-1] >= per_day else len(starts) - 1
-    sel = L[starts[0]:starts[0] + n_days * per_day]
+    n_days = len(starts) - 1                      # whole days only: from the first marker launch up to the last one
+    sel = L[starts[0]:starts[-1]]
+    per_day = len(sel) / n_days
     by_k = collections.OrderedDict()
     for x in sel:
         d = by_k.setdefault(short(x["kernel"]), collections.defaultdict(float))
@@ -37,7 +37,7 @@ def main():
             if m != "kernel":
                 d[m] += v
     tot = collections.defaultdict(float)
-    print("mean per day over %d days (%d profiled launches each)" % (n_days, per_day))
+    print("mean per day over %d days (%.1f profiled launches each)" % (n_days, per_day))
     print("  %-44s %5s %8s %8s %8s %10s %6s %6s %6s %6s" % ("kernel", "n/day", "us", "rd MB", "wr MB", "warp-inst", "issue%", "warps%", "thr/in", "L2hit"))
     for k, d in by_k.items():
         n = d["n"]
@@ -59,7 +59,7 @@ def main():
         iv = float(sys.argv[sys.argv.index("--intervals") + 1])
         json.dump({"source": "ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,smsp__inst_executed.sum,... -k regex:k1_|k2_ "
                              "(the K1 launches of whole days of the bench; mean per day), " + sys.argv[1],
-                   "kernel": "k1_contacts (%d profiled launches per day incl. K2)" % per_day, "days": n_days,
+                   "kernel": "k1_contacts (%.1f profiled launches per day incl. K2 and the state kernels; K1 = the k1_* kernels)" % per_day, "days": n_days,
                    "dram_bytes_read": tot["dram__bytes_read.sum"], "dram_bytes_write": tot["dram__bytes_write.sum"],
                    "dram_bytes_total": tot["dram__bytes_read.sum"] + tot["dram__bytes_write.sum"],
                    "warp_instructions": tot["smsp__inst_executed.sum"], "intervals_of_day": iv}, open(out, "w"), indent=1)
