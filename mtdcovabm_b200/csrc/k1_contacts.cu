@@ -203,8 +203,11 @@ __global__ void __launch_bounds__(K1B_THREADS) k1_bin_scatter_kernel(DevCtx g, i
 }
 
 
+// bin_lo, bin_hi: the kernel takes the cells of the size bins [bin_lo, bin_hi) of the class's size-sorted list (small_bin(): bin
+// 0 = the largest cells); bin_hi <= 0 = the whole list.  The class of up to 8 intervals is split this way: G = 8 for its cells of
+// 5..8 intervals, G = 4 (eight cells per warp) for those of up to 4, which leave half of an 8-lane group idle.
 template <int G>
-__global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int cls, int list_region)
+__global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int cls, int list_region, int bin_lo, int bin_hi)
 {
     // per-lane shared slots, indexed [group base + position]
     __shared__ int32_t sh_agent[K1S_THREADS];
@@ -220,7 +223,16 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
     const uint32_t gmask = gbits << gbase;
     const int tb = (int)threadIdx.x - gl;           // group base in the block-wide shared arrays
     if (g.ctr->error) return;
-    const int total = g.ctr->class_cells[cls];
+    int total = g.ctr->class_cells[cls];            // end of this kernel's range of the list
+    int begin = 0;
+    if (bin_hi > 0) {
+        int acc = 0;
+        for (int b = 0; b < 32; b++) {
+            if (b == bin_lo) begin = acc;
+            if (b == bin_hi) total = acc;
+            acc += g.k1_bins[cls * 32 + b];
+        }
+    }
     const int32_t *list = g.class_list + (int64_t)list_region * g.class_stride;
     const int n_groups = (gridDim.x * K1S_THREADS) / G;
     const mtd_params *P = g.P;
@@ -228,7 +240,7 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
     unsigned long long acc_pairs = 0, acc_pot = 0, acc_inc = 0;
 
     // the next cell's descriptor and this lane's record are fetched while the current cell is processed
-    int w = (blockIdx.x * K1S_THREADS + (int)threadIdx.x) / G;
+    int w = begin + (blockIdx.x * K1S_THREADS + (int)threadIdx.x) / G;
     int nx_slot = 0, nx2_slot = 0, nx_m = 0, nx_cell = 0, nx_act = 0; int64_t nx_base = 0;
     IvRec nx_rec; nx_rec.agent = 0; nx_rec.order = 0xffffffffu; nx_rec.se = 0; nx_rec.pad = 0;
     if (w < total) {
@@ -463,7 +475,7 @@ __global__ void __launch_bounds__(K1S_THREADS, 4) k1_small_kernel(DevCtx g, int 
 }
 
 template <int G>
-int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int list_region)
+int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int list_region, int bin_lo = 0, int bin_hi = 0)
 {
     static int per_sm = 0;
     if (per_sm == 0) {
@@ -485,7 +497,7 @@ int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int li
     // shard's K1 loses nothing (0.715 -> 0.715 ms/day, K1 alone 0.69 -> 0.60: the prepare and chain kernels get the room)
     const int want = per_sm_cap > 0 ? per_sm_cap : (c.M >= 8000000 ? per_sm : (c.M >= 4000000 ? 3 : 2));
     const int psm = want < per_sm ? want : per_sm;
-    k1_small_kernel<G><<<sm_count * psm * rounds, K1S_THREADS, 0, st>>>(c, cls, list_region);
+    k1_small_kernel<G><<<sm_count * psm * rounds, K1S_THREADS, 0, st>>>(c, cls, list_region, bin_lo, bin_hi);
     return 1;
 }
 
@@ -591,7 +603,13 @@ int launch_k1(const DevCtx &c, cudaStream_t st, cudaStream_t aux, cudaStream_t a
     k1_tl_mark("main: before small<16> (bin sort done, prep waits)", st);
     n += launch_small<16>(c, 1, st, sm_count, sorted_small ? sorted_small + 1 : 1);
     k1_tl_mark("main: small<16> done", st);
-    n += launch_small<8>(c, 0, st, sm_count, sorted_small ? sorted_small : 0);
+    // off by default: measured slower (4.61 -> 4.80 ms/day, K1 alone 3.00 -> 3.17: a fourth persistent kernel with its own ramp and
+    // tail costs more than the idle lanes of the cells of up to 4 intervals, whose iterations are short anyway); parity-tested
+    static const int small4 = env_int("MTD_K1_SMALL4", 0);
+    if (sorted_small && small4) {                       // bins of the class: 8 - m, so [0, 4) = 5..8 intervals, [4, 32) = up to 4
+        n += launch_small<8>(c, 0, st, sm_count, sorted_small, 0, 4);
+        n += launch_small<4>(c, 0, st, sm_count, sorted_small, 4, 32);
+    } else n += launch_small<8>(c, 0, st, sm_count, sorted_small ? sorted_small : 0);
     k1_tl_mark("main: small<8> done", st);
     n += launch_small<32>(c, 2, st, sm_count, sorted_small ? sorted_small + 2 : 2);
     k1_tl_mark("main: small<32> done", st);
