@@ -495,7 +495,7 @@ int launch_small(const DevCtx &c, int cls, cudaStream_t st, int sm_count, int li
     static const int per_sm_cap = [] { const char *e = getenv("MTD_K1_SMALL_PER_SM"); return (e && *e) ? atoi(e) : 0; }();
     // default: on a rank's shard (one round, the blocks stay until the class is done) half of the resident blocks -- the
     // shard's K1 loses nothing (0.715 -> 0.715 ms/day, K1 alone 0.69 -> 0.60: the prepare and chain kernels get the room)
-    const int want = per_sm_cap > 0 ? per_sm_cap : (c.M >= 8000000 ? per_sm : (c.M >= 4000000 ? 3 : 2));
+    const int want = per_sm_cap > 0 ? per_sm_cap : (c.M >= 8000000 ? per_sm : (c.M >= 2500000 ? 3 : 2));   // 3.5M intervals (a rank of 4): 1.28 -> 1.23 ms/day with 3
     const int psm = want < per_sm ? want : per_sm;
     k1_small_kernel<G><<<sm_count * psm * rounds, K1S_THREADS, 0, st>>>(c, cls, list_region, bin_lo, bin_hi);
     return 1;
