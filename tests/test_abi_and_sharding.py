@@ -132,3 +132,19 @@ def test_two_rank_delta_exchange_gloo():
     out = mp.get_context("spawn").Manager().dict()
     mp.spawn(_worker, args=(world, port, 64, out), nprocs=world, join=True)
     assert dict(out) == {0: 1, 1: 1}
+
+
+def test_package_import_sets_hardware_queue_count_for_multi_rank_runs_only():
+    """mtdcovabm_b200/__init__.py: CUDA_DEVICE_MAX_CONNECTIONS=32 under WORLD_SIZE > 1 unless the user set a value"""
+    import subprocess
+    import sys
+    code = "import os, mtdcovabm_b200; print(os.environ.get('CUDA_DEVICE_MAX_CONNECTIONS', 'unset'))"
+
+    def run(extra):
+        env = {k: v for k, v in os.environ.items() if k not in ("WORLD_SIZE", "CUDA_DEVICE_MAX_CONNECTIONS")}
+        env.update(extra)
+        return subprocess.run([sys.executable, "-c", code], cwd=ROOT, env=env, capture_output=True, text=True).stdout.strip()
+
+    assert run({}) == "unset"
+    assert run({"WORLD_SIZE": "8"}) == "32"
+    assert run({"WORLD_SIZE": "8", "CUDA_DEVICE_MAX_CONNECTIONS": "4"}) == "4"
