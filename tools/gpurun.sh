@@ -11,6 +11,9 @@
 #   perday    per-day-stream stage times (tools/k1_per_day.py)
 #   dictapi   cost of the reference-shaped dict API on the golden days (tools/time_dict_api.py)
 #   configs   the BASELINE.json configuration shapes through the whole day loop (tools/run_config.py)
+# A/B of environment switches on the device-resident bench: tools/ab.sh (one GPU; BENCH_ARGS="--shard-of 8" runs one rank's
+# shard of an 8-rank job alone) and tools/ab_n.sh (N GPUs through torchrun); their lines are collected in
+# profiles/r02_k1_schedule_ab.txt.
 set -u
 R=${1:-quick}; T=${2:-$R}; O=gpurun_out; mkdir -p $O
 case $R in
