@@ -39,7 +39,8 @@ def close_handles():
 def pack_sched(day, trans, ts):
     if not -32768 <= int(day) <= 32767:      # 16-bit day field of the packed schedule entry (MTD_NONE = -32768 is "None")
         raise ValueError("schedule day %d does not fit the 16-bit field of the packed entry" % int(day))
-    return np.int32(np.uint32((int(day) & 0xFFFF) << 16 | (int(trans) & 0xFF) << 8 | (int(ts) & 0xFF)))
+    v = (int(day) & 0xFFFF) << 16 | (int(trans) & 0xFF) << 8 | (int(ts) & 0xFF)
+    return np.int32(v - (1 << 32) if v >= (1 << 31) else v)
 
 
 def unpack_sched(v):
@@ -61,14 +62,108 @@ class DenseState:
         self.quarantine = np.full((n, 3), NONE, np.int32); self.hosp = np.full((n, 3), NONE, np.int32)
 
 
+def _has(v):
+    return v is not None and len(v) > 0
+
+
 def _rec(arr, i, v):
     if v is not None and len(v) > 0:
         arr[i, :len(v)] = [int(x) for x in v]
 
 
-def flatten(n_agents, agents_static, agents_epi, vars_util, active_ids):
+def flatten_intervals(cells_agents_timesteps):
+    """{cellid: [(agent, start, end), ...]} in dict order = emission order (itinerary.py:1446-1452) ->
+    iv_cell i32[M], iv_agent i32[M], iv_start u8[M], iv_end u8[M]"""
+    import itertools
+    n_c = len(cells_agents_timesteps)
+    lens = np.fromiter((len(l) for l in cells_agents_timesteps.values()), np.int64, n_c)
+    M = int(lens.sum())
+    keys = np.fromiter(cells_agents_timesteps.keys(), np.int64, n_c)
+    flat = np.fromiter(itertools.chain.from_iterable(itertools.chain.from_iterable(cells_agents_timesteps.values())),
+                       np.int64, 3 * M).reshape(M, 3)
+    return (np.repeat(keys, lens).astype(np.int32), flat[:, 0].astype(np.int32), flat[:, 1].astype(np.uint8),
+            flat[:, 2].astype(np.uint8))
+
+
+# Static attributes of the LOCAL agents never change during a run (static.py:351-363; only tourists are (re)written, on
+# arrival, tourism.py:193-200,302-309), and the reference keeps one Static object for the whole run while it builds a new
+# ContactNetwork every day: their dense copy is kept per Static object and filled as agents become active.
+_static_cache = {}
+
+
+def clear_static_cache():
+    _static_cache.clear()
+
+
+def _static_arrays(n_agents, agents_static, active_ids, n_locals):
+    ent = _static_cache.get(id(agents_static))
+    if ent is None or ent[0] is not agents_static or len(ent[1]) != n_agents:
+        if len(_static_cache) >= 4:
+            _static_cache.clear()
+        ent = (agents_static, np.zeros(n_agents, bool), np.zeros(n_agents, np.int8), np.zeros(n_agents, np.int8),
+               np.ones(n_agents, np.float64), np.full(n_agents, -1, np.int32))
+        _static_cache[id(agents_static)] = ent
+    _, have, age, epi, soc, res = ent
+    active_ids = np.asarray(active_ids, np.int64)
+    todo = active_ids[~have[active_ids]]
+    get = agents_static.get
+    for a in todo.tolist():
+        age[a] = int(get(a, "age_bracket_index")); epi[a] = int(get(a, "epi_age_bracket_index"))
+        soc[a] = float(get(a, "soc_rate")); res[a] = int(get(a, "res_cellid"))
+    if n_locals is not None:
+        have[todo[todo < int(n_locals)]] = True
+    return age, epi, soc, res
+
+
+def _dict_to(arr, d, conv=int):
+    n = len(d)
+    if n:
+        arr[np.fromiter(d.keys(), np.int64, n)] = np.fromiter(map(conv, d.values()), np.int64, n)
+
+
+def flatten(n_agents, agents_static, agents_epi, vars_util, active_ids, n_locals=None):
     """-> DenseState.  Dynamic state for every agent that has a SEIR state; static attributes for `active_ids` (the
-    agents that appear in today's cells: the only ones whose attributes the path reads)."""
+    agents that appear in today's cells: the only ones whose attributes the path reads).  n_locals: ids below it are
+    local agents, whose static attributes are cached across calls (None = no caching)."""
+    st = DenseState(n_agents)
+    st.age_bracket, st.epi_age_bracket, st.soc_rate, st.res_cellid = _static_arrays(n_agents, agents_static, active_ids, n_locals)
+    _dict_to(st.seir, vars_util.agents_seir_state)
+    _dict_to(st.inf_type, vars_util.agents_infection_type)
+    _dict_to(st.inf_sev, vars_util.agents_infection_severity)
+    for a, doses in getattr(vars_util, "agents_vaccination_doses", {}).items():
+        if doses is not None and len(doses) > 0:
+            st.last_dose_day[int(a)] = int(doses[-1])           # util.py:126: only the last dose is used
+    epi_get = agents_epi.get if hasattr(agents_epi, "get") else agents_epi.__getitem__
+    sched, sched_cnt = st.sched, st.sched_cnt
+    for a in np.asarray(active_ids).tolist():          # plain Python from here on: one record of five optional lists per agent
+        e = epi_get(a)
+        if e is None:
+            continue
+        get = e.get
+        ent = get("state_transition_by_day")
+        if ent is not None and len(ent):
+            if len(ent) > MAXSCHED:
+                raise RuntimeError("agent %d holds %d schedule entries (> MTD_MAXSCHED)" % (a, len(ent)))
+            sched_cnt[a] = len(ent)
+            for j, (d, t, ts) in enumerate(ent):
+                sched[a, j] = pack_sched(d, t, ts)
+        v = get("test_day")
+        if v is not None and len(v):
+            _rec(st.test_day, a, v)
+        v = get("test_result_day")
+        if v is not None and len(v):
+            _rec(st.test_result_day, a, v)
+        v = get("quarantine_days")
+        if v is not None and len(v):
+            _rec(st.quarantine, a, v)
+        v = get("hospitalisation_days")
+        if v is not None and len(v):
+            _rec(st.hosp, a, v)
+    return st
+
+
+def flatten_reference_loop(n_agents, agents_static, agents_epi, vars_util, active_ids):
+    """the plain per-element restatement of flatten() (kept as the checker of the vectorised one, tests/test_bridge.py)"""
     st = DenseState(n_agents)
     for a in active_ids:
         a = int(a)
@@ -84,15 +179,13 @@ def flatten(n_agents, agents_static, agents_epi, vars_util, active_ids):
         st.inf_sev[int(a)] = int(v)
     for a, doses in getattr(vars_util, "agents_vaccination_doses", {}).items():
         if doses is not None and len(doses) > 0:
-            st.last_dose_day[int(a)] = int(doses[-1])           # util.py:126: only the last dose is used
+            st.last_dose_day[int(a)] = int(doses[-1])
     for a in active_ids:
         a = int(a)
         e = agents_epi.get(a) if hasattr(agents_epi, "get") else agents_epi[a]
         if e is None:
             continue
         ent = e.get("state_transition_by_day") or []
-        if len(ent) > MAXSCHED:
-            raise RuntimeError("agent %d holds %d schedule entries (> MTD_MAXSCHED)" % (a, len(ent)))
         st.sched_cnt[a] = len(ent)
         for j, (d, t, ts) in enumerate(ent):
             st.sched[a, j] = pack_sched(d, t, ts)

@@ -128,20 +128,15 @@ class ContactNetwork:
         else:
             out_rows = vu.directcontacts_by_simcelltype_by_day
         # flatten {cellid: [(agent, start, end), ...]} in dict order = emission order (itinerary.py:1446-1452)
-        cells, agents, st, en = [], [], [], []
-        for cellid, lst in vu.cells_agents_timesteps.items():
-            for (a, s, e) in lst:
-                cells.append(int(cellid)); agents.append(int(a)); st.append(int(s)); en.append(int(e))
+        iv_cell, iv_agent, iv_start, iv_end = bridge.flatten_intervals(vu.cells_agents_timesteps)
         updated_agents_ids = []
-        M = len(cells)
+        M = len(iv_cell)
         if M > 0:
-            iv_cell = np.array(cells, np.int32); iv_agent = np.array(agents, np.int32)
-            iv_start = np.array(st, np.uint8); iv_end = np.array(en, np.uint8)
             n_agents = int(self.n_locals + self.n_tourists)
             max_cell = max(int(iv_cell.max()), max((int(c) for c in self.cells_type.keys()), default=0))
             cell_type, cell_indid = self._cell_tables(max_cell)
             active = np.unique(iv_agent)
-            dense = bridge.flatten(n_agents, self.agents_static, self.agents_epi, vu, active)
+            dense = bridge.flatten(n_agents, self.agents_static, self.agents_epi, vu, active, n_locals=self.n_locals)
             h = bridge.get_handle(n_agents, max_cell + 1, M, self.params, self.device)
             bridge.upload(h, dense, cell_type, cell_indid)
             replay = self.mode == "replay"

@@ -27,8 +27,10 @@ def main():
         z = gio.load_run(name)
         ep = prm.load_json(gio.RUNS[name])
         P = prm.build_params(None, ep)
+        static = None                      # ONE Static object per run, as in the reference (static.py: built once by sim.py)
         for day in [int(d) for d in z["days"]]:
             g = gio.load_day(z, day)
+            static = static or FakeStatic(g.pre)
             pairs = None
             t_dict = []
             for rep in range(3):
@@ -37,7 +39,7 @@ def main():
                                       quarantine_enabled=g.quarantine_enabled, contact_tracing_enabled=g.contact_tracing_enabled)
                 cells_type = {c: int(t) for c, t in enumerate(g.cell_type) if t >= 0}
                 indids = {c: int(v) for c, v in enumerate(g.cell_indid) if v >= 0}
-                cn = ContactNetwork(g.n_locals, g.N - g.n_locals, 1.0, FakeStatic(g.pre), epi, vu, cells_type, indids, {}, {}, {},
+                cn = ContactNetwork(g.n_locals, g.N - g.n_locals, 1.0, static, epi, vu, cells_type, indids, {}, {}, {},
                                     prm.load_json("contactnetwork.json"), ep, dyn, mode="philox", seed=1)
                 t0 = time.perf_counter()
                 cn.simulate_contact_network(g.day, g.weekday)
